@@ -1,0 +1,158 @@
+/* peng_cuda.h — C ABI of libpeng_cuda.so, the B200 (sm_100a) replacement for PEnG-motif's
+ * data-parallel hot path.
+ *
+ * The reference (soedinglab/PEnG-motif) has no plugin / FFI interface: the path sits behind in-process
+ * C++ class seams called from Peng::process (src/peng.cpp:322-435).  Every entry point below names the
+ * reference seam it replaces (file:line relative to the reference tree); INTEGRATION.md shows the
+ * binding a reference maintainer would add at each seam.
+ *
+ * Conventions
+ *   - every function returns PENG_OK (0) or a negative PENG_E_* code and never exits the process;
+ *     peng_cuda_last_error() gives the message (the reference prints to stderr and calls exit()).
+ *   - the opaque handle owns all device memory; host buffers passed in/out are caller-owned.
+ *   - one host thread per handle; one handle per GPU; all work of a handle is ordered on one CUDA stream.
+ *   - encodings are the reference's own (src/base_pattern.h:24-29, src/iupac_pattern.h:26-30):
+ *       sequence codes 0 = other, 1..4 = A,C,G,T (src/shared/Alphabet.cpp:33-41)
+ *       base-pattern id = sum c_p * 4^p, position 0 least significant, A,C,G,T = 0..3
+ *       IUPAC id        = sum c_p * 11^p, A,C,G,T,S,W,R,Y,M,K,N = 0..10
+ *   - `precision`: PENG_F32REF reproduces the reference's float32 arithmetic operation by operation
+ *     (bit-identical tables, sequential float32 accumulation order included); PENG_F64 computes the same
+ *     quantities in double (compared at 1e-9 relative against the FP64 build of the reference).
+ *   - there is no CPU fallback: without a CUDA device every call fails with PENG_E_CUDA.
+ */
+#ifndef PENG_CUDA_H_
+#define PENG_CUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct peng_cuda_ctx* peng_handle_t;
+
+enum {
+  PENG_OK = 0,
+  PENG_E_INVALID = -1, /* bad argument / call order */
+  PENG_E_CUDA = -2,    /* CUDA runtime error (message holds cudaGetErrorString) */
+  PENG_E_IO = -3,      /* cannot open / read FASTA (reference: exit(1), src/shared/SequenceSet.cpp:430-433) */
+  PENG_E_FORMAT = -4,  /* malformed FASTA (reference: exit(1), src/shared/SequenceSet.cpp:361-373) */
+  PENG_E_NOMEM = -5
+};
+
+enum { PENG_STRAND_PLUS = 0, PENG_STRAND_BOTH = 1 };          /* Strand, src/Global.h:13-15 */
+enum { PENG_F32REF = 0, PENG_F64 = 1 };
+enum {                                                         /* tables of BasePattern, src/base_pattern.h:116-120 */
+  PENG_TABLE_BGPROB = 0,   /* pattern_bg_probabilities[order] */
+  PENG_TABLE_EXPECTED = 1, /* expected_counts */
+  PENG_TABLE_ZSCORE = 2,   /* pattern_zscore */
+  PENG_TABLE_LOGP = 3      /* pattern_logp */
+};
+
+/* ---- lifetime ------------------------------------------------------------------------------------- */
+int peng_cuda_device_count(void);
+int peng_cuda_create(int device, peng_handle_t* out);
+void peng_cuda_destroy(peng_handle_t h);
+const char* peng_cuda_last_error(peng_handle_t h); /* h may be NULL: last error of a failed create */
+/* number of kernels this handle has launched so far (bench.py's gpu_launches) */
+uint64_t peng_cuda_launch_count(peng_handle_t h);
+/* run the handle's work on a caller-owned stream (cudaStream_t passed as void*), NULL = handle's own */
+int peng_cuda_set_stream(peng_handle_t h, void* cuda_stream);
+int peng_cuda_synchronize(peng_handle_t h);
+
+/* ---- (a) ingest: SequenceSet::readFASTA + Sequence (src/shared/SequenceSet.cpp:285-447,
+ *      src/shared/Sequence.cpp:4-35) -> packed 2-bit device buffer + validity mask ------------------- */
+/* Read a FASTA file with the reference's line rules and pack it on the device. */
+int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, uint64_t* total_bases,
+                           uint32_t* min_len, uint32_t* max_len);
+/* Same for sequences the caller already holds in the reference's encoding: what a binding inside the
+ * reference passes from Sequence::getSequence()/getL() (src/shared/Sequence.h:18-19). codes = all sequences
+ * concatenated, offsets[n_seq+1]. */
+int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, const uint64_t* offsets, uint64_t n_seq);
+/* Same, codes/offsets already resident on this handle's device (no host copy). */
+int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets, uint64_t n_seq);
+/* Synthetic ChIP-seq-like set generated on the device (BASELINE.json configs[2..4]): n_seq sequences of
+ * seq_len i.i.d. uniform bases from a counter-based generator (seed, base index), motif (base codes 0..3,
+ * motif_len <= 32, may be NULL) planted in ~plant_fraction of the sequences at a uniform offset;
+ * first_seq offsets the counter so that ranks generate disjoint shards of one global set. */
+int peng_cuda_ingest_synthetic(peng_handle_t h, uint64_t n_seq, uint32_t seq_len, uint64_t seed, uint64_t first_seq,
+                               const uint8_t* motif, uint32_t motif_len, double plant_fraction, double n_fraction);
+/* Copy the ingested sequences back in the reference's encoding (tests, CPU baseline). */
+int peng_cuda_sequences_info(peng_handle_t h, uint64_t* n_seq, uint64_t* total_bases, uint32_t* min_len,
+                             uint32_t* max_len);
+int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes /* total_bases */, uint64_t* offsets /* n_seq+1 */);
+
+/* ---- background model: BackgroundModel ctor (src/shared/BackgroundModel.cpp:3-92, 490-530) ----------- */
+/* Count the (k+1)-mers of the ingested set on the device (N quirks of src/shared/Sequence.cpp:28-33
+ * included) and derive the interpolated conditional probabilities v[0..K].
+ * v_out: v[0] (4) | v[1] (16) | ... | v[K] (4^(K+1)), float for PENG_F32REF, double for PENG_F64. */
+int peng_cuda_background_model(peng_handle_t h, int K, const float* alpha /* K+1 */, int interpolate, int precision,
+                               void* v_out, int64_t* kmer_counts_out /* may be NULL, same layout */);
+/* Raw (k+1)-mer counts only, left on the device for a cross-GPU sum (see peng_cuda_device_ptr). */
+int peng_cuda_background_counts(peng_handle_t h, int K);
+int peng_cuda_background_finish(peng_handle_t h, int K, const float* alpha, int interpolate, int precision,
+                                void* v_out);
+
+/* ---- (b) counting: BasePattern::count_patterns / count_patterns_single_strand
+ *      (src/base_pattern.cpp:331-441) ------------------------------------------------------------------ */
+/* Builds the 4^W table on the device: greedy non-overlapping occurrences per (canonical) id, the
+ * "resume two behind a non-ACGT letter" rule, BOTH: mirror copy at the reverse-complement id.
+ * ltot = number of W-mers looked at (BasePattern::getLtot). */
+int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* ltot);
+int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts /* 4^W */); /* BasePattern::getPatternCounter */
+/* Multi-GPU: peng_cuda_count_local leaves the UNMIRRORED local histogram + ltot on the device;
+ * the caller sums `n_u64` uint64 at `ptr` over ranks (ncclAllReduce), then
+ * peng_cuda_count_finish applies the mirror step and publishes ltot. */
+int peng_cuda_count_local(peng_handle_t h, int W, int strand);
+int peng_cuda_count_buffer(peng_handle_t h, void** device_ptr, uint64_t* n_u64);
+int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot);
+/* Load an externally produced table instead of counting (tests; reference binding that keeps its own
+ * count_patterns). counts must already be mirrored for BOTH. */
+int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const uint64_t* counts, uint64_t ltot);
+
+/* ---- (c) background probabilities of all W-mers, expected counts, z-scores, log p-values
+ *      calculate_bg_probabilities / aggregate_double_strand_background / calculate_expected_counts /
+ *      calculate_zscores / calculate_log_pvalues (src/base_pattern.cpp:231-325) ------------------------- */
+/* v: conditional probabilities as returned by BackgroundModel::getV() (src/shared/BackgroundModel.h:85-87)
+ * flattened v[0]|v[1]|...|v[K]; both precisions are taken so that both arms can be produced.
+ * k = order used for expected counts (BasePattern::k), max_k = highest order kept (BasePattern::max_k). */
+int peng_cuda_stats(peng_handle_t h, int K, const float* v32, const double* v64, int k, int max_k);
+int peng_cuda_get_table(peng_handle_t h, int table, int order, int precision, void* out /* 4^W elems */);
+
+/* select_base_patterns (src/base_pattern.cpp:443-515).  Runs on the HOST on the float32 z table copied
+ * back from the device: the result depends on the order libstdc++'s unstable std::sort leaves exact ties
+ * in (every reverse-complement pair ties), which only the same algorithm reproduces. */
+int peng_cuda_select_base_patterns(peng_handle_t h, float z_threshold, uint64_t count_threshold,
+                                   int single_stranded, int filter_neighbors, uint64_t* out, uint64_t cap,
+                                   uint64_t* n_selected);
+
+/* ---- (d) IUPAC degenerate sums: IUPACPattern::aggregate_attributes_from_basepatterns /
+ *      count_combined_occurences (src/iupac_pattern.cpp:410-473, 806-833) ------------------------------ */
+/* For each of n IUPAC ids: n_sites = sum counts, bg_p = sum bgprob[k], expected = sum expected over the
+ * distinct (BOTH: canonical) base patterns of its expansion.  PENG_F32REF accumulates the float sums
+ * sequentially in the reference's list order (BOTH: ascending canonical id; PLUS: expansion order). */
+int peng_cuda_iupac_aggregate(peng_handle_t h, const uint64_t* iupac_ids, int n, int precision, uint64_t* n_sites,
+                              void* bg_p, void* expected);
+int peng_cuda_iupac_count(peng_handle_t h, const uint64_t* iupac_ids, int n, uint64_t* counts_out);
+
+/* ---- (e) EM: Peng::em_optimize_pwms + calculate_prob_odds (src/peng.cpp:48-197) ------------------------ */
+/* n_pwms PWMs of W x 4 (row = position, col = A,C,G,T), all refined in one batch against the count table
+ * and bgprob[bg_order]; each PWM stops when its L1 change <= threshold or after max_iterations.
+ * pwm_out holds the final PWMs after the extra normalisation of IUPACPattern(ori, pwm)
+ * (src/iupac_pattern.cpp:44-72).  float for PENG_F32REF (bit-identical to the reference), double for F64. */
+int peng_cuda_em(peng_handle_t h, int n_pwms, const void* pwm_in, int precision, double saturation, double threshold,
+                 int max_iterations, int bg_order, void* pwm_out, int* iterations_out);
+/* Multi-GPU EM: rank `part` of `n_parts` accumulates its slice of the id range; the raw (unnormalised)
+ * accumulators (n_pwms*W*4 doubles on the device at *acc_ptr) are summed over ranks by the caller between
+ * _em_accumulate and _em_update.  F64 only. */
+int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm_in, double saturation, double threshold,
+                       int max_iterations, int bg_order, int part, int n_parts, void** acc_ptr);
+int peng_cuda_em_accumulate(peng_handle_t h);
+int peng_cuda_em_update(peng_handle_t h, int* n_active);
+int peng_cuda_em_end(peng_handle_t h, double* pwm_out, int* iterations_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PENG_CUDA_H_ */

@@ -1,0 +1,458 @@
+// core_seq.cuh — per-thread bodies of the sequence-side kernels (ingest packing, k-mer start marking,
+// exact non-overlapping k-mer counting, background (k+1)-mer counting).
+//
+// Every function here is PENG_HD (__host__ __device__) and free of warp intrinsics, so that the very same
+// code that the __global__ wrappers in peng_cuda.cu run per thread can be driven thread-by-thread on a
+// CPU by tests/sim (test-only shim, never shipped) on machines without a GPU.
+//
+// Device layout of an ingested sequence set ("stream"):
+//   position q = PENG_FRONT_PAD + offsets[s] + 2*s + i   for base i of sequence s
+//   i.e. all sequences concatenated, TWO invalid separator positions after each sequence, PENG_FRONT_PAD
+//   invalid positions in front and >= PENG_TAIL_PAD behind.
+//   codes : 2 bits per position, 16 per uint32 (position q at bits 2*(q&15) of word q>>4); A,C,G,T = 0..3
+//   valid : 1 bit per position (ACGT letter of a sequence), 32 per uint32
+//   sstart: 1 bit per position, set on the first base of every sequence
+// Why two separators: the reference resumes scanning at n+2 after a run that produced k-mers ends at a
+// non-ACGT index n (src/base_pattern.cpp:369,380,347) but starts every sequence at its first base; with
+// two invalid positions between sequences the single stream rule "resume at n+2" reproduces both.
+#pragma once
+#include <stdint.h>
+
+#ifndef PENG_HD
+#ifdef __CUDACC__
+#define PENG_HD __host__ __device__ __forceinline__
+#else
+#define PENG_HD inline
+#endif
+#endif
+
+#define PENG_FRONT_PAD 64u
+#define PENG_TAIL_PAD 128u
+
+namespace peng {
+
+// ---- small bit helpers (device intrinsics with host equivalents) -------------------------------------
+PENG_HD uint32_t funnel_r(uint32_t lo, uint32_t hi, uint32_t s) {  // bits [s, s+32) of hi:lo, 0 <= s < 32
+#if defined(__CUDA_ARCH__)
+  return __funnelshift_r(lo, hi, s);
+#else
+  return s ? (lo >> s) | (hi << (32 - s)) : lo;
+#endif
+}
+PENG_HD int popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __popc(x);
+#else
+  return __builtin_popcount(x);
+#endif
+}
+PENG_HD uint32_t brev32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __brev(x);
+#else
+  x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+  x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+  x = ((x >> 4) & 0x0F0F0F0Fu) | ((x & 0x0F0F0F0Fu) << 4);
+  x = ((x >> 8) & 0x00FF00FFu) | ((x & 0x00FF00FFu) << 8);
+  return (x >> 16) | (x << 16);
+#endif
+}
+template <typename T>
+PENG_HD T ldg(const T* p) {
+#if defined(__CUDA_ARCH__)
+  return __ldg(p);
+#else
+  return *p;
+#endif
+}
+
+// Reverse complement of a W-mer id (BasePattern::getRevCompId, src/base_pattern.cpp:119-134): digit p of
+// the result is 3 - digit (W-1-p).  W <= 16, ids fit 32 bits.
+PENG_HD uint32_t revcomp_id(uint32_t id, int W) {
+  uint32_t r = brev32(id);                                          // reverses bits, also inside each pair
+  r = ((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1);          // swap the two bits of every pair back
+  r >>= (32 - 2 * W);
+  return (~r) & (W == 16 ? 0xFFFFFFFFu : ((1u << (2 * W)) - 1u));
+}
+
+PENG_HD bool bit_at(const uint32_t* mask, uint64_t q) { return (ldg(mask + (q >> 5)) >> (q & 31)) & 1u; }
+
+// ---- (a) packing --------------------------------------------------------------------------------------
+// One thread builds stream positions [32*t, 32*t+32): two code words, one valid word, one sstart word.
+// src holds the sequences concatenated WITHOUT separators, either in the reference's letter codes
+// (0 = other, 1..4 = ACGT; Alphabet::getCode, src/shared/Alphabet.cpp:33-41) or as raw FASTA letters.
+template <bool ASCII>
+PENG_HD void pack_word(uint64_t t, const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets,
+                       uint64_t n_seq, uint32_t* __restrict__ codes, uint32_t* __restrict__ valid,
+                       uint32_t* __restrict__ sstart) {
+  const uint64_t q0 = t * 32;
+  uint32_t c0 = 0, c1 = 0, v = 0, ss = 0;
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  const uint64_t stream_end = PENG_FRONT_PAD + total + 2 * n_seq;  // first position behind the last separator
+  if (q0 + 32 > PENG_FRONT_PAD && q0 < stream_end) {
+    // sequence s occupies [start(s), start(s) + len(s) + 2) with start(s) = FRONT + offsets[s] + 2 s.
+    // Find the sequence holding the first position >= FRONT of this word: largest s with start(s) <= q.
+    uint64_t q = q0 < PENG_FRONT_PAD ? PENG_FRONT_PAD : q0;
+    uint64_t lo = 0, hi = n_seq - 1;
+    while (lo < hi) {
+      uint64_t mid = (lo + hi + 1) >> 1;
+      if (PENG_FRONT_PAD + offsets[mid] + 2 * mid <= q) lo = mid; else hi = mid - 1;
+    }
+    uint64_t s = lo;
+    uint64_t s_start = PENG_FRONT_PAD + offsets[s] + 2 * s;
+    uint64_t s_len = offsets[s + 1] - offsets[s];
+    for (; q < q0 + 32 && q < stream_end; q++) {
+      while (q >= s_start + s_len + 2) {  // step over finished sequences (empty ones cannot occur)
+        s++;
+        s_start = PENG_FRONT_PAD + offsets[s] + 2 * s;
+        s_len = offsets[s + 1] - offsets[s];
+      }
+      const uint64_t i = q - s_start;
+      if (i < s_len) {
+        const uint32_t ch = src[offsets[s] + i];
+        uint32_t code, ok;
+        if (ASCII) {
+          const uint32_t up = ch & 0xDFu;  // fold case
+          ok = (up == 'A') | (up == 'C') | (up == 'G') | (up == 'T');
+          code = (up >> 1) & 3u;           // A0 C1 G3 T2
+          code ^= code >> 1;               // A0 C1 G2 T3
+        } else {
+          ok = (ch >= 1u) & (ch <= 4u);
+          code = (ch - 1u) & 3u;
+        }
+        code = ok ? code : 0u;
+        const uint32_t b = (uint32_t)(q - q0);
+        if (b < 16) c0 |= code << (2 * b); else c1 |= code << (2 * (b - 16));
+        v |= ok << b;
+        if (i == 0) ss |= 1u << b;
+      }
+    }
+  }
+  codes[2 * t] = c0;
+  codes[2 * t + 1] = c1;
+  valid[t] = v;
+  sstart[t] = ss;
+}
+
+// inverse of pack_word for one base (tests / CPU baseline export): reference letter code 0..4
+PENG_HD uint8_t unpack_code(const uint32_t* codes, const uint32_t* valid, uint64_t q) {
+  if (!bit_at(valid, q)) return 0;
+  return (uint8_t)(((ldg(codes + (q >> 4)) >> (2 * (q & 15))) & 3u) + 1u);
+}
+
+// ---- synthetic sequence sets (BASELINE.json configs[2..4]) ---------------------------------------------
+PENG_HD uint64_t mix64(uint64_t x) {  // splitmix64 finaliser: counter-based, any shard reproducible
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+struct SynthParams {
+  uint64_t n_seq, first_seq, seed;
+  uint32_t seq_len, motif_len;
+  uint32_t plant_threshold;  // plant iff (hash & 0xFFFFFF) < threshold
+  uint32_t n_threshold;      // base becomes N iff (hash & 0xFFFFFF) < threshold
+  uint64_t motif_bits;       // 2 bits per motif base; base 6 (0-based) of a 13-mer may be degenerate, see below
+  uint32_t degenerate_pos;   // motif position whose letter is C or G with p = 1/2 (S), 0xFFFFFFFF = none
+};
+
+// letter (0..3) / validity of base i of GLOBAL sequence g
+PENG_HD uint32_t synth_base(const SynthParams& P, uint64_t g, uint32_t i, uint32_t* ok) {
+  const uint64_t gi = g * (uint64_t)P.seq_len + i;
+  const uint64_t h = mix64(P.seed ^ mix64(gi >> 4));  // 16 bases (+ 16 N draws) per hash
+  uint32_t c = (uint32_t)(h >> (2 * (gi & 15))) & 3u;
+  *ok = 1;
+  if (P.n_threshold) {
+    const uint64_t hn = mix64(h ^ 0xA5A5A5A5ull ^ (gi & 15));
+    if ((uint32_t)(hn & 0xFFFFFFu) < P.n_threshold) *ok = 0;
+  }
+  if (P.motif_len && P.motif_len <= P.seq_len) {
+    const uint64_t hs = mix64((P.seed + 0x51ED27ull) ^ mix64(g));
+    if ((uint32_t)(hs & 0xFFFFFFu) < P.plant_threshold) {
+      const uint32_t off = (uint32_t)((hs >> 24) % (uint64_t)(P.seq_len - P.motif_len + 1));
+      const bool minus = (hs >> 60) & 1u;
+      if (i >= off && i < off + P.motif_len) {
+        uint32_t m = i - off;
+        if (minus) m = P.motif_len - 1 - m;
+        uint32_t mc = (uint32_t)(P.motif_bits >> (2 * m)) & 3u;
+        if (m == P.degenerate_pos) mc = ((hs >> 61) & 1u) ? 1u : 2u;
+        c = minus ? 3u - mc : mc;
+        *ok = 1;
+      }
+    }
+  }
+  return c;
+}
+
+PENG_HD void synth_word(uint64_t t, const SynthParams& P, uint32_t* __restrict__ codes,
+                        uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart) {
+  const uint64_t q0 = t * 32;
+  const uint64_t stride = (uint64_t)P.seq_len + 2;
+  const uint64_t stream_end = PENG_FRONT_PAD + P.n_seq * stride;
+  uint32_t c0 = 0, c1 = 0, v = 0, ss = 0;
+  for (uint32_t b = 0; b < 32; b++) {
+    const uint64_t q = q0 + b;
+    if (q < PENG_FRONT_PAD || q >= stream_end) continue;
+    const uint64_t s = (q - PENG_FRONT_PAD) / stride;
+    const uint32_t i = (uint32_t)((q - PENG_FRONT_PAD) - s * stride);
+    if (i >= P.seq_len) continue;
+    uint32_t ok;
+    uint32_t c = synth_base(P, P.first_seq + s, i, &ok);
+    c = ok ? c : 0u;
+    if (b < 16) c0 |= c << (2 * b); else c1 |= c << (2 * (b - 16));
+    v |= ok << b;
+    if (i == 0) ss |= 1u << b;
+  }
+  codes[2 * t] = c0;
+  codes[2 * t + 1] = c1;
+  valid[t] = v;
+  sstart[t] = ss;
+}
+
+// ---- (b1) which W-mers does the reference look at? -----------------------------------------------------
+// The reference scans each sequence with a small state machine (src/base_pattern.cpp:347-381):
+//   * a run opens where W consecutive letters are available; a failed attempt on index f resumes at f+1;
+//   * a run that produced k-mers and stopped at a non-ACGT index n resumes at n+2: the k-mer STARTING at
+//     n+1 is never looked at ("shifted" start).
+// On the stream this means: the W-mer starting at position a is looked at iff valid[a..a+W-1] are all set
+// and NOT (a is the first position of its valid segment and that segment is shifted), where
+//   shifted(a) = valid[a-2] && ( len(prev segment) >= W+1 || (len == W && !shifted(start of prev segment)) )
+// because the previous segment produced k-mers iff its effective length (len - shifted) is >= W.
+PENG_HD bool segment_is_shifted(const uint32_t* valid, uint64_t a, int W) {
+  bool flip = false;
+  for (;;) {
+    if (a < 2 || !bit_at(valid, a - 2)) return flip;  // base case false, xor flip
+    // length of the valid segment ending at a-2, capped at W+1
+    int len = 0;
+    uint64_t p = a - 2;
+    while (len <= W && bit_at(valid, p)) {  // the front pad is invalid, so p never underflows
+      len++;
+      p--;
+    }
+    if (len >= W + 1) return !flip;  // base case true
+    if (len < W) return flip;
+    a = a - 1 - (uint64_t)W;  // start of that exactly-W-long segment; shifted(a_old) = !shifted(a_new)
+    flip = !flip;
+  }
+}
+
+// One thread: kstart word t (positions [32t, 32t+32)); returns popcount (contribution to ltot).
+PENG_HD int mark_kstart_word(uint64_t t, uint64_t n_words, const uint32_t* __restrict__ valid, int W,
+                             uint32_t* __restrict__ kstart) {
+  const uint32_t v0 = ldg(valid + t);
+  const uint32_t v1 = t + 1 < n_words ? ldg(valid + t + 1) : 0u;
+  uint32_t win = v0;
+  for (int d = 1; d < W; d++) win &= funnel_r(v0, v1, (uint32_t)d);  // bit b: valid[b .. b+W-1] all set
+  if (win) {
+    const uint32_t vm1 = t ? ldg(valid + t - 1) : 0u;
+    const uint32_t prev1 = (v0 << 1) | (vm1 >> 31);  // bit b = valid[b-1]
+    const uint32_t prev2 = (v0 << 2) | (vm1 >> 30);  // bit b = valid[b-2]
+    uint32_t cand = win & ~prev1 & prev2;            // segment starts that might be shifted (rare)
+    while (cand) {
+      const uint32_t b = (uint32_t)popc32((cand & (0u - cand)) - 1u);
+      cand &= cand - 1u;
+      if (segment_is_shifted(valid, t * 32 + b, W)) win &= ~(1u << b);
+    }
+  }
+  kstart[t] = win;
+  return popc32(win);
+}
+
+// ---- (b2) exact greedy non-overlapping counting ---------------------------------------------------------
+// BasePattern::count_patterns / count_patterns_single_strand (src/base_pattern.cpp:331-441): an occurrence
+// is counted iff the last COUNTED occurrence of the same key (BOTH: min(id, revcomp id)) lies >= W
+// positions back; suppression never crosses an invalid position.  Equivalent local rule:
+//     counted(s) = looked_at(s) && no counted occurrence of key(s) among starts s-W+1 .. s-1.
+// A thread owns the k-mers whose LAST base e lies in [e0, e0 + 16*n_words) and keeps the keys of the
+// counted occurrences of the previous 15 positions in a 16-slot register ring (slot = e & 15).
+// Warm-up: it starts 48 positions early with unknown history, records every looked-at key, and is
+// "synced" once W-1 consecutive positions were clean (no equal key in their window): from then on all
+// recorded keys are truly counted and the recursion is exact.  If it is not synced when it reaches e0
+// (tandem repeats / homopolymers), count_resolve_slow() walks further back.
+template <int W>
+struct KeyT { typedef uint32_t type; };
+template <>
+struct KeyT<16> { typedef uint64_t type; };  // 32-bit ids: the "empty slot" sentinel needs a 33rd bit
+
+template <int W, bool BOTH>
+struct CountState {
+  typedef typename KeyT<W>::type key_t;
+  static constexpr key_t EMPTY = ~(key_t)0;
+  static constexpr uint32_t MASK = W == 16 ? 0xFFFFFFFFu : ((1u << (2 * (W & 15))) - 1u);
+  key_t slot[16];
+  uint32_t fwd, rc;
+
+  PENG_HD void reset() {
+#pragma unroll
+    for (int i = 0; i < 16; i++) slot[i] = EMPTY;
+    fwd = 0;
+    rc = 0;
+  }
+  // shift in base c (position e); afterwards fwd / rc are the ids of the W-mer ending at e
+  PENG_HD key_t push(uint32_t c) {
+    fwd = (fwd >> 2) | (c << (2 * W - 2));
+    rc = ((rc << 2) | (3u - c)) & MASK;
+    return (key_t)(BOTH ? (fwd < rc ? fwd : rc) : fwd);
+  }
+  template <int I>
+  PENG_HD bool window_has(key_t key) const {  // any of the W-1 previous slots equal to key?
+    bool m = false;
+#pragma unroll
+    for (int d = 1; d < W; d++) m |= (slot[(I - d) & 15] == key);
+    return m;
+  }
+};
+
+// kstart bits for the 16 k-mers ENDING at e = 16*we + i (i = 0..15): start positions e - W + 1
+PENG_HD uint32_t kstart_bits_for_end_word(const uint32_t* __restrict__ kstart, uint64_t we, int W) {
+  const int64_t s0 = (int64_t)(we * 16) - (W - 1);  // >= 0 because the stream has a front pad
+  const uint64_t w = (uint64_t)s0 >> 5;
+  const uint32_t sh = (uint32_t)s0 & 31u;
+  const uint32_t lo = ldg(kstart + w);
+  const uint32_t hi = sh > 16 ? ldg(kstart + w + 1) : 0u;
+  return funnel_r(lo, hi, sh) & 0xFFFFu;
+}
+
+// Slow path: establish the ring state in front of end position e0 by scanning from further and further
+// back until a sync point is found (the front pad guarantees one).  Plain loops, local-memory ring.
+template <int W, bool BOTH>
+PENG_HD void count_resolve_slow(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ kstart,
+                                uint64_t e0, CountState<W, BOTH>& st) {
+  typedef typename CountState<W, BOTH>::key_t key_t;
+  for (uint64_t back = 128;; back *= 2) {
+    const uint64_t start = back >= e0 ? 0 : e0 - back;  // first base pushed
+    st.reset();
+    key_t ring[16];
+    for (int i = 0; i < 16; i++) ring[i] = CountState<W, BOTH>::EMPTY;
+    bool synced = (start == 0);  // stream start: empty history is exact
+    int streak = 0;
+    for (uint64_t e = start; e < e0; e++) {
+      const uint32_t c = (ldg(codes + (e >> 4)) >> (2 * (e & 15))) & 3u;
+      const key_t key = st.push(c);
+      const bool complete = (e - start) >= (uint64_t)(W - 1);  // fwd/rc hold W real bases
+      const bool ks = complete && e + 1 >= (uint64_t)W && bit_at(kstart, e - (W - 1));
+      bool match = false;
+      for (int d = 1; d < W; d++) match |= (ring[(e - d) & 15] == key);
+      if (synced) {
+        ring[e & 15] = (ks && !match) ? key : CountState<W, BOTH>::EMPTY;
+      } else {
+        ring[e & 15] = ks ? key : CountState<W, BOTH>::EMPTY;
+        // the window of this position is fully recorded once 2(W-1) bases have been pushed
+        const bool window_known = (e - start) >= (uint64_t)(2 * (W - 1));
+        streak = (window_known && !(ks && match)) ? streak + 1 : 0;
+        if (streak >= W - 1) synced = true;
+      }
+    }
+    if (synced) {
+      for (int i = 0; i < 16; i++) st.slot[i] = ring[i];
+      return;
+    }
+  }
+}
+
+// The per-thread body.  Emits one histogram increment per counted occurrence through `emit(key)`.
+// e0 must be a multiple of 16 and >= PENG_FRONT_PAD (so the 48-position warm-up stays inside the buffer).
+template <int W, bool BOTH, typename Emit>
+PENG_HD void count_chunk(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ kstart, uint64_t e0,
+                         uint32_t n_words, Emit emit) {
+  typedef CountState<W, BOTH> State;
+  typedef typename State::key_t key_t;
+  State st;
+  st.reset();
+  const uint64_t we0 = e0 >> 4;
+
+  // ---- warm-up over the 3 code words in front of e0 ----
+  bool synced = false;
+  int streak = 0;
+  for (int wi = 0; wi < 3; wi++) {
+    const uint64_t we = we0 - 3 + wi;
+    const uint32_t cw = ldg(codes + we);
+    const uint32_t ksw = kstart_bits_for_end_word(kstart, we, W);
+#define PENG_WARM_STEP(I)                                                                     \
+  {                                                                                           \
+    const key_t key = st.push((cw >> (2 * I)) & 3u);                                          \
+    const int step = wi * 16 + I;                                                             \
+    const bool ks = ((ksw >> I) & 1u) && step >= W - 1;                                       \
+    const bool match = st.template window_has<I>(key);                                        \
+    if (synced) {                                                                             \
+      st.slot[I] = (ks && !match) ? key : State::EMPTY;                                       \
+    } else {                                                                                  \
+      st.slot[I] = ks ? key : State::EMPTY;                                                   \
+      streak = (step >= 2 * (W - 1) && !(ks && match)) ? streak + 1 : 0;                      \
+      synced = streak >= W - 1;                                                               \
+    }                                                                                         \
+  }
+    PENG_WARM_STEP(0) PENG_WARM_STEP(1) PENG_WARM_STEP(2) PENG_WARM_STEP(3)
+    PENG_WARM_STEP(4) PENG_WARM_STEP(5) PENG_WARM_STEP(6) PENG_WARM_STEP(7)
+    PENG_WARM_STEP(8) PENG_WARM_STEP(9) PENG_WARM_STEP(10) PENG_WARM_STEP(11)
+    PENG_WARM_STEP(12) PENG_WARM_STEP(13) PENG_WARM_STEP(14) PENG_WARM_STEP(15)
+#undef PENG_WARM_STEP
+  }
+  if (!synced) {
+    const uint32_t f = st.fwd, r = st.rc;  // ids are already exact (48 >= W-1 bases pushed)
+    count_resolve_slow<W, BOTH>(codes, kstart, e0, st);
+    st.fwd = f;
+    st.rc = r;
+  }
+
+  // ---- owned positions ----
+  for (uint32_t w = 0; w < n_words; w++) {
+    const uint64_t we = we0 + w;
+    const uint32_t cw = ldg(codes + we);
+    const uint32_t ksw = kstart_bits_for_end_word(kstart, we, W);
+#define PENG_MAIN_STEP(I)                                        \
+  {                                                              \
+    const key_t key = st.push((cw >> (2 * I)) & 3u);             \
+    const bool counted = ((ksw >> I) & 1u) && !st.template window_has<I>(key); \
+    st.slot[I] = counted ? key : State::EMPTY;                   \
+    if (counted) emit((uint32_t)key);                            \
+  }
+    PENG_MAIN_STEP(0) PENG_MAIN_STEP(1) PENG_MAIN_STEP(2) PENG_MAIN_STEP(3)
+    PENG_MAIN_STEP(4) PENG_MAIN_STEP(5) PENG_MAIN_STEP(6) PENG_MAIN_STEP(7)
+    PENG_MAIN_STEP(8) PENG_MAIN_STEP(9) PENG_MAIN_STEP(10) PENG_MAIN_STEP(11)
+    PENG_MAIN_STEP(12) PENG_MAIN_STEP(13) PENG_MAIN_STEP(14) PENG_MAIN_STEP(15)
+#undef PENG_MAIN_STEP
+  }
+}
+
+// ---- background (k+1)-mer counts -----------------------------------------------------------------------
+// BackgroundModel ctor (src/shared/BackgroundModel.cpp:60-84) on Sequence::kmer_ (src/shared/Sequence.cpp:28-33):
+// at base i of a sequence the window is the last min(i,8)+1 letters; the (k+1)-mer ending at i (i >= k) is
+// counted under its BaMM id (first letter most significant) if every letter of the WINDOW is ACGT; if the
+// window holds a non-ACGT letter it is counted as id 0 when each of its last k+1 letters is 'A' or
+// non-ACGT, and dropped otherwise (C remainder of a negative number, :75-80).
+// Returns for stream position q: bit k of the result = "order k is counted", ids[k] = id.
+PENG_HD uint32_t background_ids(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid,
+                                const uint32_t* __restrict__ sstart, uint64_t q, int K, uint32_t* ids) {
+  // gather the 9 positions q-8..q (front pad keeps q-8 >= 0 for real bases)
+  uint32_t letters = 0, vmask = 0;  // index j = distance back from q
+  int reach = 8;                    // how far back the window extends (stops at the sequence start)
+  for (int j = 0; j <= 8; j++) {
+    const uint64_t p = q - (uint64_t)j;
+    const uint32_t ok = bit_at(valid, p);
+    const uint32_t c = (ldg(codes + (p >> 4)) >> (2 * (p & 15))) & 3u;
+    letters |= (ok ? c : 0u) << (2 * j);
+    vmask |= ok << j;
+    if (bit_at(sstart, p)) { reach = j; break; }
+  }
+  const uint32_t window = (2u << reach) - 1u;  // reach+1 positions
+  const bool all_ok = (vmask & window) == window;
+  uint32_t res = 0;
+  for (int k = 0; k <= K; k++) {
+    if (k > reach) break;  // i >= k (loop bound :71)
+    const uint32_t m = (1u << (2 * (k + 1))) - 1u;
+    // letters has the most recent base in its lowest digit = BaMM order (first letter most significant)
+    const uint32_t y = letters & m;
+    if (all_ok) {
+      ids[k] = y;
+      res |= 1u << k;
+    } else if (y == 0) {  // invalid letters contribute 0 as well: "A or other" in all k+1 places
+      ids[k] = 0;
+      res |= 1u << k;
+    }
+  }
+  return res;
+}
+
+}  // namespace peng

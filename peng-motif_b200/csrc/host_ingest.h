@@ -1,0 +1,174 @@
+// host_ingest.h — host-side pieces of libpeng_cuda.so that are inherently serial or tiny:
+//   * FASTA record splitting with the reference's line rules (the letters themselves are translated and
+//     packed on the device),
+//   * BackgroundModel::calculateV on the <= 1364 device-counted (k+1)-mer totals,
+//   * select_base_patterns (must replay libstdc++'s std::sort tie order, see below),
+//   * IUPAC id -> per-position letter-set mask.
+// Reference citations are relative to the reference tree.
+#pragma once
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace peng_host {
+
+struct FastaRecords {
+  std::vector<char> letters;      // sequence lines of all kept records, concatenated, raw bytes
+  std::vector<uint64_t> offsets;  // n_seq + 1
+  uint64_t n_without_sequence = 0;
+};
+
+// SequenceSet::readFASTA (src/shared/SequenceSet.cpp:285-447).  Returns 0 ok, 1 cannot open, 2 malformed.
+//   - lines end at '\n' only ('\r' stays in the line and later becomes a non-ACGT letter);
+//   - `while (getline(file, line).good())`: a last line without '\n' is dropped (:304);
+//   - blank lines are skipped (:306); '>' starts a record (:308); sequence lines are concatenated (:366);
+//   - a record without sequence is ignored with a warning (:346, :417);
+//   - a space inside a sequence line, or a sequence line before any header, is fatal (:361-373).
+inline int read_fasta(const char* path, FastaRecords* out, std::string* msg) {
+  FILE* f = fopen(path, "rb");
+  if (!f) {
+    *msg = std::string("Error: Cannot open FASTA file: ") + path;
+    return 1;
+  }
+  std::vector<char> text;
+  {
+    char buf[1 << 16];
+    size_t n;
+    while ((n = fread(buf, 1, sizeof buf, f)) > 0) text.insert(text.end(), buf, buf + n);
+    fclose(f);
+  }
+  out->letters.clear();
+  out->letters.reserve(text.size());
+  out->offsets.assign(1, 0);
+  bool in_record = false;
+  uint64_t record_begin = 0;
+  const char* p = text.data();
+  const char* end = p + text.size();
+  while (p < end) {
+    const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+    if (!nl) break;  // unterminated last line: never delivered by getline().good()
+    const size_t len = (size_t)(nl - p);
+    if (len) {
+      if (p[0] == '>') {
+        if (in_record) {
+          if (out->letters.size() > record_begin) out->offsets.push_back(out->letters.size());
+          else {
+            out->n_without_sequence++;
+            fprintf(stderr, "Warning: Ignore FASTA entry without sequence: %s\n", path);
+          }
+        }
+        in_record = true;
+        record_begin = out->letters.size();
+      } else if (in_record) {
+        if (memchr(p, ' ', len)) {
+          *msg = std::string("Error: FASTA sequence contains space character: ") + path;
+          return 2;
+        }
+        out->letters.insert(out->letters.end(), p, p + len);
+      } else {
+        *msg = std::string("Error: Wrong FASTA format: ") + path;
+        return 2;
+      }
+    }
+    p = nl + 1;
+  }
+  if (in_record) {
+    if (out->letters.size() > record_begin) out->offsets.push_back(out->letters.size());
+    else {
+      out->n_without_sequence++;
+      fprintf(stderr, "Warning: Ignore FASTA entry without sequence: %s\n", path);
+    }
+  }
+  return 0;
+}
+
+// BackgroundModel::calculateV (src/shared/BackgroundModel.cpp:490-530) on counts laid out v[0]|v[1]|...|v[K].
+template <typename R>
+inline void calculate_v(const uint64_t* n_all, int K, const float* alpha, bool interpolate, R* v_all) {
+  auto off = [](int k) { return (size_t)(((1u << (2 * (k + 1))) - 4u) / 3u); };
+  const uint64_t* n0 = n_all;
+  uint64_t base_counts = 0;
+  for (int y = 0; y < 4; y++) base_counts += n0[y];
+  R* v0 = v_all;
+  for (int y = 0; y < 4; y++) v0[y] = ((R)n0[y] + (R)alpha[0] * 0.25f) / ((R)base_counts + (R)alpha[0]);
+  for (int k = 1; k <= K; k++) {
+    const uint64_t* nk = n_all + off(k);
+    const uint64_t* nk1 = n_all + off(k - 1);
+    R* vk = v_all + off(k);
+    const R* vk1 = v_all + off(k - 1);
+    const size_t Yk1 = (size_t)1 << (2 * (k + 1)), Yk = (size_t)1 << (2 * k);
+    for (size_t y = 0; y < Yk1; y++) {
+      const size_t y2 = y % Yk, yk = y / 4;
+      if (interpolate) vk[y] = ((R)nk[y] + (R)alpha[k] * vk1[y2]) / ((R)nk1[yk] + (R)alpha[k]);
+      else vk[y] = ((R)nk[y] + (R)alpha[k] * 0.25f) / ((R)nk1[yk] + (R)alpha[k]);
+    }
+    R factor = 0;
+    for (size_t y = 0; y < Yk1; y++) {
+      factor += vk[y];
+      if ((y + 1) % 4 == 0) {
+        for (int i = 0; i < 4; i++) vk[y - i] /= factor;
+        factor = 0;
+      }
+    }
+  }
+}
+
+inline uint64_t revcomp_id64(uint64_t id, int W) {
+  uint64_t r = 0;
+  for (int p = 0; p < W; p++) r |= (3 - ((id >> (2 * p)) & 3)) << (2 * (W - 1 - p));
+  return r;
+}
+
+// BasePattern::select_base_patterns (src/base_pattern.cpp:443-515).  std::sort is unstable and every
+// reverse-complement pair has bit-identical z-scores, so which member of a pair comes first — and is
+// therefore reported — is decided by libstdc++'s introsort over the full index array; the only way to
+// reproduce the reference's list is to run that same sort with the same comparator (src/base_pattern.h:166-172).
+struct ByZDescending {
+  const float* z;
+  bool operator()(const size_t i, const size_t j) const { return z[i] > z[j]; }
+};
+
+inline std::vector<uint64_t> select_base_patterns(const float* z, const uint64_t* counts, int W, float z_threshold,
+                                                  uint64_t count_threshold, bool single_stranded, bool filter_neighbors) {
+  const size_t n = (size_t)1 << (2 * W);
+  std::vector<size_t> order(n);
+  for (size_t i = 0; i < n; i++) order[i] = i;
+  std::sort(order.begin(), order.end(), ByZDescending{z});
+  std::vector<bool> seen(n, false);
+  std::vector<uint64_t> selected;
+  for (size_t r = 0; r < n; r++) {
+    const size_t id = order[r];
+    if (z[id] < z_threshold) break;
+    if (counts[id] < count_threshold) continue;
+    if (seen[id]) continue;
+    if (!single_stranded && seen[revcomp_id64(id, W)]) continue;
+    selected.push_back(id);
+    seen[id] = true;
+    if (filter_neighbors) {
+      for (int p = 0; p < W; p++) {
+        const size_t masked = id & ~((size_t)3 << (2 * p));
+        for (size_t c = 0; c < 4; c++) seen[masked | (c << (2 * p))] = true;
+      }
+    }
+  }
+  return selected;
+}
+
+// IUPAC id (sum c_p 11^p, A,C,G,T,S,W,R,Y,M,K,N = 0..10; src/iupac_pattern.h:26-30) -> nibble p = set of
+// bases the letter at position p stands for (representative_iupac_nucleotides, src/iupac_alphabet.cpp:138-180)
+inline bool iupac_letter_mask(uint64_t iupac_id, int W, uint64_t* mask) {
+  static const uint64_t sets[11] = {0x1, 0x2, 0x4, 0x8, 0x6 /*S=CG*/, 0x9 /*W=AT*/, 0x5 /*R=AG*/, 0xA /*Y=CT*/,
+                                    0x3 /*M=AC*/, 0xC /*K=GT*/, 0xF /*N*/};
+  uint64_t m = 0;
+  for (int p = 0; p < W; p++) {
+    m |= sets[iupac_id % 11] << (4 * p);
+    iupac_id /= 11;
+  }
+  *mask = m;
+  return iupac_id == 0;
+}
+
+}  // namespace peng_host

@@ -1,0 +1,1552 @@
+// peng_cuda.cu — libpeng_cuda.so: __global__ wrappers + the C ABI of include/peng_cuda.h.
+//
+// sm_100a only.  No tensor cores: nothing on this path is a dense contraction (integer histogramming,
+// element-wise table passes, small reductions).  The per-thread bodies live in core_seq.cuh / core_tab.cuh.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/peng_cuda.h"
+#include "core_seq.cuh"
+#include "core_tab.cuh"
+#include "host_ingest.h"
+
+using namespace peng;
+
+// =====================================================================================================
+// context
+// =====================================================================================================
+#define PENG_MAX_ORDER 5
+#define PENG_MAX_W 16
+
+struct peng_cuda_ctx {
+  int device = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+  int sm_count = 148;
+
+  // ---- sequences ----
+  uint64_t n_seq = 0, total_bases = 0;
+  uint32_t min_len = 0, max_len = 0;
+  uint32_t fixed_len = 0;          // > 0: all sequences have this length (synthetic), offsets implicit
+  uint64_t stream_end = 0;         // first position behind the last separator
+  uint64_t n_words32 = 0;          // 32-position words allocated (incl. pads)
+  uint32_t *d_codes = nullptr, *d_valid = nullptr, *d_sstart = nullptr, *d_kstart = nullptr;
+  uint64_t* d_offsets = nullptr;   // n_seq+1 (base coordinates), null when fixed_len
+  std::vector<uint64_t> h_offsets;
+
+  // ---- count table ----
+  int W = 0, strand = PENG_STRAND_BOTH;
+  uint64_t n_patterns = 0;
+  uint32_t* d_hist32 = nullptr;    // per-launch accumulation target of the atomics
+  uint64_t* d_counts = nullptr;    // [n_patterns] + [1] ltot slot (summed over ranks together)
+  uint64_t ltot = 0;
+  bool counts_final = false;       // mirror step applied, ltot published
+
+  // ---- background ----
+  int K = -1;
+  uint64_t* d_bgcounts = nullptr;  // v-layout, 64-bit
+  float* d_v32 = nullptr;
+  double* d_v64 = nullptr;
+  int k_used = -1, max_k = -1;
+  float* d_bg32[PENG_MAX_ORDER + 1] = {};
+  double* d_bg64[PENG_MAX_ORDER + 1] = {};
+  float *d_exp32 = nullptr, *d_z32 = nullptr, *d_logp32 = nullptr;
+  double *d_exp64 = nullptr, *d_z64 = nullptr, *d_logp64 = nullptr;
+  bool stats_ready = false;
+
+  // ---- scratch ----
+  void* d_scratch = nullptr;
+  size_t scratch_bytes = 0;
+
+  // ---- EM session (multi-GPU protocol) ----
+  struct {
+    bool open = false;
+    int n = 0, max_it = 0, order = 0, part = 0, n_parts = 1, nbx = 0;
+    double sat = 0, thr = 0;
+    double *d_old = nullptr, *d_acc = nullptr, *d_part = nullptr, *d_change = nullptr;
+    int *d_iter = nullptr, *d_active = nullptr, *d_nactive = nullptr;
+  } em;
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(peng_handle_t h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (h) h->err = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CU(h, call)                                                                                   \
+  do {                                                                                                \
+    cudaError_t e_ = (call);                                                                          \
+    if (e_ != cudaSuccess)                                                                            \
+      return fail(h, PENG_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+#define LAUNCH_CHECK(h)                \
+  do {                                 \
+    (h)->launches++;                   \
+    CU(h, cudaGetLastError());         \
+  } while (0)
+
+template <typename T>
+static int dev_alloc(peng_handle_t h, T** p, size_t n) {
+  if (*p) { cudaFree(*p); *p = nullptr; }
+  if (n == 0) n = 1;
+  cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+  if (e != cudaSuccess) {
+    *p = nullptr;
+    return fail(h, PENG_E_NOMEM, "cudaMalloc(%zu bytes) failed: %s", n * sizeof(T), cudaGetErrorString(e));
+  }
+  return PENG_OK;
+}
+template <typename T>
+static void dev_free(T** p) {
+  if (*p) cudaFree(*p);
+  *p = nullptr;
+}
+static int need_scratch(peng_handle_t h, size_t bytes) {
+  if (h->scratch_bytes >= bytes) return PENG_OK;
+  if (h->d_scratch) cudaFree(h->d_scratch);
+  h->d_scratch = nullptr;
+  h->scratch_bytes = 0;
+  cudaError_t e = cudaMalloc(&h->d_scratch, bytes);
+  if (e != cudaSuccess) return fail(h, PENG_E_NOMEM, "scratch cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+  h->scratch_bytes = bytes;
+  return PENG_OK;
+}
+#define TRY(expr)            \
+  do {                       \
+    int rc_ = (expr);        \
+    if (rc_ != PENG_OK) return rc_; \
+  } while (0)
+
+static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+// =====================================================================================================
+// kernels: ingest
+// =====================================================================================================
+template <bool ASCII>
+__global__ void k_pack(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets, uint64_t n_seq,
+                       uint32_t* __restrict__ codes, uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart,
+                       uint64_t n_words32) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n_words32) pack_word<ASCII>(t, src, offsets, n_seq, codes, valid, sstart);
+}
+
+__global__ void k_synth(SynthParams P, uint32_t* __restrict__ codes, uint32_t* __restrict__ valid,
+                        uint32_t* __restrict__ sstart, uint64_t n_words32) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n_words32) synth_word(t, P, codes, valid, sstart);
+}
+
+// one thread per stream position: write the reference letter code of real bases to out[base index]
+__global__ void k_export(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid,
+                         const uint64_t* __restrict__ offsets, uint64_t n_seq, uint32_t fixed_len,
+                         uint64_t stream_end, uint8_t* __restrict__ out) {
+  const uint64_t q = PENG_FRONT_PAD + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= stream_end) return;
+  uint64_t s, i, len, base0;
+  if (fixed_len) {
+    const uint64_t stride = (uint64_t)fixed_len + 2;
+    s = (q - PENG_FRONT_PAD) / stride;
+    i = (q - PENG_FRONT_PAD) - s * stride;
+    len = fixed_len;
+    base0 = s * fixed_len;
+  } else {
+    uint64_t lo = 0, hi = n_seq - 1;
+    while (lo < hi) {
+      const uint64_t mid = (lo + hi + 1) >> 1;
+      if (PENG_FRONT_PAD + offsets[mid] + 2 * mid <= q) lo = mid; else hi = mid - 1;
+    }
+    s = lo;
+    i = q - (PENG_FRONT_PAD + offsets[s] + 2 * s);
+    len = offsets[s + 1] - offsets[s];
+    base0 = offsets[s];
+  }
+  if (i < len) out[base0 + i] = unpack_code(codes, valid, q);
+}
+
+// =====================================================================================================
+// kernels: counting
+// =====================================================================================================
+__global__ void k_mark_kstart(const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart, uint64_t n_words32,
+                              int W, unsigned long long* __restrict__ ltot) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int n = 0;
+  if (t < n_words32) n = mark_kstart_word(t, n_words32, valid, W, kstart);
+  // block reduction: warp shuffles, then one atomic per warp
+  for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if ((threadIdx.x & 31) == 0 && n) atomicAdd(ltot, (unsigned long long)n);
+}
+
+struct EmitGlobal {
+  uint32_t* hist;
+  __device__ __forceinline__ void operator()(uint32_t key) const { atomicAdd(hist + key, 1u); }  // RED.ADD, no return
+};
+
+// Generic path (any W): one L2 atomic per counted occurrence into the 4^W uint32 table (L2-resident up to
+// W = 12).  A thread owns `words_per_chunk` code words = 16*words_per_chunk k-mer end positions.
+template <int W, bool BOTH>
+__global__ void __launch_bounds__(128) k_count_global(const uint32_t* __restrict__ codes,
+                                                      const uint32_t* __restrict__ kstart,
+                                                      uint32_t* __restrict__ hist, uint64_t first_chunk,
+                                                      uint64_t n_chunks, uint32_t words_per_chunk) {
+  const uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_chunks) return;
+  const uint64_t e0 = PENG_FRONT_PAD + (first_chunk + c) * 16ull * words_per_chunk;
+  count_chunk<W, BOTH>(codes, kstart, e0, words_per_chunk, EmitGlobal{hist});
+}
+
+// Shared-memory privatised path for 4^W * 4 B <= smem (W <= 6 as uint32 bins; W = 8 as 2 x 16-bit packed
+// bins is handled by k_count_smem16): every CTA builds a private sub-histogram with shared-memory atomics
+// and merges it into the global table once at the end.
+struct EmitShared {
+  uint32_t* sh;
+  __device__ __forceinline__ void operator()(uint32_t key) const { atomicAdd(sh + key, 1u); }
+};
+
+template <int W, bool BOTH>
+__global__ void __launch_bounds__(256) k_count_smem(const uint32_t* __restrict__ codes,
+                                                    const uint32_t* __restrict__ kstart,
+                                                    uint32_t* __restrict__ hist, uint64_t n_chunks,
+                                                    uint32_t words_per_chunk) {
+  extern __shared__ uint32_t sh[];
+  constexpr uint32_t NB = 1u << (2 * W);
+  for (uint32_t i = threadIdx.x; i < NB; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_chunks;
+       c += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t e0 = PENG_FRONT_PAD + c * 16ull * words_per_chunk;
+    count_chunk<W, BOTH>(codes, kstart, e0, words_per_chunk, EmitShared{sh});
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < NB; i += blockDim.x) {
+    const uint32_t v = sh[i];
+    if (v) atomicAdd(hist + i, v);
+  }
+}
+
+// W = 8: 65536 bins do not fit shared memory as uint32 (256 KB) but do as 16-bit halves (128 KB).  A
+// private half-word can overflow, so every increment uses the returning form of the atomic: the thread
+// that moves a half from 0x7FFF to 0x8000 owns the carry, takes 0x8000 back out of the half and adds it
+// to the global bin.  A half can therefore never reach 0x10000 (that would need 32768 further hits on the
+// same bin inside the few cycles between the two atomics of the carrying thread).
+struct EmitShared16 {
+  uint32_t* sh;
+  uint32_t* hist;
+  __device__ __forceinline__ void operator()(uint32_t key) const {
+    const uint32_t sft = (key & 1u) * 16u;
+    const uint32_t old = atomicAdd(sh + (key >> 1), 1u << sft);
+    if (((old >> sft) & 0xFFFFu) == 0x7FFFu) {
+      atomicSub(sh + (key >> 1), 0x8000u << sft);
+      atomicAdd(hist + key, 0x8000u);
+    }
+  }
+};
+
+template <int W, bool BOTH>
+__global__ void __launch_bounds__(512) k_count_smem16(const uint32_t* __restrict__ codes,
+                                                      const uint32_t* __restrict__ kstart,
+                                                      uint32_t* __restrict__ hist, uint64_t n_chunks,
+                                                      uint32_t words_per_chunk) {
+  extern __shared__ uint32_t sh[];
+  constexpr uint32_t NW = 1u << (2 * W - 1);  // packed words
+  for (uint32_t i = threadIdx.x; i < NW; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_chunks;
+       c += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t e0 = PENG_FRONT_PAD + c * 16ull * words_per_chunk;
+    count_chunk<W, BOTH>(codes, kstart, e0, words_per_chunk, EmitShared16{sh, hist});
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < NW; i += blockDim.x) {
+    const uint32_t v = sh[i];
+    if (v & 0xFFFFu) atomicAdd(hist + 2 * i, v & 0xFFFFu);
+    if (v >> 16) atomicAdd(hist + 2 * i + 1, v >> 16);
+  }
+}
+
+// fold the uint32 launch histogram into the 64-bit table and clear it ("global merge")
+__global__ void k_fold(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t v = hist[i];
+    if (v) {
+      acc[i] += v;
+      hist[i] = 0;
+    }
+  }
+}
+
+// second copy of the pair count at the reverse-complement id (src/base_pattern.cpp:387-392). Only
+// non-canonical entries are written and only canonical entries are read, so in place is race-free.
+__global__ void k_mirror(uint64_t* __restrict__ counts, int W, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t rc = revcomp_id((uint32_t)i, W);
+    if ((uint32_t)i > rc) counts[i] = counts[rc];
+  }
+}
+
+// =====================================================================================================
+// kernels: background model counts
+// =====================================================================================================
+__global__ void __launch_bounds__(256) k_bg_counts(const uint32_t* __restrict__ codes,
+                                                   const uint32_t* __restrict__ valid,
+                                                   const uint32_t* __restrict__ sstart, uint64_t stream_end, int K,
+                                                   unsigned long long* __restrict__ out, uint32_t n_bins) {
+  extern __shared__ uint32_t shb[];  // n_bins private bins
+  for (uint32_t i = threadIdx.x; i < n_bins; i += blockDim.x) shb[i] = 0;
+  __syncthreads();
+  const uint64_t n = stream_end - PENG_FRONT_PAD;
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t q = PENG_FRONT_PAD + t;
+    // separators: the two positions in front of a sequence start / the last two of the stream
+    const bool sep = q + 2 >= stream_end || bit_at(sstart, q + 1) || bit_at(sstart, q + 2);
+    if (sep) continue;
+    uint32_t ids[PENG_MAX_ORDER + 1];
+    const uint32_t m = background_ids(codes, valid, sstart, q, K, ids);
+    for (int k = 0; k <= K; k++)
+      if ((m >> k) & 1u) atomicAdd(shb + v_offset(k) + ids[k], 1u);
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n_bins; i += blockDim.x)
+    if (shb[i]) atomicAdd(out + i, (unsigned long long)shb[i]);
+}
+
+// =====================================================================================================
+// kernels: tables
+// =====================================================================================================
+template <typename R>
+__global__ void k_bgprob(const R* __restrict__ v, int W, int order, int both, R* __restrict__ out, uint64_t n) {
+  extern __shared__ unsigned char shv_raw[];
+  R* shv = reinterpret_cast<R*>(shv_raw);
+  const uint32_t nv = v_offset(order + 1);
+  for (uint32_t i = threadIdx.x; i < nv; i += blockDim.x) shv[i] = v[i];
+  __syncthreads();
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = bg_prob_entry<R>(shv, W, order, (uint32_t)i, both != 0);
+}
+
+template <typename R>
+__global__ void k_stats(const uint64_t* __restrict__ counts, const R* __restrict__ bg, uint64_t ltot,
+                        R* __restrict__ expected, R* __restrict__ z, R* __restrict__ logp, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) stats_of<R>(counts[i], bg[i], ltot, expected + i, z + i, logp + i);
+}
+
+// =====================================================================================================
+// kernels: IUPAC sums
+// =====================================================================================================
+__device__ __forceinline__ double warp_sum(double v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Order-free sums (PENG_F64, and the integer count sums of every mode): block per pattern.
+template <typename R, bool BOTH, bool WITH_FLOATS>
+__global__ void __launch_bounds__(256) k_iupac_any(const uint64_t* __restrict__ masks, int W,
+                                                   const uint64_t* __restrict__ counts, const R* __restrict__ bg,
+                                                   const R* __restrict__ expected,
+                                                   unsigned long long* __restrict__ out_n, double* __restrict__ out_bg,
+                                                   double* __restrict__ out_exp) {
+  const uint64_t mask = masks[blockIdx.x];
+  const IupacShape shape = iupac_shape(mask, W);
+  const uint64_t N = 1ull << shape.total_bits;
+  unsigned long long sn = 0;
+  double sb = 0, se = 0;
+  for (uint64_t t = threadIdx.x; t < N; t += blockDim.x) {
+    const uint32_t e = iupac_expansion_any(mask, W, shape, t);
+    if (BOTH && !iupac_is_representative(mask, W, e)) continue;
+    sn += counts[e];  // counts / bgprob / expected hold the pair value at both ids of a pair
+    if (WITH_FLOATS) {
+      sb += (double)bg[e];
+      se += (double)expected[e];
+    }
+  }
+  __shared__ unsigned long long shn[8];
+  __shared__ double shbg[8], shex[8];
+  sn = warp_sum(sn);
+  if (WITH_FLOATS) { sb = warp_sum(sb); se = warp_sum(se); }
+  const int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { shn[w] = sn; shbg[w] = sb; shex[w] = se; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long tn = 0;
+    double tb = 0, te = 0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); i++) { tn += shn[i]; tb += shbg[i]; te += shex[i]; }
+    out_n[blockIdx.x] = tn;
+    if (WITH_FLOATS) { out_bg[blockIdx.x] = tb; out_exp[blockIdx.x] = te; }
+  }
+}
+
+// PENG_F32REF, PLUS strand: float sums accumulated sequentially in the reference's expansion order
+// (src/iupac_pattern.cpp:428-441).  The block gathers 1024 values at a time, thread 0 adds them in order.
+__global__ void __launch_bounds__(256) k_iupac_f32_plus(const uint64_t* __restrict__ masks, int W,
+                                                        const float* __restrict__ bg,
+                                                        const float* __restrict__ expected,
+                                                        float* __restrict__ out_bg, float* __restrict__ out_exp) {
+  __shared__ float sbg[1024], sex[1024];
+  const uint64_t mask = masks[blockIdx.x];
+  const IupacShape shape = iupac_shape(mask, W);
+  const uint64_t N = 1ull << shape.total_bits;
+  float acc_b = 0.f, acc_e = 0.f;
+  for (uint64_t base = 0; base < N; base += 1024) {
+    const uint32_t m = (uint32_t)min((uint64_t)1024, N - base);
+    for (uint32_t i = threadIdx.x; i < m; i += blockDim.x) {
+      const uint32_t e = iupac_expansion_dfs(mask, W, shape, base + i);
+      sbg[i] = bg[e];
+      sex[i] = expected[e];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (uint32_t i = 0; i < m; i++) {
+        acc_b = __fadd_rn(acc_b, sbg[i]);
+        acc_e = __fadd_rn(acc_e, sex[i]);
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out_bg[blockIdx.x] = acc_b; out_exp[blockIdx.x] = acc_e; }
+}
+
+// PENG_F32REF, BOTH strands: the reference adds in ascending canonical-id order over distinct ids
+// (sorted list, adjacent duplicates skipped).  The block marks the canonical ids in a 4^W-bit bitmap in
+// global scratch (L2-resident) and then walks the bitmap in order: ascending + distinct for free.
+#define IUPAC_TILE_WORDS 128
+__global__ void __launch_bounds__(IUPAC_TILE_WORDS) k_iupac_f32_both(const uint64_t* __restrict__ masks, int W,
+                                                                     const float* __restrict__ bg,
+                                                                     const float* __restrict__ expected,
+                                                                     uint32_t* __restrict__ bitmaps,
+                                                                     float* __restrict__ out_bg,
+                                                                     float* __restrict__ out_exp) {
+  __shared__ float sbg[IUPAC_TILE_WORDS * 32], sex[IUPAC_TILE_WORDS * 32];
+  __shared__ uint32_t warp_tot[IUPAC_TILE_WORDS / 32];
+  __shared__ uint32_t tile_any[(1u << 20) / 32 / IUPAC_TILE_WORDS / 32 + 1];  // up to W = 10 tracked exactly
+  const uint64_t mask = masks[blockIdx.x];
+  const IupacShape shape = iupac_shape(mask, W);
+  const uint64_t N = 1ull << shape.total_bits;
+  const uint32_t n_words = W >= 3 ? (1u << (2 * W - 5)) : 1u;
+  uint32_t* bm = bitmaps + (size_t)blockIdx.x * n_words;
+  const uint32_t n_tiles = (n_words + IUPAC_TILE_WORDS - 1) / IUPAC_TILE_WORDS;
+  const bool track = n_tiles <= 32u * (sizeof(tile_any) / 4);
+  for (uint32_t i = threadIdx.x; i < n_words; i += blockDim.x) bm[i] = 0;
+  for (uint32_t i = threadIdx.x; i < sizeof(tile_any) / 4; i += blockDim.x) tile_any[i] = 0;
+  __syncthreads();
+  for (uint64_t t = threadIdx.x; t < N; t += blockDim.x) {
+    const uint32_t e = iupac_expansion_any(mask, W, shape, t);
+    const uint32_t rc = revcomp_id(e, W);
+    const uint32_t c = e < rc ? e : rc;
+    atomicOr(bm + (c >> 5), 1u << (c & 31));
+    if (track) {
+      const uint32_t tile = (c >> 5) / IUPAC_TILE_WORDS;
+      atomicOr(tile_any + (tile >> 5), 1u << (tile & 31));
+    }
+  }
+  __syncthreads();
+  float acc_b = 0.f, acc_e = 0.f;
+  for (uint32_t tile = 0; tile < n_tiles; tile++) {
+    if (track && !((tile_any[tile >> 5] >> (tile & 31)) & 1u)) continue;  // block-uniform
+    const uint32_t wi = tile * IUPAC_TILE_WORDS + threadIdx.x;
+    const uint32_t w = wi < n_words ? bm[wi] : 0u;
+    const uint32_t pc = __popc(w);
+    // exclusive scan of pc over the block: warp scan + warp totals
+    uint32_t incl = pc;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((threadIdx.x & 31) >= (unsigned)o) incl += y;
+    }
+    if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t off = incl - pc, total = 0;
+    for (int i = 0; i < IUPAC_TILE_WORDS / 32; i++) {
+      if (i < (int)(threadIdx.x >> 5)) off += warp_tot[i];
+      total += warp_tot[i];
+    }
+    uint32_t ww = w;
+    while (ww) {
+      const uint32_t b = __ffs(ww) - 1;
+      ww &= ww - 1;
+      const uint32_t id = (wi << 5) | b;
+      sbg[off] = bg[id];
+      sex[off] = expected[id];
+      off++;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (uint32_t i = 0; i < total; i++) {
+        acc_b = __fadd_rn(acc_b, sbg[i]);
+        acc_e = __fadd_rn(acc_e, sex[i]);
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { out_bg[blockIdx.x] = acc_b; out_exp[blockIdx.x] = acc_e; }
+}
+
+// =====================================================================================================
+// kernels: EM, FP64 (fast path)
+// =====================================================================================================
+// new_pwm[p][a] = sum over ids with digit_p = a of  cnt*s / (1 + s/odds),  odds = prod_p pwm[p][digit_p] / bg
+//              = sum cnt*s*prob / (prob + s*bg).
+// A warp owns a tile of 1024 consecutive ids (positions 0..4 take all values, positions >= 5 are fixed).
+// Lane l handles ids  tile + l + 32 j, j = 0..31:
+//   positions 0,1 : fixed by the lane (l & 3, (l >> 2) & 3)
+//   position 2    : digit = (l >> 4) | ((j & 1) << 1)
+//   position 3    : digit = (j >> 1) & 3          position 4 : digit = (j >> 3) & 3
+// so the per-digit partial sums live in 11 statically indexed registers and are combined across lanes with
+// warp shuffles once per tile; per-warp accumulators in shared memory, one deterministic block reduction,
+// one partial-sum row per CTA in global memory (reduced in fixed order by k_em_reduce).
+#define EM_WARPS 8
+__device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+
+template <int W>
+__global__ void __launch_bounds__(EM_WARPS * 32) k_em_accumulate_f64(
+    const uint64_t* __restrict__ counts, const double* __restrict__ bg, const double* __restrict__ pwms,
+    const int* __restrict__ active, double saturation, uint32_t tile_begin, uint32_t tile_end,
+    double* __restrict__ partials /* [n_pwm][gridDim.x][W*4] */) {
+  static_assert(W >= 6, "tile layout needs positions 0..4 plus at least one fixed position");
+  const int m = blockIdx.y;
+  if (!active[m]) return;
+  __shared__ double spwm[W * 4];
+  __shared__ double sacc[EM_WARPS][W * 4];
+  for (int i = threadIdx.x; i < W * 4; i += blockDim.x) spwm[i] = pwms[(size_t)m * W * 4 + i];
+  for (int i = threadIdx.x; i < EM_WARPS * W * 4; i += blockDim.x) (&sacc[0][0])[i] = 0.0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t d0 = lane & 3, d1 = (lane >> 2) & 3, d2lo = lane >> 4;
+  const double p01 = spwm[d0] * spwm[4 + d1];
+  double p2[2], p3[4], p4[4];
+  p2[0] = spwm[8 + d2lo];
+  p2[1] = spwm[8 + d2lo + 2];
+#pragma unroll
+  for (int a = 0; a < 4; a++) { p3[a] = spwm[12 + a]; p4[a] = spwm[16 + a]; }
+
+  for (uint32_t tile = tile_begin + blockIdx.x * EM_WARPS + warp; tile < tile_end; tile += gridDim.x * EM_WARPS) {
+    // product over the tile-fixed positions 5..W-1
+    double pfix = p01;
+#pragma unroll
+    for (int q = 5; q < W; q++) pfix *= spwm[q * 4 + ((tile >> (2 * (q - 5))) & 3u)];
+    const uint64_t id0 = ((uint64_t)tile << 10) + lane;
+    double a2[2] = {0, 0}, a3[4] = {0, 0, 0, 0}, a4[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int j = 0; j < 32; j++) {
+      const uint64_t id = id0 + 32 * j;
+      const uint64_t cnt = __ldg(counts + id);
+      double term = 0.0;
+      if (cnt) {
+        const double prob = pfix * p2[j & 1] * p3[(j >> 1) & 3] * p4[(j >> 3) & 3];
+        const double sb = saturation * __ldg(bg + id);
+        term = ((double)cnt * saturation) * prob / (prob + sb);
+      }
+      a2[j & 1] += term;
+      a3[(j >> 1) & 3] += term;
+      a4[(j >> 3) & 3] += term;
+    }
+    const double tot = a2[0] + a2[1];
+    // position 0: classes = lane bits 0-1, reduce over bits 2,3,4
+    double r0 = tot;
+    r0 += shfl_xor_d(r0, 4); r0 += shfl_xor_d(r0, 8); r0 += shfl_xor_d(r0, 16);
+    // position 1: classes = lane bits 2-3, reduce over bits 0,1,4
+    double r1 = tot;
+    r1 += shfl_xor_d(r1, 1); r1 += shfl_xor_d(r1, 2); r1 += shfl_xor_d(r1, 16);
+    // position 2: digit = (lane >> 4) | (jbit << 1): reduce over lane bits 0-3, classes = lane bit 4 x jbit
+    double r2a = a2[0], r2b = a2[1];
+#pragma unroll
+    for (int o = 1; o < 16; o <<= 1) { r2a += shfl_xor_d(r2a, o); r2b += shfl_xor_d(r2b, o); }
+    // positions 3, 4 and the tile total: full warp sums
+    double r3[4], r4[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+      r3[a] = a3[a];
+      r4[a] = a4[a];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { r3[a] += shfl_xor_d(r3[a], o); r4[a] += shfl_xor_d(r4[a], o); }
+    }
+    const double all = r3[0] + r3[1] + r3[2] + r3[3];
+    double* acc = sacc[warp];
+    if (lane < 4) acc[lane] += r0;                      // position 0, digit = lane
+    if ((lane & 0x13) == 0) acc[4 + (lane >> 2)] += r1; // position 1, digit = lane >> 2 (lanes 0,4,8,12)
+    if ((lane & 15) == 0) {                             // lanes 0 and 16: position 2
+      acc[8 + (lane >> 4)] += r2a;
+      acc[8 + (lane >> 4) + 2] += r2b;
+    }
+    if (lane == 1) {
+#pragma unroll
+      for (int a = 0; a < 4; a++) { acc[12 + a] += r3[a]; acc[16 + a] += r4[a]; }
+    }
+    if (lane == 2) {
+#pragma unroll
+      for (int q = 5; q < W; q++) acc[q * 4 + ((tile >> (2 * (q - 5))) & 3u)] += all;
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < W * 4; i += blockDim.x) {
+    double s = 0;
+#pragma unroll
+    for (int w = 0; w < EM_WARPS; w++) s += sacc[w][i];
+    partials[((size_t)m * gridDim.x + blockIdx.x) * (W * 4) + i] = s;
+  }
+}
+
+// small-W fallback (W = 2, 4): one thread per accumulator walks the table
+__global__ void k_em_accumulate_small(const uint64_t* __restrict__ counts, const double* __restrict__ bg,
+                                      const double* __restrict__ pwms, const int* __restrict__ active, int W,
+                                      double saturation, uint32_t id_begin, uint32_t id_end,
+                                      double* __restrict__ partials) {
+  const int m = blockIdx.x;
+  if (!active[m]) return;
+  const int c = threadIdx.x;
+  if (c >= W * 4) return;
+  const int p = c >> 2, a = c & 3;
+  const double* pw = pwms + (size_t)m * W * 4;
+  double s = 0;
+  for (uint32_t id = id_begin; id < id_end; id++) {
+    if (((id >> (2 * p)) & 3u) != (uint32_t)a) continue;
+    const uint64_t cnt = counts[id];
+    if (!cnt) continue;
+    double prob = 1.0;
+    for (int q = 0; q < W; q++) prob *= pw[q * 4 + ((id >> (2 * q)) & 3u)];
+    s += ((double)cnt * saturation) * prob / (prob + saturation * bg[id]);
+  }
+  partials[(size_t)m * (W * 4) + c] = s;
+}
+
+// acc[m][i] = sum_b partials[m][b][i] in fixed order
+__global__ void k_em_reduce(const double* __restrict__ partials, const int* __restrict__ active, int nbx, int WA,
+                            double* __restrict__ acc) {
+  const int m = blockIdx.x, i = threadIdx.x;
+  if (i >= WA) return;
+  if (!active[m]) return;
+  double s = 0;
+  for (int b = 0; b < nbx; b++) s += partials[((size_t)m * nbx + b) * WA + i];
+  acc[(size_t)m * WA + i] = s;
+}
+
+// normalise rows, L1 change, iteration bookkeeping (src/peng.cpp:104-144); one warp per PWM
+__global__ void k_em_update_f64(const double* __restrict__ acc, double* __restrict__ old_pwm,
+                                double* __restrict__ change, int* __restrict__ iters, int* __restrict__ active, int W,
+                                double threshold, int max_iterations, int* __restrict__ n_active) {
+  const int m = blockIdx.x;
+  if (threadIdx.x != 0) return;
+  if (active[m]) {
+    double ch = 0;
+    for (int p = 0; p < W; p++) {
+      double s = 0;
+      for (int a = 0; a < 4; a++) s += acc[(size_t)m * W * 4 + p * 4 + a];
+      for (int a = 0; a < 4; a++) {
+        const double nv = acc[(size_t)m * W * 4 + p * 4 + a] / s;
+        ch += fabs(nv - old_pwm[(size_t)m * W * 4 + p * 4 + a]);
+        old_pwm[(size_t)m * W * 4 + p * 4 + a] = nv;
+      }
+    }
+    change[m] = ch;
+    iters[m] += 1;
+    const int still = !(ch <= threshold || iters[m] >= max_iterations);
+    active[m] = still;
+    if (still) atomicAdd(n_active, 1);
+  }
+}
+
+__global__ void k_em_init(double* __restrict__ change, int* __restrict__ iters, int* __restrict__ active, int n, int W,
+                          double threshold, int max_iterations) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m < n) {
+    change[m] = (double)W;  // (src/peng.cpp:101)
+    iters[m] = 0;
+    active[m] = !((double)W <= threshold || 0 >= max_iterations);
+  }
+}
+
+// final normalisation of IUPACPattern(ori, pwm) (src/iupac_pattern.cpp:61)
+template <typename R>
+__global__ void k_em_final_normalize(R* __restrict__ pwm, int n, int W) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;  // row index over n*W
+  if (r < n * W) {
+    R s = (R)0;
+    for (int a = 0; a < 4; a++) s = Ar<R>::add(s, pwm[(size_t)r * 4 + a]);
+    for (int a = 0; a < 4; a++) pwm[(size_t)r * 4 + a] = Ar<R>::div(pwm[(size_t)r * 4 + a], s);
+  }
+}
+
+// =====================================================================================================
+// kernels: EM, float32 reference-faithful path
+// =====================================================================================================
+// (1) every term in the reference's float32 arithmetic, element-wise and therefore order-free
+__global__ void k_em_terms_f32(const uint64_t* __restrict__ counts, const float* __restrict__ bg,
+                               const float* __restrict__ pwms, const int* __restrict__ active, int W, float saturation,
+                               uint64_t n, float* __restrict__ terms) {
+  const int m = blockIdx.y;
+  if (!active[m]) return;
+  __shared__ float spwm[PENG_MAX_W * 4];
+  for (int i = threadIdx.x; i < W * 4; i += blockDim.x) spwm[i] = pwms[(size_t)m * W * 4 + i];
+  __syncthreads();
+  const uint64_t id = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (id < n) terms[(size_t)m * n + id] = em_term_f32(spwm, W, (uint32_t)id, counts[id], bg[id], saturation);
+}
+
+// (2) the reference adds the terms to new_pwm[p][a] one at a time in ascending id order
+// (src/peng.cpp:121-127): 4W independent sequential float32 chains per PWM.  One warp per chain: the lanes
+// gather the next 128 chain elements (coalesced where the chain is contiguous), lane 0 adds them in order
+// out of shared memory while the loads of the following batch are already in flight.
+#define CHAIN_BATCH 128
+__global__ void __launch_bounds__(128) k_em_chains_f32(const float* __restrict__ terms, const int* __restrict__ active,
+                                                       int W, uint64_t n, float* __restrict__ acc) {
+  const int m = blockIdx.y;
+  if (!active[m]) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x;          // position
+  const uint32_t a = warp;           // letter: 4 warps per block
+  __shared__ __align__(16) float buf[4][CHAIN_BATCH];
+  const float* t = terms + (size_t)m * n;
+  const uint32_t len = (uint32_t)(n >> 2);  // elements per chain
+  float s = 0.f;
+  float nxt[CHAIN_BATCH / 32];
+#pragma unroll
+  for (int k = 0; k < CHAIN_BATCH / 32; k++) {
+    const uint32_t idx = k * 32 + lane;
+    nxt[k] = idx < len ? t[em_chain_id(p, a, idx)] : 0.f;
+  }
+  for (uint32_t base = 0; base < len; base += CHAIN_BATCH) {
+#pragma unroll
+    for (int k = 0; k < CHAIN_BATCH / 32; k++) buf[warp][k * 32 + lane] = nxt[k];
+    __syncwarp();
+    const uint32_t nb = base + CHAIN_BATCH;
+#pragma unroll
+    for (int k = 0; k < CHAIN_BATCH / 32; k++) {
+      const uint32_t idx = nb + k * 32 + lane;
+      nxt[k] = idx < len ? t[em_chain_id(p, a, idx)] : 0.f;
+    }
+    if (lane == 0) {
+      const uint32_t cnt = min((uint32_t)CHAIN_BATCH, len - base);
+      if (cnt == CHAIN_BATCH) {
+        const float4* b4 = reinterpret_cast<const float4*>(buf[warp]);
+#pragma unroll 8
+        for (int i = 0; i < CHAIN_BATCH / 4; i++) {
+          const float4 x = b4[i];
+          s = __fadd_rn(s, x.x); s = __fadd_rn(s, x.y); s = __fadd_rn(s, x.z); s = __fadd_rn(s, x.w);
+        }
+      } else {
+        for (uint32_t i = 0; i < cnt; i++) s = __fadd_rn(s, buf[warp][i]);
+      }
+    }
+    __syncwarp();
+  }
+  if (lane == 0) acc[(size_t)m * W * 4 + p * 4 + a] = s;
+}
+
+// (3) normalize_pwm + change + swap (src/iupac_pattern.cpp:291-303, src/peng.cpp:129-143), float32, in order
+__global__ void k_em_update_f32(const float* __restrict__ acc, float* __restrict__ old_pwm, int* __restrict__ iters,
+                                int* __restrict__ active, int W, float threshold, int max_iterations,
+                                int* __restrict__ n_active) {
+  const int m = blockIdx.x;
+  if (threadIdx.x != 0 || !active[m]) return;
+  float nw[PENG_MAX_W * 4];
+  for (int p = 0; p < W; p++) {
+    float s = 0.f;
+    for (int a = 0; a < 4; a++) s = __fadd_rn(s, acc[(size_t)m * W * 4 + p * 4 + a]);
+    for (int a = 0; a < 4; a++) nw[p * 4 + a] = __fdiv_rn(acc[(size_t)m * W * 4 + p * 4 + a], s);
+  }
+  float ch = 0.f;
+  for (int i = 0; i < W * 4; i++) {
+    ch = __fadd_rn(ch, fabsf(__fsub_rn(nw[i], old_pwm[(size_t)m * W * 4 + i])));
+    old_pwm[(size_t)m * W * 4 + i] = nw[i];
+  }
+  iters[m] += 1;
+  const int still = !(ch <= threshold || iters[m] >= max_iterations);
+  active[m] = still;
+  if (still) atomicAdd(n_active, 1);
+}
+
+__global__ void k_em_init_f32(int* __restrict__ iters, int* __restrict__ active, int n, int W, float threshold,
+                              int max_iterations) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m < n) {
+    iters[m] = 0;
+    active[m] = !((float)W <= threshold || 0 >= max_iterations);
+  }
+}
+
+// =====================================================================================================
+// C ABI: lifetime
+// =====================================================================================================
+extern "C" int peng_cuda_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
+  if (!out) return fail(nullptr, PENG_E_INVALID, "out is NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return fail(nullptr, PENG_E_CUDA, "no CUDA device (%s): libpeng_cuda has no CPU fallback",
+                e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+  if (device < 0 || device >= n) return fail(nullptr, PENG_E_INVALID, "device %d out of range [0,%d)", device, n);
+  e = cudaSetDevice(device);
+  if (e != cudaSuccess) return fail(nullptr, PENG_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+  peng_cuda_ctx* h = new peng_cuda_ctx();
+  h->device = device;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) h->sm_count = prop.multiProcessorCount;
+  e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) {
+    delete h;
+    return fail(nullptr, PENG_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+  }
+  h->stream = h->own_stream;
+  *out = h;
+  return PENG_OK;
+}
+
+static void free_tables(peng_handle_t h) {
+  for (int k = 0; k <= PENG_MAX_ORDER; k++) { dev_free(&h->d_bg32[k]); dev_free(&h->d_bg64[k]); }
+  dev_free(&h->d_exp32); dev_free(&h->d_z32); dev_free(&h->d_logp32);
+  dev_free(&h->d_exp64); dev_free(&h->d_z64); dev_free(&h->d_logp64);
+  h->stats_ready = false;
+}
+static void free_em(peng_handle_t h) {
+  dev_free(&h->em.d_old); dev_free(&h->em.d_acc); dev_free(&h->em.d_part); dev_free(&h->em.d_change);
+  dev_free(&h->em.d_iter); dev_free(&h->em.d_active); dev_free(&h->em.d_nactive);
+  h->em.open = false;
+}
+
+extern "C" void peng_cuda_destroy(peng_handle_t h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  dev_free(&h->d_codes); dev_free(&h->d_valid); dev_free(&h->d_sstart); dev_free(&h->d_kstart);
+  dev_free(&h->d_offsets); dev_free(&h->d_hist32); dev_free(&h->d_counts); dev_free(&h->d_bgcounts);
+  dev_free(&h->d_v32); dev_free(&h->d_v64);
+  free_tables(h);
+  free_em(h);
+  if (h->d_scratch) cudaFree(h->d_scratch);
+  if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  delete h;
+}
+
+extern "C" const char* peng_cuda_last_error(peng_handle_t h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+extern "C" uint64_t peng_cuda_launch_count(peng_handle_t h) { return h ? h->launches : 0; }
+
+extern "C" int peng_cuda_set_stream(peng_handle_t h, void* s) {
+  if (!h) return PENG_E_INVALID;
+  h->stream = s ? (cudaStream_t)s : h->own_stream;
+  return PENG_OK;
+}
+extern "C" int peng_cuda_synchronize(peng_handle_t h) {
+  if (!h) return PENG_E_INVALID;
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+// =====================================================================================================
+// C ABI: ingest
+// =====================================================================================================
+static int alloc_stream(peng_handle_t h, uint64_t n_seq, uint64_t total_bases) {
+  h->n_seq = n_seq;
+  h->total_bases = total_bases;
+  h->stream_end = PENG_FRONT_PAD + total_bases + 2 * n_seq;
+  h->n_words32 = (h->stream_end + PENG_TAIL_PAD + 31) / 32 + 8;
+  TRY(dev_alloc(h, &h->d_codes, h->n_words32 * 2 + 8));
+  TRY(dev_alloc(h, &h->d_valid, h->n_words32 + 8));
+  TRY(dev_alloc(h, &h->d_sstart, h->n_words32 + 8));
+  TRY(dev_alloc(h, &h->d_kstart, h->n_words32 + 8));
+  // the few guard words behind n_words32 are read by funnel shifts at the very end of the stream
+  CU(h, cudaMemsetAsync(h->d_codes + h->n_words32 * 2, 0, 8 * 4, h->stream));
+  CU(h, cudaMemsetAsync(h->d_valid + h->n_words32, 0, 8 * 4, h->stream));
+  CU(h, cudaMemsetAsync(h->d_sstart + h->n_words32, 0, 8 * 4, h->stream));
+  CU(h, cudaMemsetAsync(h->d_kstart, 0, (h->n_words32 + 8) * 4, h->stream));
+  h->counts_final = false;
+  h->stats_ready = false;
+  h->W = 0;
+  return PENG_OK;
+}
+
+static void seq_lengths(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq) {
+  uint32_t mn = 0x7fffffffu, mx = 0;
+  for (uint64_t s = 0; s < n_seq; s++) {
+    const uint64_t L = offsets[s + 1] - offsets[s];
+    if (L > mx) mx = (uint32_t)L;
+    if (L < mn) mn = (uint32_t)L;
+  }
+  h->min_len = mn;
+  h->max_len = mx;
+}
+
+// src = concatenated sequences on the DEVICE (letter codes or ASCII), offsets on the host
+static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  h->fixed_len = 0;
+  h->h_offsets.assign(offsets, offsets + n_seq + 1);
+  seq_lengths(h, offsets, n_seq);
+  TRY(alloc_stream(h, n_seq, total));
+  TRY(dev_alloc(h, &h->d_offsets, n_seq + 1));
+  CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+  const unsigned block = 256;
+  if (ascii)
+    k_pack<true><<<grid_for(h->n_words32, block), block, 0, h->stream>>>(d_src, h->d_offsets, n_seq, h->d_codes,
+                                                                        h->d_valid, h->d_sstart, h->n_words32);
+  else
+    k_pack<false><<<grid_for(h->n_words32, block), block, 0, h->stream>>>(d_src, h->d_offsets, n_seq, h->d_codes,
+                                                                         h->d_valid, h->d_sstart, h->n_words32);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+
+static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
+  CU(h, cudaSetDevice(h->device));
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  TRY(need_scratch(h, (size_t)total + 16));
+  if (total) CU(h, cudaMemcpyAsync(h->d_scratch, src, total, cudaMemcpyHostToDevice, h->stream));
+  TRY(ingest_device_src(h, (const uint8_t*)h->d_scratch, offsets, n_seq, ascii));
+  CU(h, cudaStreamSynchronize(h->stream));  // the caller may free / reuse src
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, const uint64_t* offsets, uint64_t n_seq) {
+  if (!h || !offsets || (!codes && n_seq && offsets[n_seq])) return fail(h, PENG_E_INVALID, "ingest_codes: NULL argument");
+  return ingest_host_src(h, codes, offsets, n_seq, false);
+}
+
+extern "C" int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets,
+                                             uint64_t n_seq) {
+  if (!h || !offsets) return fail(h, PENG_E_INVALID, "ingest_codes_device: NULL argument");
+  CU(h, cudaSetDevice(h->device));
+  return ingest_device_src(h, (const uint8_t*)d_codes, offsets, n_seq, false);
+}
+
+extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, uint64_t* total_bases,
+                                      uint32_t* min_len, uint32_t* max_len) {
+  if (!h || !path) return fail(h, PENG_E_INVALID, "ingest_fasta: NULL argument");
+  peng_host::FastaRecords rec;
+  std::string msg;
+  const int rc = peng_host::read_fasta(path, &rec, &msg);
+  if (rc == 1) return fail(h, PENG_E_IO, "%s", msg.c_str());
+  if (rc == 2) return fail(h, PENG_E_FORMAT, "%s", msg.c_str());
+  TRY(ingest_host_src(h, (const uint8_t*)rec.letters.data(), rec.offsets.data(), rec.offsets.size() - 1, true));
+  if (n_seq) *n_seq = h->n_seq;
+  if (total_bases) *total_bases = h->total_bases;
+  if (min_len) *min_len = h->min_len;
+  if (max_len) *max_len = h->max_len;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_ingest_synthetic(peng_handle_t h, uint64_t n_seq, uint32_t seq_len, uint64_t seed,
+                                          uint64_t first_seq, const uint8_t* motif, uint32_t motif_len,
+                                          double plant_fraction, double n_fraction) {
+  if (!h || seq_len == 0 || motif_len > 32) return fail(h, PENG_E_INVALID, "ingest_synthetic: bad argument");
+  CU(h, cudaSetDevice(h->device));
+  h->fixed_len = seq_len;
+  h->h_offsets.clear();
+  dev_free(&h->d_offsets);
+  h->min_len = h->max_len = seq_len;
+  TRY(alloc_stream(h, n_seq, n_seq * (uint64_t)seq_len));
+  SynthParams P;
+  P.n_seq = n_seq;
+  P.first_seq = first_seq;
+  P.seed = seed;
+  P.seq_len = seq_len;
+  P.motif_len = motif ? motif_len : 0;
+  P.plant_threshold = (uint32_t)(std::min(1.0, std::max(0.0, plant_fraction)) * 16777216.0);
+  P.n_threshold = (uint32_t)(std::min(1.0, std::max(0.0, n_fraction)) * 16777216.0);
+  P.motif_bits = 0;
+  P.degenerate_pos = 0xFFFFFFFFu;
+  for (uint32_t i = 0; i < P.motif_len; i++) {
+    uint32_t c = motif[i];
+    if (c > 3) { P.degenerate_pos = i; c = 1; }  // code 4 = 'S' (C or G)
+    P.motif_bits |= (uint64_t)c << (2 * i);
+  }
+  const unsigned block = 256;
+  k_synth<<<grid_for(h->n_words32, block), block, 0, h->stream>>>(P, h->d_codes, h->d_valid, h->d_sstart, h->n_words32);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_sequences_info(peng_handle_t h, uint64_t* n_seq, uint64_t* total_bases, uint32_t* min_len,
+                                        uint32_t* max_len) {
+  if (!h || !h->d_codes) return fail(h, PENG_E_INVALID, "no sequences ingested");
+  if (n_seq) *n_seq = h->n_seq;
+  if (total_bases) *total_bases = h->total_bases;
+  if (min_len) *min_len = h->min_len;
+  if (max_len) *max_len = h->max_len;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes, uint64_t* offsets) {
+  if (!h || !h->d_codes) return fail(h, PENG_E_INVALID, "no sequences ingested");
+  CU(h, cudaSetDevice(h->device));
+  if (offsets) {
+    if (h->fixed_len) for (uint64_t s = 0; s <= h->n_seq; s++) offsets[s] = s * h->fixed_len;
+    else std::copy(h->h_offsets.begin(), h->h_offsets.end(), offsets);
+  }
+  if (codes && h->total_bases) {
+    TRY(need_scratch(h, h->total_bases));
+    const uint64_t n = h->stream_end - PENG_FRONT_PAD;
+    k_export<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_codes, h->d_valid, h->d_offsets, h->n_seq, h->fixed_len,
+                                                      h->stream_end, (uint8_t*)h->d_scratch);
+    LAUNCH_CHECK(h);
+    CU(h, cudaMemcpyAsync(codes, h->d_scratch, h->total_bases, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+  }
+  return PENG_OK;
+}
+
+// =====================================================================================================
+// C ABI: counting
+// =====================================================================================================
+template <int W>
+static int launch_count_W(peng_handle_t h, bool both) {
+  // chunk geometry: 16 code words (256 end positions) per thread for large inputs, less when the input is
+  // too small to fill the machine (the 48-position warm-up is then the larger share, but the run is short)
+  const uint64_t n_words16 = (h->stream_end - PENG_FRONT_PAD + 15) / 16 + 1;
+  uint32_t wpc = 16;
+  while (wpc > 1 && n_words16 / wpc < (uint64_t)h->sm_count * 1024) wpc >>= 1;
+  const uint64_t n_chunks = (n_words16 + wpc - 1) / wpc;
+  constexpr size_t bins_bytes = (size_t)4 << (2 * W);
+  if constexpr (W <= 6) {
+    const unsigned block = 256;
+    const unsigned grid = (unsigned)std::min<uint64_t>(grid_for(n_chunks, block), (uint64_t)h->sm_count * 8);
+    if (both) k_count_smem<W, true><<<grid, block, bins_bytes, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
+    else k_count_smem<W, false><<<grid, block, bins_bytes, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
+    LAUNCH_CHECK(h);
+    return PENG_OK;
+  } else if constexpr (W == 8) {
+    const unsigned block = 512;
+    const size_t smem = bins_bytes / 2;  // 128 KB of packed 16-bit bins
+    if (both) CU(h, cudaFuncSetAttribute(k_count_smem16<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else CU(h, cudaFuncSetAttribute(k_count_smem16<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)std::min<uint64_t>(grid_for(n_chunks, block), (uint64_t)h->sm_count);
+    if (both) k_count_smem16<W, true><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
+    else k_count_smem16<W, false><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
+    LAUNCH_CHECK(h);
+    return PENG_OK;
+  } else {
+  // W >= 10: global atomics; a uint32 bin cannot overflow within 2^32 positions, so split and fold
+  const uint64_t max_chunks_per_launch = (1ull << 31) / (16ull * wpc);
+  for (uint64_t first = 0; first < n_chunks; first += max_chunks_per_launch) {
+    const uint64_t nc = std::min(max_chunks_per_launch, n_chunks - first);
+    const unsigned block = 128;
+    if (both) k_count_global<W, true><<<grid_for(nc, block), block, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, first, nc, wpc);
+    else k_count_global<W, false><<<grid_for(nc, block), block, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, first, nc, wpc);
+    LAUNCH_CHECK(h);
+    if (first + nc < n_chunks) {
+      k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
+      LAUNCH_CHECK(h);
+    }
+  }
+  return PENG_OK;
+  }
+}
+
+extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
+  if (!h || !h->d_codes) return fail(h, PENG_E_INVALID, "count: no sequences ingested");
+  if (W < 2 || W > PENG_MAX_W || (W & 1)) return fail(h, PENG_E_INVALID, "count: pattern length %d must be even and in [2,16]", W);
+  if (strand != PENG_STRAND_PLUS && strand != PENG_STRAND_BOTH) return fail(h, PENG_E_INVALID, "count: bad strand");
+  CU(h, cudaSetDevice(h->device));
+  const uint64_t n = 1ull << (2 * W);
+  if (h->W != W || !h->d_counts) {
+    free_tables(h);
+    TRY(dev_alloc(h, &h->d_hist32, n));
+    TRY(dev_alloc(h, &h->d_counts, n + 1));
+  }
+  h->W = W;
+  h->strand = strand;
+  h->n_patterns = n;
+  h->counts_final = false;
+  h->stats_ready = false;
+  CU(h, cudaMemsetAsync(h->d_hist32, 0, n * 4, h->stream));
+  CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
+  k_mark_kstart<<<grid_for(h->n_words32, 256), 256, 0, h->stream>>>(h->d_valid, h->d_kstart, h->n_words32, W,
+                                                                   (unsigned long long*)(h->d_counts + n));
+  LAUNCH_CHECK(h);
+  const bool both = strand == PENG_STRAND_BOTH;
+  int rc = PENG_OK;
+  switch (W) {
+    case 2: rc = launch_count_W<2>(h, both); break;
+    case 4: rc = launch_count_W<4>(h, both); break;
+    case 6: rc = launch_count_W<6>(h, both); break;
+    case 8: rc = launch_count_W<8>(h, both); break;
+    case 10: rc = launch_count_W<10>(h, both); break;
+    case 12: rc = launch_count_W<12>(h, both); break;
+    case 14: rc = launch_count_W<14>(h, both); break;
+    case 16: rc = launch_count_W<16>(h, both); break;
+  }
+  TRY(rc);
+  k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_count_buffer(peng_handle_t h, void** device_ptr, uint64_t* n_u64) {
+  if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_buffer: nothing counted");
+  if (device_ptr) *device_ptr = h->d_counts;
+  if (n_u64) *n_u64 = h->n_patterns + 1;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
+  if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_finish: nothing counted");
+  CU(h, cudaSetDevice(h->device));
+  if (!h->counts_final) {
+    if (h->strand == PENG_STRAND_BOTH) {
+      k_mirror<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_counts, h->W, h->n_patterns);
+      LAUNCH_CHECK(h);
+    }
+    CU(h, cudaMemcpyAsync(&h->ltot, h->d_counts + h->n_patterns, 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    h->counts_final = true;
+  }
+  if (ltot) *ltot = h->ltot;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* ltot) {
+  TRY(peng_cuda_count_local(h, W, strand));
+  return peng_cuda_count_finish(h, ltot);
+}
+
+extern "C" int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts) {
+  if (!h || !h->d_counts || !h->counts_final) return fail(h, PENG_E_INVALID, "get_counts: count table not final");
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaMemcpyAsync(counts, h->d_counts, h->n_patterns * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const uint64_t* counts, uint64_t ltot) {
+  if (!h || !counts) return fail(h, PENG_E_INVALID, "set_counts: NULL argument");
+  if (W < 2 || W > PENG_MAX_W || (W & 1)) return fail(h, PENG_E_INVALID, "set_counts: bad pattern length %d", W);
+  CU(h, cudaSetDevice(h->device));
+  const uint64_t n = 1ull << (2 * W);
+  if (h->W != W || !h->d_counts) {
+    free_tables(h);
+    TRY(dev_alloc(h, &h->d_hist32, n));
+    TRY(dev_alloc(h, &h->d_counts, n + 1));
+  }
+  h->W = W;
+  h->strand = strand;
+  h->n_patterns = n;
+  CU(h, cudaMemcpyAsync(h->d_counts, counts, n * 8, cudaMemcpyHostToDevice, h->stream));
+  CU(h, cudaMemcpyAsync(h->d_counts + n, &ltot, 8, cudaMemcpyHostToDevice, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  h->ltot = ltot;
+  h->counts_final = true;
+  h->stats_ready = false;
+  return PENG_OK;
+}
+
+// =====================================================================================================
+// C ABI: background model
+// =====================================================================================================
+extern "C" int peng_cuda_background_counts(peng_handle_t h, int K) {
+  if (!h || !h->d_codes) return fail(h, PENG_E_INVALID, "background: no sequences ingested");
+  if (K < 0 || K > PENG_MAX_ORDER) return fail(h, PENG_E_INVALID, "background: order %d not in [0,%d]", K, PENG_MAX_ORDER);
+  CU(h, cudaSetDevice(h->device));
+  const uint32_t n_bins = v_offset(K + 1);
+  TRY(dev_alloc(h, &h->d_bgcounts, (size_t)n_bins));
+  CU(h, cudaMemsetAsync(h->d_bgcounts, 0, n_bins * 8, h->stream));
+  const uint64_t n = h->stream_end - PENG_FRONT_PAD;
+  const unsigned block = 256;
+  const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(grid_for(n, block), (uint64_t)h->sm_count * 8));
+  k_bg_counts<<<grid, block, n_bins * 4, h->stream>>>(h->d_codes, h->d_valid, h->d_sstart, h->stream_end, K,
+                                                     (unsigned long long*)h->d_bgcounts, n_bins);
+  LAUNCH_CHECK(h);
+  h->K = K;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_background_finish(peng_handle_t h, int K, const float* alpha, int interpolate, int precision,
+                                           void* v_out) {
+  if (!h || !h->d_bgcounts || h->K != K || !alpha || !v_out) return fail(h, PENG_E_INVALID, "background_finish: bad call");
+  CU(h, cudaSetDevice(h->device));
+  const uint32_t n_bins = v_offset(K + 1);
+  std::vector<uint64_t> n(n_bins);
+  CU(h, cudaMemcpyAsync(n.data(), h->d_bgcounts, n_bins * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  if (precision == PENG_F32REF) peng_host::calculate_v<float>(n.data(), K, alpha, interpolate != 0, (float*)v_out);
+  else peng_host::calculate_v<double>(n.data(), K, alpha, interpolate != 0, (double*)v_out);
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_background_model(peng_handle_t h, int K, const float* alpha, int interpolate, int precision,
+                                          void* v_out, int64_t* kmer_counts_out) {
+  TRY(peng_cuda_background_counts(h, K));
+  TRY(peng_cuda_background_finish(h, K, alpha, interpolate, precision, v_out));
+  if (kmer_counts_out) {
+    const uint32_t n_bins = v_offset(K + 1);
+    CU(h, cudaMemcpyAsync(kmer_counts_out, h->d_bgcounts, n_bins * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+  }
+  return PENG_OK;
+}
+
+// =====================================================================================================
+// C ABI: tables
+// =====================================================================================================
+extern "C" int peng_cuda_stats(peng_handle_t h, int K, const float* v32, const double* v64, int k, int max_k) {
+  if (!h || !h->counts_final) return fail(h, PENG_E_INVALID, "stats: count table not final");
+  if (K < 0 || K > PENG_MAX_ORDER || k < 0 || k > K || max_k < k || max_k > K || max_k > h->W - 1)
+    return fail(h, PENG_E_INVALID, "stats: bad orders K=%d k=%d max_k=%d (W=%d)", K, k, max_k, h->W);
+  if (!v32 && !v64) return fail(h, PENG_E_INVALID, "stats: no background model given");
+  CU(h, cudaSetDevice(h->device));
+  const uint64_t n = h->n_patterns;
+  const uint32_t nv = v_offset(K + 1);
+  const int both = h->strand == PENG_STRAND_BOTH;
+  const unsigned block = 256;
+  free_tables(h);
+  if (v32) {
+    TRY(dev_alloc(h, &h->d_v32, (size_t)nv));
+    CU(h, cudaMemcpyAsync(h->d_v32, v32, nv * 4, cudaMemcpyHostToDevice, h->stream));
+    for (int o = 0; o <= max_k; o++) {
+      TRY(dev_alloc(h, &h->d_bg32[o], n));
+      k_bgprob<float><<<grid_for(n, block), block, v_offset(o + 1) * 4, h->stream>>>(h->d_v32, h->W, o, both, h->d_bg32[o], n);
+      LAUNCH_CHECK(h);
+    }
+    TRY(dev_alloc(h, &h->d_exp32, n)); TRY(dev_alloc(h, &h->d_z32, n)); TRY(dev_alloc(h, &h->d_logp32, n));
+    k_stats<float><<<grid_for(n, block), block, 0, h->stream>>>(h->d_counts, h->d_bg32[k], h->ltot, h->d_exp32, h->d_z32, h->d_logp32, n);
+    LAUNCH_CHECK(h);
+  }
+  if (v64) {
+    TRY(dev_alloc(h, &h->d_v64, (size_t)nv));
+    CU(h, cudaMemcpyAsync(h->d_v64, v64, nv * 8, cudaMemcpyHostToDevice, h->stream));
+    for (int o = 0; o <= max_k; o++) {
+      TRY(dev_alloc(h, &h->d_bg64[o], n));
+      k_bgprob<double><<<grid_for(n, block), block, v_offset(o + 1) * 8, h->stream>>>(h->d_v64, h->W, o, both, h->d_bg64[o], n);
+      LAUNCH_CHECK(h);
+    }
+    TRY(dev_alloc(h, &h->d_exp64, n)); TRY(dev_alloc(h, &h->d_z64, n)); TRY(dev_alloc(h, &h->d_logp64, n));
+    k_stats<double><<<grid_for(n, block), block, 0, h->stream>>>(h->d_counts, h->d_bg64[k], h->ltot, h->d_exp64, h->d_z64, h->d_logp64, n);
+    LAUNCH_CHECK(h);
+  }
+  CU(h, cudaStreamSynchronize(h->stream));  // v32 / v64 host buffers may go away
+  h->K = K;
+  h->k_used = k;
+  h->max_k = max_k;
+  h->stats_ready = true;
+  return PENG_OK;
+}
+
+static const void* table_ptr(peng_handle_t h, int table, int order, int precision) {
+  const bool f32 = precision == PENG_F32REF;
+  switch (table) {
+    case PENG_TABLE_BGPROB:
+      if (order < 0 || order > h->max_k) return nullptr;
+      return f32 ? (const void*)h->d_bg32[order] : (const void*)h->d_bg64[order];
+    case PENG_TABLE_EXPECTED: return f32 ? (const void*)h->d_exp32 : (const void*)h->d_exp64;
+    case PENG_TABLE_ZSCORE: return f32 ? (const void*)h->d_z32 : (const void*)h->d_z64;
+    case PENG_TABLE_LOGP: return f32 ? (const void*)h->d_logp32 : (const void*)h->d_logp64;
+  }
+  return nullptr;
+}
+
+extern "C" int peng_cuda_get_table(peng_handle_t h, int table, int order, int precision, void* out) {
+  if (!h || !h->stats_ready || !out) return fail(h, PENG_E_INVALID, "get_table: stats not computed");
+  const void* p = table_ptr(h, table, order, precision);
+  if (!p) return fail(h, PENG_E_INVALID, "get_table: table %d order %d precision %d not available", table, order, precision);
+  CU(h, cudaSetDevice(h->device));
+  const size_t es = precision == PENG_F32REF ? 4 : 8;
+  CU(h, cudaMemcpyAsync(out, p, h->n_patterns * es, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_select_base_patterns(peng_handle_t h, float z_threshold, uint64_t count_threshold,
+                                              int single_stranded, int filter_neighbors, uint64_t* out, uint64_t cap,
+                                              uint64_t* n_selected) {
+  if (!h || !h->stats_ready || !h->d_z32) return fail(h, PENG_E_INVALID, "select: float32 stats not computed");
+  CU(h, cudaSetDevice(h->device));
+  std::vector<float> z(h->n_patterns);
+  std::vector<uint64_t> counts(h->n_patterns);
+  CU(h, cudaMemcpyAsync(z.data(), h->d_z32, h->n_patterns * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaMemcpyAsync(counts.data(), h->d_counts, h->n_patterns * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  std::vector<uint64_t> sel = peng_host::select_base_patterns(z.data(), counts.data(), h->W, z_threshold, count_threshold,
+                                                              single_stranded != 0, filter_neighbors != 0);
+  if (n_selected) *n_selected = sel.size();
+  if (out) std::copy(sel.begin(), sel.begin() + std::min<uint64_t>(cap, sel.size()), out);
+  return PENG_OK;
+}
+
+// =====================================================================================================
+// C ABI: IUPAC
+// =====================================================================================================
+static int iupac_masks_to_device(peng_handle_t h, const uint64_t* iupac_ids, int n, uint64_t** d_masks, size_t extra_bytes,
+                                 unsigned char** extra) {
+  std::vector<uint64_t> masks(n);
+  for (int i = 0; i < n; i++) {
+    if (!peng_host::iupac_letter_mask(iupac_ids[i], h->W, &masks[i]))
+      return fail(h, PENG_E_INVALID, "iupac id %llu is not a valid length-%d pattern", (unsigned long long)iupac_ids[i], h->W);
+  }
+  const size_t mask_bytes = ((size_t)n * 8 + 255) & ~(size_t)255;
+  TRY(need_scratch(h, mask_bytes + extra_bytes));
+  *d_masks = (uint64_t*)h->d_scratch;
+  if (extra) *extra = (unsigned char*)h->d_scratch + mask_bytes;
+  CU(h, cudaMemcpyAsync(*d_masks, masks.data(), (size_t)n * 8, cudaMemcpyHostToDevice, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));  // masks is a local
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_iupac_count(peng_handle_t h, const uint64_t* iupac_ids, int n, uint64_t* counts_out) {
+  if (!h || !h->counts_final || !iupac_ids || !counts_out || n < 0) return fail(h, PENG_E_INVALID, "iupac_count: bad call");
+  if (n == 0) return PENG_OK;
+  CU(h, cudaSetDevice(h->device));
+  uint64_t* d_masks;
+  unsigned char* extra;
+  TRY(iupac_masks_to_device(h, iupac_ids, n, &d_masks, (size_t)n * 8, &extra));
+  unsigned long long* d_out = (unsigned long long*)extra;
+  if (h->strand == PENG_STRAND_BOTH)
+    k_iupac_any<float, true, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_out, nullptr, nullptr);
+  else
+    k_iupac_any<float, false, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_out, nullptr, nullptr);
+  LAUNCH_CHECK(h);
+  CU(h, cudaMemcpyAsync(counts_out, d_out, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_iupac_aggregate(peng_handle_t h, const uint64_t* iupac_ids, int n, int precision,
+                                         uint64_t* n_sites, void* bg_p, void* expected) {
+  if (!h || !h->stats_ready || !iupac_ids || n < 0 || !n_sites || !bg_p || !expected)
+    return fail(h, PENG_E_INVALID, "iupac_aggregate: bad call (stats must be computed first)");
+  if (n == 0) return PENG_OK;
+  CU(h, cudaSetDevice(h->device));
+  const bool both = h->strand == PENG_STRAND_BOTH;
+  const int k = h->k_used;
+  uint64_t* d_masks;
+  unsigned char* extra;
+  if (precision == PENG_F64) {
+    if (!h->d_bg64[k]) return fail(h, PENG_E_INVALID, "iupac_aggregate: FP64 tables not computed");
+    TRY(iupac_masks_to_device(h, iupac_ids, n, &d_masks, (size_t)n * 24, &extra));
+    unsigned long long* d_n = (unsigned long long*)extra;
+    double* d_b = (double*)(extra + (size_t)n * 8);
+    double* d_e = (double*)(extra + (size_t)n * 16);
+    if (both) k_iupac_any<double, true, true><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, h->d_bg64[k], h->d_exp64, d_n, d_b, d_e);
+    else k_iupac_any<double, false, true><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, h->d_bg64[k], h->d_exp64, d_n, d_b, d_e);
+    LAUNCH_CHECK(h);
+    CU(h, cudaMemcpyAsync(n_sites, d_n, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(bg_p, d_b, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaMemcpyAsync(expected, d_e, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return PENG_OK;
+  }
+  if (!h->d_bg32[k]) return fail(h, PENG_E_INVALID, "iupac_aggregate: float32 tables not computed");
+  const size_t bm_words = h->W >= 3 ? ((size_t)1 << (2 * h->W - 5)) : 1;
+  const size_t out_bytes = (size_t)n * 16;
+  const size_t bm_bytes = both ? (size_t)n * bm_words * 4 : 0;
+  TRY(iupac_masks_to_device(h, iupac_ids, n, &d_masks, out_bytes + 256 + bm_bytes, &extra));
+  unsigned long long* d_n = (unsigned long long*)extra;
+  float* d_b = (float*)(extra + (size_t)n * 8);
+  float* d_e = (float*)(extra + (size_t)n * 12);
+  uint32_t* d_bm = (uint32_t*)(extra + ((out_bytes + 255) & ~(size_t)255));
+  if (both) {
+    k_iupac_any<float, true, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_n, nullptr, nullptr);
+    LAUNCH_CHECK(h);
+    k_iupac_f32_both<<<n, IUPAC_TILE_WORDS, 0, h->stream>>>(d_masks, h->W, h->d_bg32[k], h->d_exp32, d_bm, d_b, d_e);
+    LAUNCH_CHECK(h);
+  } else {
+    k_iupac_any<float, false, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_n, nullptr, nullptr);
+    LAUNCH_CHECK(h);
+    k_iupac_f32_plus<<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_bg32[k], h->d_exp32, d_b, d_e);
+    LAUNCH_CHECK(h);
+  }
+  CU(h, cudaMemcpyAsync(n_sites, d_n, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaMemcpyAsync(bg_p, d_b, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaMemcpyAsync(expected, d_e, (size_t)n * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+// =====================================================================================================
+// C ABI: EM
+// =====================================================================================================
+template <int W>
+static void launch_em_acc(peng_handle_t h, dim3 grid, const double* bg, uint32_t tb, uint32_t te) {
+  k_em_accumulate_f64<W><<<grid, EM_WARPS * 32, 0, h->stream>>>(h->d_counts, bg, h->em.d_old, h->em.d_active, h->em.sat, tb,
+                                                               te, h->em.d_part);
+}
+
+extern "C" int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm_in, double saturation, double threshold,
+                                  int max_iterations, int bg_order, int part, int n_parts, void** acc_ptr) {
+  if (!h || !h->stats_ready || !pwm_in || n_pwms <= 0) return fail(h, PENG_E_INVALID, "em: bad call (stats must be computed first)");
+  if (bg_order < 0 || bg_order > h->max_k || !h->d_bg64[bg_order]) return fail(h, PENG_E_INVALID, "em: FP64 bgprob of order %d not available", bg_order);
+  if (n_parts < 1 || part < 0 || part >= n_parts) return fail(h, PENG_E_INVALID, "em: bad partition %d/%d", part, n_parts);
+  CU(h, cudaSetDevice(h->device));
+  free_em(h);
+  auto& E = h->em;
+  const int WA = h->W * 4;
+  E.n = n_pwms; E.max_it = max_iterations; E.order = bg_order; E.part = part; E.n_parts = n_parts;
+  E.sat = saturation; E.thr = threshold;
+  if (h->W >= 6) {
+    const uint32_t n_tiles = (uint32_t)(h->n_patterns >> 10);
+    const uint32_t my_tiles = std::max<uint32_t>(1, n_tiles / n_parts);
+    uint32_t nbx = (my_tiles + EM_WARPS - 1) / EM_WARPS;
+    const uint32_t want = std::max<uint32_t>(1, (uint32_t)(h->sm_count * 4 + n_pwms - 1) / n_pwms);
+    E.nbx = (int)std::max<uint32_t>(1, std::min(nbx, want));
+  } else {
+    E.nbx = 1;
+  }
+  TRY(dev_alloc(h, &E.d_old, (size_t)n_pwms * WA));
+  TRY(dev_alloc(h, &E.d_acc, (size_t)n_pwms * WA));
+  TRY(dev_alloc(h, &E.d_part, (size_t)n_pwms * WA * E.nbx));
+  TRY(dev_alloc(h, &E.d_change, (size_t)n_pwms));
+  TRY(dev_alloc(h, &E.d_iter, (size_t)n_pwms));
+  TRY(dev_alloc(h, &E.d_active, (size_t)n_pwms));
+  TRY(dev_alloc(h, &E.d_nactive, (size_t)1));
+  CU(h, cudaMemcpyAsync(E.d_old, pwm_in, (size_t)n_pwms * WA * 8, cudaMemcpyHostToDevice, h->stream));
+  CU(h, cudaMemsetAsync(E.d_acc, 0, (size_t)n_pwms * WA * 8, h->stream));
+  k_em_init<<<grid_for(n_pwms, 64), 64, 0, h->stream>>>(E.d_change, E.d_iter, E.d_active, n_pwms, h->W, threshold, max_iterations);
+  LAUNCH_CHECK(h);
+  CU(h, cudaStreamSynchronize(h->stream));
+  E.open = true;
+  if (acc_ptr) *acc_ptr = E.d_acc;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_em_accumulate(peng_handle_t h) {
+  if (!h || !h->em.open) return fail(h, PENG_E_INVALID, "em_accumulate: no EM session");
+  CU(h, cudaSetDevice(h->device));
+  auto& E = h->em;
+  const double* bg = h->d_bg64[E.order];
+  const int WA = h->W * 4;
+  if (h->W >= 6) {
+    const uint32_t n_tiles = (uint32_t)(h->n_patterns >> 10);
+    const uint32_t tb = (uint32_t)((uint64_t)n_tiles * E.part / E.n_parts);
+    const uint32_t te = (uint32_t)((uint64_t)n_tiles * (E.part + 1) / E.n_parts);
+    dim3 grid(E.nbx, E.n);
+    switch (h->W) {
+      case 6: launch_em_acc<6>(h, grid, bg, tb, te); break;
+      case 8: launch_em_acc<8>(h, grid, bg, tb, te); break;
+      case 10: launch_em_acc<10>(h, grid, bg, tb, te); break;
+      case 12: launch_em_acc<12>(h, grid, bg, tb, te); break;
+      case 14: launch_em_acc<14>(h, grid, bg, tb, te); break;
+      case 16: launch_em_acc<16>(h, grid, bg, tb, te); break;
+    }
+    LAUNCH_CHECK(h);
+  } else {
+    const uint32_t n = (uint32_t)h->n_patterns;
+    const uint32_t ib = (uint32_t)((uint64_t)n * E.part / E.n_parts), ie = (uint32_t)((uint64_t)n * (E.part + 1) / E.n_parts);
+    k_em_accumulate_small<<<E.n, 64, 0, h->stream>>>(h->d_counts, bg, E.d_old, E.d_active, h->W, E.sat, ib, ie, E.d_part);
+    LAUNCH_CHECK(h);
+  }
+  k_em_reduce<<<E.n, 64, 0, h->stream>>>(E.d_part, E.d_active, E.nbx, WA, E.d_acc);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_em_update(peng_handle_t h, int* n_active) {
+  if (!h || !h->em.open) return fail(h, PENG_E_INVALID, "em_update: no EM session");
+  CU(h, cudaSetDevice(h->device));
+  auto& E = h->em;
+  CU(h, cudaMemsetAsync(E.d_nactive, 0, 4, h->stream));
+  k_em_update_f64<<<E.n, 32, 0, h->stream>>>(E.d_acc, E.d_old, E.d_change, E.d_iter, E.d_active, h->W, E.thr, E.max_it, E.d_nactive);
+  LAUNCH_CHECK(h);
+  if (n_active) {
+    CU(h, cudaMemcpyAsync(n_active, E.d_nactive, 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+  }
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_em_end(peng_handle_t h, double* pwm_out, int* iterations_out) {
+  if (!h || !h->em.open) return fail(h, PENG_E_INVALID, "em_end: no EM session");
+  CU(h, cudaSetDevice(h->device));
+  auto& E = h->em;
+  const int WA = h->W * 4;
+  k_em_final_normalize<double><<<grid_for((uint64_t)E.n * h->W, 64), 64, 0, h->stream>>>(E.d_old, E.n, h->W);
+  LAUNCH_CHECK(h);
+  if (pwm_out) CU(h, cudaMemcpyAsync(pwm_out, E.d_old, (size_t)E.n * WA * 8, cudaMemcpyDeviceToHost, h->stream));
+  if (iterations_out) CU(h, cudaMemcpyAsync(iterations_out, E.d_iter, (size_t)E.n * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  free_em(h);
+  return PENG_OK;
+}
+
+static int em_f32ref(peng_handle_t h, int n_pwms, const float* pwm_in, float saturation, float threshold, int max_iterations,
+                     int bg_order, float* pwm_out, int* iterations_out) {
+  if (!h->d_bg32[bg_order]) return fail(h, PENG_E_INVALID, "em: float32 bgprob of order %d not available", bg_order);
+  const int W = h->W, WA = W * 4;
+  const uint64_t n = h->n_patterns;
+  // terms buffer: n floats per PWM; batch the PWMs if that would exceed ~8 GB
+  const int batch = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)n_pwms, (8ull << 30) / (n * 4)));
+  float *d_old = nullptr, *d_acc = nullptr, *d_terms = nullptr;
+  int *d_iter = nullptr, *d_active = nullptr, *d_nact = nullptr;
+  int rc = PENG_OK;
+  auto cleanup = [&]() { dev_free(&d_old); dev_free(&d_acc); dev_free(&d_terms); dev_free(&d_iter); dev_free(&d_active); dev_free(&d_nact); };
+#define EM_TRY(x) do { rc = (x); if (rc != PENG_OK) { cleanup(); return rc; } } while (0)
+#define EM_CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return fail(h, PENG_E_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); } } while (0)
+  EM_TRY(dev_alloc(h, &d_old, (size_t)batch * WA));
+  EM_TRY(dev_alloc(h, &d_acc, (size_t)batch * WA));
+  EM_TRY(dev_alloc(h, &d_terms, (size_t)batch * n));
+  EM_TRY(dev_alloc(h, &d_iter, (size_t)batch));
+  EM_TRY(dev_alloc(h, &d_active, (size_t)batch));
+  EM_TRY(dev_alloc(h, &d_nact, (size_t)1));
+  for (int first = 0; first < n_pwms; first += batch) {
+    const int nb = std::min(batch, n_pwms - first);
+    EM_CU(cudaMemcpyAsync(d_old, pwm_in + (size_t)first * WA, (size_t)nb * WA * 4, cudaMemcpyHostToDevice, h->stream));
+    k_em_init_f32<<<grid_for(nb, 64), 64, 0, h->stream>>>(d_iter, d_active, nb, W, threshold, max_iterations);
+    h->launches++;
+    for (int it = 0; it < max_iterations; it++) {
+      EM_CU(cudaMemsetAsync(d_nact, 0, 4, h->stream));
+      k_em_terms_f32<<<dim3(grid_for(n, 256), nb), 256, 0, h->stream>>>(h->d_counts, h->d_bg32[bg_order], d_old, d_active, W, saturation, n, d_terms);
+      k_em_chains_f32<<<dim3(W, nb), 128, 0, h->stream>>>(d_terms, d_active, W, n, d_acc);
+      k_em_update_f32<<<nb, 32, 0, h->stream>>>(d_acc, d_old, d_iter, d_active, W, threshold, max_iterations, d_nact);
+      h->launches += 3;
+      EM_CU(cudaGetLastError());
+      if ((it & 3) == 3) {  // look at the convergence flags every few iterations only
+        int na = 0;
+        EM_CU(cudaMemcpyAsync(&na, d_nact, 4, cudaMemcpyDeviceToHost, h->stream));
+        EM_CU(cudaStreamSynchronize(h->stream));
+        if (na == 0) break;
+      }
+    }
+    k_em_final_normalize<float><<<grid_for((uint64_t)nb * W, 64), 64, 0, h->stream>>>(d_old, nb, W);
+    h->launches++;
+    EM_CU(cudaMemcpyAsync(pwm_out + (size_t)first * WA, d_old, (size_t)nb * WA * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (iterations_out) EM_CU(cudaMemcpyAsync(iterations_out + first, d_iter, (size_t)nb * 4, cudaMemcpyDeviceToHost, h->stream));
+    EM_CU(cudaStreamSynchronize(h->stream));
+  }
+  cleanup();
+  return PENG_OK;
+#undef EM_TRY
+#undef EM_CU
+}
+
+extern "C" int peng_cuda_em(peng_handle_t h, int n_pwms, const void* pwm_in, int precision, double saturation, double threshold,
+                            int max_iterations, int bg_order, void* pwm_out, int* iterations_out) {
+  if (!h || !h->stats_ready || !pwm_in || !pwm_out || n_pwms < 0) return fail(h, PENG_E_INVALID, "em: bad call (stats must be computed first)");
+  if (n_pwms == 0) return PENG_OK;
+  if (bg_order < 0 || bg_order > h->max_k) return fail(h, PENG_E_INVALID, "em: bgprob order %d not available", bg_order);
+  CU(h, cudaSetDevice(h->device));
+  if (precision == PENG_F32REF)
+    return em_f32ref(h, n_pwms, (const float*)pwm_in, (float)saturation, (float)threshold, max_iterations, bg_order,
+                     (float*)pwm_out, iterations_out);
+  TRY(peng_cuda_em_begin(h, n_pwms, (const double*)pwm_in, saturation, threshold, max_iterations, bg_order, 0, 1, nullptr));
+  for (int it = 0; it < max_iterations; it++) {
+    TRY(peng_cuda_em_accumulate(h));
+    int na = -1;
+    TRY(peng_cuda_em_update(h, (it & 3) == 3 ? &na : nullptr));  // sync on the convergence flags every 4th iteration
+    if (na == 0) break;
+  }
+  return peng_cuda_em_end(h, (double*)pwm_out, iterations_out);
+}

@@ -1,0 +1,153 @@
+"""ctypes binding of tests/sim/sim_kernels.cpp — TEST INFRASTRUCTURE ONLY.
+
+The per-thread CUDA kernel bodies compiled as host code and driven thread by thread (see the header of
+sim_kernels.cpp).  Used by `-m "not gpu"` tests to check kernel logic without a GPU.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SRC = os.path.join(_HERE, "sim", "sim_kernels.cpp")
+_LIB = os.path.join(_HERE, "sim", "libpeng_sim.so")
+_CSRC = os.path.join(os.path.dirname(_HERE), "peng-motif_b200", "csrc")
+FRONT_PAD = 64
+
+
+def _build():
+    deps = [_SRC, os.path.join(_CSRC, "core_seq.cuh"), os.path.join(_CSRC, "core_tab.cuh")]
+    if os.path.exists(_LIB) and os.path.getmtime(_LIB) >= max(os.path.getmtime(d) for d in deps):
+        return
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-x", "c++",
+                           _SRC, "-o", _LIB])
+
+
+_build()
+lib = C.CDLL(_LIB)
+u8p, u32p, u64p = C.POINTER(C.c_uint8), C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)
+f32p, f64p = C.POINTER(C.c_float), C.POINTER(C.c_double)
+lib.sim_n_words32.restype = C.c_uint64
+lib.sim_n_words32.argtypes = [C.c_uint64, C.c_uint64]
+lib.sim_mark.restype = C.c_uint64
+lib.sim_iupac_list.restype = C.c_uint64
+lib.sim_revcomp.restype = C.c_uint32
+lib.sim_count_keys.restype = C.c_uint64
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+class Stream:
+    def __init__(self, n_seq, total):
+        self.n_seq, self.total = n_seq, total
+        self.nw = int(lib.sim_n_words32(C.c_uint64(n_seq), C.c_uint64(total)))
+        self.codes = np.zeros(self.nw * 2 + 8, np.uint32)
+        self.valid = np.zeros(self.nw + 8, np.uint32)
+        self.sstart = np.zeros(self.nw + 8, np.uint32)
+        self.kstart = np.zeros(self.nw + 8, np.uint32)
+        self.stream_end = FRONT_PAD + total + 2 * n_seq
+
+
+def pack(src, offsets, ascii=False):
+    n_seq = len(offsets) - 1
+    total = int(offsets[-1]) if n_seq else 0
+    st = Stream(n_seq, total)
+    src = np.ascontiguousarray(src, np.uint8)
+    if src.size == 0:
+        src = np.zeros(1, np.uint8)
+    lib.sim_pack(_p(src, u8p), _p(offsets, u64p), C.c_uint64(n_seq), int(ascii), _p(st.codes, u32p), _p(st.valid, u32p),
+                 _p(st.sstart, u32p))
+    return st
+
+
+def synth(n_seq, seq_len, seed, first_seq=0, motif=None, plant_fraction=0.0, n_fraction=0.0):
+    st = Stream(n_seq, n_seq * seq_len)
+    m = np.ascontiguousarray(motif if motif is not None else [], np.uint8)
+    lib.sim_synth(C.c_uint64(n_seq), C.c_uint32(seq_len), C.c_uint64(seed), C.c_uint64(first_seq),
+                  _p(m, u8p) if motif is not None else None, C.c_uint32(len(m)), C.c_double(plant_fraction),
+                  C.c_double(n_fraction), _p(st.codes, u32p), _p(st.valid, u32p), _p(st.sstart, u32p))
+    return st
+
+
+def unpack(st, offsets):
+    out = np.zeros(max(st.total, 1), np.uint8)
+    lib.sim_unpack(_p(st.codes, u32p), _p(st.valid, u32p), _p(offsets, u64p), C.c_uint64(st.n_seq), _p(out, u8p))
+    return out[: st.total]
+
+
+def count(st, W, both=True, wpc=1, mirror=True):
+    ltot = int(lib.sim_mark(_p(st.valid, u32p), C.c_uint64(st.nw), W, _p(st.kstart, u32p)))
+    hist = np.zeros(4 ** W, np.uint64)
+    lib.sim_count(_p(st.codes, u32p), _p(st.kstart, u32p), C.c_uint64(st.stream_end), W, int(both), C.c_uint32(wpc),
+                  _p(hist, u64p))
+    if both and mirror:
+        lib.sim_mirror(_p(hist, u64p), W)
+    return hist, ltot
+
+
+def count_keys(st, W, both=True, wpc=1):
+    """W in (12, 14, 16): the multiset of counted keys without allocating a 4^W table."""
+    ltot = int(lib.sim_mark(_p(st.valid, u32p), C.c_uint64(st.nw), W, _p(st.kstart, u32p)))
+    cap = st.stream_end
+    out = np.zeros(cap, np.uint32)
+    n = lib.sim_count_keys(_p(st.codes, u32p), _p(st.kstart, u32p), C.c_uint64(st.stream_end), W, int(both),
+                           C.c_uint32(wpc), _p(out, u32p), C.c_uint64(cap))
+    return out[:n], ltot
+
+
+def bg_counts(st, K=2):
+    out = np.zeros((4 ** (K + 2) - 4) // 3, np.uint64)
+    lib.sim_bg_counts(_p(st.codes, u32p), _p(st.valid, u32p), _p(st.sstart, u32p), C.c_uint64(st.stream_end), K,
+                      _p(out, u64p))
+    return out
+
+
+def bgprob(v, W, order, both, dt=np.float32):
+    out = np.zeros(4 ** W, dt)
+    v = np.ascontiguousarray(v, dt)
+    if dt == np.float32:
+        lib.sim_bgprob_f32(_p(v, f32p), W, order, int(both), _p(out, f32p))
+    else:
+        lib.sim_bgprob_f64(_p(v, f64p), W, order, int(both), _p(out, f64p))
+    return out
+
+
+def stats(counts, bg, ltot, W):
+    dt = bg.dtype
+    e, z, lp = (np.zeros(4 ** W, dt) for _ in range(3))
+    if dt == np.float32:
+        lib.sim_stats_f32(_p(counts, u64p), _p(bg, f32p), C.c_uint64(ltot), W, _p(e, f32p), _p(z, f32p), _p(lp, f32p))
+    else:
+        lib.sim_stats_f64(_p(counts, u64p), _p(bg, f64p), C.c_uint64(ltot), W, _p(e, f64p), _p(z, f64p), _p(lp, f64p))
+    return e, z, lp
+
+
+SETS = [0x1, 0x2, 0x4, 0x8, 0x6, 0x9, 0x5, 0xA, 0x3, 0xC, 0xF]
+
+
+def iupac_mask(iid, W):
+    m = 0
+    for p in range(W):
+        m |= SETS[iid % 11] << (4 * p)
+        iid //= 11
+    return m
+
+
+def iupac_list(iid, W, mode):
+    mask = iupac_mask(int(iid), W)
+    n = 1
+    for p in range(W):
+        n *= bin((mask >> (4 * p)) & 15).count("1")
+    out = np.zeros(n, np.uint32)
+    k = lib.sim_iupac_list(C.c_uint64(mask), W, mode, _p(out, u32p))
+    return out[:k]
+
+
+def em_acc_f32(pwm, W, counts, bg, s=1e4):
+    pwm = np.ascontiguousarray(pwm, np.float32)
+    acc = np.zeros((W, 4), np.float32)
+    lib.sim_em_acc_f32(_p(pwm, f32p), W, _p(counts, u64p), _p(bg, f32p), C.c_float(s), _p(acc, f32p))
+    return acc

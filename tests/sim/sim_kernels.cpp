@@ -1,0 +1,188 @@
+// sim_kernels.cpp — TEST INFRASTRUCTURE ONLY (never shipped, never loaded by the product).
+//
+// Compiles the per-thread kernel bodies of peng-motif_b200/csrc/core_seq.cuh and core_tab.cuh as plain
+// host C++ and drives them "thread by thread" in a loop, reproducing the launch geometry of the
+// __global__ wrappers in peng_cuda.cu.  This lets the kernel LOGIC (stream layout, k-mer start marking,
+// exact non-overlap counting incl. warm-up / slow resolve, background counts, table formulas, IUPAC
+// enumeration orders, EM chain order) be checked against the oracle on machines without a GPU.
+// It is a debugging aid for `pytest -m "not gpu"`; parity proper is the `-m gpu` suite through the C ABI.
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#define PENG_HD inline
+#include "../../peng-motif_b200/csrc/core_seq.cuh"
+#include "../../peng-motif_b200/csrc/core_tab.cuh"
+
+using namespace peng;
+
+struct EmitHost {
+  uint64_t* hist;
+  void operator()(uint32_t key) const { hist[key]++; }
+};
+
+template <int W>
+static void count_W(const uint32_t* codes, const uint32_t* kstart, uint64_t stream_end, int both, uint32_t wpc, uint64_t* hist) {
+  const uint64_t n_words16 = (stream_end - PENG_FRONT_PAD + 15) / 16 + 1;
+  const uint64_t n_chunks = (n_words16 + wpc - 1) / wpc;
+  for (uint64_t c = 0; c < n_chunks; c++) {
+    const uint64_t e0 = PENG_FRONT_PAD + c * 16ull * wpc;
+    if (both) count_chunk<W, true>(codes, kstart, e0, wpc, EmitHost{hist});
+    else count_chunk<W, false>(codes, kstart, e0, wpc, EmitHost{hist});
+  }
+}
+
+struct EmitKeys {
+  std::vector<uint32_t>* keys;
+  void operator()(uint32_t key) const { keys->push_back(key); }
+};
+template <int W>
+static void count_keys_W(const uint32_t* codes, const uint32_t* kstart, uint64_t stream_end, int both, uint32_t wpc,
+                         std::vector<uint32_t>* keys) {
+  const uint64_t n_words16 = (stream_end - PENG_FRONT_PAD + 15) / 16 + 1;
+  const uint64_t n_chunks = (n_words16 + wpc - 1) / wpc;
+  for (uint64_t c = 0; c < n_chunks; c++) {
+    const uint64_t e0 = PENG_FRONT_PAD + c * 16ull * wpc;
+    if (both) count_chunk<W, true>(codes, kstart, e0, wpc, EmitKeys{keys});
+    else count_chunk<W, false>(codes, kstart, e0, wpc, EmitKeys{keys});
+  }
+}
+
+extern "C" {
+
+// large W without a 4^W table: the counted keys in emission order (out may be NULL to size)
+uint64_t sim_count_keys(const uint32_t* codes, const uint32_t* kstart, uint64_t stream_end, int W, int both, uint32_t wpc,
+                        uint32_t* out, uint64_t cap) {
+  std::vector<uint32_t> keys;
+  switch (W) {
+    case 12: count_keys_W<12>(codes, kstart, stream_end, both, wpc, &keys); break;
+    case 14: count_keys_W<14>(codes, kstart, stream_end, both, wpc, &keys); break;
+    case 16: count_keys_W<16>(codes, kstart, stream_end, both, wpc, &keys); break;
+    default: return 0;
+  }
+  for (uint64_t i = 0; i < keys.size() && i < cap; i++) out[i] = keys[i];
+  return keys.size();
+}
+
+uint64_t sim_n_words32(uint64_t n_seq, uint64_t total) {
+  return (PENG_FRONT_PAD + total + 2 * n_seq + PENG_TAIL_PAD + 31) / 32 + 8;
+}
+
+// arrays must hold n_words32*2+8 (codes) / n_words32+8 (valid, sstart) words, zero-initialised by the caller
+void sim_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, int ascii, uint32_t* codes, uint32_t* valid,
+              uint32_t* sstart) {
+  const uint64_t nw = sim_n_words32(n_seq, n_seq ? offsets[n_seq] : 0);
+  for (uint64_t t = 0; t < nw; t++) {
+    if (ascii) pack_word<true>(t, src, offsets, n_seq, codes, valid, sstart);
+    else pack_word<false>(t, src, offsets, n_seq, codes, valid, sstart);
+  }
+}
+
+void sim_synth(uint64_t n_seq, uint32_t seq_len, uint64_t seed, uint64_t first_seq, const uint8_t* motif,
+               uint32_t motif_len, double plant_fraction, double n_fraction, uint32_t* codes, uint32_t* valid,
+               uint32_t* sstart) {
+  SynthParams P;
+  P.n_seq = n_seq; P.first_seq = first_seq; P.seed = seed; P.seq_len = seq_len; P.motif_len = motif ? motif_len : 0;
+  P.plant_threshold = (uint32_t)(plant_fraction * 16777216.0);
+  P.n_threshold = (uint32_t)(n_fraction * 16777216.0);
+  P.motif_bits = 0; P.degenerate_pos = 0xFFFFFFFFu;
+  for (uint32_t i = 0; i < P.motif_len; i++) {
+    uint32_t c = motif[i];
+    if (c > 3) { P.degenerate_pos = i; c = 1; }
+    P.motif_bits |= (uint64_t)c << (2 * i);
+  }
+  const uint64_t nw = sim_n_words32(n_seq, n_seq * (uint64_t)seq_len);
+  for (uint64_t t = 0; t < nw; t++) synth_word(t, P, codes, valid, sstart);
+}
+
+void sim_unpack(const uint32_t* codes, const uint32_t* valid, const uint64_t* offsets, uint64_t n_seq, uint8_t* out) {
+  for (uint64_t s = 0; s < n_seq; s++)
+    for (uint64_t i = 0; i < offsets[s + 1] - offsets[s]; i++)
+      out[offsets[s] + i] = unpack_code(codes, valid, PENG_FRONT_PAD + offsets[s] + 2 * s + i);
+}
+
+uint64_t sim_mark(const uint32_t* valid, uint64_t n_words32, int W, uint32_t* kstart) {
+  uint64_t ltot = 0;
+  for (uint64_t t = 0; t < n_words32; t++) ltot += (uint64_t)mark_kstart_word(t, n_words32, valid, W, kstart);
+  return ltot;
+}
+
+// hist: 4^W uint64, zeroed by the caller; unmirrored (canonical bins only for BOTH)
+void sim_count(const uint32_t* codes, const uint32_t* kstart, uint64_t stream_end, int W, int both, uint32_t wpc, uint64_t* hist) {
+  switch (W) {
+    case 2: count_W<2>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 4: count_W<4>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 6: count_W<6>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 8: count_W<8>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 10: count_W<10>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 12: count_W<12>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 14: count_W<14>(codes, kstart, stream_end, both, wpc, hist); break;
+    case 16: count_W<16>(codes, kstart, stream_end, both, wpc, hist); break;
+  }
+}
+
+void sim_mirror(uint64_t* counts, int W) {
+  const uint64_t n = 1ull << (2 * W);
+  for (uint64_t i = 0; i < n; i++) {
+    const uint32_t rc = revcomp_id((uint32_t)i, W);
+    if ((uint32_t)i > rc) counts[i] = counts[rc];
+  }
+}
+
+uint32_t sim_revcomp(uint32_t id, int W) { return revcomp_id(id, W); }
+
+void sim_bg_counts(const uint32_t* codes, const uint32_t* valid, const uint32_t* sstart, uint64_t stream_end, int K,
+                   uint64_t* out) {
+  for (uint64_t q = PENG_FRONT_PAD; q < stream_end; q++) {
+    const bool sep = q + 2 >= stream_end || bit_at(sstart, q + 1) || bit_at(sstart, q + 2);
+    if (sep) continue;
+    uint32_t ids[8];
+    const uint32_t m = background_ids(codes, valid, sstart, q, K, ids);
+    for (int k = 0; k <= K; k++)
+      if ((m >> k) & 1u) out[v_offset(k) + ids[k]]++;
+  }
+}
+
+void sim_bgprob_f32(const float* v, int W, int order, int both, float* out) {
+  for (uint64_t i = 0; i < (1ull << (2 * W)); i++) out[i] = bg_prob_entry<float>(v, W, order, (uint32_t)i, both);
+}
+void sim_bgprob_f64(const double* v, int W, int order, int both, double* out) {
+  for (uint64_t i = 0; i < (1ull << (2 * W)); i++) out[i] = bg_prob_entry<double>(v, W, order, (uint32_t)i, both);
+}
+void sim_stats_f32(const uint64_t* counts, const float* bg, uint64_t ltot, int W, float* e, float* z, float* lp) {
+  for (uint64_t i = 0; i < (1ull << (2 * W)); i++) stats_of<float>(counts[i], bg[i], ltot, e + i, z + i, lp + i);
+}
+void sim_stats_f64(const uint64_t* counts, const double* bg, uint64_t ltot, int W, double* e, double* z, double* lp) {
+  for (uint64_t i = 0; i < (1ull << (2 * W)); i++) stats_of<double>(counts[i], bg[i], ltot, e + i, z + i, lp + i);
+}
+
+// IUPAC: expansion list in the reference order (PLUS: dfs; BOTH: ascending distinct canonical via the
+// representative rule + a sort done by the caller)
+uint64_t sim_iupac_list(uint64_t mask, int W, int mode /*0 dfs, 1 any, 2 representatives only*/, uint32_t* out) {
+  const IupacShape s = iupac_shape(mask, W);
+  const uint64_t N = 1ull << s.total_bits;
+  uint64_t n = 0;
+  for (uint64_t t = 0; t < N; t++) {
+    if (mode == 0) out[n++] = iupac_expansion_dfs(mask, W, s, t);
+    else {
+      const uint32_t e = iupac_expansion_any(mask, W, s, t);
+      if (mode == 1 || iupac_is_representative(mask, W, e)) out[n++] = e;
+    }
+  }
+  return n;
+}
+
+// EM float32: terms + chains exactly as k_em_terms_f32 / k_em_chains_f32 order them
+void sim_em_acc_f32(const float* pwm, int W, const uint64_t* counts, const float* bg, float s, float* acc) {
+  const uint64_t n = 1ull << (2 * W);
+  std::vector<float> terms(n);
+  for (uint64_t id = 0; id < n; id++) terms[id] = em_term_f32(pwm, W, (uint32_t)id, counts[id], bg[id], s);
+  for (int p = 0; p < W; p++)
+    for (uint32_t a = 0; a < 4; a++) {
+      float sum = 0.f;
+      for (uint32_t i = 0; i < (uint32_t)(n >> 2); i++) sum += terms[em_chain_id(p, a, i)];
+      acc[p * 4 + a] = sum;
+    }
+}
+}

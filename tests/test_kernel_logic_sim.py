@@ -1,0 +1,118 @@
+"""Kernel LOGIC on the CPU: the per-thread bodies of the CUDA kernels (peng-motif_b200/csrc/core_*.cuh) are
+compiled as host code by tests/sim and driven thread by thread with the launch geometry of the real
+kernels, then compared with the oracle.  This is a GPU-less debugging aid; the parity tests proper are the
+`-m gpu` suite, which goes through the C ABI on a B200."""
+import os
+from collections import Counter
+
+import numpy as np
+import pytest
+
+import _cases
+import _oracle as O
+import _sim as S
+
+DATA = os.path.join(_cases.GOLDEN, "data")
+
+
+@pytest.mark.parametrize("case", [c for c in _cases.golden_cases() if c["exit"] == 0], ids=lambda c: c["tag"])
+def test_count_golden_cases(case):
+    path = _cases.write_fasta(case["fasta"])
+    codes, offs, _, _ = O.read_fasta(path)
+    os.unlink(path)
+    W, both = case["W"], case["strand"] == "BOTH"
+    st = S.pack(codes, offs)
+    assert np.array_equal(S.unpack(st, offs), codes)
+    for wpc in (1, 4, 16):  # thread chunk geometry must not matter
+        hist, ltot = S.count(st, W, both, wpc)
+        assert ltot == case["ltot"]
+        assert np.array_equal(hist, _cases.case_counts(case))
+    _, n = O.f32.background_model(codes, offs)
+    assert np.array_equal(S.bg_counts(st, 2).astype(np.int64), n)
+
+
+def test_pack_ascii_equals_codes():
+    text = open(os.path.join(DATA, "MafK_100seqs.fasta")).read()
+    codes, offs, _, _ = O.read_fasta(os.path.join(DATA, "MafK_100seqs.fasta"))
+    letters = np.frombuffer("".join(l for l in text.split("\n") if not l.startswith(">")).encode(), np.uint8)
+    a, b = S.pack(letters, offs, ascii=True), S.pack(codes, offs)
+    assert np.array_equal(a.codes, b.codes) and np.array_equal(a.valid, b.valid) and np.array_equal(a.sstart, b.sstart)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_count_dirty_random(seed):
+    seqs = _cases.dirty_sequences(seed)
+    codes, offs = O.encode(seqs)
+    st = S.pack(codes, offs)
+    rng = np.random.RandomState(seed)
+    for W in (2, 4, 6, 8, 10):
+        for both in (True, False):
+            hist, ltot = S.count(st, W, both, int(rng.choice([1, 2, 16])))
+            ref, lt = O.count(codes, offs, W, both)
+            assert lt == ltot and np.array_equal(hist, ref), (W, both)
+    for W in (12, 14, 16):  # no 4^W table on the test box: compare the multiset of counted keys
+        for both in (True, False):
+            keys, ltot = S.count_keys(st, W, both, int(rng.choice([1, 2, 16])))
+            ref, lt = _cases.py_count_sparse(seqs, W, both)
+            assert lt == ltot and Counter(keys.tolist()) == ref, (W, both)
+
+
+@pytest.mark.parametrize("W,both", [(10, True), (10, False), (12, True)])
+def test_count_mafk(W, both):
+    codes, offs, _, _ = O.read_fasta(os.path.join(DATA, "MafK.fasta"))
+    st = S.pack(codes, offs)
+    hist, ltot = S.count(st, W, both, 16)
+    ref, lt = O.count(codes, offs, W, both)
+    assert lt == ltot and np.array_equal(hist, ref)
+
+
+def test_synthetic_generator_properties():
+    motif = [3, 2, 1, 3, 2, 0, 4, 3, 1, 0, 2, 1, 0]  # TGCTGASTCAGCA
+    st = S.synth(2000, 200, 1234, 0, motif, 0.3, 0.0)
+    offs = (np.arange(2001) * 200).astype(np.uint64)
+    codes = S.unpack(st, offs)
+    assert codes.min() >= 1 and codes.max() <= 4
+    frac = np.bincount(codes, minlength=5)[1:] / codes.size
+    assert np.all(np.abs(frac - 0.25) < 0.01)
+    s = "".join("NACGT"[c] for c in codes)
+    planted = sum(("TGCTGACTCAGCA" in s[i * 200:(i + 1) * 200]) or ("TGCTGAGTCAGCA" in s[i * 200:(i + 1) * 200])
+                  for i in range(2000))  # the motif is its own reverse complement up to S
+    assert 0.25 * 2000 < planted < 0.35 * 2000
+    # shards of one global set are reproducible: sequences [500, 700) generated alone equal the slice
+    part = S.synth(200, 200, 1234, 500, motif, 0.3, 0.0)
+    assert np.array_equal(S.unpack(part, offs[:201]), codes[500 * 200:700 * 200])
+    dirty = S.unpack(S.synth(500, 100, 7, 0, None, 0.0, 0.02), (np.arange(501) * 100).astype(np.uint64))
+    assert 0.01 < (dirty == 0).mean() < 0.03
+
+
+@pytest.mark.parametrize("name,W,both", [("cfg1_W8_BOTH", 8, True), ("cfg1_W8_PLUS", 8, False)])
+def test_tables(name, W, both):
+    g = np.load(os.path.join(_cases.GOLDEN, name + ".npz"))
+    codes, offs, _, _ = O.read_fasta(os.path.join(DATA, "MafK_100seqs.fasta"))
+    counts, ltot = O.count(codes, offs, W, both)
+    for dt, suf in [(np.float32, "f32"), (np.float64, "f64")]:
+        for k in range(3):
+            assert np.array_equal(S.bgprob(g["v_" + suf], W, k, both, dt), g[f"bgprob_k{k}_{suf}"])
+        e, z, lp = S.stats(counts, g[f"bgprob_k2_{suf}"], ltot, W)
+        assert np.array_equal(e, g["expected_" + suf]) and np.array_equal(z, g["z_" + suf])
+        assert np.array_equal(lp, g["logp_" + suf])  # same libm on the host; on the GPU log() may differ by 1 ulp
+
+
+@pytest.mark.parametrize("W", [4, 6, 8])
+def test_iupac_enumeration(W):
+    for iid in _cases.random_iupac_ids(W, W, 120):
+        assert np.array_equal(S.iupac_list(iid, W, 0).astype(np.uint64), O.iupac_expand(iid, W, False))
+        reps = S.iupac_list(iid, W, 2)
+        canon = np.array(sorted(min(int(x), O.revcomp(int(x), W)) for x in reps), np.uint64)
+        assert np.array_equal(canon, np.unique(O.iupac_expand(iid, W, True)))
+
+
+def test_em_chain_order_is_reference_order():
+    g = np.load(os.path.join(_cases.GOLDEN, "cfg1_W8_BOTH.npz"))
+    codes, offs, _, _ = O.read_fasta(os.path.join(DATA, "MafK_100seqs.fasta"))
+    counts, _ = O.count(codes, offs, 8, True)
+    bg = g["bgprob_k2_f32"]
+    for pwm in g["adv_pwm_f32"]:
+        acc = S.em_acc_f32(pwm, 8, counts, bg)
+        s = ((acc[:, 0] + acc[:, 1]) + acc[:, 2]) + acc[:, 3]
+        assert np.array_equal((acc / s[:, None]).astype(np.float32), O.f32.em_iteration(pwm, 8, counts, bg))
