@@ -1,0 +1,405 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the PEnG-motif hot path on B200.
+
+Metric (BASELINE.json): k-mer count Gbases/s.  A "step" = one pass of BasePattern::count_patterns over one
+resident synthetic sequence set: k-mer start marking + exact non-overlap counting into the 4^W table + fold
+(+ mirror copy / + NCCL all-reduce of the histogram for N > 1).
+
+  workload at N = 1 : BASELINE configs[2] — 1 M sequences x 200 bp, planted MafK-like motif, W = 10, both strands
+  workload at N > 1 : the same shard shape PER GPU (weak scaling): disjoint shards of one global synthetic set,
+                      per-GPU histograms + ltot combined with one NCCL all_reduce
+  --workload cfg4   : BASELINE configs[3] — 50 M x 500 bp (25 Gbp) split over the N GPUs (strong scaling)
+
+  value     whole-job Gbases/s with the packed set resident in HBM (device-timed, max over ranks)
+  e2e       the same metric through the C-ABI calls a reference binding makes, from HOST buffers:
+            peng_cuda_ingest_codes (pinned 1 B/base codes -> H2D -> pack) + peng_cuda_count + peng_cuda_get_counts
+  roofline  the dominant kernel (k_count_global): algorithmic bytes / its CUDA-event duration vs measured HBM peak
+  cpu_baseline  the reference's count_patterns (oracle/_ref, else the oracle port) on the host cores
+  extra     EM PWM-iterations/s (17 PWMs, FP64 and float32-faithful), stats-pass time, ingest rate
+
+`--impl reference` times the reference's own CPU implementation on the same config / metric.
+"""
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MOTIF = "TGCTGASTCAGCA"  # the reference's own MafK result, S = C|G
+ALGO_BYTES_PER_BASE = 0.375  # 2-bit codes + 1-bit k-mer-start mask
+
+
+def workload_shape(name, n_gpus):
+    if name == "cfg3":
+        return dict(n_seq_per_gpu=1_000_000, seq_len=200, W=10, strand="BOTH", scaling="weak",
+                    label="configs[2]: synthetic 1M x 200 bp, planted MafK-like motif, W=10, both strands (per GPU)")
+    if name == "cfg4":
+        return dict(n_seq_per_gpu=50_000_000 // n_gpus, seq_len=500, W=10, strand="BOTH", scaling="strong",
+                    label="configs[3]: synthetic 50M x 500 bp (25 Gbp) sharded over the GPUs, W=10, both strands")
+    if name == "cfg5":
+        return dict(n_seq_per_gpu=10_000_000 // n_gpus, seq_len=300, W=14, strand="PLUS", scaling="strong",
+                    label="configs[4]: synthetic 10M x 300 bp, --strand PLUS, W=14")
+    if name == "small":
+        return dict(n_seq_per_gpu=20_000, seq_len=200, W=10, strand="BOTH", scaling="weak", label="smoke-size set")
+    raise SystemExit(f"unknown workload {name}")
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks sampling (B200_PROFILING.md "clocks DURING the timed region")
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                          str(self.index), "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                                         text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=3)
+            except Exception:
+                self.proc.kill()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU arms
+# ---------------------------------------------------------------------------------------------------------
+def write_fasta_from_codes(codes, offs, path):
+    import numpy as np
+
+    lut = np.frombuffer(b"NACGT", np.uint8)
+    letters = lut[codes]
+    with open(path, "wb") as f:
+        for s in range(len(offs) - 1):
+            f.write(b">s%d\n" % s)
+            f.write(letters[int(offs[s]):int(offs[s + 1])].tobytes())
+            f.write(b"\n")
+
+
+class CpuReference:
+    """Times the reference's count_patterns on the host: oracle/_ref/ref_dump (the unmodified reference, timed
+    around a second call of its own count_patterns) if it was built, else the oracle port."""
+
+    def __init__(self, codes, offs, W, strand):
+        self.codes, self.offs, self.W, self.strand = codes, offs, W, strand
+        self.cores = os.cpu_count() or 1
+        self.ref_dump = os.path.join(ROOT, "oracle", "_ref", "ref_dump")
+        self.dir = None
+        if os.path.exists(self.ref_dump):
+            self.dir = tempfile.mkdtemp(prefix="peng_ref_")
+            write_fasta_from_codes(codes, offs, os.path.join(self.dir, "sample.fa"))
+
+    def run(self):
+        """-> (seconds of count_patterns, kind, cores)"""
+        if self.dir:
+            env = dict(os.environ, OMP_NUM_THREADS=str(self.cores))
+            r = subprocess.run([self.ref_dump, os.path.join(self.dir, "sample.fa"), str(self.W), self.strand, self.dir,
+                                "--counts-only"], capture_output=True, text=True, env=env)
+            if r.returncode == 0:
+                meta = dict(l.split() for l in open(os.path.join(self.dir, "meta.txt")))
+                return float(meta["t_count_patterns_s"]), "reference", self.cores
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import _oracle as O  # cpu_baseline leg: the one place bench.py executes oracle/
+
+        t = time.perf_counter()
+        O.count(self.codes, self.offs, self.W, self.strand == "BOTH")
+        return time.perf_counter() - t, "port", 1
+
+    def close(self):
+        if self.dir:
+            shutil.rmtree(self.dir, ignore_errors=True)
+
+
+def sample_codes_host(shape, n_sample, seed=1234):
+    """The first n_sample sequences of the synthetic workload, generated WITHOUT a GPU for the reference arm
+    when none is present (kernel bodies compiled for the host, tests/sim) — else exported from the device."""
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _sim as S
+
+    motif = ["ACGTS".index(c) for c in MOTIF]
+    st = S.synth(n_sample, shape["seq_len"], seed, 0, motif, 0.3, 0.0)
+    offs = (np.arange(n_sample + 1, dtype=np.uint64) * np.uint64(shape["seq_len"]))
+    return S.unpack(st, offs), offs
+
+
+def run_reference_arm(args, shape):
+    import numpy as np
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n_sample = min(shape["n_seq_per_gpu"], args.ref_sample)
+    codes = offs = None
+    try:
+        import _pkg
+
+        pkg = _pkg.load()
+        if pkg.load_library().peng_cuda_device_count() > 0:
+            g = pkg.PengCuda(0)
+            g.ingest_synthetic(n_sample, shape["seq_len"], 1234, 0, MOTIF, 0.3, 0.0)
+            codes, offs = g.export_codes()
+            g.close()
+    except Exception:
+        codes = None
+    if codes is None:
+        codes, offs = sample_codes_host(shape, n_sample)
+    bases = int(offs[-1])
+    times, kind, cores = [], None, 1
+    ref = CpuReference(codes, offs, shape["W"], shape["strand"])
+    for i in range(args.warmup + args.steps):
+        t, kind, cores = ref.run()
+        if i >= args.warmup:
+            times.append(t)
+    ref.close()
+    tot = sum(times)
+    value = bases * len(times) / tot / 1e9
+    sample = (f"first {n_sample} sequences x {shape['seq_len']} bp of the workload ({bases / 1e6:.0f} Mbases) per step; "
+              f"count_patterns is serial in the reference (src/peng.cpp:60-61, no pragma on src/base_pattern.cpp:331-441)")
+    line = {"impl": "reference", "metric": "kmer_count_gbases_per_s", "value": value, "unit": "Gbases/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True,
+            "scaling": shape["scaling"], "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": shape["label"], "W": shape["W"], "strand": shape["strand"]},
+            "cpu_baseline": {"value": value, "unit": "Gbases/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg3")
+    ap.add_argument("--ref-sample", type=int, default=250_000, help="sequences per CPU-reference step")
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    shape = workload_shape(args.workload, args.gpus)
+    if args.impl == "reference":
+        return run_reference_arm(args, shape)
+
+    import numpy as np
+    import torch
+
+    import _pkg
+
+    pkg = _pkg.load()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    W, strand = shape["W"], pkg.STRAND_BOTH if shape["strand"] == "BOTH" else pkg.STRAND_PLUS
+    n_local, L = shape["n_seq_per_gpu"], shape["seq_len"]
+    first_seq = rank * n_local
+    bases_local = n_local * L
+    g = pkg.PengCuda(local)
+    stream = torch.cuda.current_stream()
+    g.set_stream(stream.cuda_stream)  # the library launches on torch's current stream: torch events see its kernels
+    g.ingest_synthetic(n_local, L, 1234, first_seq, MOTIF, 0.3, 0.0)
+    g.enable_timing(True)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def step_resident():
+        if world > 1:
+            g.count_local(W, strand)
+            buf = torch.as_tensor(g.count_buffer(), device="cuda")
+            dist.all_reduce(buf)  # per-GPU histograms + ltot -> global table (NCCL over NVLink)
+            return g.count_finish()
+        return g.count(W, strand)
+
+    # ---- resident throughput ("value") ----
+    for _ in range(args.warmup):
+        flush.zero_()
+        step_resident()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kern_ms = []
+    launches0 = g.launches
+    t_wall = time.perf_counter()
+    for a, b in ev:
+        flush.zero_()  # L2 flush between timed iterations (packed set = 75 MB < L2)
+        a.record()
+        step_resident()
+        b.record()
+        kern_ms.append(g.get_timing(1))
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    launches = g.launches - launches0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t.item())
+    total_bases = bases_local * world
+    value = total_bases * args.steps / (dev_ms * 1e-3) / 1e9
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end from host buffers through the C ABI ("e2e") ----
+    codes_np, offs = g.export_codes()
+    codes_pin = torch.from_numpy(codes_np).pin_memory()
+    counts_host = torch.empty(4 ** W, dtype=torch.int64).pin_memory()
+    h2d = codes_pin.numel() + offs.nbytes
+    d2h = counts_host.numel() * 8
+
+    def step_e2e():
+        g.ingest_codes(codes_pin.numpy(), offs)  # H2D of 1 B/base codes + device packing
+        if world > 1:
+            g.count_local(W, strand)
+            buf = torch.as_tensor(g.count_buffer(), device="cuda")
+            dist.all_reduce(buf)
+            g.count_finish()
+        else:
+            g.count(W, strand)
+        g._ck(g.lib.peng_cuda_get_counts(g.h, counts_host.data_ptr()))  # D2H of the 4^W table
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = total_bases * e2e_steps / float(t.item()) / 1e9
+
+    if rank != 0:
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel ----
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json, burst copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    k_ms = sorted(kern_ms)[len(kern_ms) // 2]
+    algo_bytes = ALGO_BYTES_PER_BASE * bases_local + 4.0 * 4 ** W
+    achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel": f"k_count_global<{W},{shape['strand']}>" if W >= 10 else "k_count_smem",
+                "kernel_ms": k_ms, "algorithmic_bytes": algo_bytes, "peak_source": peak_src,
+                "note": "one L2 atomic per counted k-mer: atomic-throughput-bound far below the HBM roof (DESIGN.md)"}
+    tr = os.path.join(ROOT, "profiles", "count_kernel_traffic.json")
+    if os.path.exists(tr):
+        try:
+            roofline["traffic"] = json.load(open(tr)).get(args.workload)
+        except Exception:
+            pass
+
+    # ---- CPU baseline on a bounded sample of the same workload ----
+    n_sample = min(n_local, args.ref_sample)
+    s_codes, s_offs = codes_np[: n_sample * L], offs[: n_sample + 1]
+    ref = CpuReference(s_codes, s_offs, W, shape["strand"])
+    cpu_s, kind, cores = ref.run()
+    ref.close()
+    cpu_baseline = {"value": n_sample * L / cpu_s / 1e9, "unit": "Gbases/s", "cores": cores, "kind": kind,
+                    "sample": f"first {n_sample} sequences x {L} bp of the workload ({n_sample * L / 1e6:.0f} Mbases), "
+                              f"count_patterns only; serial in the reference, so effective parallelism is 1"}
+
+    # ---- extras: the other two BASELINE metrics on the same table ----
+    extra = {}
+    if not args.no_extras:
+        try:
+            t0 = time.perf_counter()
+            v32 = g.background_model(2, precision=pkg.F32REF)
+            v64 = g.background_model(2, precision=pkg.F64)
+            g.synchronize()
+            extra["background_model_ms"] = 1e3 * (time.perf_counter() - t0) / 2
+            t0 = time.perf_counter()
+            g.stats(v32, v64, K=2)
+            extra["stats_pass_ms_both_arms"] = 1e3 * (time.perf_counter() - t0)
+            rng = np.random.RandomState(0)
+            pw = rng.dirichlet(np.ones(4), (17, W)) * 0.3
+            for m in range(17):
+                for p in range(W):
+                    pw[m, p, "ACGT".index("TGCTGACTCAGCA"[(m + p) % 13])] += 0.7
+            pw /= pw.sum(2, keepdims=True)
+            for prec, name in ((pkg.F64, "em_fp64"), (pkg.F32REF, "em_f32_reference_faithful")):
+                g.em(pw, prec, 1e4, 0.0, 2)  # warm-up
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                _, its = g.em(pw, prec, 1e4, 0.0, 10)  # threshold 0: every PWM runs all 10 iterations
+                dt = time.perf_counter() - t0
+                extra[name] = {"pwm_iterations_per_s": float(its.sum()) / dt, "pwms": 17, "iterations": 10, "W": W,
+                               "seconds": dt, "bytes_per_bin_per_iteration": 16}
+        except Exception as e:  # extras never invalidate the headline line
+            extra["error"] = repr(e)
+
+    line = {"metric": "kmer_count_gbases_per_s", "value": value, "unit": "Gbases/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": shape["scaling"],
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": shape["label"], "W": W, "strand": shape["strand"], "n_seq_per_gpu": n_local, "seq_len": L,
+                       "seed": 1234, "motif": MOTIF, "plant_fraction": 0.3,
+                       "l2": "256 MiB buffer written between timed iterations (inputs smaller than L2)",
+                       "parallelism": f"sequence-sharded x{world}" + (", 1 NCCL all_reduce of 4^W u64 + ltot per step" if world > 1 else "")},
+            "e2e": {"value": e2e_value, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "steps": e2e_steps, "path": "peng_cuda_ingest_codes (pinned host codes) -> peng_cuda_count -> peng_cuda_get_counts"},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "wall_s_timed_region": t_wall, "extra": extra}
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -61,6 +61,12 @@ uint64_t peng_cuda_launch_count(peng_handle_t h);
 int peng_cuda_set_stream(peng_handle_t h, void* cuda_stream);
 int peng_cuda_synchronize(peng_handle_t h);
 
+/* Device-side timing of the phases of the last peng_cuda_count[_local] call (CUDA events on the handle's stream,
+ * recorded only while enabled): phase 0 = k-mer start marking, 1 = the counting kernel(s), 2 = fold (+ mirror).
+ * This is how bench.py measures the dominant kernel's duration for the roofline without a profiler. */
+int peng_cuda_enable_timing(peng_handle_t h, int on);
+int peng_cuda_get_timing(peng_handle_t h, int phase, float* milliseconds);
+
 /* ---- (a) ingest: SequenceSet::readFASTA + Sequence (src/shared/SequenceSet.cpp:285-447,
  *      src/shared/Sequence.cpp:4-35) -> packed 2-bit device buffer + validity mask ------------------- */
 /* Read a FASTA file with the reference's line rules and pack it on the device. */
@@ -107,6 +113,9 @@ int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts /* 4^W */); /* BasePa
 int peng_cuda_count_local(peng_handle_t h, int W, int strand);
 int peng_cuda_count_buffer(peng_handle_t h, void** device_ptr, uint64_t* n_u64);
 int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot);
+/* Sparse read-back for tables that are too large to copy (W >= 14): the bins at `ids`, and the sum of all bins. */
+int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uint64_t n, uint64_t* out);
+int peng_cuda_counts_total(peng_handle_t h, uint64_t* total);
 /* Load an externally produced table instead of counting (tests; reference binding that keeps its own
  * count_patterns). counts must already be mirrored for BOTH. */
 int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const uint64_t* counts, uint64_t ltot);

@@ -90,13 +90,26 @@ int main(int argc, char** argv) {
   BasePattern* bp = new BasePattern(W, strand, k, max_k, seqs, bg);
   double t_bp = now_s() - t0;
   size_t n = bp->getNumberPatterns();
+  // the hot loop alone: run count_patterns once more on the finished object (private -> -fno-access-control);
+  // it adds to pattern_counter, so take a copy of the table first and put it back afterwards
+  double t_count = 0;
+  {
+    std::vector<size_t> keep(bp->getPatternCounter(), bp->getPatternCounter() + n);
+    size_t keep_ltot = bp->ltot;
+    t0 = now_s();
+    if (strand == Strand::BOTH_STRANDS) bp->count_patterns(seqs); else bp->count_patterns_single_strand(seqs);
+    t_count = now_s() - t0;
+    std::copy(keep.begin(), keep.end(), bp->getPatternCounter());
+    bp->ltot = keep_ltot;
+  }
 
   {
     FILE* f = fopen((out + "/meta.txt").c_str(), "w");
     fprintf(f, "n_seq %zu\nmin_len %u\nmax_len %u\nW %d\nstrand %s\nltot %zu\nn_patterns %zu\nk %d\nmax_k %d\nreal_bytes %zu\n",
             seqs->getN(), seqs->getMinL(), seqs->getMaxL(), W, argv[3], bp->getLtot(), n, k, bp->max_k,
             sizeof(REAL));
-    fprintf(f, "t_read_fasta_s %.6f\nt_background_model_s %.6f\nt_base_pattern_s %.6f\n", t_read, t_bg, t_bp);
+    fprintf(f, "t_read_fasta_s %.6f\nt_background_model_s %.6f\nt_base_pattern_s %.6f\nt_count_patterns_s %.6f\n", t_read,
+            t_bg, t_bp, t_count);
     fclose(f);
   }
   {

@@ -53,6 +53,8 @@ _PROTOS = {
     "peng_cuda_launch_count": (C.c_uint64, [H]),
     "peng_cuda_set_stream": (C.c_int, [H, C.c_void_p]),
     "peng_cuda_synchronize": (C.c_int, [H]),
+    "peng_cuda_enable_timing": (C.c_int, [H, C.c_int]),
+    "peng_cuda_get_timing": (C.c_int, [H, C.c_int, f32p]),
     "peng_cuda_ingest_fasta": (C.c_int, [H, C.c_char_p, u64p, u64p, u32p, u32p]),
     "peng_cuda_ingest_codes": (C.c_int, [H, C.c_void_p, u64p, C.c_uint64]),
     "peng_cuda_ingest_codes_device": (C.c_int, [H, C.c_void_p, u64p, C.c_uint64]),
@@ -68,6 +70,8 @@ _PROTOS = {
     "peng_cuda_count_local": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_count_buffer": (C.c_int, [H, C.POINTER(C.c_void_p), u64p]),
     "peng_cuda_count_finish": (C.c_int, [H, u64p]),
+    "peng_cuda_gather_counts": (C.c_int, [H, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "peng_cuda_counts_total": (C.c_int, [H, u64p]),
     "peng_cuda_set_counts": (C.c_int, [H, C.c_int, C.c_int, C.c_void_p, C.c_uint64]),
     "peng_cuda_stats": (C.c_int, [H, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "peng_cuda_get_table": (C.c_int, [H, C.c_int, C.c_int, C.c_int, C.c_void_p]),
@@ -206,6 +210,14 @@ class PengCuda:
     def synchronize(self):
         self._ck(self.lib.peng_cuda_synchronize(self.h))
 
+    def enable_timing(self, on=True):
+        self._ck(self.lib.peng_cuda_enable_timing(self.h, int(on)))
+
+    def get_timing(self, phase):
+        ms = C.c_float()
+        self._ck(self.lib.peng_cuda_get_timing(self.h, phase, C.byref(ms)))
+        return ms.value
+
     # ---- (a) ingest ----
     def ingest_fasta(self, path):
         n, tot, mn, mx = C.c_uint64(), C.c_uint64(), C.c_uint32(), C.c_uint32()
@@ -269,7 +281,7 @@ class PengCuda:
     def count_buffer(self):
         p, n = C.c_void_p(), C.c_uint64()
         self._ck(self.lib.peng_cuda_count_buffer(self.h, C.byref(p), C.byref(n)))
-        return DeviceArray(p.value, n.value, "<u8")
+        return DeviceArray(p.value, n.value, "<i8")  # uint64 counts viewed as int64 (torch / NCCL sum is the same)
 
     def count_finish(self):
         ltot = C.c_uint64()
@@ -280,6 +292,17 @@ class PengCuda:
         out = np.zeros(4 ** self.W, np.uint64)
         self._ck(self.lib.peng_cuda_get_counts(self.h, _ptr(out)))
         return out
+
+    def gather_counts(self, ids):
+        ids = np.ascontiguousarray(ids, np.uint64)
+        out = np.zeros(len(ids), np.uint64)
+        self._ck(self.lib.peng_cuda_gather_counts(self.h, _ptr(ids), len(ids), _ptr(out)))
+        return out
+
+    def counts_total(self):
+        t = C.c_uint64()
+        self._ck(self.lib.peng_cuda_counts_total(self.h, C.byref(t)))
+        return t.value
 
     def set_counts(self, W, strand, counts, ltot):
         counts = np.ascontiguousarray(counts, np.uint64)

@@ -62,6 +62,10 @@ struct peng_cuda_ctx {
   double *d_exp64 = nullptr, *d_z64 = nullptr, *d_logp64 = nullptr;
   bool stats_ready = false;
 
+  // ---- phase timing (bench) ----
+  bool timing = false;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
   // ---- scratch ----
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
@@ -299,6 +303,19 @@ __global__ void k_mirror(uint64_t* __restrict__ counts, int W, uint64_t n) {
     const uint32_t rc = revcomp_id((uint32_t)i, W);
     if ((uint32_t)i > rc) counts[i] = counts[rc];
   }
+}
+
+__global__ void k_gather_u64(const uint64_t* __restrict__ table, const uint64_t* __restrict__ ids, uint64_t n,
+                             uint64_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = table[ids[i]];
+}
+
+__global__ void k_sum_u64(const uint64_t* __restrict__ table, uint64_t n, unsigned long long* __restrict__ total) {
+  unsigned long long s = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) s += table[i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0 && s) atomicAdd(total, s);
 }
 
 // =====================================================================================================
@@ -841,6 +858,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   free_tables(h);
   free_em(h);
   if (h->d_scratch) cudaFree(h->d_scratch);
+  for (int i = 0; i < 4; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -853,6 +871,23 @@ extern "C" int peng_cuda_set_stream(peng_handle_t h, void* s) {
   h->stream = s ? (cudaStream_t)s : h->own_stream;
   return PENG_OK;
 }
+extern "C" int peng_cuda_enable_timing(peng_handle_t h, int on) {
+  if (!h) return PENG_E_INVALID;
+  CU(h, cudaSetDevice(h->device));
+  if (on && !h->ev[0])
+    for (int i = 0; i < 4; i++) CU(h, cudaEventCreate(&h->ev[i]));
+  h->timing = on != 0;
+  return PENG_OK;
+}
+extern "C" int peng_cuda_get_timing(peng_handle_t h, int phase, float* ms) {
+  if (!h || !h->ev[0] || phase < 0 || phase > 2 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
+  CU(h, cudaSetDevice(h->device));
+  CU(h, cudaEventSynchronize(h->ev[3]));
+  CU(h, cudaEventElapsedTime(ms, h->ev[phase], h->ev[phase + 1]));
+  return PENG_OK;
+}
+#define MARK(h, i) do { if ((h)->timing) CU(h, cudaEventRecord((h)->ev[i], (h)->stream)); } while (0)
+
 extern "C" int peng_cuda_synchronize(peng_handle_t h) {
   if (!h) return PENG_E_INVALID;
   CU(h, cudaSetDevice(h->device));
@@ -1077,9 +1112,11 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   h->stats_ready = false;
   CU(h, cudaMemsetAsync(h->d_hist32, 0, n * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
+  MARK(h, 0);
   k_mark_kstart<<<grid_for(h->n_words32, 256), 256, 0, h->stream>>>(h->d_valid, h->d_kstart, h->n_words32, W,
                                                                    (unsigned long long*)(h->d_counts + n));
   LAUNCH_CHECK(h);
+  MARK(h, 1);
   const bool both = strand == PENG_STRAND_BOTH;
   int rc = PENG_OK;
   switch (W) {
@@ -1093,8 +1130,10 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
     case 16: rc = launch_count_W<16>(h, both); break;
   }
   TRY(rc);
+  MARK(h, 2);
   k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
   LAUNCH_CHECK(h);
+  MARK(h, 3);
   return PENG_OK;
 }
 
@@ -1130,6 +1169,35 @@ extern "C" int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts) {
   if (!h || !h->d_counts || !h->counts_final) return fail(h, PENG_E_INVALID, "get_counts: count table not final");
   CU(h, cudaSetDevice(h->device));
   CU(h, cudaMemcpyAsync(counts, h->d_counts, h->n_patterns * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uint64_t n, uint64_t* out) {
+  if (!h || !h->d_counts || !h->counts_final || (n && (!ids || !out))) return fail(h, PENG_E_INVALID, "gather_counts: count table not final");
+  if (n == 0) return PENG_OK;
+  for (uint64_t i = 0; i < n; i++)
+    if (ids[i] >= h->n_patterns) return fail(h, PENG_E_INVALID, "gather_counts: id out of range");
+  CU(h, cudaSetDevice(h->device));
+  TRY(need_scratch(h, n * 16));
+  uint64_t* d_ids = (uint64_t*)h->d_scratch;
+  uint64_t* d_out = d_ids + n;
+  CU(h, cudaMemcpyAsync(d_ids, ids, n * 8, cudaMemcpyHostToDevice, h->stream));
+  k_gather_u64<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_counts, d_ids, n, d_out);
+  LAUNCH_CHECK(h);
+  CU(h, cudaMemcpyAsync(out, d_out, n * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_counts_total(peng_handle_t h, uint64_t* total) {
+  if (!h || !h->d_counts || !h->counts_final || !total) return fail(h, PENG_E_INVALID, "counts_total: count table not final");
+  CU(h, cudaSetDevice(h->device));
+  TRY(need_scratch(h, 8));
+  CU(h, cudaMemsetAsync(h->d_scratch, 0, 8, h->stream));
+  k_sum_u64<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_counts, h->n_patterns, (unsigned long long*)h->d_scratch);
+  LAUNCH_CHECK(h);
+  CU(h, cudaMemcpyAsync(total, h->d_scratch, 8, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
   return PENG_OK;
 }
