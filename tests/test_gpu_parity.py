@@ -322,7 +322,9 @@ def test_em_sharded_protocol_single_gpu(gpu, pkg):
         for part in range(n_parts):
             acc = gpu.em_begin(state, max_iterations=1, part=part, n_parts=n_parts)
             gpu.em_accumulate()
+            gpu.synchronize()  # the library runs on its own stream; torch reads on the default one
             t = torch.as_tensor(acc, device="cuda").clone()
+            torch.cuda.synchronize()
             acc_sum = t if acc_sum is None else acc_sum + t
             gpu.em_end()
         rows = acc_sum.cpu().numpy().reshape(-1, 8, 4)
@@ -364,6 +366,7 @@ def test_full_size_properties(gpu, pkg):
         first, n = pkg.shard_synthetic(n_seq, r, 4)
         gpu.ingest_synthetic(n, L, seed=1234, first_seq=first, motif="TGCTGASTCAGCA", plant_fraction=0.3)
         gpu.count_local(W, pkg.STRAND_BOTH)
+        gpu.synchronize()
         import torch
 
         buf = torch.as_tensor(gpu.count_buffer(), device="cuda").cpu().numpy().view(np.uint64)
