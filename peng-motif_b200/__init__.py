@@ -68,6 +68,8 @@ _PROTOS = {
     "peng_cuda_count": (C.c_int, [H, C.c_int, C.c_int, u64p]),
     "peng_cuda_get_counts": (C.c_int, [H, C.c_void_p]),
     "peng_cuda_count_local": (C.c_int, [H, C.c_int, C.c_int]),
+    "peng_cuda_set_count_path": (C.c_int, [H, C.c_int]),
+    "peng_cuda_last_count_path": (C.c_int, [H]),
     "peng_cuda_count_buffer": (C.c_int, [H, C.POINTER(C.c_void_p), u64p]),
     "peng_cuda_count_finish": (C.c_int, [H, u64p]),
     "peng_cuda_gather_counts": (C.c_int, [H, C.c_void_p, C.c_uint64, C.c_void_p]),
@@ -273,6 +275,14 @@ class PengCuda:
         self._ck(self.lib.peng_cuda_count(self.h, W, strand, C.byref(ltot)))
         self.W, self.strand = W, strand
         return ltot.value
+
+    def set_count_path(self, path):
+        """0 auto, 1 L2-atomic kernel, 2 partition path (W = 10)."""
+        self._ck(self.lib.peng_cuda_set_count_path(self.h, int(path)))
+
+    @property
+    def last_count_path(self):
+        return int(self.lib.peng_cuda_last_count_path(self.h))
 
     def count_local(self, W, strand=STRAND_BOTH):
         self._ck(self.lib.peng_cuda_count_local(self.h, W, strand))

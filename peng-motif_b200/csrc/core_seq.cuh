@@ -237,9 +237,8 @@ PENG_HD bool segment_is_shifted(const uint32_t* valid, uint64_t a, int W) {
   }
 }
 
-// One thread: kstart word t (positions [32t, 32t+32)); returns popcount (contribution to ltot).
-PENG_HD int mark_kstart_word(uint64_t t, uint64_t n_words, const uint32_t* __restrict__ valid, int W,
-                             uint32_t* __restrict__ kstart) {
+// kstart bits of positions [32t, 32t+32)
+PENG_HD uint32_t kstart_word(uint64_t t, uint64_t n_words, const uint32_t* __restrict__ valid, int W) {
   const uint32_t v0 = ldg(valid + t);
   const uint32_t v1 = t + 1 < n_words ? ldg(valid + t + 1) : 0u;
   uint32_t win = v0;
@@ -255,8 +254,93 @@ PENG_HD int mark_kstart_word(uint64_t t, uint64_t n_words, const uint32_t* __res
       if (segment_is_shifted(valid, t * 32 + b, W)) win &= ~(1u << b);
     }
   }
+  return win;
+}
+
+// One thread: kstart word t (positions [32t, 32t+32)); returns popcount (contribution to ltot).
+PENG_HD int mark_kstart_word(uint64_t t, uint64_t n_words, const uint32_t* __restrict__ valid, int W,
+                             uint32_t* __restrict__ kstart) {
+  const uint32_t win = kstart_word(t, n_words, valid, W);
   kstart[t] = win;
   return popc32(win);
+}
+
+// ---- (b1') which looked-at W-mers MIGHT be suppressed? -------------------------------------------------
+// The partition path (peng_cuda.cu: k_count_part) counts a looked-at W-mer unconditionally when no W-mer with
+// the same key starts at any of the W-1 positions in front of it ("fast"), and hands everything else to the
+// exact ring logic of count_chunk ("slow").  Two W-mers at distance d < W have the same key iff
+//   (ff) they are equal:                   x[s+i] == x[s-d+i] for i = 0..W-1  (the stretch has period d), or
+//   (rc, BOTH only) one is the reverse complement of the other: the stretch [s-d, s+W-1] is a reverse-
+//       complement palindrome; its length W+d must be even (d = 2,4,..,W-2) and its centre lies between
+//       m = s + (W-d)/2 - 1 and m+1.  Every such palindrome contains the one of half length W/2+1 around the
+//       same centre, so  PAL(m) := x[m+1+i] == 3 - x[m-i] for i = 0..W/2  flags s = m-W/2+2 .. m (superset).
+// Letters of invalid positions read as 0: such W-mers are not looked at anyway and a superset is all the
+// fast path needs.  Everything is bit-parallel on the 2-bit code words (16 positions per word, bit 2k of a
+// result word = position k).
+PENG_HD uint32_t compress_even16(uint32_t w) {  // bits 0,2,4,..,30 -> bits 0..15
+  w &= 0x55555555u;
+  w = (w | (w >> 1)) & 0x33333333u;
+  w = (w | (w >> 2)) & 0x0F0F0F0Fu;
+  w = (w | (w >> 4)) & 0x00FF00FFu;
+  w = (w | (w >> 8)) & 0x0000FFFFu;
+  return w;
+}
+
+// cw[0..4] = code words 2u-1 .. 2u+3 (positions 32u-16 .. 32u+63); result bit b = candidate flag of the
+// W-mer starting at 32u + b.
+template <int W, bool BOTH>
+PENG_HD uint32_t conflict_candidates(const uint32_t* cw) {
+  static_assert(W >= 4 && W <= 10 && (W % 2) == 0, "window arithmetic below assumes W-1 <= 9 lags inside one word");
+  uint32_t c1 = 0, c2 = 0;  // spaced candidate flags of words 1 and 2 (positions 32u .. 32u+31)
+  // ---- (ff) ----
+#pragma unroll
+  for (int d = 1; d < W; d++) {
+    uint32_t e[3];  // e[j] bit 2k: x[p] == x[p-d] at p = 16(j+1) + k
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const uint32_t t = cw[j + 1] ^ funnel_r(cw[j], cw[j + 1], 32u - 2u * d);
+      e[j] = ~(t | (t >> 1)) & 0x55555555u;
+    }
+    // run of W consecutive equalities starting at p (p in words 1 and 2) by doubling: r2, r4, r8 = runs of
+    // 2, 4, 8; the third word only has to be right for its low positions (zeros shifted in at its top).
+    uint32_t r2[3], r4[3], r8[2];
+    r2[0] = e[0] & funnel_r(e[0], e[1], 2u);
+    r2[1] = e[1] & funnel_r(e[1], e[2], 2u);
+    r2[2] = e[2] & (e[2] >> 2);
+    r4[0] = r2[0] & funnel_r(r2[0], r2[1], 4u);
+    r4[1] = r2[1] & funnel_r(r2[1], r2[2], 4u);
+    r4[2] = r2[2] & (r2[2] >> 4);
+    r8[0] = r4[0] & funnel_r(r4[0], r4[1], 8u);
+    r8[1] = r4[1] & funnel_r(r4[1], r4[2], 8u);
+    if (W == 4) { c1 |= r4[0]; c2 |= r4[1]; }
+    if (W == 6) { c1 |= r4[0] & funnel_r(r2[0], r2[1], 8u); c2 |= r4[1] & funnel_r(r2[1], r2[2], 8u); }
+    if (W == 8) { c1 |= r8[0]; c2 |= r8[1]; }
+    if (W == 10) { c1 |= r8[0] & funnel_r(r2[0], r2[1], 16u); c2 |= r8[1] & funnel_r(r2[1], r2[2], 16u); }
+  }
+  // ---- (rc) ----
+  if (BOTH) {
+    constexpr int H = W / 2 + 1;
+    uint32_t p[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};  // PAL(m) at m = 16(j+1) + k
+#pragma unroll
+    for (int i = 0; i < H; i++) {
+#pragma unroll
+      for (int j = 0; j < 3; j++) {
+        const uint32_t a = funnel_r(cw[j + 1], cw[j + 2], 2u * (1 + i));            // x[m+1+i]
+        const uint32_t b = i ? funnel_r(cw[j], cw[j + 1], 32u - 2u * i) : cw[j + 1];  // x[m-i]
+        const uint32_t t = a ^ b;
+        p[j] &= t & (t >> 1);  // both bits set <=> complementary letters
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 3; j++) p[j] &= 0x55555555u;
+    // s is flagged by the centres m = s .. s + W/2 - 2
+#pragma unroll
+    for (int i = 0; i <= W / 2 - 2; i++) {
+      c1 |= i ? funnel_r(p[0], p[1], 2u * i) : p[0];
+      c2 |= i ? funnel_r(p[1], p[2], 2u * i) : p[1];
+    }
+  }
+  return compress_even16(c1) | (compress_even16(c2) << 16);
 }
 
 // ---- (b2) exact greedy non-overlapping counting ---------------------------------------------------------
@@ -351,7 +435,8 @@ PENG_HD void count_resolve_slow(const uint32_t* __restrict__ codes, const uint32
   }
 }
 
-// The per-thread body.  Emits one histogram increment per counted occurrence through `emit(key)`.
+// The per-thread body.  Emits one histogram increment per counted occurrence through `emit(key, i)`,
+// i = index of the occurrence's END position relative to e0.
 // e0 must be a multiple of 16 and >= PENG_FRONT_PAD (so the 48-position warm-up stays inside the buffer).
 template <int W, bool BOTH, typename Emit>
 PENG_HD void count_chunk(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ kstart, uint64_t e0,
@@ -406,7 +491,7 @@ PENG_HD void count_chunk(const uint32_t* __restrict__ codes, const uint32_t* __r
     const key_t key = st.push((cw >> (2 * I)) & 3u);             \
     const bool counted = ((ksw >> I) & 1u) && !st.template window_has<I>(key); \
     st.slot[I] = counted ? key : State::EMPTY;                   \
-    if (counted) emit((uint32_t)key);                            \
+    if (counted) emit((uint32_t)key, w * 16u + I);               \
   }
     PENG_MAIN_STEP(0) PENG_MAIN_STEP(1) PENG_MAIN_STEP(2) PENG_MAIN_STEP(3)
     PENG_MAIN_STEP(4) PENG_MAIN_STEP(5) PENG_MAIN_STEP(6) PENG_MAIN_STEP(7)

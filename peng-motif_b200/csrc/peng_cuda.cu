@@ -62,9 +62,19 @@ struct peng_cuda_ctx {
   double *d_exp64 = nullptr, *d_z64 = nullptr, *d_logp64 = nullptr;
   bool stats_ready = false;
 
+  // ---- partition path (W = 10) ----
+  int count_path = 0;              // 0 auto, 1 L2-atomic path, 2 partition path
+  bool used_partition = false;     // what the last count ran
+  uint16_t* d_part_buckets = nullptr;
+  size_t part_bucket_elems = 0;
+  uint32_t* d_part_fill = nullptr;
+  uint2* d_slow_list = nullptr;
+  size_t slow_list_elems = 0;
+  unsigned int* d_slow_count = nullptr;
+
   // ---- phase timing (bench) ----
   bool timing = false;
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   // ---- scratch ----
   void* d_scratch = nullptr;
@@ -198,7 +208,7 @@ __global__ void k_mark_kstart(const uint32_t* __restrict__ valid, uint32_t* __re
 
 struct EmitGlobal {
   uint32_t* hist;
-  __device__ __forceinline__ void operator()(uint32_t key) const { atomicAdd(hist + key, 1u); }  // RED.ADD, no return
+  __device__ __forceinline__ void operator()(uint32_t key, uint32_t) const { atomicAdd(hist + key, 1u); }  // RED.ADD, no return
 };
 
 // Generic path (any W): one L2 atomic per counted occurrence into the 4^W uint32 table (L2-resident up to
@@ -219,7 +229,7 @@ __global__ void __launch_bounds__(128) k_count_global(const uint32_t* __restrict
 // and merges it into the global table once at the end.
 struct EmitShared {
   uint32_t* sh;
-  __device__ __forceinline__ void operator()(uint32_t key) const { atomicAdd(sh + key, 1u); }
+  __device__ __forceinline__ void operator()(uint32_t key, uint32_t) const { atomicAdd(sh + key, 1u); }
 };
 
 template <int W, bool BOTH>
@@ -251,7 +261,7 @@ __global__ void __launch_bounds__(256) k_count_smem(const uint32_t* __restrict__
 struct EmitShared16 {
   uint32_t* sh;
   uint32_t* hist;
-  __device__ __forceinline__ void operator()(uint32_t key) const {
+  __device__ __forceinline__ void operator()(uint32_t key, uint32_t) const {
     const uint32_t sft = (key & 1u) * 16u;
     const uint32_t old = atomicAdd(sh + (key >> 1), 1u << sft);
     if (((old >> sft) & 0xFFFFu) == 0x7FFFu) {
@@ -280,6 +290,232 @@ __global__ void __launch_bounds__(512) k_count_smem16(const uint32_t* __restrict
     const uint32_t v = sh[i];
     if (v & 0xFFFFu) atomicAdd(hist + 2 * i, v & 0xFFFFu);
     if (v >> 16) atomicAdd(hist + 2 * i + 1, v >> 16);
+  }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// Partition path (W = 10): beyond the L2-atomic ceiling.
+//
+// One global atomic per counted W-mer caps k_count_global at the ~190 G/s random-RED rate of the L2 (DESIGN.md
+// §3.1); shared-memory atomics are ~12x faster but 4^10 bins do not fit one SM.  So the table is cut into
+// PART_NCLASS contiguous id ranges ("classes", 28 340 bins = 111 KB of uint32 each) and counting runs in stages:
+//   P  k_count_part : streams the packed sequence once; per 32 positions it derives the k-mer start mask, the
+//                     bit-parallel conflict candidates (core_seq.cuh: conflict_candidates) and pushes the FORWARD
+//                     id of every "fast" W-mer (looked at, no equal key within W-1 positions: counted for sure)
+//                     into the CTA's shared-memory queue of its class; whole 128-entry blocks of 16-bit keys go to
+//                     the CTA's private region of the class bucket in global memory (no global atomics).
+//                     Units holding a "slow" W-mer are appended to a list.
+//   S  k_count_slow : exact ring logic of count_chunk for the listed units only (tandem repeats, palindromes).
+//   H  k_hist_part  : 4 CTAs per class build the class's bins in shared memory with non-returning shared atomics
+//                     and merge them into the uint32 table.
+// k_fold_canon then adds the forward-id bins of a reverse-complement pair into the canonical bin (BOTH).
+// Skewed input cannot break exactness: a class queue that would overflow in a round is rolled back and the
+// round's keys of that class go straight to the global table; a full bucket region does the same per block.
+#define PART_NCLASS 37
+#define PART_NT 512
+#define PART_CAP 1024u
+#define PART_SLOWCAP 512u
+#define PART_CPC 4
+#define PART_HT 1024
+
+__host__ __device__ __forceinline__ uint32_t part_class_start(uint32_t c) {  // first id of class c (4^10 ids)
+  return (uint32_t)((((uint64_t)c << 20) + PART_NCLASS - 1) / PART_NCLASS);
+}
+
+__device__ __forceinline__ void part_push(uint32_t key, uint32_t pred, uint32_t cnt_s, uint32_t q_s) {
+  uint32_t c = (key * PART_NCLASS) >> 20;
+  c = pred ? c : PART_NCLASS;  // W-mers that are not pushed go to a scratch queue: no branch around the atomic
+  uint32_t slot;
+  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(cnt_s + c * 4u) : "memory");
+  const uint32_t addr = q_s + (c * PART_CAP + slot) * 2u;
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %0, %1;\n\t@p st.shared.u16 [%2], %3;\n\t}"
+               :: "r"(slot), "r"(PART_CAP), "r"(addr), "h"((uint16_t)key) : "memory");
+}
+
+template <int W, bool BOTH>
+__global__ void __launch_bounds__(PART_NT, 2) k_count_part(
+    const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
+    uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, uint16_t* __restrict__ buckets, uint32_t region_cap,
+    uint32_t* __restrict__ fill_out, uint32_t* __restrict__ hist, unsigned long long* __restrict__ ltot,
+    uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count) {
+  static_assert(W == 10, "class geometry is laid out for 4^10 ids");
+  constexpr uint32_t KEYMASK = (1u << (2 * W)) - 1u;
+  extern __shared__ uint16_t q[];  // [PART_NCLASS + 1][PART_CAP]
+  __shared__ uint32_t cnt[PART_NCLASS + 1], prev[PART_NCLASS], fill[PART_NCLASS], ovf[PART_NCLASS];
+  __shared__ uint32_t any_ovf, n_slow, slow_base;
+  __shared__ uint2 slow_q[PART_SLOWCAP];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x < PART_NCLASS) { cnt[threadIdx.x] = 0; prev[threadIdx.x] = 0; fill[threadIdx.x] = 0; ovf[threadIdx.x] = 0; }
+  if (threadIdx.x == 0) { cnt[PART_NCLASS] = 0; any_ovf = 0; n_slow = 0; }
+  __syncthreads();
+  const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(cnt), q_s = (uint32_t)__cvta_generic_to_shared(q);
+  const uint64_t n_units = unit_end - unit_begin;
+  const uint64_t n_rounds = (n_units + PART_NT - 1) / PART_NT;
+  uint32_t my_ltot = 0;
+  for (uint64_t r = blockIdx.x; r < n_rounds; r += gridDim.x) {
+    const uint64_t u = unit_begin + r * PART_NT + threadIdx.x;
+    uint32_t fast = 0, w1 = 0, w2 = 0, w3 = 0;
+    if (u < unit_end) {
+      const uint32_t ks = kstart_word(u, n_words32, valid, W);
+      kstart[u] = ks;
+      my_ltot += __popc(ks);
+      if (ks) {
+        uint32_t cw[5];
+        cw[0] = u ? __ldg(codes + 2 * u - 1) : 0u;
+        const uint2 a = __ldg(reinterpret_cast<const uint2*>(codes + 2 * u));
+        const uint2 b = __ldg(reinterpret_cast<const uint2*>(codes + 2 * u + 2));
+        cw[1] = a.x; cw[2] = a.y; cw[3] = b.x; cw[4] = b.y;
+        const uint32_t cand = conflict_candidates<W, BOTH>(cw);
+        fast = ks & ~cand;
+        const uint32_t slow = ks & cand;
+        w1 = cw[1]; w2 = cw[2]; w3 = cw[3];
+        if (slow) {
+          const uint32_t i = atomicAdd(&n_slow, 1u);
+          if (i < PART_SLOWCAP) slow_q[i] = make_uint2((uint32_t)u, slow);
+          else slow_list[atomicAdd(slow_count, 1u)] = make_uint2((uint32_t)u, slow);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i++) part_push(__funnelshift_r(w1, w2, 2 * i) & KEYMASK, fast & (1u << i), cnt_s, q_s);
+#pragma unroll
+    for (int i = 0; i < 16; i++) part_push(__funnelshift_r(w2, w3, 2 * i) & KEYMASK, fast & (0x10000u << i), cnt_s, q_s);
+    __syncthreads();
+    // ---- flush: warp w owns classes w, w+16, w+32 ----
+    for (uint32_t c = warp; c < PART_NCLASS; c += PART_NT / 32) {
+      const uint32_t n = cnt[c];
+      if (n > PART_CAP) {  // this round did not fit: roll the queue back, the round's keys of c are redone below
+        if (lane == 0) { ovf[c] = 1; any_ovf = 1; cnt[c] = prev[c]; }
+        continue;
+      }
+      const uint32_t nfl = n & ~127u;
+      if (nfl) {
+        const uint32_t base = fill[c];
+        const uint16_t* src = q + c * PART_CAP;
+        if (base + nfl <= region_cap) {
+          uint16_t* dst = buckets + ((uint64_t)c * gridDim.x + blockIdx.x) * region_cap + base;
+          for (uint32_t i = lane * 4; i < nfl; i += 128) *(uint2*)(dst + i) = *(const uint2*)(src + i);
+          if (lane == 0) fill[c] = base + nfl;
+        } else {  // private bucket region full: straight to the global table
+          const uint32_t start = part_class_start(c);
+          for (uint32_t i = lane; i < nfl; i += 32) atomicAdd(hist + start + (((uint32_t)src[i] - start) & 0xFFFFu), 1u);
+        }
+        const uint32_t rem = n - nfl;
+        uint2 v = make_uint2(0, 0);
+        if (lane * 4 < rem) v = *(const uint2*)(src + nfl + lane * 4);
+        __syncwarp();
+        if (lane * 4 < rem) *(uint2*)(q + c * PART_CAP + lane * 4) = v;
+        if (lane == 0) { cnt[c] = rem; prev[c] = rem; }
+      } else if (lane == 0) prev[c] = n;
+    }
+    if (threadIdx.x == 0) cnt[PART_NCLASS] = 0;
+    if (warp == PART_NT / 32 - 1) {  // slow units of this round -> global list (one global atomic per CTA round)
+      const uint32_t ns = min(n_slow, PART_SLOWCAP);
+      if (ns) {
+        if (lane == 0) slow_base = atomicAdd(slow_count, ns);
+        __syncwarp();
+        const uint32_t sb = slow_base;
+        for (uint32_t i = lane; i < ns; i += 32) slow_list[sb + i] = slow_q[i];
+        __syncwarp();
+        if (lane == 0) n_slow = 0;
+      }
+    }
+    __syncthreads();
+    if (any_ovf) {
+#pragma unroll 1
+      for (int i = 0; i < 32; i++) {
+        if (fast & (1u << i)) {
+          const uint32_t key = (i < 16 ? __funnelshift_r(w1, w2, 2 * i) : __funnelshift_r(w2, w3, 2 * (i - 16))) & KEYMASK;
+          if (ovf[(key * PART_NCLASS) >> 20]) atomicAdd(hist + key, 1u);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x < PART_NCLASS) ovf[threadIdx.x] = 0;
+      if (threadIdx.x == 0) any_ovf = 0;
+      __syncthreads();
+    }
+  }
+  // leftovers (< 128 per class and CTA): straight to the global table
+  for (uint32_t c = warp; c < PART_NCLASS; c += PART_NT / 32) {
+    if (lane == 0) fill_out[c * gridDim.x + blockIdx.x] = fill[c];
+    const uint32_t n = cnt[c];
+    const uint32_t start = part_class_start(c);
+    for (uint32_t i = lane; i < n; i += 32) atomicAdd(hist + start + (((uint32_t)q[c * PART_CAP + i] - start) & 0xFFFFu), 1u);
+  }
+  for (int o = 16; o > 0; o >>= 1) my_ltot += __shfl_xor_sync(0xffffffffu, my_ltot, o);
+  if (lane == 0 && my_ltot) atomicAdd(ltot, (unsigned long long)my_ltot);
+}
+
+// exact resolution of the units that hold a W-mer with an equal key close in front of it
+struct EmitSlow {
+  uint32_t* hist;
+  uint32_t mask;
+  int w1;  // W - 1
+  __device__ __forceinline__ void operator()(uint32_t key, uint32_t i) const {
+    const int b = (int)i - w1;  // start position relative to the unit
+    if (b >= 0 && b < 32 && ((mask >> b) & 1u)) atomicAdd(hist + key, 1u);
+  }
+};
+template <int W, bool BOTH>
+__global__ void __launch_bounds__(128) k_count_slow(const uint32_t* __restrict__ codes, const uint32_t* __restrict__ kstart,
+                                                    const uint2* __restrict__ slow_list,
+                                                    const unsigned int* __restrict__ slow_count, uint32_t* __restrict__ hist) {
+  const uint32_t n = *slow_count;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint2 e = slow_list[i];
+    count_chunk<W, BOTH>(codes, kstart, (uint64_t)e.x * 32u, 3, EmitSlow{hist, e.y, W - 1});
+  }
+}
+
+// stage H: CTA (class c, part p) walks the regions p, p + PART_CPC, ... of the class, one region per warp at a time
+__global__ void __launch_bounds__(PART_HT) k_hist_part(const uint16_t* __restrict__ buckets, uint32_t region_cap,
+                                                       uint32_t n_regions, const uint32_t* __restrict__ fill,
+                                                       uint32_t* __restrict__ hist) {
+  extern __shared__ uint32_t bins[];
+  const uint32_t c = blockIdx.x / PART_CPC, part = blockIdx.x % PART_CPC;
+  const uint32_t start = part_class_start(c), nb = part_class_start(c + 1) - start;
+  for (uint32_t i = threadIdx.x; i < nb; i += PART_HT) bins[i] = 0;
+  __syncthreads();
+  const uint32_t s16 = start & 0xFFFFu;
+  const uint32_t bins_s = (uint32_t)__cvta_generic_to_shared(bins);
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (uint32_t reg = part + PART_CPC * warp; reg < n_regions; reg += PART_CPC * (PART_HT / 32)) {
+    const uint32_t n8 = fill[c * n_regions + reg] >> 3;  // 16-byte groups (fill is a multiple of 128 keys)
+    const uint4* src = reinterpret_cast<const uint4*>(buckets + ((uint64_t)c * n_regions + reg) * region_cap);
+#pragma unroll 2
+    for (uint32_t g = lane; g < n8; g += 32) {
+      const uint4 v = __ldg(src + g);
+      const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t i0 = ((ws[k] & 0xFFFFu) - s16) & 0xFFFFu, i1 = ((ws[k] >> 16) - s16) & 0xFFFFu;
+        asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(bins_s + i0 * 4u) : "memory");
+        asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(bins_s + i1 * 4u) : "memory");
+      }
+    }
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < nb; i += PART_HT) {
+    const uint32_t v = bins[i];
+    if (v) atomicAdd(hist + start + i, v);
+  }
+}
+
+// BOTH on the partition path: fast W-mers sit in their forward-id bin, slow ones in the canonical bin; the pair
+// count is their sum, kept in the canonical bin (k_mirror copies it to the other id afterwards).
+__global__ void k_fold_canon(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, int W, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t rc = revcomp_id((uint32_t)i, W);
+    if ((uint32_t)i <= rc) {
+      uint64_t v = hist[i];
+      if ((uint32_t)i < rc) v += hist[rc];
+      if (v) {
+        acc[i] += v;
+        hist[i] = 0;
+        hist[rc] = 0;
+      }
+    }
   }
 }
 
@@ -858,7 +1094,8 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   free_tables(h);
   free_em(h);
   if (h->d_scratch) cudaFree(h->d_scratch);
-  for (int i = 0; i < 4; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
+  for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -875,15 +1112,17 @@ extern "C" int peng_cuda_enable_timing(peng_handle_t h, int on) {
   if (!h) return PENG_E_INVALID;
   CU(h, cudaSetDevice(h->device));
   if (on && !h->ev[0])
-    for (int i = 0; i < 4; i++) CU(h, cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i < 6; i++) CU(h, cudaEventCreate(&h->ev[i]));
   h->timing = on != 0;
   return PENG_OK;
 }
 extern "C" int peng_cuda_get_timing(peng_handle_t h, int phase, float* ms) {
-  if (!h || !h->ev[0] || phase < 0 || phase > 2 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
+  if (!h || !h->ev[0] || phase < 0 || phase > 5 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
   CU(h, cudaSetDevice(h->device));
-  CU(h, cudaEventSynchronize(h->ev[3]));
-  CU(h, cudaEventElapsedTime(ms, h->ev[phase], h->ev[phase + 1]));
+  CU(h, cudaEventSynchronize(h->ev[5]));
+  // events: 0 start | 1 k-mer starts marked | 2 stage P done | 3 slow units done | 4 counting done | 5 folded
+  static const int from[6] = {0, 1, 4, 1, 2, 3}, to[6] = {1, 4, 5, 2, 3, 4};
+  CU(h, cudaEventElapsedTime(ms, h->ev[from[phase]], h->ev[to[phase]]));
   return PENG_OK;
 }
 #define MARK(h, i) do { if ((h)->timing) CU(h, cudaEventRecord((h)->ev[i], (h)->stream)); } while (0)
@@ -1050,6 +1289,65 @@ extern "C" int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes, uint64_t*
 // =====================================================================================================
 // C ABI: counting
 // =====================================================================================================
+// Partition path driver: stage P (+ fused k-mer start marking), slow units, stage H; chunks of <= 2^30 positions so
+// that a uint32 bin cannot overflow between folds.
+template <int W>
+static int launch_count_partition(peng_handle_t h, bool both) {
+  const uint64_t n_units = h->n_words32;
+  const uint64_t units_per_chunk = 1ull << 25;
+  const unsigned grid_p = (unsigned)h->sm_count * 2;
+  const uint64_t chunk_units = std::min(n_units, units_per_chunk);
+  // private region of (class, stage-P CTA): 1.5x the expected share, at least 1024 keys, multiple of 128
+  uint64_t region_cap = (chunk_units * 32 * 3 / 2) / ((uint64_t)grid_p * PART_NCLASS);
+  region_cap = std::max<uint64_t>(1024, (region_cap + 127) & ~127ull);
+  const size_t bucket_elems = (size_t)region_cap * grid_p * PART_NCLASS;
+  if (h->part_bucket_elems < bucket_elems) {
+    TRY(dev_alloc(h, &h->d_part_buckets, bucket_elems));
+    h->part_bucket_elems = bucket_elems;
+  }
+  if (!h->d_part_fill) TRY(dev_alloc(h, &h->d_part_fill, (size_t)grid_p * PART_NCLASS));
+  if (!h->d_slow_count) TRY(dev_alloc(h, &h->d_slow_count, (size_t)1));
+  if (h->slow_list_elems < chunk_units) {
+    TRY(dev_alloc(h, &h->d_slow_list, (size_t)chunk_units));
+    h->slow_list_elems = chunk_units;
+  }
+  const size_t smem_p = (size_t)(PART_NCLASS + 1) * PART_CAP * 2;
+  const size_t smem_h = (size_t)(part_class_start(1) + 1) * 4;
+  if (both) CU(h, cudaFuncSetAttribute(k_count_part<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+  else CU(h, cudaFuncSetAttribute(k_count_part<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+  CU(h, cudaFuncSetAttribute(k_hist_part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_h));
+  unsigned long long* d_ltot = (unsigned long long*)(h->d_counts + h->n_patterns);
+  const bool single = n_units <= units_per_chunk;
+  for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
+    const uint64_t ue = std::min(n_units, ub + units_per_chunk);
+    CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
+    if (both)
+      k_count_part<W, true><<<grid_p, PART_NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, ub, ue,
+                                                                   h->d_part_buckets, (uint32_t)region_cap, h->d_part_fill,
+                                                                   h->d_hist32, d_ltot, h->d_slow_list, h->d_slow_count);
+    else
+      k_count_part<W, false><<<grid_p, PART_NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, ub, ue,
+                                                                    h->d_part_buckets, (uint32_t)region_cap, h->d_part_fill,
+                                                                    h->d_hist32, d_ltot, h->d_slow_list, h->d_slow_count);
+    LAUNCH_CHECK(h);
+    if (single) MARK(h, 2);
+    if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
+    else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
+    LAUNCH_CHECK(h);
+    if (single) MARK(h, 3);
+    k_hist_part<<<PART_NCLASS * PART_CPC, PART_HT, smem_h, h->stream>>>(h->d_part_buckets, (uint32_t)region_cap, grid_p,
+                                                                      h->d_part_fill, h->d_hist32);
+    LAUNCH_CHECK(h);
+    if (ue < n_units) {
+      if (both) k_fold_canon<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, h->n_patterns);
+      else k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
+      LAUNCH_CHECK(h);
+    }
+  }
+  h->used_partition = true;
+  return PENG_OK;
+}
+
 template <int W>
 static int launch_count_W(peng_handle_t h, bool both) {
   // chunk geometry: 16 code words (256 end positions) per thread for large inputs, less when the input is
@@ -1077,6 +1375,10 @@ static int launch_count_W(peng_handle_t h, bool both) {
     LAUNCH_CHECK(h);
     return PENG_OK;
   } else {
+  if constexpr (W == 10) {
+    const uint64_t n_pos = h->stream_end - PENG_FRONT_PAD;
+    if (h->count_path == 2 || (h->count_path == 0 && n_pos >= (1ull << 22))) return launch_count_partition<W>(h, both);
+  }
   // W >= 10: global atomics; a uint32 bin cannot overflow within 2^32 positions, so split and fold
   const uint64_t max_chunks_per_launch = (1ull << 31) / (16ull * wpc);
   for (uint64_t first = 0; first < n_chunks; first += max_chunks_per_launch) {
@@ -1112,12 +1414,18 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   h->stats_ready = false;
   CU(h, cudaMemsetAsync(h->d_hist32, 0, n * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
-  MARK(h, 0);
-  k_mark_kstart<<<grid_for(h->n_words32, 256), 256, 0, h->stream>>>(h->d_valid, h->d_kstart, h->n_words32, W,
-                                                                   (unsigned long long*)(h->d_counts + n));
-  LAUNCH_CHECK(h);
-  MARK(h, 1);
   const bool both = strand == PENG_STRAND_BOTH;
+  const bool partition = W == 10 && (h->count_path == 2 ||
+                                     (h->count_path == 0 && h->stream_end - PENG_FRONT_PAD >= (1ull << 22)));
+  h->used_partition = false;
+  MARK(h, 0);
+  if (!partition) {  // the partition path derives the k-mer starts inside its first stage
+    k_mark_kstart<<<grid_for(h->n_words32, 256), 256, 0, h->stream>>>(h->d_valid, h->d_kstart, h->n_words32, W,
+                                                                     (unsigned long long*)(h->d_counts + n));
+    LAUNCH_CHECK(h);
+  }
+  MARK(h, 1);
+  if (!partition) { MARK(h, 2); MARK(h, 3); }
   int rc = PENG_OK;
   switch (W) {
     case 2: rc = launch_count_W<2>(h, both); break;
@@ -1130,12 +1438,20 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
     case 16: rc = launch_count_W<16>(h, both); break;
   }
   TRY(rc);
-  MARK(h, 2);
-  k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
+  MARK(h, 4);
+  if (h->used_partition && both) k_fold_canon<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+  else k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
   LAUNCH_CHECK(h);
-  MARK(h, 3);
+  MARK(h, 5);
   return PENG_OK;
 }
+
+extern "C" int peng_cuda_set_count_path(peng_handle_t h, int path) {
+  if (!h || path < 0 || path > 2) return fail(h, PENG_E_INVALID, "set_count_path: path must be 0 (auto), 1 (L2 atomics) or 2 (partition)");
+  h->count_path = path;
+  return PENG_OK;
+}
+extern "C" int peng_cuda_last_count_path(peng_handle_t h) { return h ? (h->used_partition ? 2 : 1) : 0; }
 
 extern "C" int peng_cuda_count_buffer(peng_handle_t h, void** device_ptr, uint64_t* n_u64) {
   if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_buffer: nothing counted");

@@ -151,3 +151,18 @@ def em_acc_f32(pwm, W, counts, bg, s=1e4):
     acc = np.zeros((W, 4), np.float32)
     lib.sim_em_acc_f32(_p(pwm, f32p), W, _p(counts, u64p), _p(bg, f32p), C.c_float(s), _p(acc, f32p))
     return acc
+
+
+def count_part(st, W, both=True, mirror=True):
+    """The partition path's fast/slow split (k_count_part + k_count_slow + k_fold_canon), thread by thread.
+    -> (counts, ltot, stats) with stats = dict(missed, needless_slow, fast, slow_units)."""
+    hist = np.zeros(4 ** W, np.uint64)
+    stats = np.zeros(5, np.uint64)
+    lib.sim_count_part(_p(st.codes, u32p), _p(st.valid, u32p), C.c_uint64(st.nw), W, int(both), _p(hist, u64p),
+                       _p(stats, u64p))
+    if both:
+        lib.sim_fold_canon(_p(hist, u64p), W)
+        if mirror:
+            lib.sim_mirror(_p(hist, u64p), W)
+    return hist, int(stats[0]), dict(missed=int(stats[1]), needless_slow=int(stats[2]), fast=int(stats[3]),
+                                     slow_units=int(stats[4]))

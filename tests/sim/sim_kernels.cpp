@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <algorithm>
 
 #define PENG_HD inline
 #include "../../peng-motif_b200/csrc/core_seq.cuh"
@@ -19,7 +20,7 @@ using namespace peng;
 
 struct EmitHost {
   uint64_t* hist;
-  void operator()(uint32_t key) const { hist[key]++; }
+  void operator()(uint32_t key, uint32_t) const { hist[key]++; }
 };
 
 template <int W>
@@ -35,7 +36,7 @@ static void count_W(const uint32_t* codes, const uint32_t* kstart, uint64_t stre
 
 struct EmitKeys {
   std::vector<uint32_t>* keys;
-  void operator()(uint32_t key) const { keys->push_back(key); }
+  void operator()(uint32_t key, uint32_t) const { keys->push_back(key); }
 };
 template <int W>
 static void count_keys_W(const uint32_t* codes, const uint32_t* kstart, uint64_t stream_end, int both, uint32_t wpc,
@@ -184,5 +185,80 @@ void sim_em_acc_f32(const float* pwm, int W, const uint64_t* counts, const float
       for (uint32_t i = 0; i < (uint32_t)(n >> 2); i++) sum += terms[em_chain_id(p, a, i)];
       acc[p * 4 + a] = sum;
     }
+}
+}
+
+// ---- partition path (k_count_part / k_count_slow / k_fold_canon of peng_cuda.cu), thread by thread ----------
+static inline uint32_t kmer_at(const uint32_t* codes, uint64_t s, int W) {
+  const uint64_t w = s >> 4;
+  const uint32_t sh = 2u * (uint32_t)(s & 15);
+  const uint64_t both = (uint64_t)codes[w] | ((uint64_t)codes[w + 1] << 32);
+  return (uint32_t)(both >> sh) & (W == 16 ? 0xFFFFFFFFu : ((1u << (2 * W)) - 1u));
+}
+
+template <int W, bool BOTH>
+static void count_part_T(const uint32_t* codes, const uint32_t* valid, uint64_t n_words32, uint64_t* hist, uint64_t* stats) {
+  std::vector<uint32_t> kstart(n_words32 + 8, 0);
+  for (uint64_t u = 0; u < n_words32; u++) {
+    kstart[u] = kstart_word(u, n_words32, valid, W);
+    stats[0] += (uint64_t)popc32(kstart[u]);
+  }
+  for (uint64_t u = 0; u < n_words32; u++) {
+    const uint32_t ks = kstart[u];
+    if (!ks) continue;
+    uint32_t cw[5];
+    for (int j = 0; j < 5; j++) cw[j] = (2 * u + j >= 1) ? codes[2 * u - 1 + j] : 0u;
+    const uint32_t cand = conflict_candidates<W, BOTH>(cw);
+    const uint32_t fast = ks & ~cand, slow = ks & cand;
+    // brute force: does an equal key start within the W-1 positions in front?
+    for (uint32_t b = 0; b < 32; b++) {
+      const uint64_t sp = u * 32 + b;
+      const uint32_t k0 = kmer_at(codes, sp, W);
+      const uint32_t c0 = BOTH ? std::min(k0, revcomp_id(k0, W)) : k0;
+      bool truth = false;
+      for (int d = 1; d < W && (uint64_t)d <= sp; d++) {
+        const uint32_t k1 = kmer_at(codes, sp - d, W);
+        const uint32_t c1 = BOTH ? std::min(k1, revcomp_id(k1, W)) : k1;
+        truth |= (c0 == c1);
+      }
+      const bool flagged = (cand >> b) & 1u;
+      if (truth && !flagged) stats[1]++;  // missed conflict: must stay 0
+      if (!truth && flagged && ((ks >> b) & 1u)) stats[2]++;  // looked-at W-mers sent to the slow path needlessly
+    }
+    stats[3] += (uint64_t)popc32(fast);
+    for (uint32_t b = 0; b < 32; b++)
+      if ((fast >> b) & 1u) hist[kmer_at(codes, u * 32 + b, W)]++;
+    if (slow) {
+      stats[4]++;
+      auto emit = [&](uint32_t key, uint32_t i) {
+        const int32_t b = (int32_t)i - (W - 1);
+        if (b >= 0 && b < 32 && ((slow >> b) & 1u)) hist[key]++;
+      };
+      count_chunk<W, BOTH>(codes, kstart.data(), u * 32, 3, emit);
+    }
+  }
+}
+
+extern "C" {
+// hist: 4^W uint64 zeroed by the caller; BOTH: forward-id bins for fast positions, canonical for slow ones (fold with
+// sim_fold_canon).  stats[0] ltot, [1] missed conflicts (must be 0), [2] needless slow positions, [3] fast positions,
+// [4] slow units
+void sim_count_part(const uint32_t* codes, const uint32_t* valid, uint64_t n_words32, int W, int both, uint64_t* hist,
+                    uint64_t* stats) {
+  for (int i = 0; i < 5; i++) stats[i] = 0;
+  switch (W) {
+    case 4: both ? count_part_T<4, true>(codes, valid, n_words32, hist, stats) : count_part_T<4, false>(codes, valid, n_words32, hist, stats); break;
+    case 6: both ? count_part_T<6, true>(codes, valid, n_words32, hist, stats) : count_part_T<6, false>(codes, valid, n_words32, hist, stats); break;
+    case 8: both ? count_part_T<8, true>(codes, valid, n_words32, hist, stats) : count_part_T<8, false>(codes, valid, n_words32, hist, stats); break;
+    case 10: both ? count_part_T<10, true>(codes, valid, n_words32, hist, stats) : count_part_T<10, false>(codes, valid, n_words32, hist, stats); break;
+  }
+}
+// BOTH: pair sums into the canonical bin (then sim_mirror copies them to the other id)
+void sim_fold_canon(uint64_t* hist, int W) {
+  const uint64_t n = 1ull << (2 * W);
+  for (uint64_t i = 0; i < n; i++) {
+    const uint32_t rc = revcomp_id((uint32_t)i, W);
+    if ((uint32_t)i < rc) { hist[i] += hist[rc]; hist[rc] = 0; }
+  }
 }
 }

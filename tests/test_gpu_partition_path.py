@@ -1,0 +1,120 @@
+"""The partition path of the W = 10 counter (k_count_part -> k_count_slow -> k_hist_part -> k_fold_canon) against the
+oracle and against the L2-atomic path, through the C ABI.  Bit-exact, as for every count."""
+import os
+
+import numpy as np
+import pytest
+
+import _cases
+import _oracle as O
+from test_kernel_logic_sim import palindrome_rich_sequences
+
+pytestmark = pytest.mark.gpu
+DATA = os.path.join(_cases.GOLDEN, "data")
+W = 10
+
+
+@pytest.fixture()
+def part(gpu):
+    gpu.set_count_path(2)
+    yield gpu
+    gpu.set_count_path(0)
+
+
+def check(gpu, codes, offs):
+    gpu.ingest_codes(codes, offs)
+    for both in (True, False):
+        ltot = gpu.count(W, int(both))
+        assert gpu.last_count_path == 2
+        ref, lt = O.count(codes, offs, W, both)
+        assert ltot == lt, both
+        assert np.array_equal(gpu.get_counts(), ref), both
+
+
+@pytest.mark.parametrize("case", [c for c in _cases.golden_cases() if c["exit"] == 0 and c["W"] == 10], ids=lambda c: c["tag"])
+def test_golden_cases(part, pkg, case):
+    path = _cases.write_fasta(case["fasta"])
+    try:
+        part.ingest_fasta(path)
+    finally:
+        os.unlink(path)
+    ltot = part.count(W, pkg.STRAND_BOTH if case["strand"] == "BOTH" else pkg.STRAND_PLUS)
+    assert part.last_count_path == 2 and ltot == case["ltot"]
+    assert np.array_equal(part.get_counts(), _cases.case_counts(case))
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_dirty_and_palindrome_rich(part, seed):
+    seqs = _cases.dirty_sequences(seed) if seed % 2 else palindrome_rich_sequences(seed)
+    check(part, *O.encode(seqs))
+
+
+def test_mafk(part):
+    codes, offs, _, _ = O.read_fasta(os.path.join(DATA, "MafK.fasta"))
+    check(part, codes, offs)
+
+
+def test_empty_short_and_invalid(part):
+    check(part, *O.encode(["A", "ACGTACGTA", "ACGTACGTAC", "ACGTACGTACG", "N" * 40, "ACGTNACGTACGTACGTAC"]))
+
+
+@pytest.mark.parametrize("kind", ["homopolymer", "tandem", "one_class", "skewed_random"])
+def test_adversarial_queue_pressure(part, kind):
+    """Inputs that overflow a class queue (every W-mer of a round in one id range) or consist of slow units only."""
+    rng = np.random.RandomState(5)
+    if kind == "homopolymer":
+        seqs = ["A" * 5000, "T" * 3000, "C" * 777]
+    elif kind == "tandem":
+        seqs = ["ACG" * 2000, "AACCGGTT" * 900, "AT" * 1500]
+    elif kind == "one_class":
+        # all W-mers end in 'AA' (digits 8, 9 = A): a single class takes every key of every round; the varying
+        # prefix keeps most of them out of the conflict candidates
+        seqs = []
+        for _ in range(300):
+            s = []
+            for _ in range(40):
+                s.append("".join(rng.choice(list("CGT"), 8)) + "AA")
+            seqs.append("".join(s))
+    else:
+        seqs = ["".join(rng.choice(list("ACGT"), 400, p=[0.85, 0.05, 0.05, 0.05])) for _ in range(400)]
+    check(part, *O.encode(seqs))
+
+
+def test_paths_agree_on_synthetic(gpu, pkg):
+    """BASELINE configs[2] shape at reduced size + a dirty variant: partition path == L2-atomic path == oracle."""
+    for nfrac in (0.0, 0.01):
+        gpu.ingest_synthetic(60_000, 200, 99, 0, "TGCTGASTCAGCA", 0.3, nfrac)
+        codes, offs = gpu.export_codes()
+        for both in (True, False):
+            gpu.set_count_path(1)
+            l1 = gpu.count(W, int(both)); c1 = gpu.get_counts()
+            assert gpu.last_count_path == 1
+            gpu.set_count_path(2)
+            l2 = gpu.count(W, int(both)); c2 = gpu.get_counts()
+            assert gpu.last_count_path == 2
+            gpu.set_count_path(0)
+            l0 = gpu.count(W, int(both)); c0 = gpu.get_counts()
+            assert gpu.last_count_path == 2  # 12 M positions: automatic choice is the partition path
+            ref, lt = O.count(codes, offs, W, both)
+            assert l1 == l2 == l0 == lt
+            assert np.array_equal(c1, ref) and np.array_equal(c2, ref) and np.array_equal(c0, ref)
+
+
+def test_sharded_sum_matches_whole(part, pkg):
+    """count_local leaves canonical (unmirrored) bins: the sum over shards + finish equals the whole-set table."""
+    import torch
+
+    part.ingest_synthetic(40_000, 200, 7, 0, "TGCTGASTCAGCA", 0.3, 0.0)
+    ltot = part.count(W, pkg.STRAND_BOTH)
+    whole = part.get_counts()
+    acc, lt = np.zeros(4 ** W + 1, np.uint64), 0
+    for r in range(4):
+        part.ingest_synthetic(10_000, 200, 7, r * 10_000, "TGCTGASTCAGCA", 0.3, 0.0)
+        part.count_local(W, pkg.STRAND_BOTH)
+        part.synchronize()
+        acc += torch.as_tensor(part.count_buffer(), device="cuda").cpu().numpy().view(np.uint64)
+    assert int(acc[-1]) == ltot
+    rc = np.array([O.revcomp(i, W) for i in range(0, 4 ** W, 4 ** W // 64)])  # spot check of the mirror relation
+    ids = np.arange(0, 4 ** W, 4 ** W // 64)
+    canon = np.minimum(ids, rc)
+    assert np.array_equal(acc[:-1][canon], whole[ids])

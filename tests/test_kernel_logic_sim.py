@@ -116,3 +116,70 @@ def test_em_chain_order_is_reference_order():
         acc = S.em_acc_f32(pwm, 8, counts, bg)
         s = ((acc[:, 0] + acc[:, 1]) + acc[:, 2]) + acc[:, 3]
         assert np.array_equal((acc / s[:, None]).astype(np.float32), O.f32.em_iteration(pwm, 8, counts, bg))
+
+
+# ---- partition path: fast / slow split by bit-parallel conflict candidates ---------------------------------
+def palindrome_rich_sequences(seed):
+    """Reverse-complement palindromes of every length 4..40 and periodic stretches next to random sequence: the
+    inputs that must reach the slow path of the partition kernel."""
+    rng = np.random.RandomState(1000 + seed)
+    comp = {"A": "T", "C": "G", "G": "C", "T": "A"}
+    seqs = []
+    for _ in range(rng.randint(2, 6)):
+        parts = []
+        for _ in range(rng.randint(3, 12)):
+            kind = rng.randint(0, 4)
+            if kind == 0:
+                parts.append("".join(rng.choice(list("ACGT"), rng.randint(1, 40))))
+            elif kind == 1:
+                half = "".join(rng.choice(list("ACGT"), rng.randint(2, 21)))
+                parts.append(half + "".join(comp[c] for c in reversed(half)))
+            elif kind == 2:
+                unit = "".join(rng.choice(list("ACGT"), rng.randint(1, 10)))
+                parts.append((unit * 30)[: rng.randint(8, 60)])
+            else:
+                parts.append("N" * rng.randint(1, 3))
+        seqs.append("".join(parts))
+    return seqs
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_partition_path_split_is_exact(seed):
+    seqs = _cases.dirty_sequences(seed) if seed % 2 else palindrome_rich_sequences(seed)
+    codes, offs = O.encode(seqs)
+    st = S.pack(codes, offs)
+    for W in (4, 6, 8, 10):
+        for both in (True, False):
+            hist, ltot, stt = S.count_part(st, W, both)
+            ref, lt = O.count(codes, offs, W, both)
+            assert stt["missed"] == 0, (W, both, stt)
+            assert lt == ltot and np.array_equal(hist, ref), (W, both, stt)
+
+
+@pytest.mark.parametrize("case", [c for c in _cases.golden_cases() if c["exit"] == 0 and c["W"] in (4, 6, 8, 10)],
+                         ids=lambda c: c["tag"])
+def test_partition_path_golden_cases(case):
+    path = _cases.write_fasta(case["fasta"])
+    codes, offs, _, _ = O.read_fasta(path)
+    os.unlink(path)
+    hist, ltot, stt = S.count_part(S.pack(codes, offs), case["W"], case["strand"] == "BOTH")
+    assert stt["missed"] == 0 and ltot == case["ltot"]
+    assert np.array_equal(hist, _cases.case_counts(case))
+
+
+@pytest.mark.parametrize("both", [True, False])
+def test_partition_path_mafk_and_candidate_rate(both):
+    codes, offs, _, _ = O.read_fasta(os.path.join(DATA, "MafK.fasta"))
+    hist, ltot, stt = S.count_part(S.pack(codes, offs), 10, both)
+    ref, lt = O.count(codes, offs, 10, both)
+    assert stt["missed"] == 0 and lt == ltot and np.array_equal(hist, ref)
+    # the candidate test is a superset; it must stay a small one or the slow path would dominate
+    assert stt["needless_slow"] < 0.01 * ltot, stt
+    # random sequence (BASELINE configs[2] shape): ~1 looked-at W-mer in 1000 may go to the slow path
+    st = S.synth(3000, 200, 1234, 0, [3, 2, 1, 3, 2, 0, 4, 3, 1, 0, 2, 1, 0], 0.3, 0.0)
+    o = (np.arange(3001) * 200).astype(np.uint64)
+    c = S.unpack(st, o)
+    hist, ltot, stt = S.count_part(st, 10, both)
+    ref, lt = O.count(c, o, 10, both)
+    assert stt["missed"] == 0 and lt == ltot and np.array_equal(hist, ref)
+    assert ltot - stt["fast"] < 0.02 * ltot, stt
