@@ -271,7 +271,8 @@ def main():
             break  # keep the GPU under load until the clock sampler has data (single GPU only: ranks must agree)
     barrier()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kern_ms = []
+    kern_ms, phase_ms = [], []
+    partition = g.last_count_path == 2  # W = 10 on >= 4 M positions: k_count_part / k_count_slow / k_hist_part
     launches0 = g.launches
     t_wall = time.perf_counter()
     for a, b in ev:
@@ -279,7 +280,8 @@ def main():
         a.record()
         step_resident()
         b.record()
-        kern_ms.append(g.get_timing(1))
+        kern_ms.append(g.get_timing(3 if partition else 1))
+        phase_ms.append([g.get_timing(p) for p in range(6)])
     barrier()
     t_wall = time.perf_counter() - t_wall
     launches = g.launches - launches0
@@ -357,12 +359,21 @@ def main():
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     k_ms = sorted(kern_ms)[len(kern_ms) // 2]
+    ph = np.median(np.array(phase_ms), axis=0)
     algo_bytes = ALGO_BYTES_PER_BASE * bases_local + 4.0 * 4 ** W
     achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+    if partition:
+        kname = f"k_count_part<{W},{shape['strand']}> (stage P of the partition path)"
+        note = ("stage P streams the packed set once (codes + validity), derives k-mer starts and conflict candidates and "
+                "partitions 16-bit keys into class buckets; ALU-pipe bound (ncu: pipe_alu 75 %), see DESIGN.md")
+    else:
+        kname = f"k_count_global<{W},{shape['strand']}>" if W >= 10 else "k_count_smem"
+        note = "one L2 atomic per counted k-mer: atomic-throughput-bound far below the HBM roof (DESIGN.md)"
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "kernel": f"k_count_global<{W},{shape['strand']}>" if W >= 10 else "k_count_smem",
-                "kernel_ms": k_ms, "algorithmic_bytes": algo_bytes, "peak_source": peak_src,
-                "note": "one L2 atomic per counted k-mer: atomic-throughput-bound far below the HBM roof (DESIGN.md)"}
+                "kernel": kname, "kernel_ms": k_ms, "algorithmic_bytes": algo_bytes, "peak_source": peak_src, "note": note,
+                "step_phases_ms": {"mark": float(ph[0]), "count_total": float(ph[1]), "fold": float(ph[2]),
+                                   "stage_P": float(ph[3]), "slow_units": float(ph[4]), "stage_H": float(ph[5])},
+                "whole_step_frac": algo_bytes / (dev_ms / args.steps * 1e-3) / 1e9 / peak}
     tr = os.path.join(ROOT, "profiles", "count_kernel_traffic.json")
     if os.path.exists(tr):
         try:

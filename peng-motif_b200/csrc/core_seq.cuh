@@ -286,61 +286,85 @@ PENG_HD uint32_t compress_even16(uint32_t w) {  // bits 0,2,4,..,30 -> bits 0..1
   return w;
 }
 
-// cw[0..4] = code words 2u-1 .. 2u+3 (positions 32u-16 .. 32u+63); result bit b = candidate flag of the
-// W-mer starting at 32u + b.
+// cw[0..4] = code words 2u-1 .. 2u+3 (positions 32u-16 .. 32u+63).  The work is cut into independent steps so that
+// a kernel can spread them between its shared-memory operations (k_count_part); conflict_candidates() runs them
+// back to back.  c1 / c2 collect the spaced candidate flags of words 1 and 2 (positions 32u .. 32u+31).
+struct CandState {
+  uint32_t c1, c2;
+  uint32_t p[3];  // PAL(m) at m = 16(j+1) + k, being narrowed
+};
+PENG_HD void cand_init(CandState& st) {
+  st.c1 = 0; st.c2 = 0;
+  st.p[0] = st.p[1] = st.p[2] = 0xFFFFFFFFu;
+}
+// (ff) lag d: W consecutive equalities x[p] == x[p-d] starting at p
+template <int W>
+PENG_HD void cand_ff_lag(const uint32_t* cw, int d, CandState& st) {
+  static_assert(W >= 4 && W <= 10 && (W % 2) == 0, "window arithmetic assumes W-1 <= 9 lags inside one word");
+  uint32_t e[3];  // e[j] bit 2k: x[p] == x[p-d] at p = 16(j+1) + k
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const uint32_t t = cw[j + 1] ^ funnel_r(cw[j], cw[j + 1], 32u - 2u * (uint32_t)d);
+    e[j] = ~(t | (t >> 1)) & 0x55555555u;
+  }
+  // runs by doubling: r2, r4, r8 = runs of 2, 4, 8; the third word only has to be right for its low positions
+  // (zeros shifted in at its top)
+  uint32_t r2[3], r4[3], r8[2];
+  r2[0] = e[0] & funnel_r(e[0], e[1], 2u);
+  r2[1] = e[1] & funnel_r(e[1], e[2], 2u);
+  r2[2] = e[2] & (e[2] >> 2);
+  r4[0] = r2[0] & funnel_r(r2[0], r2[1], 4u);
+  r4[1] = r2[1] & funnel_r(r2[1], r2[2], 4u);
+  r4[2] = r2[2] & (r2[2] >> 4);
+  r8[0] = r4[0] & funnel_r(r4[0], r4[1], 8u);
+  r8[1] = r4[1] & funnel_r(r4[1], r4[2], 8u);
+  if (W == 4) { st.c1 |= r4[0]; st.c2 |= r4[1]; }
+  if (W == 6) { st.c1 |= r4[0] & funnel_r(r2[0], r2[1], 8u); st.c2 |= r4[1] & funnel_r(r2[1], r2[2], 8u); }
+  if (W == 8) { st.c1 |= r8[0]; st.c2 |= r8[1]; }
+  if (W == 10) { st.c1 |= r8[0] & funnel_r(r2[0], r2[1], 16u); st.c2 |= r8[1] & funnel_r(r2[1], r2[2], 16u); }
+}
+// (rc) arm i of the palindromes: x[m+1+i] complementary to x[m-i]; i = 0 .. W/2
+PENG_HD void cand_rc_arm(const uint32_t* cw, int i, CandState& st) {
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    const uint32_t a = funnel_r(cw[j + 1], cw[j + 2], 2u * (uint32_t)(1 + i));                  // x[m+1+i]
+    const uint32_t b = i ? funnel_r(cw[j], cw[j + 1], 32u - 2u * (uint32_t)i) : cw[j + 1];       // x[m-i]
+    const uint32_t t = a ^ b;
+    st.p[j] &= t & (t >> 1);  // both bits set <=> complementary letters
+  }
+}
+// (rc) s is flagged by the centres m = s .. s + W/2 - 2
+template <int W>
+PENG_HD void cand_rc_finish(CandState& st) {
+#pragma unroll
+  for (int j = 0; j < 3; j++) st.p[j] &= 0x55555555u;
+#pragma unroll
+  for (int i = 0; i <= W / 2 - 2; i++) {
+    st.c1 |= i ? funnel_r(st.p[0], st.p[1], 2u * (uint32_t)i) : st.p[0];
+    st.c2 |= i ? funnel_r(st.p[1], st.p[2], 2u * (uint32_t)i) : st.p[1];
+  }
+}
+PENG_HD uint32_t cand_result(const CandState& st) { return compress_even16(st.c1) | (compress_even16(st.c2) << 16); }
+
+// number of steps and step I of the whole computation (I is a compile-time constant after unrolling)
+template <int W, bool BOTH>
+struct CandSteps {
+  static constexpr int N_FF = W - 1, N_ARM = BOTH ? W / 2 + 1 : 0, N = N_FF + N_ARM + (BOTH ? 1 : 0);
+  PENG_HD static void run(int I, const uint32_t* cw, CandState& st) {
+    if (I < N_FF) cand_ff_lag<W>(cw, I + 1, st);
+    else if (I < N_FF + N_ARM) cand_rc_arm(cw, I - N_FF, st);
+    else if (BOTH && I == N_FF + N_ARM) cand_rc_finish<W>(st);
+  }
+};
+
+// result bit b = candidate flag of the W-mer starting at 32u + b
 template <int W, bool BOTH>
 PENG_HD uint32_t conflict_candidates(const uint32_t* cw) {
-  static_assert(W >= 4 && W <= 10 && (W % 2) == 0, "window arithmetic below assumes W-1 <= 9 lags inside one word");
-  uint32_t c1 = 0, c2 = 0;  // spaced candidate flags of words 1 and 2 (positions 32u .. 32u+31)
-  // ---- (ff) ----
+  CandState st;
+  cand_init(st);
 #pragma unroll
-  for (int d = 1; d < W; d++) {
-    uint32_t e[3];  // e[j] bit 2k: x[p] == x[p-d] at p = 16(j+1) + k
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      const uint32_t t = cw[j + 1] ^ funnel_r(cw[j], cw[j + 1], 32u - 2u * d);
-      e[j] = ~(t | (t >> 1)) & 0x55555555u;
-    }
-    // run of W consecutive equalities starting at p (p in words 1 and 2) by doubling: r2, r4, r8 = runs of
-    // 2, 4, 8; the third word only has to be right for its low positions (zeros shifted in at its top).
-    uint32_t r2[3], r4[3], r8[2];
-    r2[0] = e[0] & funnel_r(e[0], e[1], 2u);
-    r2[1] = e[1] & funnel_r(e[1], e[2], 2u);
-    r2[2] = e[2] & (e[2] >> 2);
-    r4[0] = r2[0] & funnel_r(r2[0], r2[1], 4u);
-    r4[1] = r2[1] & funnel_r(r2[1], r2[2], 4u);
-    r4[2] = r2[2] & (r2[2] >> 4);
-    r8[0] = r4[0] & funnel_r(r4[0], r4[1], 8u);
-    r8[1] = r4[1] & funnel_r(r4[1], r4[2], 8u);
-    if (W == 4) { c1 |= r4[0]; c2 |= r4[1]; }
-    if (W == 6) { c1 |= r4[0] & funnel_r(r2[0], r2[1], 8u); c2 |= r4[1] & funnel_r(r2[1], r2[2], 8u); }
-    if (W == 8) { c1 |= r8[0]; c2 |= r8[1]; }
-    if (W == 10) { c1 |= r8[0] & funnel_r(r2[0], r2[1], 16u); c2 |= r8[1] & funnel_r(r2[1], r2[2], 16u); }
-  }
-  // ---- (rc) ----
-  if (BOTH) {
-    constexpr int H = W / 2 + 1;
-    uint32_t p[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};  // PAL(m) at m = 16(j+1) + k
-#pragma unroll
-    for (int i = 0; i < H; i++) {
-#pragma unroll
-      for (int j = 0; j < 3; j++) {
-        const uint32_t a = funnel_r(cw[j + 1], cw[j + 2], 2u * (1 + i));            // x[m+1+i]
-        const uint32_t b = i ? funnel_r(cw[j], cw[j + 1], 32u - 2u * i) : cw[j + 1];  // x[m-i]
-        const uint32_t t = a ^ b;
-        p[j] &= t & (t >> 1);  // both bits set <=> complementary letters
-      }
-    }
-#pragma unroll
-    for (int j = 0; j < 3; j++) p[j] &= 0x55555555u;
-    // s is flagged by the centres m = s .. s + W/2 - 2
-#pragma unroll
-    for (int i = 0; i <= W / 2 - 2; i++) {
-      c1 |= i ? funnel_r(p[0], p[1], 2u * i) : p[0];
-      c2 |= i ? funnel_r(p[1], p[2], 2u * i) : p[1];
-    }
-  }
-  return compress_even16(c1) | (compress_even16(c2) << 16);
+  for (int I = 0; I < CandSteps<W, BOTH>::N; I++) CandSteps<W, BOTH>::run(I, cw, st);
+  return cand_result(st);
 }
 
 // ---- (b2) exact greedy non-overlapping counting ---------------------------------------------------------

@@ -68,6 +68,8 @@ struct peng_cuda_ctx {
   uint16_t* d_part_buckets = nullptr;
   size_t part_bucket_elems = 0;
   uint32_t* d_part_fill = nullptr;
+  size_t part_fill_elems = 0;
+  int part_cfg = 0;                // stage-P geometry (tuning knob, PENG_PART_CFG)
   uint2* d_slow_list = nullptr;
   size_t slow_list_elems = 0;
   unsigned int* d_slow_count = nullptr;
@@ -312,8 +314,6 @@ __global__ void __launch_bounds__(512) k_count_smem16(const uint32_t* __restrict
 // Skewed input cannot break exactness: a class queue that would overflow in a round is rolled back and the
 // round's keys of that class go straight to the global table; a full bucket region does the same per block.
 #define PART_NCLASS 37
-#define PART_NT 512
-#define PART_CAP 1024u
 #define PART_SLOWCAP 512u
 #define PART_CPC 4
 #define PART_HT 1024
@@ -322,22 +322,24 @@ __host__ __device__ __forceinline__ uint32_t part_class_start(uint32_t c) {  // 
   return (uint32_t)((((uint64_t)c << 20) + PART_NCLASS - 1) / PART_NCLASS);
 }
 
-__device__ __forceinline__ void part_push(uint32_t key, uint32_t pred, uint32_t cnt_s, uint32_t q_s) {
+template <uint32_t CAP>
+__device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t pred, uint32_t cnt_s, uint32_t q_s) {
   uint32_t c = (key * PART_NCLASS) >> 20;
   c = pred ? c : PART_NCLASS;  // W-mers that are not pushed go to a scratch queue: no branch around the atomic
   uint32_t slot;
   asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(cnt_s + c * 4u) : "memory");
-  const uint32_t addr = q_s + (c * PART_CAP + slot) * 2u;
+  const uint32_t addr = q_s + (c * CAP + slot) * 2u;
   asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %0, %1;\n\t@p st.shared.u16 [%2], %3;\n\t}"
-               :: "r"(slot), "r"(PART_CAP), "r"(addr), "h"((uint16_t)key) : "memory");
+               :: "r"(slot), "r"(CAP), "r"(addr), "h"((uint16_t)key) : "memory");
+  return slot;
 }
 
-template <int W, bool BOTH>
-__global__ void __launch_bounds__(PART_NT, 2) k_count_part(
+template <int W, bool BOTH, int PART_NT, uint32_t PART_CAP, int MINB>
+__global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
     uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, uint16_t* __restrict__ buckets, uint32_t region_cap,
     uint32_t* __restrict__ fill_out, uint32_t* __restrict__ hist, unsigned long long* __restrict__ ltot,
-    uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count) {
+    uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count, uint32_t zero) {
   static_assert(W == 10, "class geometry is laid out for 4^10 ids");
   constexpr uint32_t KEYMASK = (1u << (2 * W)) - 1u;
   extern __shared__ uint16_t q[];  // [PART_NCLASS + 1][PART_CAP]
@@ -352,34 +354,62 @@ __global__ void __launch_bounds__(PART_NT, 2) k_count_part(
   const uint64_t n_units = unit_end - unit_begin;
   const uint64_t n_rounds = (n_units + PART_NT - 1) / PART_NT;
   uint32_t my_ltot = 0;
-  for (uint64_t r = blockIdx.x; r < n_rounds; r += gridDim.x) {
+  // What one thread needs of a unit (32 k-mer starts): the three code words its keys are cut from, the mask of
+  // fast W-mers and the mask of slow ones.  Scanning a unit is ALU work only, pushing is shared-memory work only:
+  // the loop scans round r+1 in the shadow of the pushes of round r, one scan step behind every other push
+  // (ptxas keeps the source order of independent work, it does not interleave the two streams by itself).
+  struct Unit { uint32_t w1, w2, w3, fast, slow, u; };
+  uint32_t cw[5], ks;
+  CandState cs;
+  auto scan_begin = [&](uint64_t r) -> uint32_t {  // loads + k-mer starts of the thread's unit in round r
     const uint64_t u = unit_begin + r * PART_NT + threadIdx.x;
-    uint32_t fast = 0, w1 = 0, w2 = 0, w3 = 0;
-    if (u < unit_end) {
-      const uint32_t ks = kstart_word(u, n_words32, valid, W);
-      kstart[u] = ks;
-      my_ltot += __popc(ks);
-      if (ks) {
-        uint32_t cw[5];
-        cw[0] = u ? __ldg(codes + 2 * u - 1) : 0u;
-        const uint2 a = __ldg(reinterpret_cast<const uint2*>(codes + 2 * u));
-        const uint2 b = __ldg(reinterpret_cast<const uint2*>(codes + 2 * u + 2));
-        cw[1] = a.x; cw[2] = a.y; cw[3] = b.x; cw[4] = b.y;
-        const uint32_t cand = conflict_candidates<W, BOTH>(cw);
-        fast = ks & ~cand;
-        const uint32_t slow = ks & cand;
-        w1 = cw[1]; w2 = cw[2]; w3 = cw[3];
-        if (slow) {
-          const uint32_t i = atomicAdd(&n_slow, 1u);
-          if (i < PART_SLOWCAP) slow_q[i] = make_uint2((uint32_t)u, slow);
-          else slow_list[atomicAdd(slow_count, 1u)] = make_uint2((uint32_t)u, slow);
-        }
+    const bool live = r < n_rounds && u < unit_end;
+    const uint64_t uc = live ? u : unit_begin;  // clamp: dead threads read a legal address and drop the result
+    ks = kstart_word(uc, n_words32, valid, W);
+    ks = live ? ks : 0u;
+    if (live) kstart[u] = ks;
+    my_ltot += __popc(ks);
+    cw[0] = uc ? __ldg(codes + 2 * uc - 1) : 0u;
+    const uint2 a = __ldg(reinterpret_cast<const uint2*>(codes + 2 * uc));
+    const uint2 b = __ldg(reinterpret_cast<const uint2*>(codes + 2 * uc + 2));
+    cw[1] = a.x; cw[2] = a.y; cw[3] = b.x; cw[4] = b.y;
+    cand_init(cs);
+    return (uint32_t)u;
+  };
+  auto scan_end = [&](uint32_t u) -> Unit {
+    const uint32_t cand = cand_result(cs);
+    return Unit{cw[1], cw[2], cw[3], ks & ~cand, ks & cand, u};
+  };
+  typedef CandSteps<W, BOTH> Steps;
+  static_assert(Steps::N <= 16, "one scan step per two pushes");
+  uint32_t un = scan_begin(blockIdx.x);
+#pragma unroll
+  for (int I = 0; I < Steps::N; I++) Steps::run(I, cw, cs);
+  Unit cur = scan_end(un);
+  for (uint64_t r = blockIdx.x; r < n_rounds; r += gridDim.x) {
+    const uint32_t fast = cur.fast, w1 = cur.w1, w2 = cur.w2, w3 = cur.w3;
+    un = scan_begin(r + gridDim.x);
+    // `zero` is 0 at run time but opaque to the compiler: the two data dependencies it fakes (slot of push i -> inputs
+    // of scan step i/2 -> key of push i+1) are what keeps ptxas from sorting the two instruction streams apart again.
+    uint32_t link = 0;
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+      uint32_t key = (i < 16 ? __funnelshift_r(w1, w2, 2 * i) : __funnelshift_r(w2, w3, 2 * (i - 16))) & KEYMASK;
+      key ^= link;
+      const uint32_t slot = part_push<PART_CAP>(key, fast & (1u << i), cnt_s, q_s);
+      if ((i & 1) && (i >> 1) < Steps::N) {
+        const uint32_t z = slot & zero;
+        cw[1] ^= z; cw[2] ^= z; cw[3] ^= z;
+        Steps::run(i >> 1, cw, cs);
+        link = (cs.c1 | cs.p[0]) & zero;
       }
     }
-#pragma unroll
-    for (int i = 0; i < 16; i++) part_push(__funnelshift_r(w1, w2, 2 * i) & KEYMASK, fast & (1u << i), cnt_s, q_s);
-#pragma unroll
-    for (int i = 0; i < 16; i++) part_push(__funnelshift_r(w2, w3, 2 * i) & KEYMASK, fast & (0x10000u << i), cnt_s, q_s);
+    const Unit nxt = scan_end(un);
+    if (cur.slow) {
+      const uint32_t i = atomicAdd(&n_slow, 1u);
+      if (i < PART_SLOWCAP) slow_q[i] = make_uint2(cur.u, cur.slow);
+      else slow_list[atomicAdd(slow_count, 1u)] = make_uint2(cur.u, cur.slow);
+    }
     __syncthreads();
     // ---- flush: warp w owns classes w, w+16, w+32 ----
     for (uint32_t c = warp; c < PART_NCLASS; c += PART_NT / 32) {
@@ -434,6 +464,7 @@ __global__ void __launch_bounds__(PART_NT, 2) k_count_part(
       if (threadIdx.x == 0) any_ovf = 0;
       __syncthreads();
     }
+    cur = nxt;
   }
   // leftovers (< 128 per class and CTA): straight to the global table
   for (uint32_t c = warp; c < PART_NCLASS; c += PART_NT / 32) {
@@ -1068,6 +1099,7 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
     return fail(nullptr, PENG_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
   }
   h->stream = h->own_stream;
+  if (const char* e = getenv("PENG_PART_CFG")) h->part_cfg = atoi(e);
   *out = h;
   return PENG_OK;
 }
@@ -1289,13 +1321,41 @@ extern "C" int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes, uint64_t*
 // =====================================================================================================
 // C ABI: counting
 // =====================================================================================================
+// Stage-P launch geometry: threads per CTA, queue entries per class, CTAs per SM.
+struct PartArgs {
+  uint64_t ub, ue;
+  unsigned grid;
+  uint32_t region_cap;
+};
+template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM>
+static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
+  const size_t smem_p = (size_t)(PART_NCLASS + 1) * CAP * 2;
+  auto kern = k_count_part<W, BOTH, NT, CAP, PER_SM>;
+  CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
+  kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue, h->d_part_buckets,
+                                          a.region_cap, h->d_part_fill, h->d_hist32,
+                                          (unsigned long long*)(h->d_counts + h->n_patterns), h->d_slow_list, h->d_slow_count, 0u);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+static int part_cfg_per_sm(int cfg) { return cfg == 1 ? 4 : cfg == 2 ? 6 : 2; }
+template <int W, bool BOTH>
+static int launch_part(peng_handle_t h, int cfg, const PartArgs& a) {
+  switch (cfg) {
+    case 1: return launch_part_cfg<W, BOTH, 256, 512, 4>(h, a);
+    case 2: return launch_part_cfg<W, BOTH, 128, 384, 6>(h, a);
+    default: return launch_part_cfg<W, BOTH, 512, 1024, 2>(h, a);
+  }
+}
+
 // Partition path driver: stage P (+ fused k-mer start marking), slow units, stage H; chunks of <= 2^30 positions so
 // that a uint32 bin cannot overflow between folds.
 template <int W>
 static int launch_count_partition(peng_handle_t h, bool both) {
   const uint64_t n_units = h->n_words32;
   const uint64_t units_per_chunk = 1ull << 25;
-  const unsigned grid_p = (unsigned)h->sm_count * 2;
+  const int cfg = h->part_cfg;
+  const unsigned grid_p = (unsigned)h->sm_count * part_cfg_per_sm(cfg);
   const uint64_t chunk_units = std::min(n_units, units_per_chunk);
   // private region of (class, stage-P CTA): 1.5x the expected share, at least 1024 keys, multiple of 128
   uint64_t region_cap = (chunk_units * 32 * 3 / 2) / ((uint64_t)grid_p * PART_NCLASS);
@@ -1305,31 +1365,24 @@ static int launch_count_partition(peng_handle_t h, bool both) {
     TRY(dev_alloc(h, &h->d_part_buckets, bucket_elems));
     h->part_bucket_elems = bucket_elems;
   }
-  if (!h->d_part_fill) TRY(dev_alloc(h, &h->d_part_fill, (size_t)grid_p * PART_NCLASS));
+  if (h->part_fill_elems < (size_t)grid_p * PART_NCLASS) {
+    TRY(dev_alloc(h, &h->d_part_fill, (size_t)grid_p * PART_NCLASS));
+    h->part_fill_elems = (size_t)grid_p * PART_NCLASS;
+  }
   if (!h->d_slow_count) TRY(dev_alloc(h, &h->d_slow_count, (size_t)1));
   if (h->slow_list_elems < chunk_units) {
     TRY(dev_alloc(h, &h->d_slow_list, (size_t)chunk_units));
     h->slow_list_elems = chunk_units;
   }
-  const size_t smem_p = (size_t)(PART_NCLASS + 1) * PART_CAP * 2;
   const size_t smem_h = (size_t)(part_class_start(1) + 1) * 4;
-  if (both) CU(h, cudaFuncSetAttribute(k_count_part<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
-  else CU(h, cudaFuncSetAttribute(k_count_part<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
   CU(h, cudaFuncSetAttribute(k_hist_part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_h));
-  unsigned long long* d_ltot = (unsigned long long*)(h->d_counts + h->n_patterns);
   const bool single = n_units <= units_per_chunk;
   for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
     const uint64_t ue = std::min(n_units, ub + units_per_chunk);
     CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
-    if (both)
-      k_count_part<W, true><<<grid_p, PART_NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, ub, ue,
-                                                                   h->d_part_buckets, (uint32_t)region_cap, h->d_part_fill,
-                                                                   h->d_hist32, d_ltot, h->d_slow_list, h->d_slow_count);
-    else
-      k_count_part<W, false><<<grid_p, PART_NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, ub, ue,
-                                                                    h->d_part_buckets, (uint32_t)region_cap, h->d_part_fill,
-                                                                    h->d_hist32, d_ltot, h->d_slow_list, h->d_slow_count);
-    LAUNCH_CHECK(h);
+    const PartArgs a{ub, ue, grid_p, (uint32_t)region_cap};
+    const int rc_p = both ? launch_part<W, true>(h, cfg, a) : launch_part<W, false>(h, cfg, a);
+    TRY(rc_p);
     if (single) MARK(h, 2);
     if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
     else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
