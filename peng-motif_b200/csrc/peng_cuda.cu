@@ -39,7 +39,10 @@ struct peng_cuda_ctx {
   uint64_t stream_end = 0;         // first position behind the last separator
   uint64_t n_words32 = 0;          // 32-position words allocated (incl. pads)
   uint32_t *d_codes = nullptr, *d_valid = nullptr, *d_sstart = nullptr, *d_kstart = nullptr;
-  uint64_t* d_offsets = nullptr;   // n_seq+1 (base coordinates), null when fixed_len
+  uint64_t* d_offsets = nullptr;   // n_seq+1 (base coordinates), unused when fixed_len
+  size_t cap_words32 = 0, cap_offsets = 0;  // allocated capacities: re-ingesting a set of similar size reuses the buffers
+  cudaStream_t copy_stream = nullptr;       // H2D of ingest chunks, overlapped with packing on `stream`
+  cudaEvent_t copy_ev[2] = {nullptr, nullptr};
   std::vector<uint64_t> h_offsets;
 
   // ---- count table ----
@@ -157,9 +160,9 @@ static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)(
 template <bool ASCII>
 __global__ void k_pack(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets, uint64_t n_seq,
                        uint32_t* __restrict__ codes, uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart,
-                       uint64_t n_words32) {
-  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n_words32) pack_word<ASCII>(t, src, offsets, n_seq, codes, valid, sstart);
+                       uint64_t t_begin, uint64_t t_end) {
+  const uint64_t t = t_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < t_end) pack_word<ASCII>(t, src, offsets, n_seq, codes, valid, sstart);
 }
 
 __global__ void k_synth(SynthParams P, uint32_t* __restrict__ codes, uint32_t* __restrict__ valid,
@@ -1126,6 +1129,8 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   free_tables(h);
   free_em(h);
   if (h->d_scratch) cudaFree(h->d_scratch);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  for (int i = 0; i < 2; i++) if (h->copy_ev[i]) cudaEventDestroy(h->copy_ev[i]);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
   for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -1174,18 +1179,20 @@ static int alloc_stream(peng_handle_t h, uint64_t n_seq, uint64_t total_bases) {
   h->total_bases = total_bases;
   h->stream_end = PENG_FRONT_PAD + total_bases + 2 * n_seq;
   h->n_words32 = (h->stream_end + PENG_TAIL_PAD + 31) / 32 + 8;
-  TRY(dev_alloc(h, &h->d_codes, h->n_words32 * 2 + 8));
-  TRY(dev_alloc(h, &h->d_valid, h->n_words32 + 8));
-  TRY(dev_alloc(h, &h->d_sstart, h->n_words32 + 8));
-  TRY(dev_alloc(h, &h->d_kstart, h->n_words32 + 8));
+  if (h->cap_words32 < h->n_words32) {
+    TRY(dev_alloc(h, &h->d_codes, h->n_words32 * 2 + 8));
+    TRY(dev_alloc(h, &h->d_valid, h->n_words32 + 8));
+    TRY(dev_alloc(h, &h->d_sstart, h->n_words32 + 8));
+    TRY(dev_alloc(h, &h->d_kstart, h->n_words32 + 8));
+    h->cap_words32 = h->n_words32;
+  }
   // the few guard words behind n_words32 are read by funnel shifts at the very end of the stream
   CU(h, cudaMemsetAsync(h->d_codes + h->n_words32 * 2, 0, 8 * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_valid + h->n_words32, 0, 8 * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_sstart + h->n_words32, 0, 8 * 4, h->stream));
-  CU(h, cudaMemsetAsync(h->d_kstart, 0, (h->n_words32 + 8) * 4, h->stream));
+  CU(h, cudaMemsetAsync(h->d_kstart + h->n_words32, 0, 8 * 4, h->stream));  // the rest is written by every count
   h->counts_final = false;
   h->stats_ready = false;
-  h->W = 0;
   return PENG_OK;
 }
 
@@ -1200,32 +1207,78 @@ static void seq_lengths(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq
   h->max_len = mx;
 }
 
-// src = concatenated sequences on the DEVICE (letter codes or ASCII), offsets on the host
-static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
-  const uint64_t total = n_seq ? offsets[n_seq] : 0;
-  h->fixed_len = 0;
-  h->h_offsets.assign(offsets, offsets + n_seq + 1);
-  seq_lengths(h, offsets, n_seq);
-  TRY(alloc_stream(h, n_seq, total));
-  TRY(dev_alloc(h, &h->d_offsets, n_seq + 1));
-  CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+static int launch_pack(peng_handle_t h, const uint8_t* d_src, bool ascii, uint64_t t_begin, uint64_t t_end) {
+  if (t_end <= t_begin) return PENG_OK;
   const unsigned block = 256;
   if (ascii)
-    k_pack<true><<<grid_for(h->n_words32, block), block, 0, h->stream>>>(d_src, h->d_offsets, n_seq, h->d_codes,
-                                                                        h->d_valid, h->d_sstart, h->n_words32);
+    k_pack<true><<<grid_for(t_end - t_begin, block), block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid,
+                                                                          h->d_sstart, t_begin, t_end);
   else
-    k_pack<false><<<grid_for(h->n_words32, block), block, 0, h->stream>>>(d_src, h->d_offsets, n_seq, h->d_codes,
-                                                                         h->d_valid, h->d_sstart, h->n_words32);
+    k_pack<false><<<grid_for(t_end - t_begin, block), block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid,
+                                                                           h->d_sstart, t_begin, t_end);
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
 
+static int prepare_ingest(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq) {
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  h->fixed_len = 0;
+  TRY(alloc_stream(h, n_seq, total));
+  if (h->cap_offsets < n_seq + 1) {
+    TRY(dev_alloc(h, &h->d_offsets, n_seq + 1));
+    h->cap_offsets = n_seq + 1;
+  }
+  return PENG_OK;
+}
+
+// src = concatenated sequences on the DEVICE (letter codes or ASCII), offsets on the host
+static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
+  TRY(prepare_ingest(h, offsets, n_seq));
+  CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
+  TRY(launch_pack(h, d_src, ascii, 0, h->n_words32));
+  h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping in the shadow of the device work
+  seq_lengths(h, offsets, n_seq);
+  return PENG_OK;
+}
+
+// src on the HOST: the copy is cut into chunks on a second stream, the packing kernel follows chunk by chunk on the
+// handle's stream (a word is packed once every base of its 32 positions has arrived), so that packing, and the host's
+// own bookkeeping, hide behind the PCIe transfer.
 static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
   CU(h, cudaSetDevice(h->device));
   const uint64_t total = n_seq ? offsets[n_seq] : 0;
   TRY(need_scratch(h, (size_t)total + 16));
-  if (total) CU(h, cudaMemcpyAsync(h->d_scratch, src, total, cudaMemcpyHostToDevice, h->stream));
-  TRY(ingest_device_src(h, (const uint8_t*)h->d_scratch, offsets, n_seq, ascii));
+  TRY(prepare_ingest(h, offsets, n_seq));
+  if (!h->copy_stream) {
+    CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) CU(h, cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
+  }
+  uint8_t* d_src = (uint8_t*)h->d_scratch;
+  // the copy stream must not run ahead of earlier work on the handle's stream that still reads the scratch buffer
+  CU(h, cudaEventRecord(h->copy_ev[0], h->stream));
+  CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
+  CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+  const uint64_t chunk = 32ull << 20;
+  uint64_t t_done = 0, s_hint = 0;
+  int flip = 0;
+  for (uint64_t b0 = 0; b0 < total || b0 == 0; b0 += chunk) {
+    const uint64_t b1 = std::min(total, b0 + chunk);
+    if (b1 > b0) CU(h, cudaMemcpyAsync(d_src + b0, src + b0, b1 - b0, cudaMemcpyHostToDevice, h->copy_stream));
+    CU(h, cudaEventRecord(h->copy_ev[flip], h->copy_stream));
+    CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[flip], 0));
+    flip ^= 1;
+    uint64_t t_end = h->n_words32;
+    if (b1 < total) {  // every position in front of base b1 is complete: q1 = FRONT + b1 + 2 * (sequence holding b1)
+      const uint64_t* it = std::upper_bound(offsets + s_hint, offsets + n_seq + 1, b1);
+      s_hint = (uint64_t)(it - offsets) - 1;
+      t_end = (PENG_FRONT_PAD + b1 + 2 * s_hint) / 32;
+    }
+    TRY(launch_pack(h, d_src, ascii, t_done, t_end));
+    t_done = std::max(t_done, t_end);
+    if (total == 0) break;
+  }
+  h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping while the DMA engine works
+  seq_lengths(h, offsets, n_seq);
   CU(h, cudaStreamSynchronize(h->stream));  // the caller may free / reuse src
   return PENG_OK;
 }
@@ -1266,6 +1319,7 @@ extern "C" int peng_cuda_ingest_synthetic(peng_handle_t h, uint64_t n_seq, uint3
   h->fixed_len = seq_len;
   h->h_offsets.clear();
   dev_free(&h->d_offsets);
+  h->cap_offsets = 0;
   h->min_len = h->max_len = seq_len;
   TRY(alloc_stream(h, n_seq, n_seq * (uint64_t)seq_len));
   SynthParams P;
