@@ -134,6 +134,9 @@ int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const uint64_t* cou
  * k = order used for expected counts (BasePattern::k), max_k = highest order kept (BasePattern::max_k). */
 int peng_cuda_stats(peng_handle_t h, int K, const float* v32, const double* v64, int k, int max_k);
 int peng_cuda_get_table(peng_handle_t h, int table, int order, int precision, void* out /* 4^W elems */);
+/* Sparse read-back: out[i] = table[ids[i]] (float for PENG_F32REF, double for PENG_F64) — what
+ * BasePattern::print_patterns and getOptimizationScore read for the selected seeds (src/base_pattern.cpp:180-224,517-532). */
+int peng_cuda_gather_table(peng_handle_t h, int table, int order, int precision, const uint64_t* ids, uint64_t n, void* out);
 
 /* select_base_patterns (src/base_pattern.cpp:443-515).  Runs on the HOST on the float32 z table copied
  * back from the device: the result depends on the order libstdc++'s unstable std::sort leaves exact ties

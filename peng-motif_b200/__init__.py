@@ -77,6 +77,7 @@ _PROTOS = {
     "peng_cuda_set_counts": (C.c_int, [H, C.c_int, C.c_int, C.c_void_p, C.c_uint64]),
     "peng_cuda_stats": (C.c_int, [H, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "peng_cuda_get_table": (C.c_int, [H, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "peng_cuda_gather_table": (C.c_int, [H, C.c_int, C.c_int, C.c_int, u64p, C.c_uint64, C.c_void_p]),
     "peng_cuda_select_base_patterns": (C.c_int, [H, C.c_float, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_uint64, u64p]),
     "peng_cuda_iupac_aggregate": (C.c_int, [H, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "peng_cuda_iupac_count": (C.c_int, [H, C.c_void_p, C.c_int, C.c_void_p]),
@@ -331,6 +332,12 @@ class PengCuda:
     def get_table(self, table, precision=F32REF, order=0):
         out = np.zeros(4 ** self.W, np.float32 if precision == F32REF else np.float64)
         self._ck(self.lib.peng_cuda_get_table(self.h, table, order, precision, _ptr(out)))
+        return out
+
+    def gather_table(self, table, ids, precision=F32REF, order=0):
+        ids = np.ascontiguousarray(ids, np.uint64)
+        out = np.zeros(len(ids), np.float32 if precision == F32REF else np.float64)
+        self._ck(self.lib.peng_cuda_gather_table(self.h, table, order, precision, ids.ctypes.data_as(u64p), len(ids), _ptr(out)))
         return out
 
     def select_base_patterns(self, z_threshold=10.0, count_threshold=3, single_stranded=None, filter_neighbors=True):

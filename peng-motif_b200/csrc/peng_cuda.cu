@@ -1762,6 +1762,35 @@ extern "C" int peng_cuda_get_table(peng_handle_t h, int table, int order, int pr
   return PENG_OK;
 }
 
+// sparse read-back of a float / double table: out[i] = table[ids[i]] (the host driver prints a handful of rows)
+template <typename R>
+__global__ void k_gather_real(const R* __restrict__ table, const uint64_t* __restrict__ ids, uint64_t n, R* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = table[ids[i]];
+}
+
+extern "C" int peng_cuda_gather_table(peng_handle_t h, int table, int order, int precision, const uint64_t* ids, uint64_t n,
+                                      void* out) {
+  if (!h || !h->stats_ready || (n && (!ids || !out))) return fail(h, PENG_E_INVALID, "gather_table: stats not computed");
+  const void* p = table_ptr(h, table, order, precision);
+  if (!p) return fail(h, PENG_E_INVALID, "gather_table: table %d order %d precision %d not available", table, order, precision);
+  if (n == 0) return PENG_OK;
+  for (uint64_t i = 0; i < n; i++)
+    if (ids[i] >= h->n_patterns) return fail(h, PENG_E_INVALID, "gather_table: id out of range");
+  CU(h, cudaSetDevice(h->device));
+  const size_t es = precision == PENG_F32REF ? 4 : 8;
+  TRY(need_scratch(h, n * 8 + n * es));
+  uint64_t* d_ids = (uint64_t*)h->d_scratch;
+  void* d_out = (void*)(d_ids + n);
+  CU(h, cudaMemcpyAsync(d_ids, ids, n * 8, cudaMemcpyHostToDevice, h->stream));
+  if (precision == PENG_F32REF) k_gather_real<float><<<grid_for(n, 256), 256, 0, h->stream>>>((const float*)p, d_ids, n, (float*)d_out);
+  else k_gather_real<double><<<grid_for(n, 256), 256, 0, h->stream>>>((const double*)p, d_ids, n, (double*)d_out);
+  LAUNCH_CHECK(h);
+  CU(h, cudaMemcpyAsync(out, d_out, n * es, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_select_base_patterns(peng_handle_t h, float z_threshold, uint64_t count_threshold,
                                               int single_stranded, int filter_neighbors, uint64_t* out, uint64_t cap,
                                               uint64_t* n_selected) {
