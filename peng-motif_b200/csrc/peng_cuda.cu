@@ -79,7 +79,7 @@ struct peng_cuda_ctx {
 
   // ---- phase timing (bench) ----
   bool timing = false;
-  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   // ---- scratch ----
   void* d_scratch = nullptr;
@@ -325,15 +325,26 @@ __host__ __device__ __forceinline__ uint32_t part_class_start(uint32_t c) {  // 
   return (uint32_t)((((uint64_t)c << 20) + PART_NCLASS - 1) / PART_NCLASS);
 }
 
+// One push: class c = floor(key * NCLASS / 2^20) as a single high multiply, slot = cnt[c]++, 16-bit store if the slot
+// exists.  W-mers that are not pushed go to a scratch queue: ptxas turns a PREDICATED returning shared atomic into a
+// branch (BSSY / BRA / BSYNC per push), an unconditional one on a dummy counter is cheaper.  Stage P is bound by the
+// half-rate ALU pipe (ncu: pipe_alu 75 %), so the address arithmetic is written as multiply-adds (FMA pipe).
 template <uint32_t CAP>
-__device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t pred, uint32_t cnt_s, uint32_t q_s) {
-  uint32_t c = (key * PART_NCLASS) >> 20;
-  c = pred ? c : PART_NCLASS;  // W-mers that are not pushed go to a scratch queue: no branch around the atomic
+__device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t push, uint32_t cnt_s, uint32_t q_s) {
+  uint32_t c = __umulhi(key, (uint32_t)PART_NCLASS << 12);
+  c = push ? c : PART_NCLASS;
+  const uint32_t cnt_addr = c * 4u + cnt_s;
+  const uint32_t base = c * (CAP * 2u) + q_s;
   uint32_t slot;
-  asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(cnt_s + c * 4u) : "memory");
-  const uint32_t addr = q_s + (c * CAP + slot) * 2u;
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %0, %1;\n\t@p st.shared.u16 [%2], %3;\n\t}"
-               :: "r"(slot), "r"(CAP), "r"(addr), "h"((uint16_t)key) : "memory");
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t.reg .u32 a;\n\t"
+      "atom.shared.add.u32 %0, [%1], 1;\n\t"
+      "setp.lt.u32 q, %0, %2;\n\t"
+      "mad.lo.u32 a, %0, 2, %3;\n\t"
+      "@q st.shared.u16 [a], %4;\n\t}"
+      : "=r"(slot)
+      : "r"(cnt_addr), "r"(CAP), "r"(base), "h"((uint16_t)key)
+      : "memory");
   return slot;
 }
 
@@ -401,8 +412,7 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
       key ^= link;
       const uint32_t slot = part_push<PART_CAP>(key, fast & (1u << i), cnt_s, q_s);
       if ((i & 1) && (i >> 1) < Steps::N) {
-        const uint32_t z = slot & zero;
-        cw[1] ^= z; cw[2] ^= z; cw[3] ^= z;
+        cw[2] ^= slot & zero;
         Steps::run(i >> 1, cw, cs);
         link = (cs.c1 | cs.p[0]) & zero;
       }
@@ -1132,7 +1142,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   for (int i = 0; i < 2; i++) if (h->copy_ev[i]) cudaEventDestroy(h->copy_ev[i]);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
-  for (int i = 0; i < 6; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
 }
@@ -1149,7 +1159,7 @@ extern "C" int peng_cuda_enable_timing(peng_handle_t h, int on) {
   if (!h) return PENG_E_INVALID;
   CU(h, cudaSetDevice(h->device));
   if (on && !h->ev[0])
-    for (int i = 0; i < 6; i++) CU(h, cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i < 8; i++) CU(h, cudaEventCreate(&h->ev[i]));
   h->timing = on != 0;
   return PENG_OK;
 }
@@ -1157,8 +1167,9 @@ extern "C" int peng_cuda_get_timing(peng_handle_t h, int phase, float* ms) {
   if (!h || !h->ev[0] || phase < 0 || phase > 5 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
   CU(h, cudaSetDevice(h->device));
   CU(h, cudaEventSynchronize(h->ev[5]));
-  // events: 0 start | 1 k-mer starts marked | 2 stage P done | 3 slow units done | 4 counting done | 5 folded
-  static const int from[6] = {0, 1, 4, 1, 2, 3}, to[6] = {1, 4, 5, 2, 3, 4};
+  // events: 0 start | 1 k-mer starts marked | 4 counting done | 5 folded; of the first chunk of the partition path:
+  // 6 stage P launched | 2 stage P done | 3 slow units done | 7 stage H done
+  static const int from[6] = {0, 1, 4, 6, 2, 3}, to[6] = {1, 4, 5, 2, 3, 7};
   CU(h, cudaEventElapsedTime(ms, h->ev[from[phase]], h->ev[to[phase]]));
   return PENG_OK;
 }
@@ -1430,21 +1441,22 @@ static int launch_count_partition(peng_handle_t h, bool both) {
   }
   const size_t smem_h = (size_t)(part_class_start(1) + 1) * 4;
   CU(h, cudaFuncSetAttribute(k_hist_part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_h));
-  const bool single = n_units <= units_per_chunk;
   for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
     const uint64_t ue = std::min(n_units, ub + units_per_chunk);
     CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
     const PartArgs a{ub, ue, grid_p, (uint32_t)region_cap};
+    if (ub == 0) MARK(h, 6);  // phases 3..5 time the stages of the FIRST chunk (a full one whenever there are several)
     const int rc_p = both ? launch_part<W, true>(h, cfg, a) : launch_part<W, false>(h, cfg, a);
     TRY(rc_p);
-    if (single) MARK(h, 2);
+    if (ub == 0) MARK(h, 2);
     if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
     else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
     LAUNCH_CHECK(h);
-    if (single) MARK(h, 3);
+    if (ub == 0) MARK(h, 3);
     k_hist_part<<<PART_NCLASS * PART_CPC, PART_HT, smem_h, h->stream>>>(h->d_part_buckets, (uint32_t)region_cap, grid_p,
                                                                       h->d_part_fill, h->d_hist32);
     LAUNCH_CHECK(h);
+    if (ub == 0) MARK(h, 7);
     if (ue < n_units) {
       if (both) k_fold_canon<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, h->n_patterns);
       else k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
@@ -1532,7 +1544,7 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
     LAUNCH_CHECK(h);
   }
   MARK(h, 1);
-  if (!partition) { MARK(h, 2); MARK(h, 3); }
+  if (!partition) { MARK(h, 6); MARK(h, 2); MARK(h, 3); MARK(h, 7); }
   int rc = PENG_OK;
   switch (W) {
     case 2: rc = launch_count_W<2>(h, both); break;

@@ -294,6 +294,7 @@ void filter_redundancy(float merge_bit_factor, const float* v0, std::vector<Moti
 int run(const Options& opt) {
   Stopwatch watch{opt.timings};
   Device dev(opt.device);
+  watch.lap("CUDA context");
 
   // ---- Global::init (src/Global.cpp:60-79): the input set, and the background set if it is another file ----
   uint64_t n_seq = 0, total_bases = 0;
