@@ -13,61 +13,54 @@
 #include <string>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 namespace peng_host {
 
-struct FastaRecords {
-  std::vector<char> letters;      // sequence lines of all kept records, concatenated, raw bytes
-  std::vector<uint64_t> offsets;  // n_seq + 1
-  uint64_t n_without_sequence = 0;
-};
-
-// SequenceSet::readFASTA (src/shared/SequenceSet.cpp:285-447).  Returns 0 ok, 1 cannot open, 2 malformed.
+// SequenceSet::readFASTA (src/shared/SequenceSet.cpp:285-447) as a single pass over the file image that hands the
+// sequence bytes to a sink as it finds them (the sink of libpeng_cuda copies them into pinned staging buffers whose
+// DMA to the device overlaps the scan).  Returns 0 ok, 2 malformed (message in *msg).
 //   - lines end at '\n' only ('\r' stays in the line and later becomes a non-ACGT letter);
 //   - `while (getline(file, line).good())`: a last line without '\n' is dropped (:304);
 //   - blank lines are skipped (:306); '>' starts a record (:308); sequence lines are concatenated (:366);
 //   - a record without sequence is ignored with a warning (:346, :417);
 //   - a space inside a sequence line, or a sequence line before any header, is fatal (:361-373).
-inline int read_fasta(const char* path, FastaRecords* out, std::string* msg) {
-  FILE* f = fopen(path, "rb");
-  if (!f) {
-    *msg = std::string("Error: Cannot open FASTA file: ") + path;
-    return 1;
-  }
-  std::vector<char> text;
-  {
-    char buf[1 << 16];
-    size_t n;
-    while ((n = fread(buf, 1, sizeof buf, f)) > 0) text.insert(text.end(), buf, buf + n);
-    fclose(f);
-  }
-  out->letters.clear();
-  out->letters.reserve(text.size());
-  out->offsets.assign(1, 0);
+// Sink: void letters(const char* p, size_t n)  — next n sequence bytes of the current record
+//       void end_record(const char* header, size_t header_len) — the current record is complete (it had >= 1 byte)
+//       void end_of_file(bool last_record_kept) — whether the file's final record was a complete one
+template <typename Sink>
+inline int scan_fasta(const char* text, size_t size, const char* path, Sink& sink, std::string* msg) {
   bool in_record = false;
-  uint64_t record_begin = 0;
-  const char* p = text.data();
-  const char* end = p + text.size();
+  uint64_t record_bytes = 0;
+  const char* header = nullptr;
+  size_t header_len = 0;
+  const char* p = text;
+  const char* end = text + size;
+  auto close_record = [&]() {
+    if (record_bytes) sink.end_record(header, header_len);
+    else fprintf(stderr, "Warning: Ignore FASTA entry without sequence: %s\n", path);
+  };
   while (p < end) {
     const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
     if (!nl) break;  // unterminated last line: never delivered by getline().good()
     const size_t len = (size_t)(nl - p);
     if (len) {
       if (p[0] == '>') {
-        if (in_record) {
-          if (out->letters.size() > record_begin) out->offsets.push_back(out->letters.size());
-          else {
-            out->n_without_sequence++;
-            fprintf(stderr, "Warning: Ignore FASTA entry without sequence: %s\n", path);
-          }
-        }
+        if (in_record) close_record();
         in_record = true;
-        record_begin = out->letters.size();
+        record_bytes = 0;
+        header = p + 1;
+        header_len = len - 1;
       } else if (in_record) {
         if (memchr(p, ' ', len)) {
           *msg = std::string("Error: FASTA sequence contains space character: ") + path;
           return 2;
         }
-        out->letters.insert(out->letters.end(), p, p + len);
+        sink.letters(p, len);
+        record_bytes += len;
       } else {
         *msg = std::string("Error: Wrong FASTA format: ") + path;
         return 2;
@@ -75,14 +68,42 @@ inline int read_fasta(const char* path, FastaRecords* out, std::string* msg) {
     }
     p = nl + 1;
   }
-  if (in_record) {
-    if (out->letters.size() > record_begin) out->offsets.push_back(out->letters.size());
-    else {
-      out->n_without_sequence++;
-      fprintf(stderr, "Warning: Ignore FASTA entry without sequence: %s\n", path);
-    }
-  }
+  if (in_record) close_record();
+  sink.end_of_file(in_record && record_bytes > 0);
   return 0;
+}
+
+// The whole file as one read-only mapping (page cache pages, no copy).  An empty file maps to size 0.
+struct MappedFile {
+  const char* data = nullptr;
+  size_t size = 0;
+  int open_file(const char* path);  // 0 ok, 1 cannot open
+  ~MappedFile();
+};
+inline int MappedFile::open_file(const char* path) {
+  const int fd = open(path, O_RDONLY);
+  if (fd < 0) return 1;
+  struct stat st;
+  if (fstat(fd, &st) != 0 || !S_ISREG(st.st_mode)) {
+    close(fd);
+    return 1;
+  }
+  size = (size_t)st.st_size;
+  if (size) {
+    void* m = mmap(nullptr, size, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
+    if (m == MAP_FAILED) {
+      close(fd);
+      size = 0;
+      return 1;
+    }
+    madvise(m, size, MADV_SEQUENTIAL);
+    data = static_cast<const char*>(m);
+  }
+  close(fd);
+  return 0;
+}
+inline MappedFile::~MappedFile() {
+  if (data) munmap(const_cast<char*>(data), size);
 }
 
 // BackgroundModel::calculateV (src/shared/BackgroundModel.cpp:490-530) on counts laid out v[0]|v[1]|...|v[K].

@@ -43,6 +43,8 @@ struct peng_cuda_ctx {
   size_t cap_words32 = 0, cap_offsets = 0;  // allocated capacities: re-ingesting a set of similar size reuses the buffers
   cudaStream_t copy_stream = nullptr;       // H2D of ingest chunks, overlapped with packing on `stream`
   cudaEvent_t copy_ev[2] = {nullptr, nullptr};
+  uint8_t* pin[2] = {nullptr, nullptr};    // pinned staging buffers of the streaming FASTA ingest
+  cudaEvent_t pin_ev[2] = {nullptr, nullptr};
   std::vector<uint64_t> h_offsets;
 
   // ---- count table ----
@@ -1141,6 +1143,8 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   if (h->d_scratch) cudaFree(h->d_scratch);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   for (int i = 0; i < 2; i++) if (h->copy_ev[i]) cudaEventDestroy(h->copy_ev[i]);
+  for (int i = 0; i < 2; i++) if (h->pin[i]) cudaFreeHost(h->pin[i]);
+  for (int i = 0; i < 2; i++) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
   for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
@@ -1306,15 +1310,107 @@ extern "C" int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_code
   return ingest_device_src(h, (const uint8_t*)d_codes, offsets, n_seq, false);
 }
 
+// Streaming FASTA ingest: the file is mapped, one host pass splits it into records with the reference's line rules
+// (host_ingest.h: scan_fasta) and copies the sequence bytes into two pinned staging buffers; every full buffer goes to
+// the device on the copy stream while the scan fills the other one.  Letters are translated and packed on the device
+// once the record table is known (k_pack).
+#define PENG_PIN_BYTES (16u << 20)
+struct StagingSink {
+  peng_handle_t h;
+  uint8_t* d_src;
+  int cur = 0;
+  size_t fill = 0;
+  uint64_t sent = 0;  // bytes handed to the DMA engine so far
+  int rc = PENG_OK;
+  std::vector<uint64_t> offsets{0};
+  std::vector<std::pair<const char*, size_t>> segments;  // lines of the record being read (for the warning below)
+  const char* last_header = nullptr;
+  size_t last_header_len = 0;
+  std::vector<std::pair<const char*, size_t>> last_segments;
+  int flush() {
+    if (fill == 0 || rc != PENG_OK) return rc;
+    peng_handle_t hh = h;
+    auto fail_cuda = [&](cudaError_t e) { rc = fail(hh, PENG_E_CUDA, "ingest_fasta: %s", cudaGetErrorString(e)); return rc; };
+    cudaError_t e = cudaMemcpyAsync(d_src + sent, h->pin[cur], fill, cudaMemcpyHostToDevice, h->copy_stream);
+    if (e != cudaSuccess) return fail_cuda(e);
+    if ((e = cudaEventRecord(h->pin_ev[cur], h->copy_stream)) != cudaSuccess) return fail_cuda(e);
+    sent += fill;
+    fill = 0;
+    cur ^= 1;
+    if ((e = cudaEventSynchronize(h->pin_ev[cur])) != cudaSuccess) return fail_cuda(e);  // its previous copy has left
+    return rc;
+  }
+  void letters(const char* p, size_t n) {
+    segments.emplace_back(p, n);
+    while (n && rc == PENG_OK) {
+      const size_t m = std::min<size_t>(n, PENG_PIN_BYTES - fill);
+      memcpy(h->pin[cur] + fill, p, m);
+      fill += m;
+      p += m;
+      n -= m;
+      if (fill == PENG_PIN_BYTES) flush();
+    }
+  }
+  void end_record(const char* header, size_t header_len) {
+    offsets.push_back(sent + fill);
+    last_header = header;
+    last_header_len = header_len;
+    last_segments.swap(segments);
+    segments.clear();
+  }
+  bool last_kept = false;
+  void end_of_file(bool last_record_kept) { last_kept = last_record_kept; }
+};
+
 extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, uint64_t* total_bases,
                                       uint32_t* min_len, uint32_t* max_len) {
   if (!h || !path) return fail(h, PENG_E_INVALID, "ingest_fasta: NULL argument");
-  peng_host::FastaRecords rec;
+  CU(h, cudaSetDevice(h->device));
+  peng_host::MappedFile file;
+  if (file.open_file(path) != 0) return fail(h, PENG_E_IO, "Error: Cannot open FASTA file: %s", path);
+  TRY(need_scratch(h, file.size + 16));  // the sequence bytes are a subset of the file's
+  if (!h->copy_stream) {
+    CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) CU(h, cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
+  }
+  if (!h->pin[0])
+    for (int i = 0; i < 2; i++) {
+      CU(h, cudaHostAlloc((void**)&h->pin[i], PENG_PIN_BYTES, cudaHostAllocDefault));
+      CU(h, cudaEventCreateWithFlags(&h->pin_ev[i], cudaEventDisableTiming));
+    }
+  // the copy stream must not run ahead of earlier work on the handle's stream that still reads the scratch buffer
+  CU(h, cudaEventRecord(h->copy_ev[0], h->stream));
+  CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
+  StagingSink sink;
+  sink.h = h;
+  sink.d_src = (uint8_t*)h->d_scratch;
   std::string msg;
-  const int rc = peng_host::read_fasta(path, &rec, &msg);
-  if (rc == 1) return fail(h, PENG_E_IO, "%s", msg.c_str());
-  if (rc == 2) return fail(h, PENG_E_FORMAT, "%s", msg.c_str());
-  TRY(ingest_host_src(h, (const uint8_t*)rec.letters.data(), rec.offsets.data(), rec.offsets.size() - 1, true));
+  const int rc = peng_host::scan_fasta(file.data, file.size, path, sink, &msg);
+  if (rc != 0) {
+    cudaStreamSynchronize(h->copy_stream);
+    return fail(h, PENG_E_FORMAT, "%s", msg.c_str());
+  }
+  TRY(sink.flush());
+  TRY(sink.rc);
+  const uint64_t ns = sink.offsets.size() - 1;
+  // SequenceSet::readFASTA reports undefined letters for the LAST record only (src/shared/SequenceSet.cpp:395-405)
+  if (ns && sink.last_kept) {
+    const std::string name = sink.last_header_len ? std::string(sink.last_header, sink.last_header_len) : std::to_string(ns);
+    for (const auto& seg : sink.last_segments)
+      for (size_t i = 0; i < seg.second; i++) {
+        const char c = seg.first[i], up = (char)(c & 0xDF);
+        if (up != 'A' && up != 'C' && up != 'G' && up != 'T')
+          fprintf(stderr, "Warning: The FASTA file contains an undefined base: %c at sequence %s\n", c, name.c_str());
+      }
+  }
+  TRY(prepare_ingest(h, sink.offsets.data(), ns));
+  CU(h, cudaMemcpyAsync(h->d_offsets, sink.offsets.data(), (ns + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+  CU(h, cudaEventRecord(h->copy_ev[1], h->copy_stream));
+  CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[1], 0));
+  TRY(launch_pack(h, sink.d_src, true, 0, h->n_words32));
+  seq_lengths(h, sink.offsets.data(), ns);
+  h->h_offsets.swap(sink.offsets);
+  CU(h, cudaStreamSynchronize(h->stream));
   if (n_seq) *n_seq = h->n_seq;
   if (total_bases) *total_bases = h->total_bases;
   if (min_len) *min_len = h->min_len;

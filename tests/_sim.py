@@ -17,7 +17,7 @@ FRONT_PAD = 64
 
 
 def _build():
-    deps = [_SRC, os.path.join(_CSRC, "core_seq.cuh"), os.path.join(_CSRC, "core_tab.cuh")]
+    deps = [_SRC, os.path.join(_CSRC, "core_seq.cuh"), os.path.join(_CSRC, "core_tab.cuh"), os.path.join(_CSRC, "host_ingest.h")]
     if os.path.exists(_LIB) and os.path.getmtime(_LIB) >= max(os.path.getmtime(d) for d in deps):
         return
     subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-x", "c++",
@@ -166,3 +166,19 @@ def count_part(st, W, both=True, mirror=True):
             lib.sim_mirror(_p(hist, u64p), W)
     return hist, int(stats[0]), dict(missed=int(stats[1]), needless_slow=int(stats[2]), fast=int(stats[3]),
                                      slow_units=int(stats[4]))
+
+
+def scan_fasta(path):
+    """host_ingest.h: scan_fasta on a mapped file -> (codes in the reference's encoding, offsets) or raises ValueError."""
+    n_seq, n_let = C.c_uint64(), C.c_uint64()
+    rc = lib.sim_scan_fasta(os.fsencode(path), C.byref(n_seq), C.byref(n_let), None, None)
+    if rc:
+        raise ValueError(f"scan_fasta rc={rc}")
+    letters = np.zeros(max(n_let.value, 1), np.uint8)
+    offsets = np.zeros(n_seq.value + 1, np.uint64)
+    lib.sim_scan_fasta(os.fsencode(path), C.byref(n_seq), C.byref(n_let), letters.ctypes.data_as(C.c_char_p), _p(offsets, u64p))
+    letters = letters[: n_let.value]
+    lut = np.zeros(256, np.uint8)
+    for i, ch in enumerate("ACGT"):
+        lut[ord(ch)] = lut[ord(ch.lower())] = i + 1
+    return lut[letters], offsets

@@ -262,3 +262,32 @@ void sim_fold_canon(uint64_t* hist, int W) {
   }
 }
 }
+
+// ---- FASTA record splitting (host_ingest.h: scan_fasta + MappedFile), the host half of peng_cuda_ingest_fasta ----
+#include "../../peng-motif_b200/csrc/host_ingest.h"
+namespace {
+struct VectorSink {
+  std::vector<char> letters_;
+  std::vector<uint64_t> offsets{0};
+  bool last_kept = false;
+  void letters(const char* p, size_t n) { letters_.insert(letters_.end(), p, p + n); }
+  void end_record(const char*, size_t) { offsets.push_back(letters_.size()); }
+  void end_of_file(bool k) { last_kept = k; }
+};
+}  // namespace
+extern "C" {
+// returns 0 ok, 1 cannot open, 2 malformed; letters (raw bytes) / offsets may be NULL to size
+int sim_scan_fasta(const char* path, uint64_t* n_seq, uint64_t* n_letters, char* letters, uint64_t* offsets) {
+  peng_host::MappedFile f;
+  if (f.open_file(path) != 0) return 1;
+  VectorSink sink;
+  std::string msg;
+  const int rc = peng_host::scan_fasta(f.data, f.size, path, sink, &msg);
+  if (rc) return rc;
+  *n_seq = sink.offsets.size() - 1;
+  *n_letters = sink.letters_.size();
+  if (letters) memcpy(letters, sink.letters_.data(), sink.letters_.size());
+  if (offsets) memcpy(offsets, sink.offsets.data(), sink.offsets.size() * 8);
+  return 0;
+}
+}

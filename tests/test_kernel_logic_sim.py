@@ -183,3 +183,37 @@ def test_partition_path_mafk_and_candidate_rate(both):
     ref, lt = O.count(c, o, 10, both)
     assert stt["missed"] == 0 and lt == ltot and np.array_equal(hist, ref)
     assert ltot - stt["fast"] < 0.02 * ltot, stt
+
+
+# ---- FASTA record splitting of the streaming ingest (host_ingest.h: scan_fasta) ---------------------------
+@pytest.mark.parametrize("case", _cases.golden_cases(), ids=lambda c: c["tag"])
+def test_scan_fasta_small_cases(case):
+    path = _cases.write_fasta(case["fasta"])
+    try:
+        if case["exit"] != 0:
+            with pytest.raises(ValueError):
+                S.scan_fasta(path)
+            return
+        codes, offs = S.scan_fasta(path)
+        ref_codes, ref_offs, _, _ = O.read_fasta(path)
+    finally:
+        os.unlink(path)
+    assert np.array_equal(offs, ref_offs) and np.array_equal(codes, ref_codes[: len(codes)])
+
+
+@pytest.mark.parametrize("text", ["", "\n\n", ">a\n", ">a\nACGT", ">a\nACGT\n>b\n", ">\nAC\nGT\n\n>x y\nNNAC\r\n", ">a\n>b\n>c\nA\n",
+                                  ">a\nACGT\n>b\nAC"])
+def test_scan_fasta_edge_files(text):
+    """empty file, blank lines only, header without sequence, unterminated last line, CR, empty header, trailing record cut"""
+    path = _cases.write_fasta(text)
+    try:
+        codes, offs = S.scan_fasta(path)
+        ref_codes, ref_offs, _, _ = O.read_fasta(path)
+    finally:
+        os.unlink(path)
+    assert np.array_equal(offs, ref_offs) and np.array_equal(codes, ref_codes[: len(codes)])
+
+
+def test_scan_fasta_missing_file():
+    with pytest.raises(ValueError):
+        S.scan_fasta("/nonexistent/file.fa")
