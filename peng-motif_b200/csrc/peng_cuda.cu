@@ -350,7 +350,7 @@ __device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t push, uint3
   return slot;
 }
 
-template <int W, bool BOTH, int PART_NT, uint32_t PART_CAP, int MINB>
+template <int W, bool BOTH, int PART_NT, uint32_t PART_CAP, int MINB, bool LINK>
 __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
     uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, uint16_t* __restrict__ buckets, uint32_t region_cap,
@@ -414,9 +414,9 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
       key ^= link;
       const uint32_t slot = part_push<PART_CAP>(key, fast & (1u << i), cnt_s, q_s);
       if ((i & 1) && (i >> 1) < Steps::N) {
-        cw[2] ^= slot & zero;
+        if (LINK) cw[2] ^= slot & zero;
         Steps::run(i >> 1, cw, cs);
-        link = (cs.c1 | cs.p[0]) & zero;
+        if (LINK) link = (cs.c1 | cs.p[0]) & zero;
       }
     }
     const Unit nxt = scan_end(un);
@@ -1488,10 +1488,10 @@ struct PartArgs {
   unsigned grid;
   uint32_t region_cap;
 };
-template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM>
+template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM, bool LINK>
 static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
   const size_t smem_p = (size_t)(PART_NCLASS + 1) * CAP * 2;
-  auto kern = k_count_part<W, BOTH, NT, CAP, PER_SM>;
+  auto kern = k_count_part<W, BOTH, NT, CAP, PER_SM, LINK>;
   CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
   kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue, h->d_part_buckets,
                                           a.region_cap, h->d_part_fill, h->d_hist32,
@@ -1499,13 +1499,17 @@ static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
-static int part_cfg_per_sm(int cfg) { return cfg == 1 ? 4 : cfg == 2 ? 6 : 2; }
+// PENG_PART_CFG: geometry 0..2, +4 = without the scan/push interleaving dependencies
+static int part_cfg_per_sm(int cfg) { return (cfg & 3) == 1 ? 4 : (cfg & 3) == 2 ? 6 : 2; }
 template <int W, bool BOTH>
 static int launch_part(peng_handle_t h, int cfg, const PartArgs& a) {
   switch (cfg) {
-    case 1: return launch_part_cfg<W, BOTH, 256, 512, 4>(h, a);
-    case 2: return launch_part_cfg<W, BOTH, 128, 384, 6>(h, a);
-    default: return launch_part_cfg<W, BOTH, 512, 1024, 2>(h, a);
+    case 1: return launch_part_cfg<W, BOTH, 256, 512, 4, true>(h, a);
+    case 2: return launch_part_cfg<W, BOTH, 128, 384, 6, true>(h, a);
+    case 4: return launch_part_cfg<W, BOTH, 512, 1024, 2, false>(h, a);
+    case 5: return launch_part_cfg<W, BOTH, 256, 512, 4, false>(h, a);
+    case 6: return launch_part_cfg<W, BOTH, 128, 384, 6, false>(h, a);
+    default: return launch_part_cfg<W, BOTH, 512, 1024, 2, true>(h, a);
   }
 }
 

@@ -75,15 +75,19 @@ def main():
             out["reference_returncode"] = rr.returncode
             if rr.returncode == 0:
                 out["meme_identical"] = open(os.path.join(d, "ours.meme")).read() == open(os.path.join(d, "ref.meme")).read()
-                out["stdout_same_lines"] = sorted(r.stdout.splitlines()) == sorted(rr.stdout.splitlines())
                 out["speedup"] = out["reference_cpu_seconds"] / out["b200_seconds"]
-                if not out["stdout_same_lines"]:
+                # byte-exact console comparison needs the reference single-threaded: its "Calculating PWMs" loop is an
+                # OpenMP loop whose output lines interleave with more threads
+                t0 = time.perf_counter()
+                r1 = subprocess.run([ref, fasta, "-w", "10", "--threads", "1", "-o", os.path.join(d, "ref1.meme")], capture_output=True, text=True)
+                out["reference_cpu_seconds_1_thread"] = time.perf_counter() - t0
+                out["stdout_identical_vs_1_thread"] = r.stdout == r1.stdout
+                out["meme_identical_vs_1_thread"] = open(os.path.join(d, "ours.meme")).read() == open(os.path.join(d, "ref1.meme")).read()
+                out["stdout_lines"] = len(r.stdout.splitlines())
+                if not out["stdout_identical_vs_1_thread"]:
                     import difflib
-                    out["stdout_diff"] = list(difflib.unified_diff(rr.stdout.splitlines(), r.stdout.splitlines(), "reference", "b200",
+                    out["stdout_diff"] = list(difflib.unified_diff(r1.stdout.splitlines(), r.stdout.splitlines(), "reference", "b200",
                                                                    lineterm="", n=0))[:60]
-                if not out["meme_identical"]:
-                    out["ours_meme_head"] = open(os.path.join(d, "ours.meme")).read()[:1500]
-                    out["ref_meme_head"] = open(os.path.join(d, "ref.meme")).read()[:1500]
     print(json.dumps(out))
 
 
