@@ -817,7 +817,7 @@ __global__ void __launch_bounds__(IUPAC_TILE_WORDS) k_iupac_f32_both(const uint6
 __device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
 
 template <int W>
-__global__ void __launch_bounds__(EM_WARPS * 32) k_em_accumulate_f64(
+__global__ void __launch_bounds__(EM_WARPS * 32, 2) k_em_accumulate_f64(
     const uint64_t* __restrict__ counts, const double* __restrict__ bg, const double* __restrict__ pwms,
     const int* __restrict__ active, double saturation, uint32_t tile_begin, uint32_t tile_end,
     double* __restrict__ partials /* [n_pwm][gridDim.x][W*4] */) {
@@ -845,19 +845,48 @@ __global__ void __launch_bounds__(EM_WARPS * 32) k_em_accumulate_f64(
     for (int q = 5; q < W; q++) pfix *= spwm[q * 4 + ((tile >> (2 * (q - 5))) & 3u)];
     const uint64_t id0 = ((uint64_t)tile << 10) + lane;
     double a2[2] = {0, 0}, a3[4] = {0, 0, 0, 0}, a4[4] = {0, 0, 0, 0};
+    // The 32 ids of a lane are read in four batches of 8 (count and background probability of every id, unconditionally),
+    // the loads of the next batch issued before the arithmetic of the current one: at W >= 12 the tables live in HBM and
+    // a load -> test -> dependent load chain per id left the kernel latency-bound (ncu: long scoreboard 32 stalls per
+    // issue, FP64 pipe 9 %, DRAM 2 %).
+    uint64_t cn[2][8];
+    double bn[2][8];
 #pragma unroll
-    for (int j = 0; j < 32; j++) {
-      const uint64_t id = id0 + 32 * j;
-      const uint64_t cnt = __ldg(counts + id);
-      double term = 0.0;
-      if (cnt) {
-        const double prob = pfix * p2[j & 1] * p3[(j >> 1) & 3] * p4[(j >> 3) & 3];
-        const double sb = saturation * __ldg(bg + id);
-        term = ((double)cnt * saturation) * prob / (prob + sb);
+    for (int k = 0; k < 8; k++) {
+      cn[0][k] = __ldg(counts + id0 + 32 * k);
+      bn[0][k] = __ldg(bg + id0 + 32 * k);
+    }
+#pragma unroll
+    for (int g = 0; g < 4; g++) {
+      if (g < 3) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          cn[(g + 1) & 1][k] = __ldg(counts + id0 + 32 * (8 * (g + 1) + k));
+          bn[(g + 1) & 1][k] = __ldg(bg + id0 + 32 * (8 * (g + 1) + k));
+        }
       }
-      a2[j & 1] += term;
-      a3[(j >> 1) & 3] += term;
-      a4[(j >> 3) & 3] += term;
+      // A batch whose 256 ids are all empty (the usual case in a sparse long-k-mer table) is skipped by the whole warp;
+      // otherwise all 8 terms are evaluated without a per-id branch, so that the 8 dependent FP64 chains (3 multiplies,
+      // the division's Newton steps) overlap.
+      uint64_t any = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) any |= cn[g & 1][k];
+      if (__any_sync(0xffffffffu, any != 0)) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const int j = 8 * g + k;
+          const double prob = pfix * p2[j & 1] * p3[(j >> 1) & 3] * p4[(j >> 3) & 3];
+          const double sb = saturation * bn[g & 1][k];
+          // an empty bin contributes 0; its quotient is formed with numerator count 1 because a zero numerator sends the
+          // FP64 division to its slow path (subroutine call), which at 50 % empty bins doubled the kernel time
+          const uint64_t cnt = cn[g & 1][k];
+          const double q = ((double)(cnt | (uint64_t)(cnt == 0)) * saturation) * prob / (prob + sb);
+          const double term = cnt ? q : 0.0;
+          a2[j & 1] += term;
+          a3[(j >> 1) & 3] += term;
+          a4[(j >> 3) & 3] += term;
+        }
+      }
     }
     const double tot = a2[0] + a2[1];
     // position 0: classes = lane bits 0-1, reduce over bits 2,3,4

@@ -303,6 +303,58 @@ def test_em_random_pwms(gpu, pkg, W, both):
             assert it64 == its64[i] and rel_ok(out64[i], r64), (W, thr, i)
 
 
+def test_long_kmer_tables_iupac_em_W12(gpu, pkg):
+    """The long-k-mer end of the path (BASELINE configs[4] asks for the EM table at large W): every stage at W = 12
+    (16.8 M bins) against the oracle — tables of both arms, IUPAC sums, EM."""
+    W, both = 12, False
+    rng = np.random.RandomState(1212)
+    motif = "TGCTGAGTCAGC"
+    seqs = []
+    for _ in range(300):
+        s = list(rng.choice(list("ACGT"), 150))
+        if rng.rand() < 0.6:
+            p = rng.randint(0, 150 - W)
+            s[p:p + W] = motif
+        seqs.append("".join(s))
+    codes, offs = O.encode(seqs)
+    gpu.ingest_codes(codes, offs)
+    ltot = gpu.count(W, int(both))
+    counts = gpu.get_counts()
+    ref_counts, ref_ltot = O.count(codes, offs, W, both)
+    assert ltot == ref_ltot and np.array_equal(counts, ref_counts)
+    v32 = gpu.background_model(2, precision=pkg.F32REF)
+    v64 = gpu.background_model(2, precision=pkg.F64)
+    gpu.stats(v32, v64, K=2, k=2, max_k=2)
+    bg32 = O.f32.bg_probabilities(v32, W, 2)
+    bg64 = O.f64.bg_probabilities(v64, W, 2)
+    assert np.array_equal(gpu.get_table(pkg.TABLE_BGPROB, pkg.F32REF, 2), bg32)
+    assert rel_ok(gpu.get_table(pkg.TABLE_BGPROB, pkg.F64, 2), bg64)
+    e32, z32, _ = O.f32.stats(counts, bg32, ltot, W)
+    assert np.array_equal(gpu.get_table(pkg.TABLE_EXPECTED, pkg.F32REF), e32)
+    assert np.array_equal(gpu.get_table(pkg.TABLE_ZSCORE, pkg.F32REF), z32)
+    assert np.array_equal(gpu.select_base_patterns(10.0, 3, None, True), O.f32.select(z32, counts, W, 10.0, 3, True, True))
+    ids = [pkg.iupac_id("TGCTGASTCAGC"), pkg.iupac_id("TGCTGANNCAGC"), pkg.iupac_id("WSCTGAGTCAGY")]
+    sites, bgp, ex = gpu.iupac_aggregate(ids, pkg.F32REF)
+    for i, iid in enumerate(ids):
+        a = O.f32.iupac_aggregate(iid, W, both, counts, bg32, e32, len(seqs))
+        assert sites[i] == a["n_sites"] and bgp[i] == a["bg_p"] and ex[i] == a["expected"]
+    pwms = []
+    for i in range(2):
+        pw = rng.dirichlet(np.ones(4) * 0.5, W) * 0.2
+        for p, ch in enumerate(motif):
+            pw[p, "ACGT".index(ch)] += 0.8
+        pw /= pw.sum(1, keepdims=True)
+        pwms.append(pw)
+    pwms = np.array(pwms)
+    out, its = gpu.em(pwms.astype(np.float32), pkg.F32REF, 1e4, 0.08, 3, 2)
+    out64, its64 = gpu.em(pwms, pkg.F64, 1e4, 0.08, 3, 2)
+    for i in range(len(pwms)):
+        r, it = O.f32.em(pwms[i].astype(np.float32), W, counts, bg32, 1e4, 0.08, 3)
+        assert it == its[i] and np.array_equal(out[i], r)
+        r64, it64 = O.f64.em(pwms[i], W, counts, bg64, 1e4, 0.08, 3)
+        assert it64 == its64[i] and rel_ok(out64[i], r64)
+
+
 def test_em_sharded_protocol_single_gpu(gpu, pkg):
     """The multi-GPU EM protocol (index-sliced accumulation + sum of the accumulators) with both slices run
     on one GPU one after the other: must agree with the unsliced result to 1e-9."""
