@@ -182,3 +182,23 @@ def scan_fasta(path):
     for i, ch in enumerate("ACGT"):
         lut[ord(ch)] = lut[ord(ch.lower())] = i + 1
     return lut[letters], offsets
+
+
+def select(z, counts, W, z_threshold=10.0, count_threshold=3, single_stranded=False, filter_neighbors=True):
+    """host_ingest.h: select_base_patterns (pruned introsort) -> selected ids"""
+    z = np.ascontiguousarray(z, np.float32)
+    counts = np.ascontiguousarray(counts, np.uint64)
+    out = np.zeros(len(z), np.uint64)
+    lib.sim_select.restype = C.c_uint64
+    n = lib.sim_select(_p(z, f32p), _p(counts, u64p), C.c_int(W), C.c_float(z_threshold), C.c_uint64(count_threshold),
+                       C.c_int(int(single_stranded)), C.c_int(int(filter_neighbors)), _p(out, u64p), C.c_uint64(len(out)))
+    return out[:n].copy()
+
+
+def sort_leading(z, threshold):
+    """-> (guaranteed length, order left by the pruned sort, order left by std::sort)"""
+    z = np.ascontiguousarray(z, np.float32)
+    a, b = np.zeros(len(z), np.uint64), np.zeros(len(z), np.uint64)
+    lib.sim_sort_leading.restype = C.c_uint64
+    lead = lib.sim_sort_leading(_p(z, f32p), C.c_uint64(len(z)), C.c_float(threshold), _p(a, u64p), _p(b, u64p))
+    return int(lead), a, b

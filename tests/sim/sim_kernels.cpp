@@ -291,3 +291,23 @@ int sim_scan_fasta(const char* path, uint64_t* n_seq, uint64_t* n_letters, char*
   return 0;
 }
 }
+
+// ---- seed selection (host_ingest.h: select_base_patterns with the pruned introsort) and the leading part of the sort ----
+extern "C" {
+uint64_t sim_select(const float* z, const uint64_t* counts, int W, float z_threshold, uint64_t count_threshold, int single_stranded,
+                    int filter_neighbors, uint64_t* out, uint64_t cap) {
+  std::vector<uint64_t> sel = peng_host::select_base_patterns(z, counts, W, z_threshold, count_threshold, single_stranded != 0,
+                                                              filter_neighbors != 0);
+  for (size_t i = 0; i < sel.size() && i < cap; i++) out[i] = sel[i];
+  return sel.size();
+}
+// leading = ids the pruned sort guarantees, full = plain std::sort of all n ids; returns the guaranteed length
+uint64_t sim_sort_leading(const float* z, uint64_t n, float threshold, uint64_t* leading, uint64_t* full) {
+  std::vector<size_t> a(n), b(n);
+  for (size_t i = 0; i < n; i++) a[i] = b[i] = i;
+  const size_t lead = peng_host::sort_leading_ids(a, z, threshold);
+  std::sort(b.begin(), b.end(), peng_host::ByZDescending{z});
+  for (size_t i = 0; i < n; i++) { leading[i] = a[i]; full[i] = b[i]; }
+  return lead;
+}
+}

@@ -217,3 +217,53 @@ def test_scan_fasta_edge_files(text):
 def test_scan_fasta_missing_file():
     with pytest.raises(ValueError):
         S.scan_fasta("/nonexistent/file.fa")
+
+
+# ---- seed selection: the pruned introsort must leave the ids with z >= threshold exactly where std::sort leaves them ----
+def _z_tables(seed, n):
+    """tie-heavy z tables: reverse-complement-like exact pairs, plateaus of equal values, a few large values"""
+    rng = np.random.RandomState(seed)
+    kind = seed % 4
+    if kind == 0:
+        z = rng.standard_normal(n).astype(np.float32)
+    elif kind == 1:
+        z = np.round(rng.standard_normal(n) * 3).astype(np.float32)  # ~20 distinct values: massive ties
+    elif kind == 2:
+        half = rng.standard_normal(n // 2).astype(np.float32) * 4
+        z = np.concatenate([half, half[::-1]])  # every value exactly twice
+    else:
+        z = np.sort(rng.standard_normal(n).astype(np.float32) * 5)[:: -1 if seed % 8 == 3 else 1].copy()  # sorted / reversed
+    hot = rng.choice(n, 200, replace=False)
+    z[hot] = np.round(rng.uniform(5, 60, 200), 1).astype(np.float32)
+    z[hot[:50]] = z[hot[50:100]]  # exact ties among the large values too
+    return z
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_pruned_sort_matches_std_sort(seed):
+    n = 4 ** 8 if seed % 2 else 4 ** 9
+    z = _z_tables(seed, n)
+    for thr in (10.0, 3.0, 0.0, -1.0, 1e9, -1e9):
+        lead, a, b = S.sort_leading(z, thr)
+        k = int((z >= thr).sum())
+        assert lead >= k, (thr, lead, k)
+        assert np.array_equal(a[:k], b[:k]), thr
+        assert (z[a[lead:].astype(np.int64)] < thr).all()
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_select_matches_oracle(seed):
+    W = 8
+    n = 4 ** W
+    z = _z_tables(seed, n)
+    counts = np.random.RandomState(100 + seed).randint(0, 8, n).astype(np.uint64)
+    for thr, ct, single, fn in ((10.0, 3, False, True), (3.0, 1, True, False), (0.5, 2, False, False)):
+        assert np.array_equal(S.select(z, counts, W, thr, ct, single, fn), O.f32.select(z, counts, W, thr, ct, single, fn))
+
+
+def test_select_with_nan_falls_back_to_plain_sort():
+    W = 8
+    z = _z_tables(1, 4 ** W)
+    z[123] = np.nan
+    lead, a, b = S.sort_leading(z, 10.0)
+    assert lead == len(z) and np.array_equal(a, b)
