@@ -63,8 +63,8 @@ int peng_cuda_synchronize(peng_handle_t h);
 
 /* Device-side timing of the phases of the last peng_cuda_count[_local] call (CUDA events on the handle's stream,
  * recorded only while enabled): phase 0 = k-mer start marking (fused into stage P on the partition path),
- * 1 = the counting kernel(s), 2 = fold; partition path only: 3 = stage P, 4 = slow units, 5 = stage H of the first
- * chunk of <= 2^30 stream positions (the only one for sets up to 1 Gbp).
+ * 1 = the counting kernel(s), 2 = fold; partition path only: 3 = stage P, 4 = slow units, 5 = stage H, 6 = stage P2
+ * (deep path of W >= 12, else 0) of the first chunk of <= 2^30 stream positions (the only one for sets up to 1 Gbp).
  * This is how bench.py measures the dominant kernel's duration for the roofline without a profiler. */
 int peng_cuda_enable_timing(peng_handle_t h, int on);
 int peng_cuda_get_timing(peng_handle_t h, int phase, float* milliseconds);
@@ -109,9 +109,11 @@ int peng_cuda_background_finish(peng_handle_t h, int K, const float* alpha, int 
  * ltot = number of W-mers looked at (BasePattern::getLtot). */
 int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* ltot);
 int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts /* 4^W */); /* BasePattern::getPatternCounter */
-/* Counting kernel family for W = 10: 0 = automatic (partition path from 4 M stream positions on), 1 = one L2 atomic
- * per counted W-mer (k_count_global), 2 = partition path (k_count_part / k_count_slow / k_hist_part: shared-memory
- * histograms per id range).  Both produce the same table bit for bit; other pattern lengths ignore the setting. */
+/* Counting kernel family for W >= 10: 0 = automatic (partition path from 4 M stream positions on), 1 = one L2 atomic
+ * per counted W-mer (k_count_global), 2 = partition path (W = 10: k_count_part / k_count_slow / k_hist_part, shared-
+ * memory histograms per id range; W = 12, 14, 16: the deep path k_count_part / k_count_slow / k_part2 / k_hist_leaf),
+ * 3 = as 2 with the second stage of the deep path replaced by one L2 RED per id (k_hist_l2; a cross-check for tests).
+ * All produce the same table bit for bit; shorter pattern lengths ignore the setting. */
 int peng_cuda_set_count_path(peng_handle_t h, int path);
 int peng_cuda_last_count_path(peng_handle_t h); /* 1 or 2: what the last peng_cuda_count[_local] ran */
 /* Multi-GPU: peng_cuda_count_local leaves the UNMIRRORED local histogram + ltot on the device;

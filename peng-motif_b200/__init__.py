@@ -278,7 +278,7 @@ class PengCuda:
         return ltot.value
 
     def set_count_path(self, path):
-        """0 auto, 1 L2-atomic kernel, 2 partition path (W = 10)."""
+        """0 auto, 1 L2-atomic kernel, 2 partition path (W >= 10), 3 partition path with L2-RED second stage (W >= 12)."""
         self._ck(self.lib.peng_cuda_set_count_path(self.h, int(path)))
 
     @property

@@ -300,7 +300,7 @@ PENG_HD void cand_init(CandState& st) {
 // (ff) lag d: W consecutive equalities x[p] == x[p-d] starting at p
 template <int W>
 PENG_HD void cand_ff_lag(const uint32_t* cw, int d, CandState& st) {
-  static_assert(W >= 4 && W <= 10 && (W % 2) == 0, "window arithmetic assumes W-1 <= 9 lags inside one word");
+  static_assert(W >= 4 && W <= 16 && (W % 2) == 0, "window arithmetic assumes W-1 <= 15 lags inside one word");
   uint32_t e[3];  // e[j] bit 2k: x[p] == x[p-d] at p = 16(j+1) + k
 #pragma unroll
   for (int j = 0; j < 3; j++) {
@@ -308,8 +308,8 @@ PENG_HD void cand_ff_lag(const uint32_t* cw, int d, CandState& st) {
     e[j] = ~(t | (t >> 1)) & 0x55555555u;
   }
   // runs by doubling: r2, r4, r8 = runs of 2, 4, 8; the third word only has to be right for its low positions
-  // (zeros shifted in at its top)
-  uint32_t r2[3], r4[3], r8[2];
+  // (zeros shifted in at its top): a run that starts at position 31 of the unit ends at 31 + 15 = 46 < 48
+  uint32_t r2[3], r4[3], r8[3];
   r2[0] = e[0] & funnel_r(e[0], e[1], 2u);
   r2[1] = e[1] & funnel_r(e[1], e[2], 2u);
   r2[2] = e[2] & (e[2] >> 2);
@@ -318,10 +318,17 @@ PENG_HD void cand_ff_lag(const uint32_t* cw, int d, CandState& st) {
   r4[2] = r2[2] & (r2[2] >> 4);
   r8[0] = r4[0] & funnel_r(r4[0], r4[1], 8u);
   r8[1] = r4[1] & funnel_r(r4[1], r4[2], 8u);
+  r8[2] = r4[2] & (r4[2] >> 8);
   if (W == 4) { st.c1 |= r4[0]; st.c2 |= r4[1]; }
   if (W == 6) { st.c1 |= r4[0] & funnel_r(r2[0], r2[1], 8u); st.c2 |= r4[1] & funnel_r(r2[1], r2[2], 8u); }
   if (W == 8) { st.c1 |= r8[0]; st.c2 |= r8[1]; }
   if (W == 10) { st.c1 |= r8[0] & funnel_r(r2[0], r2[1], 16u); st.c2 |= r8[1] & funnel_r(r2[1], r2[2], 16u); }
+  if (W == 12) { st.c1 |= r8[0] & funnel_r(r4[0], r4[1], 16u); st.c2 |= r8[1] & funnel_r(r4[1], r4[2], 16u); }
+  if (W == 14) {
+    st.c1 |= r8[0] & funnel_r(r4[0], r4[1], 16u) & funnel_r(r2[0], r2[1], 24u);
+    st.c2 |= r8[1] & funnel_r(r4[1], r4[2], 16u) & funnel_r(r2[1], r2[2], 24u);
+  }
+  if (W == 16) { st.c1 |= r8[0] & funnel_r(r8[0], r8[1], 16u); st.c2 |= r8[1] & funnel_r(r8[1], r8[2], 16u); }
 }
 // (rc) arm i of the palindromes: x[m+1+i] complementary to x[m-i]; i = 0 .. W/2
 PENG_HD void cand_rc_arm(const uint32_t* cw, int i, CandState& st) {

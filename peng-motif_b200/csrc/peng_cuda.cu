@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/peng_cuda.h"
@@ -78,10 +79,16 @@ struct peng_cuda_ctx {
   uint2* d_slow_list = nullptr;
   size_t slow_list_elems = 0;
   unsigned int* d_slow_count = nullptr;
+  // ---- deep partition path (W >= 12): bucket levels 1 (32-bit ids), 2a (32-bit, W = 16 only), 2 (16-bit leaf entries) ----
+  void* d_deep_buckets[3] = {nullptr, nullptr, nullptr};
+  size_t deep_bucket_bytes[3] = {0, 0, 0};
+  uint32_t* d_deep_fill[3] = {nullptr, nullptr, nullptr};
+  size_t deep_fill_elems[3] = {0, 0, 0};
+  int deep_mode = 0;               // 0: stage P -> P2 -> leaf histograms, 1: stage P -> L2 REDs (reference variant, tests)
 
   // ---- phase timing (bench) ----
   bool timing = false;
-  cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   // ---- scratch ----
   void* d_scratch = nullptr;
@@ -327,44 +334,87 @@ __host__ __device__ __forceinline__ uint32_t part_class_start(uint32_t c) {  // 
   return (uint32_t)((((uint64_t)c << 20) + PART_NCLASS - 1) / PART_NCLASS);
 }
 
-// One push: class c = floor(key * NCLASS / 2^20) as a single high multiply, slot = cnt[c]++, 16-bit store if the slot
+// Class geometry of stage P.
+//   W = 10 : 37 id ranges of 28 340 bins (one shared-memory histogram each in stage H), 16-bit entries (the low half of
+//            the id; a class spans < 2^16 ids).
+//   W >= 12: "deep" partition path (see k_part2 / k_hist_leaf below): 32 classes = the top 5 bits of the 2W-bit id, 32-bit
+//            entries (the whole id); stage P2 splits every class again until a leaf of 2^15 bins fits shared memory.
+template <int W>
+struct PartGeom {
+  static constexpr uint32_t NCLASS = 32;
+  typedef uint32_t entry_t;
+  typedef uint4 vec_t;  // 4 entries
+  __device__ __forceinline__ static uint32_t cls(uint32_t key) { return key >> (2 * W - 5); }
+  __device__ __forceinline__ static uint32_t id_of(uint32_t e, uint32_t) { return e; }
+};
+template <>
+struct PartGeom<10> {
+  static constexpr uint32_t NCLASS = PART_NCLASS;
+  typedef uint16_t entry_t;
+  typedef uint2 vec_t;
+  __device__ __forceinline__ static uint32_t cls(uint32_t key) { return __umulhi(key, (uint32_t)PART_NCLASS << 12); }
+  __device__ __forceinline__ static uint32_t id_of(uint32_t e, uint32_t c) {
+    const uint32_t start = part_class_start(c);
+    return start + ((e - start) & 0xFFFFu);
+  }
+};
+
+// One push: class c (W = 10: floor(key * NCLASS / 2^20) as a single high multiply), slot = cnt[c]++, store if the slot
 // exists.  W-mers that are not pushed go to a scratch queue: ptxas turns a PREDICATED returning shared atomic into a
 // branch (BSSY / BRA / BSYNC per push), an unconditional one on a dummy counter is cheaper.  Stage P is bound by the
 // half-rate ALU pipe (ncu: pipe_alu 75 %), so the address arithmetic is written as multiply-adds (FMA pipe).
-template <uint32_t CAP>
+template <int W, uint32_t CAP>
 __device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t push, uint32_t cnt_s, uint32_t q_s) {
-  uint32_t c = __umulhi(key, (uint32_t)PART_NCLASS << 12);
-  c = push ? c : PART_NCLASS;
+  typedef PartGeom<W> G;
+  uint32_t c = G::cls(key);
+  c = push ? c : G::NCLASS;
   const uint32_t cnt_addr = c * 4u + cnt_s;
-  const uint32_t base = c * (CAP * 2u) + q_s;
+  const uint32_t base = c * (CAP * (uint32_t)sizeof(typename G::entry_t)) + q_s;
   uint32_t slot;
-  asm volatile(
-      "{\n\t.reg .pred q;\n\t.reg .u32 a;\n\t"
-      "atom.shared.add.u32 %0, [%1], 1;\n\t"
-      "setp.lt.u32 q, %0, %2;\n\t"
-      "mad.lo.u32 a, %0, 2, %3;\n\t"
-      "@q st.shared.u16 [a], %4;\n\t}"
-      : "=r"(slot)
-      : "r"(cnt_addr), "r"(CAP), "r"(base), "h"((uint16_t)key)
-      : "memory");
+  if constexpr (sizeof(typename G::entry_t) == 2) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t.reg .u32 a;\n\t"
+        "atom.shared.add.u32 %0, [%1], 1;\n\t"
+        "setp.lt.u32 q, %0, %2;\n\t"
+        "mad.lo.u32 a, %0, 2, %3;\n\t"
+        "@q st.shared.u16 [a], %4;\n\t}"
+        : "=r"(slot)
+        : "r"(cnt_addr), "r"(CAP), "r"(base), "h"((uint16_t)key)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t.reg .u32 a;\n\t"
+        "atom.shared.add.u32 %0, [%1], 1;\n\t"
+        "setp.lt.u32 q, %0, %2;\n\t"
+        "mad.lo.u32 a, %0, 4, %3;\n\t"
+        "@q st.shared.u32 [a], %4;\n\t}"
+        : "=r"(slot)
+        : "r"(cnt_addr), "r"(CAP), "r"(base), "r"(key)
+        : "memory");
+  }
   return slot;
 }
 
 template <int W, bool BOTH, int PART_NT, uint32_t PART_CAP, int MINB, bool LINK>
 __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
-    uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, uint16_t* __restrict__ buckets, uint32_t region_cap,
+    uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, typename PartGeom<W>::entry_t* __restrict__ buckets, uint32_t region_cap,
     uint32_t* __restrict__ fill_out, uint32_t* __restrict__ hist, unsigned long long* __restrict__ ltot,
     uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count, uint32_t zero) {
-  static_assert(W == 10, "class geometry is laid out for 4^10 ids");
-  constexpr uint32_t KEYMASK = (1u << (2 * W)) - 1u;
-  extern __shared__ uint16_t q[];  // [PART_NCLASS + 1][PART_CAP]
-  __shared__ uint32_t cnt[PART_NCLASS + 1], prev[PART_NCLASS], fill[PART_NCLASS], ovf[PART_NCLASS];
+  static_assert(W >= 10 && W <= 16, "class geometries exist for 4^10 ids (one level) and 4^12 .. 4^16 ids (deep path)");
+  typedef PartGeom<W> G;
+  typedef typename G::entry_t entry_t;
+  typedef typename G::vec_t vec_t;
+  constexpr uint32_t PART_NCLASS_ = G::NCLASS;
+  constexpr uint32_t KEYMASK = W == 16 ? 0xFFFFFFFFu : (1u << (2 * (W & 15))) - 1u;
+  extern __shared__ __align__(16) unsigned char q_raw[];
+  entry_t* q = reinterpret_cast<entry_t*>(q_raw);  // [NCLASS + 1][PART_CAP]
+  __shared__ uint32_t cnt[PART_NCLASS_ + 1], prev[PART_NCLASS_], fill[PART_NCLASS_], ovf[PART_NCLASS_];
   __shared__ uint32_t any_ovf, n_slow, slow_base;
   __shared__ uint2 slow_q[PART_SLOWCAP];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x < PART_NCLASS) { cnt[threadIdx.x] = 0; prev[threadIdx.x] = 0; fill[threadIdx.x] = 0; ovf[threadIdx.x] = 0; }
-  if (threadIdx.x == 0) { cnt[PART_NCLASS] = 0; any_ovf = 0; n_slow = 0; }
+  if (threadIdx.x < PART_NCLASS_) { cnt[threadIdx.x] = 0; prev[threadIdx.x] = 0; fill[threadIdx.x] = 0; ovf[threadIdx.x] = 0; }
+  if (threadIdx.x == 0) { cnt[PART_NCLASS_] = 0; any_ovf = 0; n_slow = 0; }
   __syncthreads();
   const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(cnt), q_s = (uint32_t)__cvta_generic_to_shared(q);
   const uint64_t n_units = unit_end - unit_begin;
@@ -397,7 +447,8 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     return Unit{cw[1], cw[2], cw[3], ks & ~cand, ks & cand, u};
   };
   typedef CandSteps<W, BOTH> Steps;
-  static_assert(Steps::N <= 16, "one scan step per two pushes");
+  constexpr bool STEP_PER_PUSH = Steps::N > 16;  // W >= 12: one scan step behind every push instead of every other
+  static_assert(Steps::N <= 32, "at most one scan step per push");
   uint32_t un = scan_begin(blockIdx.x);
 #pragma unroll
   for (int I = 0; I < Steps::N; I++) Steps::run(I, cw, cs);
@@ -412,10 +463,11 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     for (int i = 0; i < 32; i++) {
       uint32_t key = (i < 16 ? __funnelshift_r(w1, w2, 2 * i) : __funnelshift_r(w2, w3, 2 * (i - 16))) & KEYMASK;
       key ^= link;
-      const uint32_t slot = part_push<PART_CAP>(key, fast & (1u << i), cnt_s, q_s);
-      if ((i & 1) && (i >> 1) < Steps::N) {
+      const uint32_t slot = part_push<W, PART_CAP>(key, fast & (1u << i), cnt_s, q_s);
+      const int step = STEP_PER_PUSH ? i : (i >> 1);
+      if ((STEP_PER_PUSH || (i & 1)) && step < Steps::N) {
         if (LINK) cw[2] ^= slot & zero;
-        Steps::run(i >> 1, cw, cs);
+        Steps::run(step, cw, cs);
         if (LINK) link = (cs.c1 | cs.p[0]) & zero;
       }
     }
@@ -427,7 +479,7 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     }
     __syncthreads();
     // ---- flush: warp w owns classes w, w+16, w+32 ----
-    for (uint32_t c = warp; c < PART_NCLASS; c += PART_NT / 32) {
+    for (uint32_t c = warp; c < PART_NCLASS_; c += PART_NT / 32) {
       const uint32_t n = cnt[c];
       if (n > PART_CAP) {  // this round did not fit: roll the queue back, the round's keys of c are redone below
         if (lane == 0) { ovf[c] = 1; any_ovf = 1; cnt[c] = prev[c]; }
@@ -436,24 +488,23 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
       const uint32_t nfl = n & ~127u;
       if (nfl) {
         const uint32_t base = fill[c];
-        const uint16_t* src = q + c * PART_CAP;
+        const entry_t* src = q + c * PART_CAP;
         if (base + nfl <= region_cap) {
-          uint16_t* dst = buckets + ((uint64_t)c * gridDim.x + blockIdx.x) * region_cap + base;
-          for (uint32_t i = lane * 4; i < nfl; i += 128) *(uint2*)(dst + i) = *(const uint2*)(src + i);
+          entry_t* dst = buckets + ((uint64_t)c * gridDim.x + blockIdx.x) * region_cap + base;
+          for (uint32_t i = lane * 4; i < nfl; i += 128) *(vec_t*)(dst + i) = *(const vec_t*)(src + i);
           if (lane == 0) fill[c] = base + nfl;
         } else {  // private bucket region full: straight to the global table
-          const uint32_t start = part_class_start(c);
-          for (uint32_t i = lane; i < nfl; i += 32) atomicAdd(hist + start + (((uint32_t)src[i] - start) & 0xFFFFu), 1u);
+          for (uint32_t i = lane; i < nfl; i += 32) atomicAdd(hist + G::id_of((uint32_t)src[i], c), 1u);
         }
         const uint32_t rem = n - nfl;
-        uint2 v = make_uint2(0, 0);
-        if (lane * 4 < rem) v = *(const uint2*)(src + nfl + lane * 4);
+        vec_t v = vec_t();
+        if (lane * 4 < rem) v = *(const vec_t*)(src + nfl + lane * 4);
         __syncwarp();
-        if (lane * 4 < rem) *(uint2*)(q + c * PART_CAP + lane * 4) = v;
+        if (lane * 4 < rem) *(vec_t*)(q + c * PART_CAP + lane * 4) = v;
         if (lane == 0) { cnt[c] = rem; prev[c] = rem; }
       } else if (lane == 0) prev[c] = n;
     }
-    if (threadIdx.x == 0) cnt[PART_NCLASS] = 0;
+    if (threadIdx.x == 0) cnt[PART_NCLASS_] = 0;
     if (warp == PART_NT / 32 - 1) {  // slow units of this round -> global list (one global atomic per CTA round)
       const uint32_t ns = min(n_slow, PART_SLOWCAP);
       if (ns) {
@@ -471,22 +522,21 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
       for (int i = 0; i < 32; i++) {
         if (fast & (1u << i)) {
           const uint32_t key = (i < 16 ? __funnelshift_r(w1, w2, 2 * i) : __funnelshift_r(w2, w3, 2 * (i - 16))) & KEYMASK;
-          if (ovf[(key * PART_NCLASS) >> 20]) atomicAdd(hist + key, 1u);
+          if (ovf[G::cls(key)]) atomicAdd(hist + key, 1u);
         }
       }
       __syncthreads();
-      if (threadIdx.x < PART_NCLASS) ovf[threadIdx.x] = 0;
+      if (threadIdx.x < PART_NCLASS_) ovf[threadIdx.x] = 0;
       if (threadIdx.x == 0) any_ovf = 0;
       __syncthreads();
     }
     cur = nxt;
   }
   // leftovers (< 128 per class and CTA): straight to the global table
-  for (uint32_t c = warp; c < PART_NCLASS; c += PART_NT / 32) {
+  for (uint32_t c = warp; c < PART_NCLASS_; c += PART_NT / 32) {
     if (lane == 0) fill_out[c * gridDim.x + blockIdx.x] = fill[c];
     const uint32_t n = cnt[c];
-    const uint32_t start = part_class_start(c);
-    for (uint32_t i = lane; i < n; i += 32) atomicAdd(hist + start + (((uint32_t)q[c * PART_CAP + i] - start) & 0xFFFFu), 1u);
+    for (uint32_t i = lane; i < n; i += 32) atomicAdd(hist + G::id_of((uint32_t)q[c * PART_CAP + i], c), 1u);
   }
   for (int o = 16; o > 0; o >>= 1) my_ltot += __shfl_xor_sync(0xffffffffu, my_ltot, o);
   if (lane == 0 && my_ltot) atomicAdd(ltot, (unsigned long long)my_ltot);
@@ -544,6 +594,272 @@ __global__ void __launch_bounds__(PART_HT) k_hist_part(const uint16_t* __restric
   for (uint32_t i = threadIdx.x; i < nb; i += PART_HT) {
     const uint32_t v = bins[i];
     if (v) atomicAdd(hist + start + i, v);
+  }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// Deep partition path (W = 12, 14, 16): 4^W bins neither fit one SM (W = 10: 37 classes did) nor, from W = 14 on, the
+// L2 — one RED per counted W-mer then pays a DRAM read-modify-write of a 32-byte sector (W = 14: 24 Gbases/s).
+// Stage P (k_count_part with PartGeom<W>) splits the ids by their top 5 bits into 32-bit entries; stage P2 (k_part2)
+// splits every class again by the next NC2 bits — into 32-bit entries while more than 15 + 8 bits are left (W = 16),
+// finally into 16-bit entries holding the low 15 bits — and stage H (k_hist_leaf) builds each leaf of 2^15 bins in
+// shared memory and adds it to the table with coalesced plain read-modify-writes (a leaf has one owner CTA).
+// Every stage writes CTA-private regions (no global atomics), keeps exactness under skew the way stage P does (queue
+// overflow: roll the round back, its keys of that class go straight to the table; region full: same per block).
+#define DEEP_LEAF_BITS 15
+#define DEEP_P2_NT 256
+#define DEEP_P2_KPT 16  // keys per thread and round (4 x 16-byte loads)
+#define DEEP_P2_NQ 256  // shared-memory queues per CTA: one per lane of its 8 warps in the flush
+
+// Stage P2.  in : regions [c1][r] of in_cap 32-bit ids, in_fill[c1 * n_in + r] of them valid (multiple of 4);
+// CTA (c1, g) owns the input regions r = g, g + G, ... of class c1.  A key goes to queue
+//   qi = (class field << SUB_BITS) | (lane & (2^SUB_BITS - 1)),   class field = (id >> shift) & (2^NC2_BITS - 1):
+// few classes (W = 12: 16) are spread over sub-queues so that the slot atomics of a warp do not pile up on a handful
+// of counters.  Queue qi of CTA g flushes whole 64-entry blocks to its private region
+//   [(leaf * G + g) << SUB_BITS | sub],  leaf = c1 << NC2_BITS | class field,
+// so a leaf owns G << SUB_BITS regions.  Per round a lane owns one queue in the flush (fill / rollback state in registers).
+template <int NC2_BITS, int SUB_BITS, uint32_t CAP, typename OUT_T>
+__global__ void __launch_bounds__(DEEP_P2_NT, 4) k_part2(const uint32_t* __restrict__ in, uint32_t in_cap, uint32_t n_in,
+                                                         const uint32_t* __restrict__ in_fill, uint32_t G, uint32_t shift,
+                                                         OUT_T* __restrict__ out, uint32_t out_cap,
+                                                         uint32_t* __restrict__ out_fill, uint32_t* __restrict__ hist) {
+  static_assert(NC2_BITS + SUB_BITS == 8 && DEEP_P2_NQ == 256 && DEEP_P2_NT == 256, "one queue per lane of the 8 warps");
+  constexpr uint32_t GRAN = 64;  // entries per flushed block
+  constexpr uint32_t NQ = DEEP_P2_NQ, CMASK = (1u << NC2_BITS) - 1u, SMASK = (1u << SUB_BITS) - 1u;
+  extern __shared__ __align__(16) unsigned char q_raw[];
+  OUT_T* q = reinterpret_cast<OUT_T*>(q_raw);  // [NQ + 1][CAP]
+  __shared__ uint32_t cnt[NQ + 1];
+  __shared__ uint8_t ovf[NQ];
+  __shared__ uint32_t any_ovf;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  cnt[threadIdx.x] = 0;
+  ovf[threadIdx.x] = 0;
+  if (threadIdx.x == 0) { cnt[NQ] = 0; any_ovf = 0; }
+  __syncthreads();
+  const uint32_t c1 = blockIdx.x / G, g = blockIdx.x % G;
+  const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(cnt), q_s = (uint32_t)__cvta_generic_to_shared(q);
+  const uint32_t sub = lane & SMASK;
+  // flush ownership: this thread owns queue myq = threadIdx.x
+  const uint32_t myq = threadIdx.x;
+  const uint32_t my_leaf = (c1 << NC2_BITS) | (myq >> SUB_BITS);
+  const uint64_t my_region = ((uint64_t)(my_leaf * G + g) << SUB_BITS) | (myq & SMASK);
+  uint32_t my_fill = 0, my_prev = 0;
+  constexpr uint32_t ROUND = DEEP_P2_NT * DEEP_P2_KPT;
+  // The CTA walks (region r, offset base) round by round; the keys of round i + 1 are loaded right behind the pushes of
+  // round i (into the same registers), so that their latency hides behind the barrier and the flush.
+  uint32_t r = g, base = 0, n = 0;
+  while (r < n_in && (n = in_fill[c1 * n_in + r]) == 0) r += G;
+  uint32_t key[DEEP_P2_KPT];
+  uint32_t live = 0;
+  auto load_round = [&](uint32_t rr, uint32_t bb, uint32_t nn) {
+    const uint4* src = reinterpret_cast<const uint4*>(in + ((uint64_t)c1 * n_in + rr) * in_cap);
+    live = 0;
+#pragma unroll
+    for (int j = 0; j < DEEP_P2_KPT / 4; j++) {
+      const uint32_t i = bb + (j * DEEP_P2_NT + threadIdx.x) * 4;  // nn is a multiple of 4: a 16-byte group is whole
+      const bool ok = i < nn;
+      const uint4 v = ok ? __ldg(src + (i >> 2)) : make_uint4(0, 0, 0, 0);
+      key[4 * j] = v.x; key[4 * j + 1] = v.y; key[4 * j + 2] = v.z; key[4 * j + 3] = v.w;
+      live |= ok ? (0xFu << (4 * j)) : 0u;
+    }
+  };
+  if (r < n_in) load_round(r, base, n);
+  while (r < n_in) {
+    {
+      const uint32_t cur_r = r, cur_base = base, cur_n = n;
+      // ---- pushes: slot atomics in batches of 8 (their results are not awaited one by one), then the stores ----
+#pragma unroll
+      for (int k0 = 0; k0 < DEEP_P2_KPT; k0 += 8) {
+        uint32_t slot[8], qb[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          uint32_t c = (((key[k0 + k] >> shift) & CMASK) << SUB_BITS) | sub;
+          c = (live >> (k0 + k)) & 1u ? c : NQ;
+          qb[k] = c * (CAP * (uint32_t)sizeof(OUT_T)) + q_s;
+          asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot[k]) : "r"(c * 4u + cnt_s) : "memory");
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          if constexpr (sizeof(OUT_T) == 2) {
+            asm volatile(
+                "{\n\t.reg .pred q;\n\t.reg .u32 a;\n\t"
+                "setp.lt.u32 q, %0, %1;\n\t"
+                "mad.lo.u32 a, %0, 2, %2;\n\t"
+                "@q st.shared.u16 [a], %3;\n\t}"
+                :: "r"(slot[k]), "r"(CAP), "r"(qb[k]), "h"((uint16_t)(key[k0 + k] & ((1u << DEEP_LEAF_BITS) - 1u)))
+                : "memory");
+          } else {
+            asm volatile(
+                "{\n\t.reg .pred q;\n\t.reg .u32 a;\n\t"
+                "setp.lt.u32 q, %0, %1;\n\t"
+                "mad.lo.u32 a, %0, 4, %2;\n\t"
+                "@q st.shared.u32 [a], %3;\n\t}"
+                :: "r"(slot[k]), "r"(CAP), "r"(qb[k]), "r"(key[k0 + k])
+                : "memory");
+          }
+        }
+      }
+      // ---- next round's keys ----
+      base += ROUND;
+      while (r < n_in && base >= n) {
+        r += G;
+        base = 0;
+        n = r < n_in ? in_fill[c1 * n_in + r] : 0;
+      }
+      if (r < n_in) load_round(r, base, n);
+      __syncthreads();
+      // ---- flush: lane l of warp w owns queue 32 w + l.  The four 8-lane groups of the warp work on four queues at a
+      // time (one 64-entry block = 8 lanes x 16 bytes of 16-bit entries): group s walks the full queues among 8 s .. 8 s + 7.
+      {
+        uint32_t nq = cnt[myq];
+        const bool over = nq > CAP;  // this round did not fit: roll the queue back, its keys of the round are redone below
+        if (over) { ovf[myq] = 1; any_ovf = 1; cnt[myq] = my_prev; nq = my_prev; }
+        const bool full = nq >= GRAN;  // my_prev < GRAN: a rolled-back queue has nothing to flush
+        if (!full) my_prev = nq;
+        uint32_t m = __ballot_sync(0xffffffffu, full);
+        const uint32_t grp = lane >> 3, gl = lane & 7;
+        while (m) {
+          const uint32_t mg = (m >> (8 * grp)) & 0xFFu;  // this group's full queues
+          const bool act = mg != 0;
+          const uint32_t l = act ? 8 * grp + (uint32_t)__ffs(mg) - 1u : lane;
+          m &= ~((mg & (0u - mg)) << (8 * grp));
+          m = __reduce_and_sync(0xffffffffu, m);  // every group cleared its own bit
+          const uint32_t qi = warp * 32 + l;
+          const uint32_t n_l = __shfl_sync(0xffffffffu, nq, l), fb = __shfl_sync(0xffffffffu, my_fill, l);
+          const uint32_t nfl_l = n_l & ~(GRAN - 1);
+          OUT_T* qs = q + qi * CAP;
+          const uint64_t region = ((uint64_t)(((c1 << NC2_BITS) | (qi >> SUB_BITS)) * G + g) << SUB_BITS) | (qi & SMASK);
+          const bool fits = fb + nfl_l <= out_cap;
+          if (act) {
+            if (fits) {
+              OUT_T* dst = out + region * out_cap + fb;
+              for (uint32_t i = gl * 8; i < nfl_l; i += GRAN) {  // one trip unless a queue took >= 2 blocks in a round
+#pragma unroll
+                for (uint32_t v = 0; v < sizeof(OUT_T) / 2; v++)
+                  *(uint4*)((unsigned char*)(dst + i) + 16 * v) = *(const uint4*)((const unsigned char*)(qs + i) + 16 * v);
+              }
+            } else {  // region full: straight to the table
+              const uint32_t leaf = (c1 << NC2_BITS) | (qi >> SUB_BITS);
+              for (uint32_t i = gl; i < nfl_l; i += 8) {
+                const uint32_t id = sizeof(OUT_T) == 2 ? ((leaf << DEEP_LEAF_BITS) | (uint32_t)qs[i]) : (uint32_t)qs[i];
+                atomicAdd(hist + id, 1u);
+              }
+            }
+          }
+          // the < 64 entries behind the flushed blocks move to the front (whole 8-entry pieces: what lies behind the
+          // last valid entry is never read)
+          const uint32_t rem = n_l - nfl_l;
+          uint4 mv[sizeof(OUT_T) / 2];
+          const bool mover = act && gl * 8 < rem;
+          if (mover) {
+#pragma unroll
+            for (uint32_t v = 0; v < sizeof(OUT_T) / 2; v++) mv[v] = *(const uint4*)((const unsigned char*)(qs + nfl_l + gl * 8) + 16 * v);
+          }
+          __syncwarp();
+          if (mover) {
+#pragma unroll
+            for (uint32_t v = 0; v < sizeof(OUT_T) / 2; v++) *(uint4*)((unsigned char*)(qs + gl * 8) + 16 * v) = mv[v];
+          }
+          if (act && lane == l) {
+            if (fits) my_fill = fb + nfl_l;
+            cnt[myq] = rem;
+            my_prev = rem;
+          }
+        }
+      }
+      if (threadIdx.x == 0) cnt[NQ] = 0;
+      __syncthreads();
+      if (any_ovf) {  // rare: the round's keys are read again (the registers already hold the next round)
+        const uint4* src = reinterpret_cast<const uint4*>(in + ((uint64_t)c1 * n_in + cur_r) * in_cap);
+#pragma unroll 1
+        for (int j = 0; j < DEEP_P2_KPT / 4; j++) {
+          const uint32_t i = cur_base + (j * DEEP_P2_NT + threadIdx.x) * 4;
+          if (i < cur_n) {
+            const uint4 v = __ldg(src + (i >> 2));
+            const uint32_t ks[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int t = 0; t < 4; t++)
+              if (ovf[(((ks[t] >> shift) & CMASK) << SUB_BITS) | sub]) atomicAdd(hist + ks[t], 1u);
+          }
+        }
+        __syncthreads();
+        ovf[threadIdx.x] = 0;
+        if (threadIdx.x == 0) any_ovf = 0;
+        __syncthreads();
+      }
+    }
+  }
+  // leftovers (< GRAN per queue): straight to the table
+  out_fill[my_region] = my_fill;
+  __syncthreads();
+  for (uint32_t qi = warp; qi < NQ; qi += DEEP_P2_NT / 32) {
+    const uint32_t leaf = (c1 << NC2_BITS) | (qi >> SUB_BITS);
+    const uint32_t nq = cnt[qi];
+    for (uint32_t i = lane; i < nq; i += 32) {
+      const uint32_t e = (uint32_t)q[qi * CAP + i];
+      atomicAdd(hist + (sizeof(OUT_T) == 2 ? ((leaf << DEEP_LEAF_BITS) | e) : e), 1u);
+    }
+  }
+}
+
+// stage H of the deep path: CTA = leaf; regions [leaf][0 .. n_reg) of 16-bit entries (low 15 bits of the id), one region
+// per warp at a time; the leaf's 2^15 bins are built in shared memory and added to the table with 16-byte plain
+// read-modify-writes (this CTA is the only writer of the leaf's bins in this launch).
+__global__ void __launch_bounds__(1024, 1) k_hist_leaf(const uint16_t* __restrict__ buckets, uint32_t region_cap, uint32_t n_reg,
+                                                       const uint32_t* __restrict__ fill, uint32_t* __restrict__ hist) {
+  extern __shared__ __align__(16) uint32_t bins[];
+  constexpr uint32_t NB = 1u << DEEP_LEAF_BITS;
+  __shared__ uint32_t any;
+  const uint32_t leaf = blockIdx.x;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) any = 0;
+  __syncthreads();
+  uint32_t mine = 0;
+  for (uint32_t r = threadIdx.x; r < n_reg; r += 1024) mine |= fill[(uint64_t)leaf * n_reg + r];
+  if (mine) any = 1;
+  uint4* b4 = reinterpret_cast<uint4*>(bins);
+#pragma unroll
+  for (uint32_t i = threadIdx.x; i < NB / 4; i += 1024) b4[i] = make_uint4(0, 0, 0, 0);
+  __syncthreads();
+  if (!any) return;
+  const uint32_t bins_s = (uint32_t)__cvta_generic_to_shared(bins);
+  for (uint32_t r = warp; r < n_reg; r += 32) {
+    const uint32_t n8 = fill[(uint64_t)leaf * n_reg + r] >> 3;  // 16-byte groups (fill is a multiple of 64 entries)
+    const uint4* src = reinterpret_cast<const uint4*>(buckets + ((uint64_t)leaf * n_reg + r) * region_cap);
+#pragma unroll 2
+    for (uint32_t gi = lane; gi < n8; gi += 32) {
+      const uint4 v = __ldg(src + gi);
+      const uint32_t ws[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(bins_s + (ws[k] & 0xFFFFu) * 4u) : "memory");
+        asm volatile("red.shared.add.u32 [%0], 1;" :: "r"(bins_s + (ws[k] >> 16) * 4u) : "memory");
+      }
+    }
+  }
+  __syncthreads();
+  uint4* dst = reinterpret_cast<uint4*>(hist + ((uint64_t)leaf << DEEP_LEAF_BITS));
+  uint4 d[NB / 4 / 1024];
+#pragma unroll
+  for (uint32_t k = 0; k < NB / 4 / 1024; k++) d[k] = dst[threadIdx.x + k * 1024];
+#pragma unroll
+  for (uint32_t k = 0; k < NB / 4 / 1024; k++) {
+    const uint4 v = b4[threadIdx.x + k * 1024];
+    d[k].x += v.x; d[k].y += v.y; d[k].z += v.z; d[k].w += v.w;
+    if (v.x | v.y | v.z | v.w) dst[threadIdx.x + k * 1024] = d[k];
+  }
+}
+
+// Reference variant of the deep path (PENG_DEEP_MODE=1, tests): the 32-bit ids of stage P go to the table with one
+// RED each, class after class, so that the bins in flight (1/32 of the table) stay L2-resident up to W = 14.
+__global__ void __launch_bounds__(512) k_hist_l2(const uint32_t* __restrict__ buckets, uint32_t region_cap, uint32_t n_regions,
+                                                 uint32_t n_class, const uint32_t* __restrict__ fill, uint32_t* __restrict__ hist) {
+  for (uint32_t c = 0; c < n_class; c++) {
+    for (uint32_t r = blockIdx.x; r < n_regions; r += gridDim.x) {
+      const uint32_t n = fill[c * n_regions + r];
+      const uint32_t* src = buckets + ((uint64_t)c * n_regions + r) * region_cap;
+      for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) atomicAdd(hist + __ldg(src + i), 1u);
+    }
   }
 }
 
@@ -1144,6 +1460,7 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
   }
   h->stream = h->own_stream;
   if (const char* e = getenv("PENG_PART_CFG")) h->part_cfg = atoi(e);
+  if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
   *out = h;
   return PENG_OK;
 }
@@ -1175,6 +1492,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   for (int i = 0; i < 2; i++) if (h->pin[i]) cudaFreeHost(h->pin[i]);
   for (int i = 0; i < 2; i++) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
+  for (int i = 0; i < 3; i++) { dev_free(&h->d_deep_buckets[i]); dev_free(&h->d_deep_fill[i]); }
   for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   delete h;
@@ -1192,17 +1510,17 @@ extern "C" int peng_cuda_enable_timing(peng_handle_t h, int on) {
   if (!h) return PENG_E_INVALID;
   CU(h, cudaSetDevice(h->device));
   if (on && !h->ev[0])
-    for (int i = 0; i < 8; i++) CU(h, cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i < 9; i++) CU(h, cudaEventCreate(&h->ev[i]));
   h->timing = on != 0;
   return PENG_OK;
 }
 extern "C" int peng_cuda_get_timing(peng_handle_t h, int phase, float* ms) {
-  if (!h || !h->ev[0] || phase < 0 || phase > 5 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
+  if (!h || !h->ev[0] || phase < 0 || phase > 6 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
   CU(h, cudaSetDevice(h->device));
   CU(h, cudaEventSynchronize(h->ev[5]));
   // events: 0 start | 1 k-mer starts marked | 4 counting done | 5 folded; of the first chunk of the partition path:
-  // 6 stage P launched | 2 stage P done | 3 slow units done | 7 stage H done
-  static const int from[6] = {0, 1, 4, 6, 2, 3}, to[6] = {1, 4, 5, 2, 3, 7};
+  // 6 stage P launched | 2 stage P done | 3 slow units done | 8 stage P2 done (deep path, else = 3) | 7 stage H done
+  static const int from[7] = {0, 1, 4, 6, 2, 8, 3}, to[7] = {1, 4, 5, 2, 3, 7, 8};
   CU(h, cudaEventElapsedTime(ms, h->ev[from[phase]], h->ev[to[phase]]));
   return PENG_OK;
 }
@@ -1516,14 +1834,17 @@ struct PartArgs {
   uint64_t ub, ue;
   unsigned grid;
   uint32_t region_cap;
+  void* buckets;
+  uint32_t* fill;
 };
 template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM, bool LINK>
 static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
-  const size_t smem_p = (size_t)(PART_NCLASS + 1) * CAP * 2;
+  typedef PartGeom<W> G;
+  const size_t smem_p = (size_t)(G::NCLASS + 1) * CAP * sizeof(typename G::entry_t);
   auto kern = k_count_part<W, BOTH, NT, CAP, PER_SM, LINK>;
   CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
-  kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue, h->d_part_buckets,
-                                          a.region_cap, h->d_part_fill, h->d_hist32,
+  kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue,
+                                          (typename G::entry_t*)a.buckets, a.region_cap, a.fill, h->d_hist32,
                                           (unsigned long long*)(h->d_counts + h->n_patterns), h->d_slow_list, h->d_slow_count, 0u);
   LAUNCH_CHECK(h);
   return PENG_OK;
@@ -1573,7 +1894,7 @@ static int launch_count_partition(peng_handle_t h, bool both) {
   for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
     const uint64_t ue = std::min(n_units, ub + units_per_chunk);
     CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
-    const PartArgs a{ub, ue, grid_p, (uint32_t)region_cap};
+    const PartArgs a{ub, ue, grid_p, (uint32_t)region_cap, h->d_part_buckets, h->d_part_fill};
     if (ub == 0) MARK(h, 6);  // phases 3..5 time the stages of the FIRST chunk (a full one whenever there are several)
     const int rc_p = both ? launch_part<W, true>(h, cfg, a) : launch_part<W, false>(h, cfg, a);
     TRY(rc_p);
@@ -1581,7 +1902,7 @@ static int launch_count_partition(peng_handle_t h, bool both) {
     if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
     else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
     LAUNCH_CHECK(h);
-    if (ub == 0) MARK(h, 3);
+    if (ub == 0) { MARK(h, 3); MARK(h, 8); }
     k_hist_part<<<PART_NCLASS * PART_CPC, PART_HT, smem_h, h->stream>>>(h->d_part_buckets, (uint32_t)region_cap, grid_p,
                                                                       h->d_part_fill, h->d_hist32);
     LAUNCH_CHECK(h);
@@ -1594,6 +1915,130 @@ static int launch_count_partition(peng_handle_t h, bool both) {
   }
   h->used_partition = true;
   return PENG_OK;
+}
+
+
+// Deep partition path driver (W = 12, 14, 16), see k_part2.  Chunks of <= 2^30 positions bound the bucket memory; the
+// uint32 table is folded into the 64-bit one only when a bin could overflow (2^32 positions since the last fold).
+template <typename T>
+static int deep_reserve(peng_handle_t h, int level, size_t bucket_elems, size_t fill_elems) {
+  const size_t bytes = bucket_elems * sizeof(T);
+  if (h->deep_bucket_bytes[level] < bytes) {
+    unsigned char* p = (unsigned char*)h->d_deep_buckets[level];
+    TRY(dev_alloc(h, &p, bytes));
+    h->d_deep_buckets[level] = p;
+    h->deep_bucket_bytes[level] = bytes;
+  }
+  if (h->deep_fill_elems[level] < fill_elems) {
+    TRY(dev_alloc(h, &h->d_deep_fill[level], fill_elems));
+    h->deep_fill_elems[level] = fill_elems;
+  }
+  return PENG_OK;
+}
+static uint32_t deep_region_cap(uint64_t keys, uint64_t n_regions, uint32_t min_cap) {
+  uint64_t cap = keys * 3 / 2 / n_regions;
+  cap = std::max<uint64_t>(min_cap, (cap + 127) & ~127ull);
+  return (uint32_t)cap;
+}
+template <int NC2_BITS, int SUB_BITS, uint32_t CAP, typename OUT_T>
+static int launch_part2(peng_handle_t h, const uint32_t* in, uint32_t in_cap, uint32_t n_in, const uint32_t* in_fill,
+                        uint32_t n_c1, uint32_t G, uint32_t shift, OUT_T* out, uint32_t out_cap, uint32_t* out_fill) {
+  const size_t smem = (size_t)(DEEP_P2_NQ + 1) * CAP * sizeof(OUT_T) + 256;  // the remainder move reads whole 16-byte pieces
+  auto kern = k_part2<NC2_BITS, SUB_BITS, CAP, OUT_T>;
+  CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<n_c1 * G, DEEP_P2_NT, smem, h->stream>>>(in, in_cap, n_in, in_fill, G, shift, out, out_cap, out_fill, h->d_hist32);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+
+template <int W>
+static int launch_count_deep(peng_handle_t h, bool both) {
+  typedef PartGeom<W> G1;
+  constexpr uint32_t NC1 = G1::NCLASS;
+  const uint64_t n_units = h->n_words32;
+  const uint64_t units_per_chunk = 1ull << 25;
+  const unsigned grid_p = (unsigned)h->sm_count * 2;
+  const uint64_t chunk_units = std::min(n_units, units_per_chunk);
+  const uint64_t chunk_keys = chunk_units * 32;
+  // stage P2: 4 CTAs of 256 threads per SM; G2 CTAs per stage-P class.  A leaf owns n_reg regions (see k_part2).
+  const uint32_t G2 = std::max(1u, (unsigned)h->sm_count * 4 / NC1);
+  const uint32_t cap1 = deep_region_cap(chunk_keys, (uint64_t)grid_p * NC1, 1024);
+  TRY(deep_reserve<uint32_t>(h, 0, (size_t)cap1 * grid_p * NC1, (size_t)grid_p * NC1));
+  constexpr uint32_t LEAVES = 1u << (2 * W - DEEP_LEAF_BITS);
+  // W = 12: 5 + 4 class bits (16 sub-queues each); W = 14: 5 + 8; W = 16: 5 + 4 (32-bit entries, 16 sub-queues) + 8
+  const uint32_t n_reg2a = G2 << 4;                      // W = 16: regions per middle class
+  const uint32_t n_reg = W == 12 ? (G2 << 4) : W == 14 ? G2 : 1u;  // regions per leaf
+  uint32_t cap2a = 0, cap2 = 0;
+  if (h->deep_mode == 0) {
+    if (W == 16) {
+      cap2a = deep_region_cap(chunk_keys, (uint64_t)NC1 * 16 * n_reg2a, 256);
+      TRY(deep_reserve<uint32_t>(h, 1, (size_t)cap2a * NC1 * 16 * n_reg2a, (size_t)NC1 * 16 * n_reg2a));
+    }
+    cap2 = deep_region_cap(chunk_keys, (uint64_t)LEAVES * n_reg, 256);
+    TRY(deep_reserve<uint16_t>(h, 2, (size_t)cap2 * LEAVES * n_reg, (size_t)LEAVES * n_reg));
+  }
+  if (!h->d_slow_count) TRY(dev_alloc(h, &h->d_slow_count, (size_t)1));
+  if (h->slow_list_elems < chunk_units) {
+    TRY(dev_alloc(h, &h->d_slow_list, (size_t)chunk_units));
+    h->slow_list_elems = chunk_units;
+  }
+  const size_t smem_leaf = (size_t)4 << DEEP_LEAF_BITS;
+  CU(h, cudaFuncSetAttribute(k_hist_leaf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_leaf));
+  uint32_t* b1 = (uint32_t*)h->d_deep_buckets[0];
+  uint32_t* f1 = h->d_deep_fill[0];
+  uint64_t pos_since_fold = 0;
+  for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
+    const uint64_t ue = std::min(n_units, ub + units_per_chunk);
+    if (pos_since_fold + (ue - ub) * 32 > 0xFFFFFFFFull) {  // a uint32 bin could overflow: fold first
+      if (both) k_fold_canon<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, h->n_patterns);
+      else k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
+      LAUNCH_CHECK(h);
+      pos_since_fold = 0;
+    }
+    pos_since_fold += (ue - ub) * 32;
+    CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
+    const PartArgs a{ub, ue, grid_p, cap1, b1, f1};
+    if (ub == 0) MARK(h, 6);
+    const int rc_p = both ? launch_part_cfg<W, true, 512, 768, 2, false>(h, a) : launch_part_cfg<W, false, 512, 768, 2, false>(h, a);
+    TRY(rc_p);
+    if (ub == 0) MARK(h, 2);
+    if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
+    else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
+    LAUNCH_CHECK(h);
+    if (ub == 0) MARK(h, 3);
+    if (h->deep_mode == 1) {
+      if (ub == 0) MARK(h, 8);
+      k_hist_l2<<<grid_p, 512, 0, h->stream>>>(b1, cap1, grid_p, NC1, f1, h->d_hist32);
+      LAUNCH_CHECK(h);
+    } else {
+      uint16_t* b2 = (uint16_t*)h->d_deep_buckets[2];
+      uint32_t* f2 = h->d_deep_fill[2];
+      if (W == 12) {
+        TRY((launch_part2<4, 4, 104, uint16_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS, b2, cap2, f2)));
+      } else if (W == 14) {
+        TRY((launch_part2<8, 0, 104, uint16_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS, b2, cap2, f2)));
+      } else {
+        uint32_t* b2a = (uint32_t*)h->d_deep_buckets[1];
+        uint32_t* f2a = h->d_deep_fill[1];
+        TRY((launch_part2<4, 4, 104, uint32_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS + 8, b2a, cap2a, f2a)));
+        TRY((launch_part2<8, 0, 104, uint16_t>(h, b2a, cap2a, n_reg2a, f2a, NC1 * 16, 1, DEEP_LEAF_BITS, b2, cap2, f2)));
+      }
+      if (ub == 0) MARK(h, 8);
+      k_hist_leaf<<<LEAVES, 1024, smem_leaf, h->stream>>>(b2, cap2, n_reg, f2, h->d_hist32);
+      LAUNCH_CHECK(h);
+    }
+    if (ub == 0) MARK(h, 7);
+  }
+  h->used_partition = true;
+  return PENG_OK;
+}
+
+// which inputs take a partition path (count_path 0 = automatic)
+static bool use_partition(peng_handle_t h, int W) {
+  if (W < 10 || h->count_path == 1) return false;
+  if (h->count_path == 2) return true;
+  return h->stream_end - PENG_FRONT_PAD >= (1ull << 22);
 }
 
 template <int W>
@@ -1624,8 +2069,9 @@ static int launch_count_W(peng_handle_t h, bool both) {
     return PENG_OK;
   } else {
   if constexpr (W == 10) {
-    const uint64_t n_pos = h->stream_end - PENG_FRONT_PAD;
-    if (h->count_path == 2 || (h->count_path == 0 && n_pos >= (1ull << 22))) return launch_count_partition<W>(h, both);
+    if (use_partition(h, W)) return launch_count_partition<W>(h, both);
+  } else {
+    if (use_partition(h, W)) return launch_count_deep<W>(h, both);
   }
   // W >= 10: global atomics; a uint32 bin cannot overflow within 2^32 positions, so split and fold
   const uint64_t max_chunks_per_launch = (1ull << 31) / (16ull * wpc);
@@ -1663,8 +2109,7 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   CU(h, cudaMemsetAsync(h->d_hist32, 0, n * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
   const bool both = strand == PENG_STRAND_BOTH;
-  const bool partition = W == 10 && (h->count_path == 2 ||
-                                     (h->count_path == 0 && h->stream_end - PENG_FRONT_PAD >= (1ull << 22)));
+  const bool partition = use_partition(h, W);
   h->used_partition = false;
   MARK(h, 0);
   if (!partition) {  // the partition path derives the k-mer starts inside its first stage
@@ -1673,7 +2118,7 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
     LAUNCH_CHECK(h);
   }
   MARK(h, 1);
-  if (!partition) { MARK(h, 6); MARK(h, 2); MARK(h, 3); MARK(h, 7); }
+  if (!partition) { MARK(h, 6); MARK(h, 2); MARK(h, 3); MARK(h, 8); MARK(h, 7); }
   int rc = PENG_OK;
   switch (W) {
     case 2: rc = launch_count_W<2>(h, both); break;
@@ -1695,8 +2140,10 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
 }
 
 extern "C" int peng_cuda_set_count_path(peng_handle_t h, int path) {
-  if (!h || path < 0 || path > 2) return fail(h, PENG_E_INVALID, "set_count_path: path must be 0 (auto), 1 (L2 atomics) or 2 (partition)");
-  h->count_path = path;
+  if (!h || path < 0 || path > 3)
+    return fail(h, PENG_E_INVALID, "set_count_path: path must be 0 (auto), 1 (L2 atomics), 2 (partition) or 3 (partition, L2-RED second stage)");
+  h->count_path = path == 3 ? 2 : path;
+  h->deep_mode = path == 3 ? 1 : 0;
   return PENG_OK;
 }
 extern "C" int peng_cuda_last_count_path(peng_handle_t h) { return h ? (h->used_partition ? 2 : 1) : 0; }

@@ -168,6 +168,18 @@ def count_part(st, W, both=True, mirror=True):
                                      slow_units=int(stats[4]))
 
 
+def count_part_keys(st, W, both=True):
+    """W in (12, 14, 16): the partition path's split without a 4^W table -> (sorted canonical keys, ltot, stats)."""
+    stats = np.zeros(5, np.uint64)
+    cap = st.stream_end
+    out = np.zeros(cap, np.uint32)
+    lib.sim_count_part_keys.restype = C.c_uint64
+    n = lib.sim_count_part_keys(_p(st.codes, u32p), _p(st.valid, u32p), C.c_uint64(st.nw), W, int(both), _p(out, u32p),
+                                C.c_uint64(cap), _p(stats, u64p))
+    return np.sort(out[:n]), int(stats[0]), dict(missed=int(stats[1]), needless_slow=int(stats[2]), fast=int(stats[3]),
+                                                 slow_units=int(stats[4]))
+
+
 def scan_fasta(path):
     """host_ingest.h: scan_fasta on a mapped file -> (codes in the reference's encoding, offsets) or raises ValueError."""
     n_seq, n_let = C.c_uint64(), C.c_uint64()

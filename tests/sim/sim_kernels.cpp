@@ -197,7 +197,8 @@ static inline uint32_t kmer_at(const uint32_t* codes, uint64_t s, int W) {
 }
 
 template <int W, bool BOTH>
-static void count_part_T(const uint32_t* codes, const uint32_t* valid, uint64_t n_words32, uint64_t* hist, uint64_t* stats) {
+static void count_part_T(const uint32_t* codes, const uint32_t* valid, uint64_t n_words32, uint64_t* hist, uint64_t* stats,
+                         std::vector<uint32_t>* keys = nullptr) {
   std::vector<uint32_t> kstart(n_words32 + 8, 0);
   for (uint64_t u = 0; u < n_words32; u++) {
     kstart[u] = kstart_word(u, n_words32, valid, W);
@@ -227,12 +228,19 @@ static void count_part_T(const uint32_t* codes, const uint32_t* valid, uint64_t 
     }
     stats[3] += (uint64_t)popc32(fast);
     for (uint32_t b = 0; b < 32; b++)
-      if ((fast >> b) & 1u) hist[kmer_at(codes, u * 32 + b, W)]++;
+      if ((fast >> b) & 1u) {
+        const uint32_t k = kmer_at(codes, u * 32 + b, W);
+        if (keys) keys->push_back(BOTH ? std::min(k, revcomp_id(k, W)) : k);  // sparse mode: canonical keys
+        else hist[k]++;
+      }
     if (slow) {
       stats[4]++;
       auto emit = [&](uint32_t key, uint32_t i) {
         const int32_t b = (int32_t)i - (W - 1);
-        if (b >= 0 && b < 32 && ((slow >> b) & 1u)) hist[key]++;
+        if (b >= 0 && b < 32 && ((slow >> b) & 1u)) {
+          if (keys) keys->push_back(key);
+          else hist[key]++;
+        }
       };
       count_chunk<W, BOTH>(codes, kstart.data(), u * 32, 3, emit);
     }
@@ -251,7 +259,21 @@ void sim_count_part(const uint32_t* codes, const uint32_t* valid, uint64_t n_wor
     case 6: both ? count_part_T<6, true>(codes, valid, n_words32, hist, stats) : count_part_T<6, false>(codes, valid, n_words32, hist, stats); break;
     case 8: both ? count_part_T<8, true>(codes, valid, n_words32, hist, stats) : count_part_T<8, false>(codes, valid, n_words32, hist, stats); break;
     case 10: both ? count_part_T<10, true>(codes, valid, n_words32, hist, stats) : count_part_T<10, false>(codes, valid, n_words32, hist, stats); break;
+    case 12: both ? count_part_T<12, true>(codes, valid, n_words32, hist, stats) : count_part_T<12, false>(codes, valid, n_words32, hist, stats); break;
   }
+}
+// W in (12, 14, 16) without a 4^W table: the canonical keys of the counted occurrences (fast + slow), unordered
+uint64_t sim_count_part_keys(const uint32_t* codes, const uint32_t* valid, uint64_t n_words32, int W, int both, uint32_t* out,
+                             uint64_t cap, uint64_t* stats) {
+  for (int i = 0; i < 5; i++) stats[i] = 0;
+  std::vector<uint32_t> keys;
+  switch (W) {
+    case 12: both ? count_part_T<12, true>(codes, valid, n_words32, nullptr, stats, &keys) : count_part_T<12, false>(codes, valid, n_words32, nullptr, stats, &keys); break;
+    case 14: both ? count_part_T<14, true>(codes, valid, n_words32, nullptr, stats, &keys) : count_part_T<14, false>(codes, valid, n_words32, nullptr, stats, &keys); break;
+    case 16: both ? count_part_T<16, true>(codes, valid, n_words32, nullptr, stats, &keys) : count_part_T<16, false>(codes, valid, n_words32, nullptr, stats, &keys); break;
+  }
+  if (out) for (uint64_t i = 0; i < keys.size() && i < cap; i++) out[i] = keys[i];
+  return keys.size();
 }
 // BOTH: pair sums into the canonical bin (then sim_mirror copies them to the other id)
 void sim_fold_canon(uint64_t* hist, int W) {

@@ -156,6 +156,47 @@ def test_partition_path_split_is_exact(seed):
             assert lt == ltot and np.array_equal(hist, ref), (W, both, stt)
 
 
+def long_period_sequences(seed):
+    """Tandem repeats with units of 1..15 letters, long reverse-complement palindromes and random stretches: the
+    conflict shapes of the long pattern lengths (lags up to W - 1 = 15)."""
+    rng = np.random.RandomState(2000 + seed)
+    comp = {"A": "T", "C": "G", "G": "C", "T": "A"}
+    seqs = []
+    for _ in range(rng.randint(2, 5)):
+        parts = []
+        for _ in range(rng.randint(4, 14)):
+            kind = rng.randint(0, 4)
+            if kind == 0:
+                parts.append("".join(rng.choice(list("ACGT"), rng.randint(1, 60))))
+            elif kind == 1:
+                half = "".join(rng.choice(list("ACGT"), rng.randint(4, 30)))
+                parts.append(half + "".join(comp[c] for c in reversed(half)))
+            elif kind == 2:
+                unit = "".join(rng.choice(list("ACGT"), rng.randint(1, 16)))
+                parts.append((unit * 40)[: rng.randint(12, 90)])
+            else:
+                parts.append("N" * rng.randint(1, 3))
+        seqs.append("".join(parts))
+    return seqs
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_partition_path_split_long_patterns(seed):
+    """W = 12, 14, 16 (deep partition path): the fast/slow split emits exactly the keys of the exact ring logic."""
+    seqs = _cases.dirty_sequences(seed) if seed % 3 == 0 else long_period_sequences(seed)
+    codes, offs = O.encode(seqs)
+    st = S.pack(codes, offs)
+    for W in (12, 14, 16):
+        for both in (True, False):
+            keys, ltot, stt = S.count_part_keys(st, W, both)
+            ref, lt = S.count_keys(st, W, both)
+            assert stt["missed"] == 0, (W, both, stt)
+            assert lt == ltot and np.array_equal(keys, np.sort(ref)), (W, both, stt)
+    hist, ltot, stt = S.count_part(st, 12, True)
+    ref, lt = O.count(codes, offs, 12, True)
+    assert stt["missed"] == 0 and lt == ltot and np.array_equal(hist, ref)
+
+
 @pytest.mark.parametrize("case", [c for c in _cases.golden_cases() if c["exit"] == 0 and c["W"] in (4, 6, 8, 10)],
                          ids=lambda c: c["tag"])
 def test_partition_path_golden_cases(case):
