@@ -109,7 +109,7 @@ int peng_cuda_background_finish(peng_handle_t h, int K, const float* alpha, int 
  * ltot = number of W-mers looked at (BasePattern::getLtot). */
 int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* ltot);
 int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts /* 4^W */); /* BasePattern::getPatternCounter */
-/* Counting kernel family for W >= 10: 0 = automatic (partition path from 4 M stream positions on), 1 = one L2 atomic
+/* Counting kernel family for W >= 10: 0 = automatic (partition path from 2^22 / 2^25 / 2^24 / 2^28 stream positions on for W = 10 / 12 / 14 / 16), 1 = one L2 atomic
  * per counted W-mer (k_count_global), 2 = partition path (W = 10: k_count_part / k_count_slow / k_hist_part, shared-
  * memory histograms per id range; W = 12, 14, 16: the deep path k_count_part / k_count_slow / k_part2 / k_hist_leaf),
  * 3 = as 2 with the second stage of the deep path replaced by one L2 RED per id (k_hist_l2; a cross-check for tests).

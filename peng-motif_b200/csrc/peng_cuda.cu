@@ -608,7 +608,13 @@ __global__ void __launch_bounds__(PART_HT) k_hist_part(const uint16_t* __restric
 // overflow: roll the round back, its keys of that class go straight to the table; region full: same per block).
 #define DEEP_LEAF_BITS 15
 #define DEEP_P2_NT 256
-#define DEEP_P2_KPT 16  // keys per thread and round (4 x 16-byte loads)
+#ifndef DEEP_P2_KPT
+#define DEEP_P2_KPT 16  // keys per thread and round (16-byte loads)
+#endif
+#ifndef DEEP_P2_MINB
+#define DEEP_P2_MINB 4  // CTAs per SM
+#endif
+#define DEEP_P2_CAP (DEEP_P2_KPT == 8 ? 88 : DEEP_P2_KPT == 16 ? 104 : 136)  // 63 left over + one round's share + 5 sigma, multiple of 8
 #define DEEP_P2_NQ 256  // shared-memory queues per CTA: one per lane of its 8 warps in the flush
 
 // Stage P2.  in : regions [c1][r] of in_cap 32-bit ids, in_fill[c1 * n_in + r] of them valid (multiple of 4);
@@ -619,7 +625,7 @@ __global__ void __launch_bounds__(PART_HT) k_hist_part(const uint16_t* __restric
 //   [(leaf * G + g) << SUB_BITS | sub],  leaf = c1 << NC2_BITS | class field,
 // so a leaf owns G << SUB_BITS regions.  Per round a lane owns one queue in the flush (fill / rollback state in registers).
 template <int NC2_BITS, int SUB_BITS, uint32_t CAP, typename OUT_T>
-__global__ void __launch_bounds__(DEEP_P2_NT, 4) k_part2(const uint32_t* __restrict__ in, uint32_t in_cap, uint32_t n_in,
+__global__ void __launch_bounds__(DEEP_P2_NT, DEEP_P2_MINB) k_part2(const uint32_t* __restrict__ in, uint32_t in_cap, uint32_t n_in,
                                                          const uint32_t* __restrict__ in_fill, uint32_t G, uint32_t shift,
                                                          OUT_T* __restrict__ out, uint32_t out_cap,
                                                          uint32_t* __restrict__ out_fill, uint32_t* __restrict__ hist) {
@@ -1962,7 +1968,7 @@ static int launch_count_deep(peng_handle_t h, bool both) {
   const uint64_t chunk_units = std::min(n_units, units_per_chunk);
   const uint64_t chunk_keys = chunk_units * 32;
   // stage P2: 4 CTAs of 256 threads per SM; G2 CTAs per stage-P class.  A leaf owns n_reg regions (see k_part2).
-  const uint32_t G2 = std::max(1u, (unsigned)h->sm_count * 4 / NC1);
+  const uint32_t G2 = std::max(1u, (unsigned)h->sm_count * DEEP_P2_MINB / NC1);
   const uint32_t cap1 = deep_region_cap(chunk_keys, (uint64_t)grid_p * NC1, 1024);
   TRY(deep_reserve<uint32_t>(h, 0, (size_t)cap1 * grid_p * NC1, (size_t)grid_p * NC1));
   constexpr uint32_t LEAVES = 1u << (2 * W - DEEP_LEAF_BITS);
@@ -2015,14 +2021,14 @@ static int launch_count_deep(peng_handle_t h, bool both) {
       uint16_t* b2 = (uint16_t*)h->d_deep_buckets[2];
       uint32_t* f2 = h->d_deep_fill[2];
       if (W == 12) {
-        TRY((launch_part2<4, 4, 104, uint16_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS, b2, cap2, f2)));
+        TRY((launch_part2<4, 4, DEEP_P2_CAP, uint16_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS, b2, cap2, f2)));
       } else if (W == 14) {
-        TRY((launch_part2<8, 0, 104, uint16_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS, b2, cap2, f2)));
+        TRY((launch_part2<8, 0, DEEP_P2_CAP, uint16_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS, b2, cap2, f2)));
       } else {
         uint32_t* b2a = (uint32_t*)h->d_deep_buckets[1];
         uint32_t* f2a = h->d_deep_fill[1];
-        TRY((launch_part2<4, 4, 104, uint32_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS + 8, b2a, cap2a, f2a)));
-        TRY((launch_part2<8, 0, 104, uint16_t>(h, b2a, cap2a, n_reg2a, f2a, NC1 * 16, 1, DEEP_LEAF_BITS, b2, cap2, f2)));
+        TRY((launch_part2<4, 4, DEEP_P2_CAP, uint32_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS + 8, b2a, cap2a, f2a)));
+        TRY((launch_part2<8, 0, DEEP_P2_CAP, uint16_t>(h, b2a, cap2a, n_reg2a, f2a, NC1 * 16, 1, DEEP_LEAF_BITS, b2, cap2, f2)));
       }
       if (ub == 0) MARK(h, 8);
       k_hist_leaf<<<LEAVES, 1024, smem_leaf, h->stream>>>(b2, cap2, n_reg, f2, h->d_hist32);
@@ -2038,7 +2044,10 @@ static int launch_count_deep(peng_handle_t h, bool both) {
 static bool use_partition(peng_handle_t h, int W) {
   if (W < 10 || h->count_path == 1) return false;
   if (h->count_path == 2) return true;
-  return h->stream_end - PENG_FRONT_PAD >= (1ull << 22);
+  // measured crossovers against the L2-atomic kernel (tools/count_bench.py, PENG_COUNT_PATH=1|2): the deep path pays fixed
+  // costs per level (W = 16: 2^17 leaves), the L2 path pays per id once the table leaves the L2 (W >= 14)
+  const int log2_min = W == 10 ? 22 : W == 12 ? 25 : W == 14 ? 24 : 28;
+  return h->stream_end - PENG_FRONT_PAD >= (1ull << log2_min);
 }
 
 template <int W>

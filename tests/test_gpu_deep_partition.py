@@ -107,7 +107,8 @@ def test_paths_agree_on_synthetic(gpu, pkg):
             ref, lt = O.count(codes, offs, 12, both)
             for path in (0, 2, 3):
                 gpu.set_count_path(path)
-                assert gpu.count(12, int(both)) == lt and gpu.last_count_path == 2  # 12 M positions: automatic = deep
+                assert gpu.count(12, int(both)) == lt
+                assert gpu.last_count_path == (2 if path else 1)  # 12 M positions: below the W = 12 crossover of 2^25
                 assert np.array_equal(gpu.get_counts(), ref), (both, path)
             for W in (14, 16):
                 ids = np.random.RandomState(W).randint(0, 4 ** W, 1 << 20, dtype=np.int64).astype(np.uint64)
