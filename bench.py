@@ -311,8 +311,8 @@ def main():
         a.record()
         step_resident()
         b.record()
-        kern_ms.append(g.get_timing(3 if partition else 1))
-        phase_ms.append([g.get_timing(p) for p in range(6)])
+        kern_ms.append(g.get_timing((6 if W > 10 else 3) if partition else 1))
+        phase_ms.append([g.get_timing(p) for p in range(7)])
     barrier()
     t_wall = time.perf_counter() - t_wall
     launches = g.launches - launches0
@@ -396,7 +396,15 @@ def main():
     launch_bases = min(bases_local, 2 ** 30) if partition else bases_local
     algo_bytes = ALGO_BYTES_PER_BASE * launch_bases + 4.0 * 4 ** W
     achieved = algo_bytes / (k_ms * 1e-3) / 1e9
-    if partition:
+    if partition and W > 10:
+        # deep partition path: the largest kernel is stage P2, a pure 256-way split of the 32-bit ids of one chunk:
+        # algorithmic bytes = 4 B read + 2 B written per id
+        algo_bytes = 6.0 * launch_bases
+        achieved = algo_bytes / (k_ms * 1e-3) / 1e9
+        kname = f"k_part2 (stage P2 of the deep partition path, W = {W})"
+        note = ("stage P2 splits the 32-bit ids of a stage-P class 256 ways into 16-bit leaf entries through shared-memory queues; "
+                "bound by shared-memory wavefronts (bank conflicts of the slot atomics / scattered stores) and issue, see DESIGN.md")
+    elif partition:
         kname = f"k_count_part<{W},{shape['strand']}> (stage P of the partition path)"
         note = ("stage P streams the packed set once (codes + validity), derives k-mer starts and conflict candidates and "
                 "partitions 16-bit keys into class buckets; ALU-pipe bound (ncu: pipe_alu 75 %), see DESIGN.md")
@@ -406,7 +414,8 @@ def main():
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "kernel": kname, "kernel_ms": k_ms, "algorithmic_bytes": algo_bytes, "peak_source": peak_src, "note": note,
                 "step_phases_ms": {"mark": float(ph[0]), "count_total": float(ph[1]), "fold": float(ph[2]),
-                                   "stage_P": float(ph[3]), "slow_units": float(ph[4]), "stage_H": float(ph[5])},
+                                   "stage_P": float(ph[3]), "slow_units": float(ph[4]), "stage_H": float(ph[5]),
+                                   "stage_P2": float(ph[6])},
                 "whole_step_frac": (ALGO_BYTES_PER_BASE * bases_local + 4.0 * 4 ** W) / (dev_ms / args.steps * 1e-3) / 1e9 / peak}
     tr = os.path.join(ROOT, "profiles", "count_kernel_traffic.json")
     if os.path.exists(tr):
