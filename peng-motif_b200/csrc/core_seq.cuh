@@ -297,39 +297,102 @@ PENG_HD void cand_init(CandState& st) {
   st.c1 = 0; st.c2 = 0;
   st.p[0] = st.p[1] = st.p[2] = 0xFFFFFFFFu;
 }
-// (ff) lag d: W consecutive equalities x[p] == x[p-d] starting at p
+// (ff) A W-mer at s has an equal W-mer d < W positions in front of it iff x[p] == x[p-d] for p = s .. s+W-1 (W
+// consecutive equalities at lag d).  Then x also repeats at every multiple D = m d < W of the lag, over the shorter
+// stretch p = s+D-d .. s+W-1: at least R = W-D+d equalities at lag D ENDING at s+W-1.  So one "proxy" test
+//     run of R equalities at lag D ending at s+W-1        (R <= W - D + d for every lag d | D it stands for)
+// covers all those d at once; it is a superset test (false alarms at rate 4^-R per position, R >= 7), which is all the
+// fast/slow split needs.  cand_ff_run(cw, D, R) ORs the flags of one such test into st; R = W is the exact test of lag D.
+// The table FfLags<W> lists the tests per pattern length: 6 instead of 9 lags at W = 10, 7 instead of 13 at W = 14.
 template <int W>
-PENG_HD void cand_ff_lag(const uint32_t* cw, int d, CandState& st) {
+PENG_HD void cand_ff_run(const uint32_t* cw, int D, int R, CandState& st) {
   static_assert(W >= 4 && W <= 16 && (W % 2) == 0, "window arithmetic assumes W-1 <= 15 lags inside one word");
-  uint32_t e[3];  // e[j] bit 2k: x[p] == x[p-d] at p = 16(j+1) + k
+  uint32_t e[3];  // e[j] bit 2k: x[p] == x[p-D] at p = 16(j+1) + k
 #pragma unroll
   for (int j = 0; j < 3; j++) {
-    const uint32_t t = cw[j + 1] ^ funnel_r(cw[j], cw[j + 1], 32u - 2u * (uint32_t)d);
+    const uint32_t t = cw[j + 1] ^ funnel_r(cw[j], cw[j + 1], 32u - 2u * (uint32_t)D);
     e[j] = ~(t | (t >> 1)) & 0x55555555u;
   }
-  // runs by doubling: r2, r4, r8 = runs of 2, 4, 8; the third word only has to be right for its low positions
-  // (zeros shifted in at its top): a run that starts at position 31 of the unit ends at 31 + 15 = 46 < 48
-  uint32_t r2[3], r4[3], r8[3];
-  r2[0] = e[0] & funnel_r(e[0], e[1], 2u);
-  r2[1] = e[1] & funnel_r(e[1], e[2], 2u);
-  r2[2] = e[2] & (e[2] >> 2);
-  r4[0] = r2[0] & funnel_r(r2[0], r2[1], 4u);
-  r4[1] = r2[1] & funnel_r(r2[1], r2[2], 4u);
-  r4[2] = r2[2] & (r2[2] >> 4);
-  r8[0] = r4[0] & funnel_r(r4[0], r4[1], 8u);
-  r8[1] = r4[1] & funnel_r(r4[1], r4[2], 8u);
-  r8[2] = r4[2] & (r4[2] >> 8);
-  if (W == 4) { st.c1 |= r4[0]; st.c2 |= r4[1]; }
-  if (W == 6) { st.c1 |= r4[0] & funnel_r(r2[0], r2[1], 8u); st.c2 |= r4[1] & funnel_r(r2[1], r2[2], 8u); }
-  if (W == 8) { st.c1 |= r8[0]; st.c2 |= r8[1]; }
-  if (W == 10) { st.c1 |= r8[0] & funnel_r(r2[0], r2[1], 16u); st.c2 |= r8[1] & funnel_r(r2[1], r2[2], 16u); }
-  if (W == 12) { st.c1 |= r8[0] & funnel_r(r4[0], r4[1], 16u); st.c2 |= r8[1] & funnel_r(r4[1], r4[2], 16u); }
-  if (W == 14) {
-    st.c1 |= r8[0] & funnel_r(r4[0], r4[1], 16u) & funnel_r(r2[0], r2[1], 24u);
-    st.c2 |= r8[1] & funnel_r(r4[1], r4[2], 16u) & funnel_r(r2[1], r2[2], 24u);
+  // runs by doubling: r2, r4, r8 = runs of 2, 4, 8 starting at the bit's position; the third word only has to be right
+  // for its low positions (zeros shifted in at its top): a run that starts at position 31 of the unit ends at 31 + 15
+  // = 46 < 48.  sh(X, k) = X seen k positions further on.
+#define PENG_SH(X, k, j) ((j) < 2 ? funnel_r(X[j], X[(j) + 1 < 3 ? (j) + 1 : 2], 2u * (uint32_t)(k)) : (X[2] >> (2u * (uint32_t)(k))))
+  uint32_t r2[3], r4[3], r8[3], run[3];
+#pragma unroll
+  for (int j = 0; j < 3; j++) r2[j] = e[j] & PENG_SH(e, 1, j);
+#pragma unroll
+  for (int j = 0; j < 3; j++) r4[j] = r2[j] & PENG_SH(r2, 2, j);
+#pragma unroll
+  for (int j = 0; j < 3; j++) r8[j] = r4[j] & PENG_SH(r4, 4, j);
+#pragma unroll
+  for (int j = 0; j < 3; j++) {
+    uint32_t v;
+    if (R == 4) v = r4[j];
+    else if (R == 6) v = r4[j] & PENG_SH(r2, 4, j);
+    else if (R == 7) v = r4[j] & PENG_SH(r4, 3, j);
+    else if (R == 8) v = r8[j];
+    else if (R == 9) v = r8[j] & PENG_SH(e, 8, j);
+    else if (R == 10) v = r8[j] & PENG_SH(r2, 8, j);
+    else if (R == 11) v = r8[j] & PENG_SH(r4, 7, j);
+    else if (R == 12) v = r8[j] & PENG_SH(r4, 8, j);
+    else if (R == 14) v = r8[j] & PENG_SH(r4, 8, j) & PENG_SH(r2, 12, j);
+    else v = r8[j] & PENG_SH(r8, 8, j);  // R == 16
+    run[j] = v;
   }
-  if (W == 16) { st.c1 |= r8[0] & funnel_r(r8[0], r8[1], 16u); st.c2 |= r8[1] & funnel_r(r8[1], r8[2], 16u); }
+  const int off = W - R;  // the run starts at s + off
+  st.c1 |= off ? PENG_SH(run, off, 0) : run[0];
+  st.c2 |= off ? PENG_SH(run, off, 1) : run[1];
+#undef PENG_SH
 }
+// exact test of lag d (all W equalities)
+template <int W>
+PENG_HD void cand_ff_lag(const uint32_t* cw, int d, CandState& st) { cand_ff_run<W>(cw, d, W, st); }
+
+// the lag tests of a pattern length: (D, R) pairs that together cover every lag d = 1 .. W-1 (checked at compile time)
+template <int W>
+struct FfLags {  // short patterns: every lag exactly
+  static constexpr int N = W - 1;
+  PENG_HD static constexpr int D(int i) { return i + 1; }
+  PENG_HD static constexpr int R(int) { return W; }
+};
+template <>
+struct FfLags<10> {  // 4 (R 7) covers 1, 2, 4; 6 (R 7) covers 3, 6
+  static constexpr int N = 6;
+  PENG_HD static constexpr int D(int i) { return i == 0 ? 4 : i == 1 ? 6 : i == 2 ? 5 : i + 4; }  // 4 6 5 7 8 9
+  PENG_HD static constexpr int R(int i) { return i < 2 ? 7 : 10; }
+};
+template <>
+struct FfLags<12> {  // 6 (R 7): 1, 2, 3, 6; 8 (R 8): 4, 8; 10 (R 7): 5, 10
+  static constexpr int N = 6;
+  PENG_HD static constexpr int D(int i) { return i == 0 ? 6 : i == 1 ? 8 : i == 2 ? 10 : 2 * i + 1; }  // 6 8 10 7 9 11
+  PENG_HD static constexpr int R(int i) { return i == 0 ? 7 : i == 1 ? 8 : i == 2 ? 7 : 12; }
+};
+template <>
+struct FfLags<14> {  // 8 (R 7): 1, 2, 4, 8; 9 (R 8): 3, 9; 12 (R 8): 6, 12; 10 (R 9): 5, 10
+  static constexpr int N = 7;
+  PENG_HD static constexpr int D(int i) { return i == 0 ? 8 : i == 1 ? 9 : i == 2 ? 12 : i == 3 ? 10 : i == 4 ? 7 : i == 5 ? 11 : 13; }
+  PENG_HD static constexpr int R(int i) { return i == 0 ? 7 : i == 1 ? 8 : i == 2 ? 8 : i == 3 ? 9 : 14; }
+};
+template <>
+struct FfLags<16> {  // 10 (R 7): 1, 2, 5, 10; 12 (R 7): 3, 4, 6, 12; 14 (R 9): 7, 14
+  static constexpr int N = 8;
+  PENG_HD static constexpr int D(int i) { return i == 0 ? 10 : i == 1 ? 12 : i == 2 ? 14 : i == 3 ? 8 : i == 4 ? 9 : 2 * i + 1; }  // 10 12 14 8 9 11 13 15
+  PENG_HD static constexpr int R(int i) { return i < 2 ? 7 : i == 2 ? 9 : 16; }
+};
+template <int W>
+constexpr bool ff_lags_cover_all() {
+  for (int d = 1; d < W; d++) {
+    bool ok = false;
+    for (int i = 0; i < FfLags<W>::N; i++) {
+      const int D = FfLags<W>::D(i), R = FfLags<W>::R(i);
+      if (D < W && D % d == 0 && R <= W - D + d) ok = true;
+    }
+    if (!ok) return false;
+  }
+  return true;
+}
+static_assert(ff_lags_cover_all<4>() && ff_lags_cover_all<6>() && ff_lags_cover_all<8>() && ff_lags_cover_all<10>() &&
+              ff_lags_cover_all<12>() && ff_lags_cover_all<14>() && ff_lags_cover_all<16>(), "a lag is not covered");
 // (rc) arm i of the palindromes: x[m+1+i] complementary to x[m-i]; i = 0 .. W/2
 PENG_HD void cand_rc_arm(const uint32_t* cw, int i, CandState& st) {
 #pragma unroll
@@ -356,9 +419,9 @@ PENG_HD uint32_t cand_result(const CandState& st) { return compress_even16(st.c1
 // number of steps and step I of the whole computation (I is a compile-time constant after unrolling)
 template <int W, bool BOTH>
 struct CandSteps {
-  static constexpr int N_FF = W - 1, N_ARM = BOTH ? W / 2 + 1 : 0, N = N_FF + N_ARM + (BOTH ? 1 : 0);
+  static constexpr int N_FF = FfLags<W>::N, N_ARM = BOTH ? W / 2 + 1 : 0, N = N_FF + N_ARM + (BOTH ? 1 : 0);
   PENG_HD static void run(int I, const uint32_t* cw, CandState& st) {
-    if (I < N_FF) cand_ff_lag<W>(cw, I + 1, st);
+    if (I < N_FF) cand_ff_run<W>(cw, FfLags<W>::D(I), FfLags<W>::R(I), st);
     else if (I < N_FF + N_ARM) cand_rc_arm(cw, I - N_FF, st);
     else if (BOTH && I == N_FF + N_ARM) cand_rc_finish<W>(st);
   }
