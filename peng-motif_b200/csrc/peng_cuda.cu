@@ -55,6 +55,10 @@ struct peng_cuda_ctx {
   uint64_t* d_counts = nullptr;    // [n_patterns] + [1] ltot slot (summed over ranks together)
   uint64_t ltot = 0;
   bool counts_final = false;       // mirror step applied, ltot published
+  cudaStream_t side_stream = nullptr;  // the slow units run beside stage H (W = 10) / stage P2 (deep path)
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool fuse_mirror = false;        // peng_cuda_count (single GPU): the final fold may write the mirror copy as well
+  bool mirrored = false;           // ... and did
 
   // ---- background ----
   int K = -1;
@@ -886,6 +890,26 @@ __global__ void k_fold_canon(uint32_t* __restrict__ hist, uint64_t* __restrict__
     }
   }
 }
+// The only fold of a count (sets below 2^30 positions): the 64-bit table is written, not added to, so it needs no
+// clearing beforehand; MIRROR also writes the pair count at the reverse-complement id (single-GPU peng_cuda_count: no
+// separate k_mirror pass).  Without MIRROR the non-canonical entries are written as 0.
+template <bool MIRROR>
+__global__ void k_fold_canon_first(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, int W, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t rc = revcomp_id((uint32_t)i, W);
+    if ((uint32_t)i <= rc) {
+      uint64_t v = hist[i];
+      if ((uint32_t)i < rc) v += hist[rc];
+      acc[i] = v;
+      if ((uint32_t)i < rc) acc[rc] = MIRROR ? v : 0ull;
+      if (v) {
+        hist[i] = 0;
+        hist[rc] = 0;
+      }
+    }
+  }
+}
 
 // fold the uint32 launch histogram into the 64-bit table and clear it ("global merge")
 __global__ void k_fold(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, uint64_t n) {
@@ -896,6 +920,14 @@ __global__ void k_fold(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, 
       acc[i] += v;
       hist[i] = 0;
     }
+  }
+}
+__global__ void k_fold_first(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t v = hist[i];
+    acc[i] = v;
+    if (v) hist[i] = 0;
   }
 }
 
@@ -1465,6 +1497,13 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
     return fail(nullptr, PENG_E_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
   }
   h->stream = h->own_stream;
+  if (cudaStreamCreateWithFlags(&h->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    g_create_error = "peng_cuda_create: side stream / events";
+    delete h;
+    return PENG_E_CUDA;
+  }
   if (const char* e = getenv("PENG_PART_CFG")) h->part_cfg = atoi(e);
   if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
   *out = h;
@@ -1501,6 +1540,9 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   for (int i = 0; i < 3; i++) { dev_free(&h->d_deep_buckets[i]); dev_free(&h->d_deep_fill[i]); }
   for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
+  if (h->side_stream) cudaStreamDestroy(h->side_stream);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   delete h;
 }
 
@@ -1525,8 +1567,9 @@ extern "C" int peng_cuda_get_timing(peng_handle_t h, int phase, float* ms) {
   CU(h, cudaSetDevice(h->device));
   CU(h, cudaEventSynchronize(h->ev[5]));
   // events: 0 start | 1 k-mer starts marked | 4 counting done | 5 folded; of the first chunk of the partition path:
-  // 6 stage P launched | 2 stage P done | 3 slow units done | 8 stage P2 done (deep path, else = 3) | 7 stage H done
-  static const int from[7] = {0, 1, 4, 6, 2, 8, 3}, to[7] = {1, 4, 5, 2, 3, 7, 8};
+  // 6 stage P launched | 2 stage P done | 3 slow units done (side stream, beside stage H / P2) | 8 stage P2 done (deep
+  // path, else = 2) | 7 stage H done
+  static const int from[7] = {0, 1, 4, 6, 2, 8, 2}, to[7] = {1, 4, 5, 2, 3, 7, 8};
   CU(h, cudaEventElapsedTime(ms, h->ev[from[phase]], h->ev[to[phase]]));
   return PENG_OK;
 }
@@ -1869,6 +1912,20 @@ static int launch_part(peng_handle_t h, int cfg, const PartArgs& a) {
   }
 }
 
+// The exact resolution of the slow units (few threads, latency-bound) runs on a side stream beside the next stage, which
+// only touches the table through atomics; `ev_join` is awaited before anything that does not.
+template <int W>
+static int launch_slow_beside(peng_handle_t h, bool both, bool mark) {
+  CU(h, cudaEventRecord(h->ev_fork, h->stream));
+  CU(h, cudaStreamWaitEvent(h->side_stream, h->ev_fork, 0));
+  if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->side_stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
+  else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->side_stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
+  LAUNCH_CHECK(h);
+  if (mark && h->timing) CU(h, cudaEventRecord(h->ev[3], h->side_stream));
+  CU(h, cudaEventRecord(h->ev_join, h->side_stream));
+  return PENG_OK;
+}
+
 // Partition path driver: stage P (+ fused k-mer start marking), slow units, stage H; chunks of <= 2^30 positions so
 // that a uint32 bin cannot overflow between folds.
 template <int W>
@@ -1905,13 +1962,12 @@ static int launch_count_partition(peng_handle_t h, bool both) {
     const int rc_p = both ? launch_part<W, true>(h, cfg, a) : launch_part<W, false>(h, cfg, a);
     TRY(rc_p);
     if (ub == 0) MARK(h, 2);
-    if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
-    else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
-    LAUNCH_CHECK(h);
-    if (ub == 0) { MARK(h, 3); MARK(h, 8); }
+    TRY(launch_slow_beside<W>(h, both, ub == 0));
+    if (ub == 0) MARK(h, 8);
     k_hist_part<<<PART_NCLASS * PART_CPC, PART_HT, smem_h, h->stream>>>(h->d_part_buckets, (uint32_t)region_cap, grid_p,
                                                                       h->d_part_fill, h->d_hist32);
     LAUNCH_CHECK(h);
+    CU(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
     if (ub == 0) MARK(h, 7);
     if (ue < n_units) {
       if (both) k_fold_canon<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, h->n_patterns);
@@ -2009,14 +2065,12 @@ static int launch_count_deep(peng_handle_t h, bool both) {
     const int rc_p = both ? launch_part_cfg<W, true, 512, 768, 2, false>(h, a) : launch_part_cfg<W, false, 512, 768, 2, false>(h, a);
     TRY(rc_p);
     if (ub == 0) MARK(h, 2);
-    if (both) k_count_slow<W, true><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
-    else k_count_slow<W, false><<<h->sm_count * 4, 128, 0, h->stream>>>(h->d_codes, h->d_kstart, h->d_slow_list, h->d_slow_count, h->d_hist32);
-    LAUNCH_CHECK(h);
-    if (ub == 0) MARK(h, 3);
+    TRY(launch_slow_beside<W>(h, both, ub == 0));
     if (h->deep_mode == 1) {
       if (ub == 0) MARK(h, 8);
       k_hist_l2<<<grid_p, 512, 0, h->stream>>>(b1, cap1, grid_p, NC1, f1, h->d_hist32);
       LAUNCH_CHECK(h);
+      CU(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
     } else {
       uint16_t* b2 = (uint16_t*)h->d_deep_buckets[2];
       uint32_t* f2 = h->d_deep_fill[2];
@@ -2030,6 +2084,7 @@ static int launch_count_deep(peng_handle_t h, bool both) {
         TRY((launch_part2<4, 4, DEEP_P2_CAP, uint32_t>(h, b1, cap1, grid_p, f1, NC1, G2, DEEP_LEAF_BITS + 8, b2a, cap2a, f2a)));
         TRY((launch_part2<8, 0, DEEP_P2_CAP, uint16_t>(h, b2a, cap2a, n_reg2a, f2a, NC1 * 16, 1, DEEP_LEAF_BITS, b2, cap2, f2)));
       }
+      CU(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));  // the leaf merge is not atomic: the slow units must be in
       if (ub == 0) MARK(h, 8);
       k_hist_leaf<<<LEAVES, 1024, smem_leaf, h->stream>>>(b2, cap2, n_reg, f2, h->d_hist32);
       LAUNCH_CHECK(h);
@@ -2116,7 +2171,11 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   h->counts_final = false;
   h->stats_ready = false;
   CU(h, cudaMemsetAsync(h->d_hist32, 0, n * 4, h->stream));
-  CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
+  // up to 2^30 stream positions (pads included) every path folds exactly once, at the end: that fold writes the whole 64-bit table
+  const bool single_fold = h->n_words32 <= (1ull << 25);  // one chunk of every path
+  if (single_fold) CU(h, cudaMemsetAsync(h->d_counts + n, 0, 8, h->stream));
+  else CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
+  h->mirrored = false;
   const bool both = strand == PENG_STRAND_BOTH;
   const bool partition = use_partition(h, W);
   h->used_partition = false;
@@ -2141,7 +2200,13 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   }
   TRY(rc);
   MARK(h, 4);
-  if (h->used_partition && both) k_fold_canon<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+  if (h->used_partition && both) {
+    if (single_fold && h->fuse_mirror) {
+      k_fold_canon_first<true><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+      h->mirrored = true;
+    } else if (single_fold) k_fold_canon_first<false><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+    else k_fold_canon<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+  } else if (single_fold) k_fold_first<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
   else k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
   LAUNCH_CHECK(h);
   MARK(h, 5);
@@ -2168,7 +2233,7 @@ extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
   if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_finish: nothing counted");
   CU(h, cudaSetDevice(h->device));
   if (!h->counts_final) {
-    if (h->strand == PENG_STRAND_BOTH) {
+    if (h->strand == PENG_STRAND_BOTH && !h->mirrored) {
       k_mirror<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_counts, h->W, h->n_patterns);
       LAUNCH_CHECK(h);
     }
@@ -2181,7 +2246,10 @@ extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
 }
 
 extern "C" int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* ltot) {
-  TRY(peng_cuda_count_local(h, W, strand));
+  if (h) h->fuse_mirror = true;
+  const int rc = peng_cuda_count_local(h, W, strand);
+  if (h) h->fuse_mirror = false;
+  TRY(rc);
   return peng_cuda_count_finish(h, ltot);
 }
 
