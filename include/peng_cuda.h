@@ -79,6 +79,13 @@ int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, u
  * concatenated, offsets[n_seq+1]. */
 int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, const uint64_t* offsets, uint64_t n_seq);
 /* Same, codes/offsets already resident on this handle's device (no host copy). */
+/* How host buffers travel (peng_cuda_ingest_codes): 0 = automatic — with >= 4 host threads and AVX-512 the first part
+ * of the set is packed into the 2-bit device layout BY THE HOST THREADS (0.375 B/base over PCIe) while the DMA engine
+ * moves the raw bytes of the rest for the device to pack; 1 = raw bytes only; 2 = host packing only.  host_fraction
+ * in [0, 1] fixes the packed share of the bases (< 0: derived from the thread count).  Threads: PENG_HOST_THREADS,
+ * else hardware threads / LOCAL_WORLD_SIZE.  The device buffers are bit-identical in every mode. */
+int peng_cuda_set_ingest_mode(peng_handle_t h, int mode, double host_fraction);
+uint64_t peng_cuda_last_ingest_host_packed(peng_handle_t h); /* sequences packed by the host in the last ingest */
 int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets, uint64_t n_seq);
 /* Synthetic ChIP-seq-like set generated on the device (BASELINE.json configs[2..4]): n_seq sequences of
  * seq_len i.i.d. uniform bases from a counter-based generator (seed, base index), motif (base codes 0..3,

@@ -55,6 +55,8 @@ _PROTOS = {
     "peng_cuda_synchronize": (C.c_int, [H]),
     "peng_cuda_enable_timing": (C.c_int, [H, C.c_int]),
     "peng_cuda_get_timing": (C.c_int, [H, C.c_int, f32p]),
+    "peng_cuda_set_ingest_mode": (C.c_int, [H, C.c_int, C.c_double]),
+    "peng_cuda_last_ingest_host_packed": (C.c_uint64, [H]),
     "peng_cuda_ingest_fasta": (C.c_int, [H, C.c_char_p, u64p, u64p, u32p, u32p]),
     "peng_cuda_ingest_codes": (C.c_int, [H, C.c_void_p, u64p, C.c_uint64]),
     "peng_cuda_ingest_codes_device": (C.c_int, [H, C.c_void_p, u64p, C.c_uint64]),
@@ -233,6 +235,14 @@ class PengCuda:
         offsets = np.ascontiguousarray(offsets, np.uint64)
         self._ck(self.lib.peng_cuda_ingest_codes(self.h, _ptr(codes), offsets.ctypes.data_as(u64p), len(offsets) - 1))
         self.n_seq = len(offsets) - 1
+
+    def set_ingest_mode(self, mode=0, host_fraction=-1.0):
+        """0 automatic (hybrid host / device packing), 1 raw bytes, 2 host packing only."""
+        self._ck(self.lib.peng_cuda_set_ingest_mode(self.h, int(mode), float(host_fraction)))
+
+    @property
+    def last_ingest_host_packed(self):
+        return int(self.lib.peng_cuda_last_ingest_host_packed(self.h))
 
     def ingest_codes_device(self, device_ptr, offsets):
         offsets = np.ascontiguousarray(offsets, np.uint64)

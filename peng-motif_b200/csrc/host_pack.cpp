@@ -1,0 +1,367 @@
+// host_pack.cpp — see host_pack.h.  Compiled by g++ (-O3), linked into libpeng_cuda.so.
+#include "host_pack.h"
+
+#include <immintrin.h>
+
+#include <algorithm>
+#include <atomic>
+#include <condition_variable>
+#include <cstdlib>
+#include <mutex>
+#include <thread>
+
+namespace peng_hostpack {
+
+bool have_avx512() {
+  static const bool ok = __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw");
+  return ok;
+}
+
+// ---- up to 64 letters -> 128 code bits + 64 validity bits (bits of positions >= n are zero) --------------------------
+// codes: 0 = other, 1..4 = ACGT (Alphabet::getCode, src/shared/Alphabet.cpp:33-41); ascii: FASTA letters, either case.
+static inline void chunk_scalar(const uint8_t* p, uint32_t n, bool ascii, uint64_t& lo, uint64_t& hi, uint64_t& v) {
+  uint64_t c[2] = {0, 0}, vv = 0;
+  for (uint32_t i = 0; i < n; i++) {
+    const uint32_t ch = p[i];
+    uint32_t ok, code;
+    if (ascii) {
+      const uint32_t up = ch & 0xDFu;
+      ok = (up == 'A') | (up == 'C') | (up == 'G') | (up == 'T');
+      code = (up >> 1) & 3u;
+      code ^= code >> 1;
+    } else {
+      ok = (ch >= 1u) & (ch <= 4u);
+      code = (ch - 1u) & 3u;
+    }
+    code = ok ? code : 0u;
+    c[i >> 5] |= (uint64_t)code << (2 * (i & 31));
+    vv |= (uint64_t)ok << i;
+  }
+  lo = c[0];
+  hi = c[1];
+  v = vv;
+}
+
+__attribute__((target("avx512f,avx512bw"))) static inline void chunk_avx512(const uint8_t* p, uint32_t n, bool ascii, uint64_t& lo,
+                                                                            uint64_t& hi, uint64_t& v) {
+  const __mmask64 lm = n >= 64 ? ~(__mmask64)0 : (((__mmask64)1 << n) - 1);
+  const __m512i z = _mm512_maskz_loadu_epi8(lm, p);
+  __mmask64 ok;
+  __m512i code;
+  if (ascii) {
+    const __m512i up = _mm512_and_si512(z, _mm512_set1_epi8((char)0xDF));
+    ok = _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('A')) | _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('C')) |
+         _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('G')) | _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('T'));
+    ok &= lm;
+    __m512i c = _mm512_and_si512(_mm512_srli_epi16(up, 1), _mm512_set1_epi8(3));          // A0 C1 G3 T2
+    c = _mm512_xor_si512(c, _mm512_and_si512(_mm512_srli_epi16(c, 1), _mm512_set1_epi8(1)));  // A0 C1 G2 T3
+    code = _mm512_maskz_mov_epi8(ok, c);
+  } else {
+    const __m512i t = _mm512_sub_epi8(z, _mm512_set1_epi8(1));
+    ok = _mm512_cmplt_epu8_mask(t, _mm512_set1_epi8(4)) & lm;
+    code = _mm512_maskz_mov_epi8(ok, _mm512_and_si512(t, _mm512_set1_epi8(3)));
+  }
+  // 4 letters per byte: b0 + 4 b1 (16-bit lanes), then + 16 (b2 + 4 b3) (32-bit lanes), then the low byte of every lane
+  const __m512i m1 = _mm512_maddubs_epi16(code, _mm512_set1_epi16(0x0401));
+  const __m512i m2 = _mm512_madd_epi16(m1, _mm512_set1_epi32(0x00100001));
+  const __m128i b = _mm512_cvtepi32_epi8(m2);
+  lo = (uint64_t)_mm_cvtsi128_si64(b);
+  hi = (uint64_t)_mm_extract_epi64(b, 1);
+  v = (uint64_t)ok;
+}
+
+// ---- sequential bit writer over 64-position blocks --------------------------------------------------------------------
+struct BitWriter {
+  uint64_t* codes;
+  uint64_t* valid;
+  uint64_t blk0, blk;
+  uint32_t fill;  // positions of the current block already written
+  uint64_t lo, hi, v;
+  bool first_partial;  // the current block was entered in the middle (range boundary)
+  std::vector<Partial>* out;
+
+  void begin(uint64_t q) {
+    blk = q >> 6;
+    fill = (uint32_t)(q & 63);
+    lo = hi = v = 0;
+    first_partial = fill != 0;
+  }
+  inline void emit() {
+    if (first_partial) {
+      out->push_back(Partial{blk, lo, hi, v});
+      first_partial = false;
+    } else {
+      codes[2 * (blk - blk0)] = lo;
+      codes[2 * (blk - blk0) + 1] = hi;
+      valid[blk - blk0] = v;
+    }
+    blk++;
+    lo = hi = v = 0;
+  }
+  // n in 1..64 positions; the bits of c_lo / c_hi / vv behind position n are zero.  Branch-free up to the block test:
+  // the alignment changes with every sequence, so tests on `fill` would mispredict.
+  inline void append(uint64_t c_lo, uint64_t c_hi, uint64_t vv, uint32_t n) {
+    typedef unsigned __int128 u128;
+    const u128 c = ((u128)c_hi << 64) | c_lo;
+    const uint32_t sh = 2 * fill;  // 0 .. 126
+    const u128 in = c << sh;
+    const u128 over = (c >> 1) >> (127 - sh);  // what fell out at the top (0 for sh = 0)
+    lo |= (uint64_t)in;
+    hi |= (uint64_t)(in >> 64);
+    v |= vv << fill;
+    const uint64_t over_v = (vv >> 1) >> (63 - fill);
+    const uint32_t tot = fill + n;
+    if (tot >= 64) {
+      emit();
+      lo = (uint64_t)over;
+      hi = (uint64_t)(over >> 64);
+      v = over_v;
+      fill = tot - 64;
+    } else {
+      fill = tot;
+    }
+  }
+  void zeros(uint64_t n) {
+    while (n) {
+      const uint32_t k = (uint32_t)std::min<uint64_t>(n, 64u - fill);
+      append(0, 0, 0, k);
+      n -= k;
+    }
+  }
+  void end() {
+    if (fill) out->push_back(Partial{blk, lo, hi, v});
+  }
+};
+
+__attribute__((target("avx512f,avx512bw"))) static void run_avx512(const Share& sh, BitWriter& w) {
+  for (uint64_t s = sh.s_begin; s < sh.s_end; s++) {
+    const uint8_t* p = sh.src + sh.offsets[s];
+    const uint64_t L = sh.offsets[s + 1] - sh.offsets[s];
+    uint32_t sep = 2;  // the two separator positions (core_seq.cuh) ride on the last chunk where they fit
+    for (uint64_t i = 0; i < L; i += 64) {
+      uint32_t n = (uint32_t)std::min<uint64_t>(64, L - i);
+      uint64_t lo, hi, v;
+      chunk_avx512(p + i, n, sh.ascii, lo, hi, v);
+      if (i + 64 >= L && n <= 62) { n += 2; sep = 0; }
+      w.append(lo, hi, v, n);
+    }
+    if (sep) w.append(0, 0, 0, 2);
+  }
+}
+static void run_scalar(const Share& sh, BitWriter& w) {
+  for (uint64_t s = sh.s_begin; s < sh.s_end; s++) {
+    const uint8_t* p = sh.src + sh.offsets[s];
+    const uint64_t L = sh.offsets[s + 1] - sh.offsets[s];
+    uint32_t sep = 2;  // the two separator positions (core_seq.cuh) ride on the last chunk where they fit
+    for (uint64_t i = 0; i < L; i += 64) {
+      uint32_t n = (uint32_t)std::min<uint64_t>(64, L - i);
+      uint64_t lo, hi, v;
+      chunk_scalar(p + i, n, sh.ascii, lo, hi, v);
+      if (i + 64 >= L && n <= 62) { n += 2; sep = 0; }
+      w.append(lo, hi, v, n);
+    }
+    if (sep) w.append(0, 0, 0, 2);
+  }
+}
+
+void pack_share(const Share& sh) {
+  BitWriter w;
+  w.codes = sh.codes64;
+  w.valid = sh.valid64;
+  w.blk0 = sh.blk0;
+  w.out = sh.partials;
+  if (sh.lead_zero) {
+    w.begin(0);
+    w.zeros(sh.front_pad);
+  } else {
+    w.begin(sh.front_pad + sh.offsets[sh.s_begin] + 2 * sh.s_begin);
+  }
+  static const bool no_avx = getenv("PENG_HOST_PACK_SCALAR") != nullptr;
+  if (have_avx512() && !no_avx) run_avx512(sh, w); else run_scalar(sh, w);
+  if (sh.q_end_pad) {
+    const uint64_t q = (w.blk << 6) + w.fill;
+    if (sh.q_end_pad > q) w.zeros(sh.q_end_pad - q);
+  }
+  w.end();
+}
+
+// ---- worker pool ------------------------------------------------------------------------------------------------------
+struct Pool::Impl {
+  std::vector<std::thread> workers;
+  std::mutex m;
+  std::condition_variable cv_work, cv_done;
+  uint64_t generation = 0;
+  bool stop = false;
+  void (*fn)(int, void*) = nullptr;
+  void* arg = nullptr;
+  int n_tasks = 0;
+  std::atomic<int> next{0};
+  int busy = 0;  // workers still inside the current generation
+
+  void drain() {
+    for (;;) {
+      const int i = next.fetch_add(1, std::memory_order_relaxed);
+      if (i >= n_tasks) break;
+      fn(i, arg);
+    }
+  }
+  void worker() {
+    uint64_t seen = 0;
+    for (;;) {
+      {
+        std::unique_lock<std::mutex> lk(m);
+        cv_work.wait(lk, [&] { return stop || generation != seen; });
+        if (stop) return;
+        seen = generation;
+      }
+      drain();
+      {
+        std::lock_guard<std::mutex> lk(m);
+        if (--busy == 0) cv_done.notify_one();
+      }
+    }
+  }
+};
+
+Pool::Pool(int n_threads) : p_(new Impl), n_(std::max(1, n_threads)) {
+  for (int i = 1; i < n_; i++) p_->workers.emplace_back([this] { p_->worker(); });
+}
+Pool::~Pool() {
+  {
+    std::lock_guard<std::mutex> lk(p_->m);
+    p_->stop = true;
+  }
+  p_->cv_work.notify_all();
+  for (auto& t : p_->workers) t.join();
+  delete p_;
+}
+void Pool::run(int n_tasks, void (*fn)(int, void*), void* arg) {
+  if (n_tasks <= 0) return;
+  {
+    std::lock_guard<std::mutex> lk(p_->m);
+    p_->fn = fn;
+    p_->arg = arg;
+    p_->n_tasks = n_tasks;
+    p_->next.store(0, std::memory_order_relaxed);
+    p_->busy = (int)p_->workers.size();
+    p_->generation++;
+  }
+  p_->cv_work.notify_all();
+  p_->drain();  // the caller works too
+  std::unique_lock<std::mutex> lk(p_->m);
+  p_->cv_done.wait(lk, [&] { return p_->busy == 0; });
+}
+
+Pool& global_pool() {
+  static Pool* pool = [] {
+    int n = 0;
+    if (const char* e = getenv("PENG_HOST_THREADS")) n = atoi(e);
+    if (n <= 0) {
+      n = (int)std::thread::hardware_concurrency();
+      if (const char* e = getenv("LOCAL_WORLD_SIZE")) {  // one process per GPU (torchrun): share the cores
+        const int w = atoi(e);
+        if (w > 1) n = std::max(1, n / w);
+      }
+    }
+    return new Pool(std::min(std::max(n, 1), 32));  // never destroyed: worker threads must not be joined at exit
+  }();
+  return *pool;
+}
+
+
+// ---- one phase --------------------------------------------------------------------------------------------------------
+void phase_blocks(const Phase& ph, uint64_t* blk0, uint64_t* blk1) {
+  const uint64_t q0 = ph.first ? 0 : ph.front_pad + ph.offsets[ph.s_begin] + 2 * ph.s_begin;
+  const uint64_t q1 = ph.last ? ph.q_total : ph.front_pad + ph.offsets[ph.s_end] + 2 * ph.s_end;
+  *blk0 = q0 >> 6;
+  *blk1 = q1 >> 6;
+}
+
+uint64_t plan_phase(const uint64_t* offsets, uint64_t n_seq, uint64_t s_begin, uint32_t front_pad, bool first, uint64_t max_blocks) {
+  const uint64_t q0 = first ? 0 : front_pad + offsets[s_begin] + 2 * s_begin;
+  const uint64_t blk0 = q0 >> 6;
+  uint64_t lo = s_begin, hi = n_seq;  // invariant: lo fits
+  while (lo < hi) {
+    const uint64_t mid = (lo + hi + 1) >> 1;
+    const uint64_t q1 = front_pad + offsets[mid] + 2 * mid;
+    if ((q1 >> 6) + 1 - blk0 <= max_blocks) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+namespace {
+struct PhaseRun {
+  const Phase* ph;
+  uint64_t blk0;
+  std::vector<uint64_t> cut;  // share i = sequences [cut[i], cut[i + 1])
+  std::vector<std::vector<Partial>> partials;
+};
+void phase_task(int i, void* arg) {
+  PhaseRun& r = *(PhaseRun*)arg;
+  const Phase& ph = *r.ph;
+  const int n = (int)r.cut.size() - 1;
+  Share sh;
+  sh.src = ph.src;
+  sh.offsets = ph.offsets;
+  sh.s_begin = r.cut[i];
+  sh.s_end = r.cut[i + 1];
+  sh.ascii = ph.ascii;
+  sh.front_pad = ph.front_pad;
+  sh.lead_zero = ph.first && i == 0;
+  sh.q_end_pad = (ph.last && i == n - 1) ? ph.q_total : 0;
+  sh.blk0 = r.blk0;
+  sh.codes64 = ph.codes64;
+  sh.valid64 = ph.valid64;
+  sh.partials = &r.partials[i];
+  if (sh.s_begin == sh.s_end && !sh.lead_zero && !sh.q_end_pad) return;
+  pack_share(sh);
+}
+}  // namespace
+
+void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry) {
+  uint64_t blk0, blk1;
+  phase_blocks(ph, &blk0, &blk1);
+  PhaseRun r;
+  r.ph = &ph;
+  r.blk0 = blk0;
+  // shares of about equal numbers of bases, cut at sequence boundaries
+  const uint64_t b0 = ph.offsets[ph.s_begin], b1 = ph.offsets[ph.s_end];
+  // four shares per thread, handed out dynamically: a thread that loses its core for a moment does not hold up the phase
+  int n = pool.size() * 4;
+  if (b1 - b0 < (uint64_t)n * 65536) n = (int)std::max<uint64_t>(1, (b1 - b0) / 65536);
+  r.cut.push_back(ph.s_begin);
+  for (int i = 1; i < n; i++) {
+    const uint64_t target = b0 + (b1 - b0) * (uint64_t)i / (uint64_t)n;
+    const uint64_t* it = std::lower_bound(ph.offsets + r.cut.back(), ph.offsets + ph.s_end, target);
+    r.cut.push_back((uint64_t)(it - ph.offsets));
+  }
+  r.cut.push_back(ph.s_end);
+  r.partials.resize(n);
+  pool.run(n, phase_task, &r);
+  // boundary blocks: OR the contributions (at most two per share, plus the carry of the previous phase)
+  std::vector<Partial> all;
+  if (*has_carry) all.push_back(*carry);
+  for (auto& v : r.partials) all.insert(all.end(), v.begin(), v.end());
+  std::sort(all.begin(), all.end(), [](const Partial& a, const Partial& b) { return a.blk < b.blk; });
+  *has_carry = false;
+  for (size_t i = 0; i < all.size();) {
+    Partial acc = all[i];
+    size_t j = i + 1;
+    for (; j < all.size() && all[j].blk == acc.blk; j++) {
+      acc.lo |= all[j].lo;
+      acc.hi |= all[j].hi;
+      acc.v |= all[j].v;
+    }
+    if (acc.blk < blk1) {
+      ph.codes64[2 * (acc.blk - blk0)] = acc.lo;
+      ph.codes64[2 * (acc.blk - blk0) + 1] = acc.hi;
+      ph.valid64[acc.blk - blk0] = acc.v;
+    } else {
+      *carry = acc;
+      *has_carry = true;
+    }
+    i = j;
+  }
+}
+
+}  // namespace peng_hostpack

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -17,6 +18,7 @@
 #include "core_seq.cuh"
 #include "core_tab.cuh"
 #include "host_ingest.h"
+#include "host_pack.h"
 
 using namespace peng;
 
@@ -79,6 +81,9 @@ struct peng_cuda_ctx {
   size_t part_bucket_elems = 0;
   uint32_t* d_part_fill = nullptr;
   size_t part_fill_elems = 0;
+  int ingest_mode = 0;             // 0 auto (hybrid where it pays), 1 raw bytes + device packing, 2 host packing
+  double ingest_fraction = -1;     // share of the bases packed on the host (< 0: from the thread count)
+  uint64_t last_ingest_packed = 0; // sequences the host packed in the last ingest
   int part_cfg = 0;                // stage-P geometry (tuning knob, PENG_PART_CFG)
   uint2* d_slow_list = nullptr;
   size_t slow_list_elems = 0;
@@ -1505,6 +1510,8 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
     return PENG_E_CUDA;
   }
   if (const char* e = getenv("PENG_PART_CFG")) h->part_cfg = atoi(e);
+  if (const char* e = getenv("PENG_INGEST_MODE")) h->ingest_mode = !strcmp(e, "raw") ? 1 : !strcmp(e, "packed") ? 2 : 0;
+  if (const char* e = getenv("PENG_HOST_PACK_FRACTION")) h->ingest_fraction = atof(e);
   if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
   *out = h;
   return PENG_OK;
@@ -1618,6 +1625,42 @@ static void seq_lengths(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq
   h->max_len = mx;
 }
 
+// host copy of the offsets + shortest / longest sequence, on the pool's threads (1.4 ms single-threaded for 10^6 records)
+struct BookTask {
+  const uint64_t* offsets;
+  uint64_t* dst;
+  uint64_t n_seq;
+  int n_tasks;
+  uint32_t mn[64], mx[64];
+};
+static void book_task(int i, void* arg) {
+  BookTask& b = *(BookTask*)arg;
+  const uint64_t s0 = b.n_seq * (uint64_t)i / b.n_tasks, s1 = b.n_seq * (uint64_t)(i + 1) / b.n_tasks;
+  uint32_t mn = 0x7fffffffu, mx = 0;
+  for (uint64_t s = s0; s < s1; s++) {
+    const uint64_t L = b.offsets[s + 1] - b.offsets[s];
+    if (L > mx) mx = (uint32_t)L;
+    if (L < mn) mn = (uint32_t)L;
+  }
+  b.mn[i] = mn;
+  b.mx[i] = mx;
+  memcpy(b.dst + s0, b.offsets + s0, (s1 - s0 + (i == b.n_tasks - 1 ? 1 : 0)) * sizeof(uint64_t));
+}
+static void host_bookkeeping_parallel(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq) {
+  if (h->h_offsets.size() != n_seq + 1) h->h_offsets.resize(n_seq + 1);
+  peng_hostpack::Pool& pool = peng_hostpack::global_pool();
+  BookTask b;
+  b.offsets = offsets;
+  b.dst = h->h_offsets.data();
+  b.n_seq = n_seq;
+  b.n_tasks = std::min(pool.size(), 64);
+  pool.run(b.n_tasks, book_task, &b);
+  uint32_t mn = 0x7fffffffu, mx = 0;
+  for (int i = 0; i < b.n_tasks; i++) { mn = std::min(mn, b.mn[i]); mx = std::max(mx, b.mx[i]); }
+  h->min_len = mn;
+  h->max_len = mx;
+}
+
 static int launch_pack(peng_handle_t h, const uint8_t* d_src, bool ascii, uint64_t t_begin, uint64_t t_end) {
   if (t_end <= t_begin) return PENG_OK;
   const unsigned block = 256;
@@ -1652,10 +1695,173 @@ static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64
   return PENG_OK;
 }
 
+#define PENG_PIN_BYTES (16u << 20)
+static int need_copy_stream_and_pins(peng_handle_t h, bool pins) {
+  if (!h->copy_stream) {
+    CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) CU(h, cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
+  }
+  if (pins && !h->pin[0])
+    for (int i = 0; i < 2; i++) {
+      CU(h, cudaHostAlloc((void**)&h->pin[i], PENG_PIN_BYTES, cudaHostAllocDefault));
+      CU(h, cudaEventCreateWithFlags(&h->pin_ev[i], cudaEventDisableTiming));
+    }
+  return PENG_OK;
+}
+
+// sequence-start bits of the sequences whose first base lies in front of word t_end (the words are cleared beforehand)
+__global__ void k_sstart_scatter(const uint64_t* __restrict__ offsets, uint64_t n_seq, uint64_t t_end, uint32_t* __restrict__ sstart) {
+  const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_seq) return;
+  const uint64_t q = PENG_FRONT_PAD + offsets[s] + 2 * s;
+  if ((q >> 5) < t_end && offsets[s + 1] > offsets[s]) atomicOr(sstart + (q >> 5), 1u << (q & 31));
+}
+
+// src on the HOST, hybrid ingest.  One byte per base over PCIe (~46 GB/s) is the bound of the plain path below, so the
+// host threads pack the FIRST part of the set into the device layout themselves (host_pack.h: 0.375 B/base cross the bus)
+// while the DMA engine moves the raw bytes of the REST, which k_pack packs on the device as before.  The split
+// f = Rh / (Rp + 0.625 Rh) equalises the two (Rh = host packing rate, Rp = PCIe rate in bases/s).  The 64-position block
+// that holds the split is written whole by k_pack (the raw copy starts 128 bases early), the host's part of it is dropped.
+// returns 1 when the set does not qualify (few threads, no AVX-512, a sequence longer than a phase): the caller runs the
+// plain path.
+static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
+  using namespace peng_hostpack;
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  if (h->ingest_mode == 1) return 1;
+  const bool force = h->ingest_mode == 2;
+  Pool& pool = global_pool();
+  // automatic choice only where it pays; an explicit mode or fraction is taken as given (tests, tuning)
+  if (!force && h->ingest_fraction < 0 && (!have_avx512() || pool.size() < 4 || total < (1ull << 22))) return 1;
+  h->last_ingest_packed = 0;
+  double f = 1.0;
+  if (!force) {
+    const double rh = 3.75 * pool.size(), rp = 46.0;  // Gbases/s: measured packing rate per thread (60 at 16), PCIe rate
+    f = rh / (rp + 0.625 * rh);
+    if (h->ingest_fraction >= 0) f = h->ingest_fraction;
+    f = std::min(1.0, std::max(0.0, f));
+  } else if (h->ingest_fraction >= 0) {
+    f = std::min(1.0, std::max(0.0, h->ingest_fraction));
+  }
+  uint64_t s_split = n_seq;
+  if (f < 1.0) s_split = (uint64_t)(std::upper_bound(offsets, offsets + n_seq + 1, (uint64_t)(f * (double)total)) - offsets) - 1;
+  if (s_split == 0) return 1;
+  const uint64_t max_blocks = PENG_PIN_BYTES / 24;  // 16 B of codes + 8 B of validity per block of 64 positions
+  // every phase must hold at least one sequence
+  {
+    uint64_t s = 0;
+    bool first = true;
+    while (s < s_split) {
+      const uint64_t e = std::min(s_split, plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks - 4));
+      if (e == s) return 1;
+      s = e;
+      first = false;
+    }
+  }
+  CU(h, cudaSetDevice(h->device));
+  TRY(prepare_ingest(h, offsets, n_seq));
+  TRY(need_copy_stream_and_pins(h, true));
+  const uint64_t q_total = ((h->n_words32 * 32 + 63) / 64) * 64;
+  const uint64_t n_blocks = q_total / 64;
+  const uint64_t q_split = PENG_FRONT_PAD + offsets[s_split] + 2 * s_split;
+  const uint64_t blk_split = s_split < n_seq ? (q_split >> 6) : n_blocks;
+  const uint64_t b_lo = s_split < n_seq ? offsets[s_split] - std::min<uint64_t>(offsets[s_split], 128) : total;
+  if (s_split < n_seq) TRY(need_scratch(h, (size_t)(total - b_lo) + 16));
+  CU(h, cudaEventRecord(h->copy_ev[0], h->stream));
+  CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
+  CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+  // ---- the raw rest: queued first, the DMA engine works on it while the host packs ----
+  if (s_split < n_seq) {
+    const uint8_t* d_src = (const uint8_t*)h->d_scratch - b_lo;  // indexed by absolute base offset, never read below b_lo
+    const uint64_t chunk = 32ull << 20;
+    uint64_t t_done = blk_split * 2, s_hint = s_split;
+    int flip = 0;
+    for (uint64_t b0 = b_lo; b0 < total; b0 += chunk) {
+      const uint64_t b1 = std::min(total, b0 + chunk);
+      CU(h, cudaMemcpyAsync((uint8_t*)h->d_scratch + (b0 - b_lo), src + b0, b1 - b0, cudaMemcpyHostToDevice, h->copy_stream));
+      CU(h, cudaEventRecord(h->copy_ev[flip], h->copy_stream));
+      CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[flip], 0));
+      flip ^= 1;
+      uint64_t t_end = h->n_words32;
+      if (b1 < total) {
+        const uint64_t* it = std::upper_bound(offsets + s_hint, offsets + n_seq + 1, b1);
+        s_hint = (uint64_t)(it - offsets) - 1;
+        t_end = (PENG_FRONT_PAD + b1 + 2 * s_hint) / 32;
+      }
+      if (t_end > t_done) {
+        TRY(launch_pack(h, d_src, ascii, t_done, t_end));
+        t_done = t_end;
+      }
+    }
+  }
+  // ---- the packed part, phase by phase through the two pinned staging buffers ----
+  bool has_carry = false;
+  Partial carry{};
+  int buf = 0;
+  bool first = true;
+  static const bool dbg = getenv("PENG_INGEST_DEBUG") != nullptr;
+  double t_pack = 0, t_wait = 0, t_issue = 0;
+  auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  const double t_start = now();
+  for (uint64_t s = 0;;) {
+    uint64_t e = std::min(s_split, plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks - 4));
+    // the last phase of a fully packed set also writes the tail pad; if that does not fit, the tail gets a phase of its own
+    bool last = false;
+    if (s_split == n_seq && e == n_seq) {
+      const uint64_t q0 = first ? 0 : PENG_FRONT_PAD + offsets[s] + 2 * s;
+      last = n_blocks - (q0 >> 6) <= max_blocks - 4;
+    }
+    double t0 = now();
+    CU(h, cudaEventSynchronize(h->pin_ev[buf]));  // the previous copy out of this staging buffer is done
+    t_wait += now() - t0;
+    uint64_t* codes64 = (uint64_t*)h->pin[buf];
+    uint64_t* valid64 = codes64 + 2 * max_blocks;
+    Phase ph{src, offsets, s, e, ascii, PENG_FRONT_PAD, first, last, q_total, codes64, valid64};
+    uint64_t blk0, blk1;
+    phase_blocks(ph, &blk0, &blk1);
+    t0 = now();
+    pack_phase(pool, ph, &has_carry, &carry);
+    t_pack += now() - t0;
+    t0 = now();
+    blk1 = std::min(blk1, blk_split);  // the block of the split belongs to k_pack
+    if (blk1 > blk0) {
+      CU(h, cudaMemcpyAsync(h->d_codes + blk0 * 4, codes64, (blk1 - blk0) * 16, cudaMemcpyHostToDevice, h->copy_stream));
+      CU(h, cudaMemcpyAsync(h->d_valid + blk0 * 2, valid64, (blk1 - blk0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
+    }
+    CU(h, cudaEventRecord(h->pin_ev[buf], h->copy_stream));
+    t_issue += now() - t0;
+    buf ^= 1;
+    first = false;
+    s = e;
+    if (last || (s >= s_split && s_split < n_seq)) break;
+  }
+  // sequence starts of the packed part (k_pack writes those of its own words)
+  const uint64_t t_split = std::min<uint64_t>(blk_split * 2, h->n_words32);
+  CU(h, cudaMemsetAsync(h->d_sstart, 0, t_split * 4, h->stream));
+  CU(h, cudaEventRecord(h->copy_ev[1], h->copy_stream));
+  CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[1], 0));  // the offsets and every staged block have arrived
+  k_sstart_scatter<<<grid_for(std::max<uint64_t>(n_seq, 1), 256), 256, 0, h->stream>>>(h->d_offsets, n_seq, t_split, h->d_sstart);
+  LAUNCH_CHECK(h);
+  const double t_loop = now();
+  host_bookkeeping_parallel(h, offsets, n_seq);
+  const double t_book = now();
+  CU(h, cudaStreamSynchronize(h->stream));
+  if (dbg)
+    fprintf(stderr, "[ingest] threads %d split %.2f: phases %.2f ms (pack %.2f, wait %.2f, issue %.2f), bookkeeping %.2f, final sync %.2f\n",
+            pool.size(), (double)offsets[s_split] / (double)std::max<uint64_t>(total, 1), 1e3 * (t_loop - t_start), 1e3 * t_pack,
+            1e3 * t_wait, 1e3 * t_issue, 1e3 * (t_book - t_loop), 1e3 * (now() - t_book));
+  h->last_ingest_packed = s_split;
+  return PENG_OK;
+}
+
 // src on the HOST: the copy is cut into chunks on a second stream, the packing kernel follows chunk by chunk on the
 // handle's stream (a word is packed once every base of its 32 positions has arrived), so that packing, and the host's
 // own bookkeeping, hide behind the PCIe transfer.
 static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
+  h->last_ingest_packed = 0;
+  {
+    const int rc = ingest_host_hybrid(h, src, offsets, n_seq, ascii);
+    if (rc != 1) return rc;  // done (or failed); 1 = not applicable, plain path
+  }
   CU(h, cudaSetDevice(h->device));
   const uint64_t total = n_seq ? offsets[n_seq] : 0;
   TRY(need_scratch(h, (size_t)total + 16));
@@ -1699,6 +1905,14 @@ extern "C" int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, con
   return ingest_host_src(h, codes, offsets, n_seq, false);
 }
 
+extern "C" int peng_cuda_set_ingest_mode(peng_handle_t h, int mode, double host_fraction) {
+  if (!h || mode < 0 || mode > 2 || host_fraction > 1.0) return fail(h, PENG_E_INVALID, "set_ingest_mode: mode 0..2, fraction <= 1 (< 0: automatic)");
+  h->ingest_mode = mode;
+  h->ingest_fraction = host_fraction;
+  return PENG_OK;
+}
+extern "C" uint64_t peng_cuda_last_ingest_host_packed(peng_handle_t h) { return h ? h->last_ingest_packed : 0; }
+
 extern "C" int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets,
                                              uint64_t n_seq) {
   if (!h || !offsets) return fail(h, PENG_E_INVALID, "ingest_codes_device: NULL argument");
@@ -1710,7 +1924,6 @@ extern "C" int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_code
 // (host_ingest.h: scan_fasta) and copies the sequence bytes into two pinned staging buffers; every full buffer goes to
 // the device on the copy stream while the scan fills the other one.  Letters are translated and packed on the device
 // once the record table is known (k_pack).
-#define PENG_PIN_BYTES (16u << 20)
 struct StagingSink {
   peng_handle_t h;
   uint8_t* d_src;

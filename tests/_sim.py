@@ -17,10 +17,11 @@ FRONT_PAD = 64
 
 
 def _build():
-    deps = [_SRC, os.path.join(_CSRC, "core_seq.cuh"), os.path.join(_CSRC, "core_tab.cuh"), os.path.join(_CSRC, "host_ingest.h")]
+    deps = [_SRC, os.path.join(_CSRC, "core_seq.cuh"), os.path.join(_CSRC, "core_tab.cuh"), os.path.join(_CSRC, "host_ingest.h"),
+            os.path.join(_CSRC, "host_pack.cpp"), os.path.join(_CSRC, "host_pack.h")]
     if os.path.exists(_LIB) and os.path.getmtime(_LIB) >= max(os.path.getmtime(d) for d in deps):
         return
-    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-x", "c++",
+    subprocess.check_call(["/usr/bin/g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-pthread", "-x", "c++",
                            _SRC, "-o", _LIB])
 
 
@@ -178,6 +179,19 @@ def count_part_keys(st, W, both=True):
                                 C.c_uint64(cap), _p(stats, u64p))
     return np.sort(out[:n]), int(stats[0]), dict(missed=int(stats[1]), needless_slow=int(stats[2]), fast=int(stats[3]),
                                                  slow_units=int(stats[4]))
+
+
+def host_pack(src, offsets, ascii=False, n_threads=4, max_blocks=1 << 14):
+    """host_pack.cpp: the packed ingest's host half, all phases -> (codes words, valid words, phases) in the device layout."""
+    src = np.ascontiguousarray(src, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    n_seq = len(offsets) - 1
+    nw = int(lib.sim_n_words32(C.c_uint64(n_seq), C.c_uint64(int(offsets[-1]))))
+    codes = np.full(2 * nw + 8, 0xDEADBEEF, np.uint32)
+    valid = np.full(nw + 8, 0xDEADBEEF, np.uint32)
+    ph = lib.sim_host_pack(_p(src, u8p), _p(offsets, u64p), C.c_uint64(n_seq), int(ascii), int(n_threads), C.c_uint64(max_blocks),
+                           C.c_uint64(nw), _p(codes, u32p), _p(valid, u32p))
+    return codes, valid, nw, ph
 
 
 def scan_fasta(path):

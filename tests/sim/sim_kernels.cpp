@@ -333,3 +333,43 @@ uint64_t sim_sort_leading(const float* z, uint64_t n, float threshold, uint64_t*
   return lead;
 }
 }
+
+// ---- host half of the packed ingest (host_pack.cpp): all phases into one host image of the device arrays ----------------
+#include "../../peng-motif_b200/csrc/host_pack.cpp"
+extern "C" {
+// codes32: 2 * n_words32 + 8 words, valid32: n_words32 + 8 words (as the device allocates them); returns the number of
+// phases, or -1 when a sequence does not fit a phase
+int sim_host_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, int ascii, int n_threads, uint64_t max_blocks,
+                  uint64_t n_words32, uint32_t* codes32, uint32_t* valid32) {
+  using namespace peng_hostpack;
+  Pool pool(n_threads);
+  const uint64_t q_total = ((n_words32 * 32 + 63) / 64) * 64;
+  const uint64_t n_blocks = q_total / 64;
+  std::vector<uint64_t> sc(2 * max_blocks + 2), sv(max_blocks + 1);
+  bool has_carry = false;
+  Partial carry{};
+  int phases = 0;
+  uint64_t s = 0;
+  bool first = true;
+  for (;;) {
+    uint64_t e = plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks);
+    bool last = e == n_seq;
+    if (last) {  // the tail pad must fit as well
+      const uint64_t q0 = first ? 0 : PENG_FRONT_PAD + offsets[s] + 2 * s;
+      if (n_blocks - (q0 >> 6) > max_blocks) last = false;
+    }
+    if (e == s && !last) return -1;
+    Phase ph{src, offsets, s, e, ascii != 0, PENG_FRONT_PAD, first, last, q_total, sc.data(), sv.data()};
+    uint64_t blk0, blk1;
+    phase_blocks(ph, &blk0, &blk1);
+    pack_phase(pool, ph, &has_carry, &carry);
+    memcpy(codes32 + blk0 * 4, sc.data(), (blk1 - blk0) * 16);
+    memcpy(valid32 + blk0 * 2, sv.data(), (blk1 - blk0) * 8);
+    phases++;
+    if (last) break;
+    s = e;
+    first = false;
+  }
+  return has_carry ? -2 : phases;
+}
+}

@@ -1,0 +1,77 @@
+"""peng_cuda_ingest_codes from host buffers: raw bytes + device packing, host packing (host_pack.cpp) and the hybrid of the
+two must leave bit-identical device buffers — checked through everything that reads them: export, k-mer counts (codes +
+validity), background counts (sequence starts)."""
+import numpy as np
+import pytest
+
+import _cases
+import _oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture()
+def g(gpu):
+    yield gpu
+    gpu.set_ingest_mode(0, -1.0)
+
+
+def fingerprint(gpu, codes, offs, W=8):
+    c2, o2 = gpu.export_codes()
+    assert np.array_equal(o2, offs) and np.array_equal(c2, np.where(codes > 4, 0, codes))
+    ltot = gpu.count(W, 1)
+    counts = gpu.get_counts()
+    _, bg = gpu.background_model(2, return_counts=True)
+    return ltot, counts, bg
+
+
+def check_modes(gpu, codes, offs, modes):
+    gpu.set_ingest_mode(1, -1.0)
+    gpu.ingest_codes(codes, offs)
+    assert gpu.last_ingest_host_packed == 0
+    ref = fingerprint(gpu, codes, offs)
+    r2, lt = O.count(codes, offs, 8, True)
+    assert ref[0] == lt and np.array_equal(ref[1], r2)
+    for mode, frac in modes:
+        gpu.set_ingest_mode(mode, frac)
+        gpu.ingest_codes(codes, offs)
+        if mode == 2 or frac >= 0.5:
+            assert gpu.last_ingest_host_packed > 0, (mode, frac)
+        got = fingerprint(gpu, codes, offs)
+        assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and np.array_equal(got[2], ref[2]), (mode, frac)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_small_dirty_sets(g, seed):
+    codes, offs = O.encode(_cases.dirty_sequences(seed, n_max=30, len_max=900))
+    check_modes(g, codes, offs, [(2, -1.0), (0, 0.5), (0, 0.05), (0, 0.97)])
+
+
+def test_ragged_lengths_many_phases(g):
+    rng = np.random.RandomState(11)
+    lens = rng.randint(1, 600, 400_000)  # 120 M bases: 3 staging phases when packed entirely on the host
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    codes = rng.randint(0, 5, int(offs[-1])).astype(np.uint8)
+    check_modes(g, codes, offs, [(2, -1.0), (0, 0.77), (0, 0.31), (0, -1.0)])
+
+
+def test_fixed_length_set_and_automatic_choice(g, pkg):
+    g.ingest_synthetic(300_000, 200, 5, 0, "TGCTGASTCAGCA", 0.3, 0.01)
+    codes, offs = g.export_codes()
+    check_modes(g, codes, offs, [(2, -1.0), (0, 0.6)])
+    g.set_ingest_mode(0, -1.0)  # automatic: hybrid with >= 4 host threads and AVX-512, raw otherwise — same buffers either way
+    g.ingest_codes(codes, offs)
+    assert g.count(10, 1) > 0
+    ref, lt = O.count(codes, offs, 10, True)
+    assert np.array_equal(g.get_counts(), ref)
+
+
+def test_long_sequence_falls_back(g):
+    rng = np.random.RandomState(2)
+    offs = np.array([0, 1000, 50_001_000, 50_002_000], np.uint64)  # 50 M letters in one record: more than a staging phase
+    codes = rng.randint(1, 5, int(offs[-1])).astype(np.uint8)
+    g.set_ingest_mode(2, -1.0)
+    g.ingest_codes(codes, offs)
+    assert g.last_ingest_host_packed == 0  # plain path
+    c2, _ = g.export_codes()
+    assert np.array_equal(c2, codes)

@@ -308,3 +308,51 @@ def test_select_with_nan_falls_back_to_plain_sort():
     z[123] = np.nan
     lead, a, b = S.sort_leading(z, 10.0)
     assert lead == len(z) and np.array_equal(a, b)
+
+
+# ---- packed ingest: the host threads write the device layout themselves (host_pack.cpp) ------------------------------------
+def _host_pack_matches(src, offs, ascii, n_threads, max_blocks):
+    st = S.pack(src, offs, ascii)
+    codes, valid, nw, phases = S.host_pack(src, offs, ascii, n_threads, max_blocks)
+    assert phases > 0, phases
+    q = ((nw * 32 + 63) // 64) * 64  # positions written (whole 64-position blocks)
+    assert np.array_equal(codes[: q // 16][: 2 * nw], st.codes[: 2 * nw]), (n_threads, max_blocks)
+    assert np.array_equal(valid[: q // 32][:nw], st.valid[:nw]), (n_threads, max_blocks)
+    assert not codes[2 * nw: q // 16].any() and not valid[nw: q // 32].any()
+    return phases
+
+
+@pytest.mark.parametrize("seed", range(10))
+def test_host_pack_equals_device_pack(seed):
+    seqs = _cases.dirty_sequences(seed, n_max=30, len_max=700)
+    codes, offs = O.encode(seqs)
+    for n_threads, max_blocks in ((1, 1 << 14), (3, 1 << 14), (4, 40), (7, 23)):
+        _host_pack_matches(codes, offs, False, n_threads, max_blocks)
+    text = np.frombuffer("".join(seqs).encode(), np.uint8)
+    lower = np.frombuffer("".join(seqs).lower().replace("n", "x").encode(), np.uint8)
+    _host_pack_matches(text, offs, True, 3, 64)
+    _host_pack_matches(lower, offs, True, 2, 1 << 14)
+
+
+def test_host_pack_many_phases_and_threads():
+    rng = np.random.RandomState(3)
+    lens = rng.randint(1, 300, 5000)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    codes = rng.randint(0, 5, int(offs[-1])).astype(np.uint8)
+    assert _host_pack_matches(codes, offs, False, 8, 512) > 10
+    _host_pack_matches(codes, offs, False, 16, 1 << 16)
+    # fixed length 200 (BASELINE configs[2] shape), lengths around the 64-letter chunk size, and an empty set
+    offs = (np.arange(3001) * 200).astype(np.uint64)
+    _host_pack_matches(rng.randint(1, 5, 600000).astype(np.uint8), offs, False, 5, 2000)
+    for L in (1, 2, 61, 62, 63, 64, 65, 126, 127, 128, 129):
+        offs = (np.arange(41) * L).astype(np.uint64)
+        _host_pack_matches(rng.randint(0, 5, 40 * L).astype(np.uint8), offs, False, 3, 9)
+    _host_pack_matches(np.zeros(0, np.uint8), np.zeros(1, np.uint64), False, 4, 64)
+
+
+def test_host_pack_scalar_path_and_oversized_sequence():
+    rng = np.random.RandomState(4)
+    offs = np.array([0, 50, 5000, 5100], np.uint64)
+    codes = rng.randint(0, 5, 5100).astype(np.uint8)
+    assert S.host_pack(codes, offs, False, 2, 16)[3] == -1  # the 4950-letter sequence needs 78 blocks
+    _host_pack_matches(codes, offs, False, 2, 200)

@@ -1,0 +1,17 @@
+"""Host-buffer ingest timing per mode: raw bytes + device packing / host packing / hybrid (peng_cuda_set_ingest_mode)."""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import _pkg
+pkg = _pkg.load()
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+g = pkg.PengCuda(0)
+g.ingest_synthetic(n, 200, 1234, 0, "TGCTGASTCAGCA", 0.3, 0.0)
+codes, offs = g.export_codes()
+pin = torch.from_numpy(codes).pin_memory()
+for mode, frac in [(1, -1), (2, -1), (0, -1), (0, 0.3), (0, 0.5), (0, 0.65), (0, 0.8)]:
+    g.set_ingest_mode(mode, frac)
+    ts = []
+    for i in range(8):
+        t0 = time.perf_counter(); g.ingest_codes(pin.numpy(), offs); g.synchronize(); ts.append(time.perf_counter() - t0)
+    print(f"mode {mode} fraction {frac}: {1e3 * np.median(ts[2:]):.2f} ms  ({n * 200 / np.median(ts[2:]) / 1e9:.1f} Gbases/s), host-packed {g.last_ingest_host_packed}", flush=True)
