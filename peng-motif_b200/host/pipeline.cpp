@@ -18,6 +18,8 @@
 #include <iostream>
 #include <memory>
 #include <set>
+#include <unordered_map>
+#include <unordered_set>
 
 #include "peng_host.h"
 
@@ -87,31 +89,96 @@ void optimize_iupac_patterns(const Device& dev, const Options& opt, int W, const
   const size_t pseudo_expected = (size_t)((float)n_sequences * opt.enrich_pseudocount_factor);
   const unsigned n_seq_u = (unsigned)n_sequences;
 
-  auto aggregate = [&](const std::vector<uint64_t>& ids, std::vector<Motif>& motifs) {
-    const int n = (int)ids.size();
-    std::vector<uint64_t> sites((size_t)n);
-    std::vector<float> bgp((size_t)n), expected((size_t)n);
-    dev.check(peng_cuda_iupac_aggregate(dev.h, ids.data(), n, PENG_F32REF, sites.data(), bgp.data(), expected.data()));
-    motifs.assign((size_t)n, Motif());
-    for (int i = 0; i < n; i++) {
-      motifs[(size_t)i].pattern = ids[(size_t)i];
-      motifs[(size_t)i].length = W;
-      set_aggregated_attributes(motifs[(size_t)i], sites[(size_t)i], bgp[(size_t)i], expected[(size_t)i]);
+  // Degenerate sums are pure functions of the pattern, so they are cached per IUPAC id: `fetch` asks the device for the ids
+  // it has not seen yet (one call, chunked only to bound the kernel's scratch), `aggregate` reads the cache.
+  struct Agg { uint64_t sites; float bgp, expected; };
+  std::unordered_map<uint64_t, Agg> cache;
+  auto fetch = [&](const std::vector<uint64_t>& ids) {
+    std::vector<uint64_t> need;
+    {
+      std::unordered_set<uint64_t> asked;
+      for (uint64_t id : ids)
+        if (!cache.count(id) && asked.insert(id).second) need.push_back(id);
+    }
+    const size_t max_call = W <= 10 ? 8192 : W == 12 ? 1024 : 64;  // BOTH: 4^W bits of scratch per pattern
+    for (size_t at = 0; at < need.size(); at += max_call) {
+      const int n = (int)std::min(max_call, need.size() - at);
+      std::vector<uint64_t> sites((size_t)n);
+      std::vector<float> bgp((size_t)n), expected((size_t)n);
+      dev.check(peng_cuda_iupac_aggregate(dev.h, need.data() + at, n, PENG_F32REF, sites.data(), bgp.data(), expected.data()));
+      for (int i = 0; i < n; i++) cache[need[at + (size_t)i]] = Agg{sites[(size_t)i], bgp[(size_t)i], expected[(size_t)i]};
     }
   };
+  auto aggregate = [&](const std::vector<uint64_t>& ids, std::vector<Motif>& motifs) {
+    fetch(ids);
+    const int n = (int)ids.size();
+    motifs.assign((size_t)n, Motif());
+    for (int i = 0; i < n; i++) {
+      const Agg& a = cache[ids[(size_t)i]];
+      motifs[(size_t)i].pattern = ids[(size_t)i];
+      motifs[(size_t)i].length = W;
+      set_aggregated_attributes(motifs[(size_t)i], a.sites, a.bgp, a.expected);
+    }
+  };
+  auto seed_score = [&](size_t si) -> float {  // BasePattern::getOptimizationScore (src/base_pattern.cpp:180-224)
+    switch (opt.score) {
+      case Score::LogPval: return seed_cols.logp[si];
+      case Score::ExpCounts: return (seed_cols.expected[si] + (float)pseudo_expected) / (float)seed_cols.counts[si];
+      default: return mutual_information_score((float)(unsigned)seed_cols.counts[si], seed_cols.expected[si], n_seq_u);
+    }
+  };
+  auto sweep_candidates = [&](uint64_t mother, std::vector<uint64_t>& candidates) {
+    for (int p = 0; p < W; p++) {
+      const int c = iupac_letter_at(mother, p);
+      const uint64_t masked = mother - (uint64_t)c * iupac_factor(p);
+      for (int r : similar_letters(c)) candidates.push_back(masked + (uint64_t)r * iupac_factor(p));
+    }
+  };
+
+  // Speculative pass: the climbs of ALL seeds advance in lockstep, one device call per round for the sweeps of every climb
+  // that is still improving (the reference climbs seed after seed, <= W x 10 patterns per call and a host round trip
+  // each).  A climb here ignores the `seen` set, which can only cut a climb short, so the sequential replay below walks a
+  // prefix of what was computed here and finds every sum in the cache; nothing is printed in this pass.
+  {
+    struct Climb { uint64_t pattern; float score; bool active; };
+    std::vector<Climb> climbs;
+    std::vector<uint64_t> ids;
+    for (size_t si = 0; si < seeds.size(); si++) {
+      climbs.push_back(Climb{base_id_to_iupac_id(seeds[si], W), seed_score(si), true});
+      ids.push_back(climbs.back().pattern);
+    }
+    fetch(ids);
+    for (int round = 0; round < 64; round++) {
+      ids.clear();
+      for (const Climb& c : climbs)
+        if (c.active) sweep_candidates(c.pattern, ids);
+      if (ids.empty()) break;
+      fetch(ids);
+      for (Climb& c : climbs) {
+        if (!c.active) continue;
+        std::vector<uint64_t> cand;
+        sweep_candidates(c.pattern, cand);
+        std::vector<Motif> mutants;
+        aggregate(cand, mutants);
+        c.active = false;
+        for (const Motif& mutant : mutants) {
+          const float score = motif_score(mutant, opt.score, pseudo_expected, n_seq_u);
+          if (score < c.score) {
+            c.active = true;
+            c.score = score;
+            c.pattern = mutant.pattern;
+          }
+        }
+      }
+    }
+  }
 
   for (size_t si = 0; si < seeds.size(); si++) {
     const uint64_t seed = seeds[si];
     std::vector<Motif> one;
     aggregate({base_id_to_iupac_id(seed, W)}, one);
     Motif best_mutant = one[0];
-    // score of the seed from the BASE tables (BasePattern::getOptimizationScore, src/base_pattern.cpp:180-224)
-    float best_score;
-    switch (opt.score) {
-      case Score::LogPval: best_score = seed_cols.logp[si]; break;
-      case Score::ExpCounts: best_score = (seed_cols.expected[si] + (float)pseudo_expected) / (float)seed_cols.counts[si]; break;
-      default: best_score = mutual_information_score((float)(unsigned)seed_cols.counts[si], seed_cols.expected[si], n_seq_u);
-    }
+    float best_score = seed_score(si);  // from the BASE tables
     print_climb_line(best_mutant, best_score);
 
     bool found_better = true;
@@ -120,11 +187,7 @@ void optimize_iupac_patterns(const Device& dev, const Options& opt, int W, const
       const uint64_t mother = best_mutant.pattern;
       std::set<uint64_t> current_seen;
       std::vector<uint64_t> candidates;
-      for (int p = 0; p < W; p++) {
-        const int c = iupac_letter_at(mother, p);
-        const uint64_t masked = mother - (uint64_t)c * iupac_factor(p);
-        for (int r : similar_letters(c)) candidates.push_back(masked + (uint64_t)r * iupac_factor(p));
-      }
+      sweep_candidates(mother, candidates);
       std::vector<Motif> mutants;
       aggregate(candidates, mutants);
       for (const Motif& mutant : mutants) {
