@@ -2148,8 +2148,8 @@ static int launch_count_partition(peng_handle_t h, bool both) {
   const int cfg = h->part_cfg;
   const unsigned grid_p = (unsigned)h->sm_count * part_cfg_per_sm(cfg);
   const uint64_t chunk_units = std::min(n_units, units_per_chunk);
-  // private region of (class, stage-P CTA): 1.5x the expected share, at least 1024 keys, multiple of 128
-  uint64_t region_cap = (chunk_units * 32 * 3 / 2) / ((uint64_t)grid_p * PART_NCLASS);
+  // private region of (class, stage-P CTA): 2x the expected share (composition skew of real genomes: a class of an AT-rich set takes ~1.6x its uniform share), at least 1024 keys, multiple of 128
+  uint64_t region_cap = (chunk_units * 32 * 2) / ((uint64_t)grid_p * PART_NCLASS);
   region_cap = std::max<uint64_t>(1024, (region_cap + 127) & ~127ull);
   const size_t bucket_elems = (size_t)region_cap * grid_p * PART_NCLASS;
   if (h->part_bucket_elems < bucket_elems) {
@@ -2211,7 +2211,7 @@ static int deep_reserve(peng_handle_t h, int level, size_t bucket_elems, size_t 
   return PENG_OK;
 }
 static uint32_t deep_region_cap(uint64_t keys, uint64_t n_regions, uint32_t min_cap) {
-  uint64_t cap = keys * 3 / 2 / n_regions;
+  uint64_t cap = keys * 2 / n_regions;
   cap = std::max<uint64_t>(min_cap, (cap + 127) & ~127ull);
   return (uint32_t)cap;
 }

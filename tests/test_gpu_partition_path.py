@@ -118,3 +118,23 @@ def test_sharded_sum_matches_whole(part, pkg):
     ids = np.arange(0, 4 ** W, 4 ** W // 64)
     canon = np.minimum(ids, rc)
     assert np.array_equal(acc[:-1][canon], whole[ids])
+
+
+def test_composition_skew_at_scale(gpu, pkg):
+    """An AT-rich set (and an extreme one) large enough for the automatic partition paths: the classes are far from
+    equally filled, bucket regions of the heavy classes may run full (their blocks then go straight to the table)."""
+    rng = np.random.RandomState(17)
+    for p in ([0.32, 0.18, 0.18, 0.32], [0.7, 0.1, 0.1, 0.1]):
+        n, L = 120_000, 200
+        codes = (rng.choice(4, n * L, p=p) + 1).astype(np.uint8)
+        offs = (np.arange(n + 1) * L).astype(np.uint64)
+        gpu.ingest_codes(codes, offs)
+        for Wt, both in ((10, True), (10, False), (12, False)):
+            gpu.set_count_path(1)
+            l1 = gpu.count(Wt, int(both)); c1 = gpu.get_counts()
+            gpu.set_count_path(2)
+            l2 = gpu.count(Wt, int(both)); c2 = gpu.get_counts()
+            assert gpu.last_count_path == 2 and l1 == l2 and np.array_equal(c1, c2), (p, Wt, both)
+    gpu.set_count_path(0)
+    ref, lt = O.count(codes, offs, 10, True)
+    assert gpu.count(10, 1) == lt and np.array_equal(gpu.get_counts(), ref)
