@@ -129,6 +129,13 @@ int peng_cuda_last_count_path(peng_handle_t h); /* 1 or 2: what the last peng_cu
 int peng_cuda_count_local(peng_handle_t h, int W, int strand);
 int peng_cuda_count_buffer(peng_handle_t h, void** device_ptr, uint64_t* n_u64);
 int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot);
+/* The same with a 32-bit exchange, for sets of fewer than 2^32 stream positions IN TOTAL over all ranks and at most 2^30
+ * per rank (no uint32 bin, nor ltot, can overflow in the sum): _count_local32 leaves the UNFOLDED uint32 launch table with
+ * ltot in word 4^W; the caller sums `n_u32` uint32 at `ptr` over ranks — half the bytes of the 64-bit exchange —;
+ * _count_finish32 folds (reverse-complement pairs, mirror) once, after the sum, and publishes ltot. */
+int peng_cuda_count_local32(peng_handle_t h, int W, int strand);
+int peng_cuda_count_buffer32(peng_handle_t h, void** device_ptr, uint64_t* n_u32);
+int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot);
 /* Sparse read-back for tables that are too large to copy (W >= 14): the bins at `ids`, and the sum of all bins. */
 int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uint64_t n, uint64_t* out);
 int peng_cuda_counts_total(peng_handle_t h, uint64_t* total);

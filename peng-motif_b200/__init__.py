@@ -74,6 +74,9 @@ _PROTOS = {
     "peng_cuda_last_count_path": (C.c_int, [H]),
     "peng_cuda_count_buffer": (C.c_int, [H, C.POINTER(C.c_void_p), u64p]),
     "peng_cuda_count_finish": (C.c_int, [H, u64p]),
+    "peng_cuda_count_local32": (C.c_int, [H, C.c_int, C.c_int]),
+    "peng_cuda_count_buffer32": (C.c_int, [H, C.POINTER(C.c_void_p), u64p]),
+    "peng_cuda_count_finish32": (C.c_int, [H, u64p]),
     "peng_cuda_gather_counts": (C.c_int, [H, C.c_void_p, C.c_uint64, C.c_void_p]),
     "peng_cuda_counts_total": (C.c_int, [H, u64p]),
     "peng_cuda_set_counts": (C.c_int, [H, C.c_int, C.c_int, C.c_void_p, C.c_uint64]),
@@ -307,6 +310,21 @@ class PengCuda:
     def count_finish(self):
         ltot = C.c_uint64()
         self._ck(self.lib.peng_cuda_count_finish(self.h, C.byref(ltot)))
+        return ltot.value
+
+    # 32-bit exchange: sets of < 2^32 positions in total over all ranks, <= 2^30 per rank
+    def count_local32(self, W, strand=STRAND_BOTH):
+        self._ck(self.lib.peng_cuda_count_local32(self.h, W, strand))
+        self.W, self.strand = W, strand
+
+    def count_buffer32(self):
+        p, n = C.c_void_p(), C.c_uint64()
+        self._ck(self.lib.peng_cuda_count_buffer32(self.h, C.byref(p), C.byref(n)))
+        return DeviceArray(p.value, n.value, "<i4")  # uint32 bins viewed as int32 (two's-complement sum is the same)
+
+    def count_finish32(self):
+        ltot = C.c_uint64()
+        self._ck(self.lib.peng_cuda_count_finish32(self.h, C.byref(ltot)))
         return ltot.value
 
     def get_counts(self):

@@ -61,6 +61,8 @@ struct peng_cuda_ctx {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool fuse_mirror = false;        // peng_cuda_count (single GPU): the final fold may write the mirror copy as well
   bool mirrored = false;           // ... and did
+  bool defer_fold = false;         // peng_cuda_count_local32: leave the uint32 table unfolded for a 32-bit exchange
+  bool fold_deferred = false;      // ... and it was left
 
   // ---- background ----
   int K = -1;
@@ -934,6 +936,13 @@ __global__ void k_fold_first(uint32_t* __restrict__ hist, uint64_t* __restrict__
     acc[i] = v;
     if (v) hist[i] = 0;
   }
+}
+
+// 32-bit exchange (peng_cuda_count_local32 / _finish32): ltot rides in word n of the uint32 table
+__global__ void k_ltot_to32(const uint64_t* __restrict__ ltot64, uint32_t* __restrict__ word) { *word = (uint32_t)*ltot64; }
+__global__ void k_ltot_from32(uint32_t* __restrict__ word, uint64_t* __restrict__ ltot64) {
+  *ltot64 = *word;
+  *word = 0;
 }
 
 // second copy of the pair count at the reverse-complement id (src/base_pattern.cpp:387-392). Only
@@ -2375,7 +2384,7 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   const uint64_t n = 1ull << (2 * W);
   if (h->W != W || !h->d_counts) {
     free_tables(h);
-    TRY(dev_alloc(h, &h->d_hist32, n));
+    TRY(dev_alloc(h, &h->d_hist32, n + 4));
     TRY(dev_alloc(h, &h->d_counts, n + 1));
   }
   h->W = W;
@@ -2383,7 +2392,7 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   h->n_patterns = n;
   h->counts_final = false;
   h->stats_ready = false;
-  CU(h, cudaMemsetAsync(h->d_hist32, 0, n * 4, h->stream));
+  CU(h, cudaMemsetAsync(h->d_hist32, 0, (n + 4) * 4, h->stream));
   // up to 2^30 stream positions (pads included) every path folds exactly once, at the end: that fold writes the whole 64-bit table
   const bool single_fold = h->n_words32 <= (1ull << 25);  // one chunk of every path
   if (single_fold) CU(h, cudaMemsetAsync(h->d_counts + n, 0, 8, h->stream));
@@ -2413,15 +2422,24 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   }
   TRY(rc);
   MARK(h, 4);
-  if (h->used_partition && both) {
+  h->fold_deferred = false;
+  if (h->defer_fold && single_fold) {
+    // 32-bit exchange: the caller sums the uint32 table (+ ltot in word n) over the ranks, peng_cuda_count_finish32 folds
+    k_ltot_to32<<<1, 1, 0, h->stream>>>(h->d_counts + n, h->d_hist32 + n);
+    LAUNCH_CHECK(h);
+    h->fold_deferred = true;
+  } else if (h->used_partition && both) {
     if (single_fold && h->fuse_mirror) {
       k_fold_canon_first<true><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
       h->mirrored = true;
     } else if (single_fold) k_fold_canon_first<false><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
     else k_fold_canon<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
-  } else if (single_fold) k_fold_first<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
-  else k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
-  LAUNCH_CHECK(h);
+    LAUNCH_CHECK(h);
+  } else {
+    if (single_fold) k_fold_first<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
+    else k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
+    LAUNCH_CHECK(h);
+  }
   MARK(h, 5);
   return PENG_OK;
 }
@@ -2437,13 +2455,49 @@ extern "C" int peng_cuda_last_count_path(peng_handle_t h) { return h ? (h->used_
 
 extern "C" int peng_cuda_count_buffer(peng_handle_t h, void** device_ptr, uint64_t* n_u64) {
   if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_buffer: nothing counted");
+  if (h->fold_deferred) return fail(h, PENG_E_INVALID, "count_buffer: the table is unfolded (peng_cuda_count_buffer32)");
   if (device_ptr) *device_ptr = h->d_counts;
   if (n_u64) *n_u64 = h->n_patterns + 1;
   return PENG_OK;
 }
 
+// 32-bit exchange for multi-GPU sets of fewer than 2^32 positions IN TOTAL (no uint32 bin, nor ltot, can overflow in the
+// sum): half the bytes of the 64-bit exchange cross NVLink, and the fold runs once, after the sum, mirror included.
+extern "C" int peng_cuda_count_local32(peng_handle_t h, int W, int strand) {
+  if (!h) return PENG_E_INVALID;
+  h->defer_fold = true;
+  const int rc = peng_cuda_count_local(h, W, strand);
+  h->defer_fold = false;
+  TRY(rc);
+  if (!h->fold_deferred) return fail(h, PENG_E_INVALID, "count_local32: the local set has more than 2^30 positions, use the 64-bit exchange");
+  return PENG_OK;
+}
+extern "C" int peng_cuda_count_buffer32(peng_handle_t h, void** device_ptr, uint64_t* n_u32) {
+  if (!h || !h->d_hist32 || !h->fold_deferred) return fail(h, PENG_E_INVALID, "count_buffer32: no unfolded table (peng_cuda_count_local32 first)");
+  if (device_ptr) *device_ptr = h->d_hist32;
+  if (n_u32) *n_u32 = h->n_patterns + 1;
+  return PENG_OK;
+}
+extern "C" int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot) {
+  if (!h || !h->d_hist32 || !h->fold_deferred) return fail(h, PENG_E_INVALID, "count_finish32: no unfolded table (peng_cuda_count_local32 first)");
+  CU(h, cudaSetDevice(h->device));
+  const uint64_t n = h->n_patterns;
+  k_ltot_from32<<<1, 1, 0, h->stream>>>(h->d_hist32 + n, h->d_counts + n);
+  LAUNCH_CHECK(h);
+  if (h->used_partition && h->strand == PENG_STRAND_BOTH) {
+    k_fold_canon_first<true><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->W, n);
+    h->mirrored = true;
+  } else {
+    k_fold_first<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
+  }
+  LAUNCH_CHECK(h);
+  h->fold_deferred = false;
+  return peng_cuda_count_finish(h, ltot);
+}
+
 extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
   if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_finish: nothing counted");
+  if (h->fold_deferred) return fail(h, PENG_E_INVALID, "count_finish: the table is unfolded (peng_cuda_count_finish32)");
   CU(h, cudaSetDevice(h->device));
   if (!h->counts_final) {
     if (h->strand == PENG_STRAND_BOTH && !h->mirrored) {
@@ -2510,7 +2564,7 @@ extern "C" int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const ui
   const uint64_t n = 1ull << (2 * W);
   if (h->W != W || !h->d_counts) {
     free_tables(h);
-    TRY(dev_alloc(h, &h->d_hist32, n));
+    TRY(dev_alloc(h, &h->d_hist32, n + 4));
     TRY(dev_alloc(h, &h->d_counts, n + 1));
   }
   h->W = W;

@@ -138,3 +138,29 @@ def test_composition_skew_at_scale(gpu, pkg):
     gpu.set_count_path(0)
     ref, lt = O.count(codes, offs, 10, True)
     assert gpu.count(10, 1) == lt and np.array_equal(gpu.get_counts(), ref)
+
+
+@pytest.mark.parametrize("W_,both,n", [(10, True, 40_000), (10, False, 40_000), (8, True, 4_000), (12, True, 4_000), (14, False, 100_000)])
+def test_sharded_sum32_matches_whole(gpu, pkg, W_, both, n):
+    """The 32-bit exchange: unfolded uint32 tables (+ ltot in word 4^W) of 4 shards summed as the all-reduce would, written
+    back, folded once by count_finish32 — equals the whole-set table, on the partition paths and on the L2-atomic path."""
+    import torch
+
+    gpu.set_count_path(0)
+    gpu.ingest_synthetic(n, 200, 7, 0, "TGCTGASTCAGCA", 0.3, 0.01)
+    ltot = gpu.count(W_, int(both))
+    ids = np.random.RandomState(1).randint(0, 4 ** W_, 1 << 16, dtype=np.int64).astype(np.uint64)
+    whole, total = gpu.gather_counts(ids), gpu.counts_total()
+    acc = None
+    for r in range(4):
+        gpu.ingest_synthetic(n // 4, 200, 7, r * (n // 4), "TGCTGASTCAGCA", 0.3, 0.01)
+        gpu.count_local32(W_, int(both))
+        gpu.synchronize()  # the handle works on its own stream, torch on another
+        buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
+        acc = buf.clone() if acc is None else acc + buf
+        with pytest.raises(pkg.PengCudaError):
+            gpu.count_finish()  # the 64-bit finish must refuse an unfolded table
+    buf.copy_(acc)  # what the all-reduce leaves on every rank
+    torch.cuda.synchronize()
+    assert gpu.count_finish32() == ltot
+    assert np.array_equal(gpu.gather_counts(ids), whole) and gpu.counts_total() == total
