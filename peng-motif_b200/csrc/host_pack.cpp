@@ -10,6 +10,8 @@
 #include <mutex>
 #include <thread>
 
+#include <unistd.h>
+
 namespace peng_hostpack {
 
 bool have_avx512() {
@@ -253,7 +255,11 @@ void Pool::run(int n_tasks, void (*fn)(int, void*), void* arg) {
 }
 
 Pool& global_pool() {
-  static Pool* pool = [] {
+  static Pool* pool = nullptr;
+  static pid_t owner = 0;
+  static std::mutex m;
+  std::lock_guard<std::mutex> lk(m);
+  if (!pool || owner != getpid()) {  // a forked child has none of the parent's worker threads: it gets its own pool
     int n = 0;
     if (const char* e = getenv("PENG_HOST_THREADS")) n = atoi(e);
     if (n <= 0) {
@@ -263,11 +269,11 @@ Pool& global_pool() {
         if (w > 1) n = std::max(1, n / w);
       }
     }
-    return new Pool(std::min(std::max(n, 1), 32));  // never destroyed: worker threads must not be joined at exit
-  }();
+    pool = new Pool(std::min(std::max(n, 1), 32));  // never destroyed: worker threads must not be joined at exit
+    owner = getpid();
+  }
   return *pool;
 }
-
 
 // ---- one phase --------------------------------------------------------------------------------------------------------
 void phase_blocks(const Phase& ph, uint64_t* blk0, uint64_t* blk1) {
