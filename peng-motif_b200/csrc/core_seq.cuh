@@ -416,6 +416,95 @@ PENG_HD void cand_rc_finish(CandState& st) {
 }
 PENG_HD uint32_t cand_result(const CandState& st) { return compress_even16(st.c1) | (compress_even16(st.c2) << 16); }
 
+// ---- the same tests on BIT PLANES --------------------------------------------------------------------------
+// The 2-bit layout spends two bit lanes per position, so every shift / AND of the scan above moves 16 positions.  With the
+// two bits of a code in separate words (plane H = bit 1, plane L = bit 0, position 32u + b at bit b of word u; written
+// once per ingest by k_make_planes) the same tests move 32 positions per instruction, the three 16-position words of a
+// unit and its look-ahead become two words, and the flags come out one bit per position (no compress at the end).
+// pl[0..5] = H[u-1], H[u], H[u+1], L[u-1], L[u], L[u+1].  The flags are identical to conflict_candidates() (tests/sim).
+struct CandStatePl {
+  uint32_t c;     // candidate flags of positions 32u .. 32u+31
+  uint32_t p[2];  // PAL(m) at m = 32u + 32j + k, being narrowed
+};
+PENG_HD void cand_pl_init(CandStatePl& st) { st.c = 0; st.p[0] = st.p[1] = 0xFFFFFFFFu; }
+template <int W>
+PENG_HD void cand_pl_ff_run(const uint32_t* pl, int D, int R, CandStatePl& st) {
+  static_assert(W >= 4 && W <= 16 && (W % 2) == 0, "window arithmetic assumes W-1 <= 15 lags");
+  uint32_t e[2];  // e[j] bit k: x[p] == x[p-D] at p = 32u + 32j + k
+#pragma unroll
+  for (int j = 0; j < 2; j++) {
+    const uint32_t th = pl[j + 1] ^ funnel_r(pl[j], pl[j + 1], 32u - (uint32_t)D);
+    e[j] = ~(th | (pl[j + 4] ^ funnel_r(pl[j + 3], pl[j + 4], 32u - (uint32_t)D)));
+  }
+  // runs by doubling; the look-ahead word only has to be right for its low positions (a run that starts at position 31
+  // of the unit ends at 31 + 15 = 46 < 64)
+#define PENG_SHP(X, k, j) ((j) == 0 ? funnel_r(X[0], X[1], (uint32_t)(k)) : (X[1] >> (uint32_t)(k)))
+  uint32_t r2[2], r4[2], r8[2], run[2];
+#pragma unroll
+  for (int j = 0; j < 2; j++) r2[j] = e[j] & PENG_SHP(e, 1, j);
+#pragma unroll
+  for (int j = 0; j < 2; j++) r4[j] = r2[j] & PENG_SHP(r2, 2, j);
+#pragma unroll
+  for (int j = 0; j < 2; j++) r8[j] = r4[j] & PENG_SHP(r4, 4, j);
+#pragma unroll
+  for (int j = 0; j < 2; j++) {
+    uint32_t v;
+    if (R == 4) v = r4[j];
+    else if (R == 6) v = r4[j] & PENG_SHP(r2, 4, j);
+    else if (R == 7) v = r4[j] & PENG_SHP(r4, 3, j);
+    else if (R == 8) v = r8[j];
+    else if (R == 9) v = r8[j] & PENG_SHP(e, 8, j);
+    else if (R == 10) v = r8[j] & PENG_SHP(r2, 8, j);
+    else if (R == 11) v = r8[j] & PENG_SHP(r4, 7, j);
+    else if (R == 12) v = r8[j] & PENG_SHP(r4, 8, j);
+    else if (R == 14) v = r8[j] & PENG_SHP(r4, 8, j) & PENG_SHP(r2, 12, j);
+    else v = r8[j] & PENG_SHP(r8, 8, j);  // R == 16
+    run[j] = v;
+  }
+  const int off = W - R;  // the run starts at s + off
+  st.c |= off ? PENG_SHP(run, off, 0) : run[0];
+#undef PENG_SHP
+}
+// (rc) arm i: x[m+1+i] complementary to x[m-i] <=> both planes differ
+PENG_HD void cand_pl_rc_arm(const uint32_t* pl, int i, CandStatePl& st) {
+#pragma unroll
+  for (int j = 0; j < 2; j++) {
+    const uint32_t ah = j == 0 ? funnel_r(pl[1], pl[2], (uint32_t)(1 + i)) : (pl[2] >> (uint32_t)(1 + i));  // x[m+1+i]
+    const uint32_t al = j == 0 ? funnel_r(pl[4], pl[5], (uint32_t)(1 + i)) : (pl[5] >> (uint32_t)(1 + i));
+    const uint32_t bh = i ? funnel_r(pl[j], pl[j + 1], 32u - (uint32_t)i) : pl[j + 1];                       // x[m-i]
+    const uint32_t bl = i ? funnel_r(pl[j + 3], pl[j + 4], 32u - (uint32_t)i) : pl[j + 4];
+    const uint32_t t = st.p[j] & (ah ^ bh);
+    st.p[j] = t & (al ^ bl);
+  }
+}
+template <int W>
+PENG_HD void cand_pl_rc_finish(CandStatePl& st) {
+#pragma unroll
+  for (int i = 0; i <= W / 2 - 2; i++) st.c |= i ? funnel_r(st.p[0], st.p[1], (uint32_t)i) : st.p[0];
+}
+template <int W, bool BOTH>
+struct CandStepsPl {
+  static constexpr int N_FF = FfLags<W>::N, N_ARM = BOTH ? W / 2 + 1 : 0, N = N_FF + N_ARM + (BOTH ? 1 : 0);
+  PENG_HD static void run(int I, const uint32_t* pl, CandStatePl& st) {
+    if (I < N_FF) cand_pl_ff_run<W>(pl, FfLags<W>::D(I), FfLags<W>::R(I), st);
+    else if (I < N_FF + N_ARM) cand_pl_rc_arm(pl, I - N_FF, st);
+    else if (BOTH && I == N_FF + N_ARM) cand_pl_rc_finish<W>(st);
+  }
+};
+template <int W, bool BOTH>
+PENG_HD uint32_t conflict_candidates_planes(const uint32_t* pl) {
+  CandStatePl st;
+  cand_pl_init(st);
+#pragma unroll
+  for (int I = 0; I < CandStepsPl<W, BOTH>::N; I++) CandStepsPl<W, BOTH>::run(I, pl, st);
+  return st.c;
+}
+// planes of one unit from its two code words (what k_make_planes stores): hi = bit 1 of every code, lo = bit 0
+PENG_HD void planes_of_unit(uint32_t c0, uint32_t c1, uint32_t* hi, uint32_t* lo) {
+  *lo = compress_even16(c0) | (compress_even16(c1) << 16);
+  *hi = compress_even16(c0 >> 1) | (compress_even16(c1 >> 1) << 16);
+}
+
 // number of steps and step I of the whole computation (I is a compile-time constant after unrolling)
 template <int W, bool BOTH>
 struct CandSteps {

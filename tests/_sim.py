@@ -181,6 +181,14 @@ def count_part_keys(st, W, both=True):
                                                  slow_units=int(stats[4]))
 
 
+def cand_planes_mismatch(st, W, both=True):
+    """Bit-plane conflict scan against the 2-bit one over every unit of the stream -> (units that differ, flags set)."""
+    n_flagged = C.c_uint64()
+    lib.sim_cand_planes_mismatch.restype = C.c_uint64
+    bad = lib.sim_cand_planes_mismatch(_p(st.codes, u32p), C.c_uint64(st.nw), W, int(both), C.byref(n_flagged))
+    return int(bad), int(n_flagged.value)
+
+
 def host_pack(src, offsets, ascii=False, n_threads=4, max_blocks=1 << 14):
     """host_pack.cpp: the packed ingest's host half, all phases -> (codes words, valid words, phases) in the device layout."""
     src = np.ascontiguousarray(src, np.uint8)

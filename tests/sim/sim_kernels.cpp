@@ -275,6 +275,38 @@ uint64_t sim_count_part_keys(const uint32_t* codes, const uint32_t* valid, uint6
   if (out) for (uint64_t i = 0; i < keys.size() && i < cap; i++) out[i] = keys[i];
   return keys.size();
 }
+}  // extern "C"
+// bit-plane form of the conflict scan (conflict_candidates_planes) against the 2-bit form, unit by unit: number of units
+// whose 32 flags differ (must be 0); *n_flagged = flags set in total (so that the test knows the scan saw conflicts)
+template <int W, bool BOTH>
+static uint64_t cand_planes_T(const uint32_t* codes, uint64_t n_words32, uint64_t* n_flagged) {
+  std::vector<uint32_t> hi(n_words32 + 2, 0), lo(n_words32 + 2, 0);
+  for (uint64_t u = 0; u < n_words32; u++) planes_of_unit(codes[2 * u], codes[2 * u + 1], &hi[u], &lo[u]);
+  uint64_t bad = 0;
+  for (uint64_t u = 0; u + 1 < n_words32; u++) {
+    uint32_t cw[5];
+    for (int j = 0; j < 5; j++) cw[j] = (2 * u + j >= 1) ? codes[2 * u - 1 + j] : 0u;
+    const uint32_t pl[6] = {u ? hi[u - 1] : 0u, hi[u], hi[u + 1], u ? lo[u - 1] : 0u, lo[u], lo[u + 1]};
+    const uint32_t a = conflict_candidates<W, BOTH>(cw), b = conflict_candidates_planes<W, BOTH>(pl);
+    bad += a != b;
+    *n_flagged += (uint64_t)popc32(b);
+  }
+  return bad;
+}
+extern "C" uint64_t sim_cand_planes_mismatch(const uint32_t* codes, uint64_t n_words32, int W, int both, uint64_t* n_flagged) {
+  *n_flagged = 0;
+  switch (W) {
+    case 4: return both ? cand_planes_T<4, true>(codes, n_words32, n_flagged) : cand_planes_T<4, false>(codes, n_words32, n_flagged);
+    case 6: return both ? cand_planes_T<6, true>(codes, n_words32, n_flagged) : cand_planes_T<6, false>(codes, n_words32, n_flagged);
+    case 8: return both ? cand_planes_T<8, true>(codes, n_words32, n_flagged) : cand_planes_T<8, false>(codes, n_words32, n_flagged);
+    case 10: return both ? cand_planes_T<10, true>(codes, n_words32, n_flagged) : cand_planes_T<10, false>(codes, n_words32, n_flagged);
+    case 12: return both ? cand_planes_T<12, true>(codes, n_words32, n_flagged) : cand_planes_T<12, false>(codes, n_words32, n_flagged);
+    case 14: return both ? cand_planes_T<14, true>(codes, n_words32, n_flagged) : cand_planes_T<14, false>(codes, n_words32, n_flagged);
+    case 16: return both ? cand_planes_T<16, true>(codes, n_words32, n_flagged) : cand_planes_T<16, false>(codes, n_words32, n_flagged);
+  }
+  return ~0ull;
+}
+extern "C" {
 // BOTH: pair sums into the canonical bin (then sim_mirror copies them to the other id)
 void sim_fold_canon(uint64_t* hist, int W) {
   const uint64_t n = 1ull << (2 * W);

@@ -197,6 +197,19 @@ def test_partition_path_split_long_patterns(seed):
     assert stt["missed"] == 0 and lt == ltot and np.array_equal(hist, ref)
 
 
+@pytest.mark.parametrize("seed", range(8))
+def test_bit_plane_scan_equals_two_bit_scan(seed):
+    """conflict_candidates_planes (what stage P runs) flags exactly the W-mers conflict_candidates flags, every W."""
+    seqs = _cases.dirty_sequences(seed) if seed % 2 == 0 else long_period_sequences(seed)
+    codes, offs = O.encode(seqs)
+    st = S.pack(codes, offs)
+    for W in (4, 6, 8, 10, 12, 14, 16):
+        for both in (True, False):
+            bad, flagged = S.cand_planes_mismatch(st, W, both)
+            assert bad == 0, (W, both, bad)
+            assert flagged > 0 or seed % 2 == 0, (W, both)
+
+
 @pytest.mark.parametrize("case", [c for c in _cases.golden_cases() if c["exit"] == 0 and c["W"] in (4, 6, 8, 10)],
                          ids=lambda c: c["tag"])
 def test_partition_path_golden_cases(case):
