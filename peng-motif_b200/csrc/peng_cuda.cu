@@ -79,6 +79,9 @@ struct peng_cuda_ctx {
   // ---- partition path (W = 10) ----
   int count_path = 0;              // 0 auto, 1 L2-atomic path, 2 partition path
   bool used_partition = false;     // what the last count ran
+  uint2* d_planes = nullptr;       // bit planes of d_codes, {bit 1, bit 0} per 32 positions (ensure_planes)
+  size_t cap_planes = 0;
+  bool planes_valid = false;
   uint16_t* d_part_buckets = nullptr;
   size_t part_bucket_elems = 0;
   uint32_t* d_part_fill = nullptr;
@@ -353,17 +356,20 @@ __host__ __device__ __forceinline__ uint32_t part_class_start(uint32_t c) {  // 
 template <int W>
 struct PartGeom {
   static constexpr uint32_t NCLASS = 32;
+  static constexpr bool RAW_KEYS = false;
   typedef uint32_t entry_t;
   typedef uint4 vec_t;  // 4 entries
-  __device__ __forceinline__ static uint32_t cls(uint32_t key) { return key >> (2 * W - 5); }
+  __device__ __forceinline__ static uint32_t cls(uint32_t key, uint32_t link = 0) { return (key ^ link) >> (2 * W - 5); }
   __device__ __forceinline__ static uint32_t id_of(uint32_t e, uint32_t) { return e; }
 };
 template <>
 struct PartGeom<10> {
   static constexpr uint32_t NCLASS = PART_NCLASS;
+  static constexpr bool RAW_KEYS = true;  // stage P pushes words whose bits above 2 W are not cleared
   typedef uint16_t entry_t;
   typedef uint2 vec_t;
-  __device__ __forceinline__ static uint32_t cls(uint32_t key) { return __umulhi(key, (uint32_t)PART_NCLASS << 12); }
+  // floor(id * NCLASS / 2^20) of the low 20 bits: the shift clears what lies above them (multiply + high multiply, FMA pipe)
+  __device__ __forceinline__ static uint32_t cls(uint32_t key, uint32_t link = 0) { return __umulhi(key * 4096u + link, (uint32_t)PART_NCLASS); }
   __device__ __forceinline__ static uint32_t id_of(uint32_t e, uint32_t c) {
     const uint32_t start = part_class_start(c);
     return start + ((e - start) & 0xFFFFu);
@@ -375,9 +381,9 @@ struct PartGeom<10> {
 // branch (BSSY / BRA / BSYNC per push), an unconditional one on a dummy counter is cheaper.  Stage P is bound by the
 // half-rate ALU pipe (ncu: pipe_alu 75 %), so the address arithmetic is written as multiply-adds (FMA pipe).
 template <int W, uint32_t CAP>
-__device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t push, uint32_t cnt_s, uint32_t q_s) {
+__device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t push, uint32_t cnt_s, uint32_t q_s, uint32_t link) {
   typedef PartGeom<W> G;
-  uint32_t c = G::cls(key);
+  uint32_t c = G::cls(key, link);  // link: 0 at run time (k_count_part), a dependency for the scheduler only
   c = push ? c : G::NCLASS;
   const uint32_t cnt_addr = c * 4u + cnt_s;
   const uint32_t base = c * (CAP * (uint32_t)sizeof(typename G::entry_t)) + q_s;
@@ -406,9 +412,9 @@ __device__ __forceinline__ uint32_t part_push(uint32_t key, uint32_t push, uint3
   return slot;
 }
 
-template <int W, bool BOTH, int PART_NT, uint32_t PART_CAP, int MINB, bool LINK>
+template <int W, bool BOTH, int PART_NT, uint32_t PART_CAP, int MINB, bool LINK, bool PL>
 __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
-    const uint32_t* __restrict__ codes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
+    const uint32_t* __restrict__ codes, const uint2* __restrict__ planes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
     uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, typename PartGeom<W>::entry_t* __restrict__ buckets, uint32_t region_cap,
     uint32_t* __restrict__ fill_out, uint32_t* __restrict__ hist, unsigned long long* __restrict__ ltot,
     uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count, uint32_t zero) {
@@ -435,9 +441,12 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
   // fast W-mers and the mask of slow ones.  Scanning a unit is ALU work only, pushing is shared-memory work only:
   // the loop scans round r+1 in the shadow of the pushes of round r, one scan step behind every other push
   // (ptxas keeps the source order of independent work, it does not interleave the two streams by itself).
+  // PL: the scan runs on the bit planes of units u-1, u, u+1 (sw = H[3], L[3]), else on the code words 2u-1 .. 2u+3.
   struct Unit { uint32_t w1, w2, w3, fast, slow, u; };
-  uint32_t cw[5], ks;
-  CandState cs;
+  typedef typename std::conditional<PL, CandStatePl, CandState>::type State;
+  typedef typename std::conditional<PL, CandStepsPl<W, BOTH>, CandSteps<W, BOTH>>::type Steps;
+  uint32_t sw[6], kw[3], ks;
+  State cs;
   auto scan_begin = [&](uint64_t r) -> uint32_t {  // loads + k-mer starts of the thread's unit in round r
     const uint64_t u = unit_begin + r * PART_NT + threadIdx.x;
     const bool live = r < n_rounds && u < unit_end;
@@ -446,23 +455,38 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     ks = live ? ks : 0u;
     if (live) kstart[u] = ks;
     my_ltot += __popc(ks);
-    cw[0] = uc ? __ldg(codes + 2 * uc - 1) : 0u;
     const uint2 a = __ldg(reinterpret_cast<const uint2*>(codes + 2 * uc));
-    const uint2 b = __ldg(reinterpret_cast<const uint2*>(codes + 2 * uc + 2));
-    cw[1] = a.x; cw[2] = a.y; cw[3] = b.x; cw[4] = b.y;
-    cand_init(cs);
+    if constexpr (PL) {
+      const uint2 p0 = uc ? __ldg(planes + uc - 1) : make_uint2(0u, 0u);
+      const uint2 p1 = __ldg(planes + uc), p2 = __ldg(planes + uc + 1);
+      sw[0] = p0.x; sw[1] = p1.x; sw[2] = p2.x; sw[3] = p0.y; sw[4] = p1.y; sw[5] = p2.y;
+      kw[0] = a.x; kw[1] = a.y; kw[2] = __ldg(codes + 2 * uc + 2);
+      cand_pl_init(cs);
+    } else {
+      sw[0] = uc ? __ldg(codes + 2 * uc - 1) : 0u;
+      const uint2 b = __ldg(reinterpret_cast<const uint2*>(codes + 2 * uc + 2));
+      sw[1] = a.x; sw[2] = a.y; sw[3] = b.x; sw[4] = b.y;
+      kw[0] = a.x; kw[1] = a.y; kw[2] = b.x;
+      cand_init(cs);
+    }
     return (uint32_t)u;
   };
   auto scan_end = [&](uint32_t u) -> Unit {
-    const uint32_t cand = cand_result(cs);
-    return Unit{cw[1], cw[2], cw[3], ks & ~cand, ks & cand, u};
+    uint32_t cand;
+    if constexpr (PL) cand = cs.c;
+    else cand = cand_result(cs);
+    return Unit{kw[0], kw[1], kw[2], ks & ~cand, ks & cand, u};
   };
-  typedef CandSteps<W, BOTH> Steps;
+  auto link_in = [&](uint32_t v) { sw[PL ? 1 : 2] ^= v; };  // the unit's own word
+  auto link_out = [&]() -> uint32_t {
+    if constexpr (PL) return cs.c | cs.p[0];
+    else return cs.c1 | cs.p[0];
+  };
   constexpr bool STEP_PER_PUSH = Steps::N > 16;  // W >= 12: one scan step behind every push instead of every other
   static_assert(Steps::N <= 32, "at most one scan step per push");
   uint32_t un = scan_begin(blockIdx.x);
 #pragma unroll
-  for (int I = 0; I < Steps::N; I++) Steps::run(I, cw, cs);
+  for (int I = 0; I < Steps::N; I++) Steps::run(I, sw, cs);
   Unit cur = scan_end(un);
   for (uint64_t r = blockIdx.x; r < n_rounds; r += gridDim.x) {
     const uint32_t fast = cur.fast, w1 = cur.w1, w2 = cur.w2, w3 = cur.w3;
@@ -472,14 +496,15 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     uint32_t link = 0;
 #pragma unroll
     for (int i = 0; i < 32; i++) {
-      uint32_t key = (i < 16 ? __funnelshift_r(w1, w2, 2 * i) : __funnelshift_r(w2, w3, 2 * (i - 16))) & KEYMASK;
-      key ^= link;
-      const uint32_t slot = part_push<W, PART_CAP>(key, fast & (1u << i), cnt_s, q_s);
+      // W = 10: the letters behind the W-mer stay in the word — cls_raw() shifts them out, the 16-bit store drops them
+      uint32_t key = i < 16 ? __funnelshift_r(w1, w2, 2 * i) : __funnelshift_r(w2, w3, 2 * (i - 16));
+      if (!G::RAW_KEYS) key &= KEYMASK;
+      const uint32_t slot = part_push<W, PART_CAP>(key, fast & (1u << i), cnt_s, q_s, link);
       const int step = STEP_PER_PUSH ? i : (i >> 1);
       if ((STEP_PER_PUSH || (i & 1)) && step < Steps::N) {
-        if (LINK) cw[2] ^= slot & zero;
-        Steps::run(step, cw, cs);
-        if (LINK) link = (cs.c1 | cs.p[0]) & zero;
+        if (LINK) link_in(slot & zero);
+        Steps::run(step, sw, cs);
+        if (LINK) link = link_out() & zero;
       }
     }
     const Unit nxt = scan_end(un);
@@ -1552,6 +1577,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   for (int i = 0; i < 2; i++) if (h->copy_ev[i]) cudaEventDestroy(h->copy_ev[i]);
   for (int i = 0; i < 2; i++) if (h->pin[i]) cudaFreeHost(h->pin[i]);
   for (int i = 0; i < 2; i++) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
+  dev_free(&h->d_planes);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
   for (int i = 0; i < 3; i++) { dev_free(&h->d_deep_buckets[i]); dev_free(&h->d_deep_fill[i]); }
   for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -1620,6 +1646,7 @@ static int alloc_stream(peng_handle_t h, uint64_t n_seq, uint64_t total_bases) {
   CU(h, cudaMemsetAsync(h->d_kstart + h->n_words32, 0, 8 * 4, h->stream));  // the rest is written by every count
   h->counts_final = false;
   h->stats_ready = false;
+  h->planes_valid = false;
   return PENG_OK;
 }
 
@@ -2100,6 +2127,28 @@ extern "C" int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes, uint64_t*
 // =====================================================================================================
 // C ABI: counting
 // =====================================================================================================
+// bit planes of the codes (core_seq.cuh: conflict_candidates_planes), once per ingest, by the first count that wants them
+__global__ void __launch_bounds__(256) k_make_planes(const uint2* __restrict__ codes, uint2* __restrict__ planes, uint64_t n_words32) {
+  const uint64_t u = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+  if (u >= n_words32) return;
+  const uint2 c = __ldg(codes + u);
+  uint2 o;
+  planes_of_unit(c.x, c.y, &o.x, &o.y);
+  planes[u] = o;
+}
+static int ensure_planes(peng_handle_t h) {
+  if (h->planes_valid) return PENG_OK;
+  if (h->cap_planes < h->n_words32 + 8) {
+    TRY(dev_alloc(h, &h->d_planes, h->n_words32 + 8));
+    h->cap_planes = h->n_words32 + 8;
+  }
+  CU(h, cudaMemsetAsync(h->d_planes + h->n_words32, 0, 8 * sizeof(uint2), h->stream));
+  k_make_planes<<<grid_for(h->n_words32, 256), 256, 0, h->stream>>>(reinterpret_cast<const uint2*>(h->d_codes), h->d_planes, h->n_words32);
+  LAUNCH_CHECK(h);
+  h->planes_valid = true;
+  return PENG_OK;
+}
+
 // Stage-P launch geometry: threads per CTA, queue entries per class, CTAs per SM.
 struct PartArgs {
   uint64_t ub, ue;
@@ -2108,13 +2157,14 @@ struct PartArgs {
   void* buckets;
   uint32_t* fill;
 };
-template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM, bool LINK>
+template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM, bool LINK, bool PL = true>
 static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
+  if (PL) TRY(ensure_planes(h));
   typedef PartGeom<W> G;
   const size_t smem_p = (size_t)(G::NCLASS + 1) * CAP * sizeof(typename G::entry_t);
-  auto kern = k_count_part<W, BOTH, NT, CAP, PER_SM, LINK>;
+  auto kern = k_count_part<W, BOTH, NT, CAP, PER_SM, LINK, PL>;
   CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
-  kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue,
+  kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_planes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue,
                                           (typename G::entry_t*)a.buckets, a.region_cap, a.fill, h->d_hist32,
                                           (unsigned long long*)(h->d_counts + h->n_patterns), h->d_slow_list, h->d_slow_count, 0u);
   LAUNCH_CHECK(h);
@@ -2130,6 +2180,7 @@ static int launch_part(peng_handle_t h, int cfg, const PartArgs& a) {
     case 4: return launch_part_cfg<W, BOTH, 512, 1024, 2, false>(h, a);
     case 5: return launch_part_cfg<W, BOTH, 256, 512, 4, false>(h, a);
     case 6: return launch_part_cfg<W, BOTH, 128, 384, 6, false>(h, a);
+    case 8: return launch_part_cfg<W, BOTH, 512, 1024, 2, true, false>(h, a);  // the 2-bit conflict scan (A/B)
     default: return launch_part_cfg<W, BOTH, 512, 1024, 2, true>(h, a);
   }
 }
