@@ -419,7 +419,8 @@ def main():
     elif partition:
         kname = f"k_count_part<{W},{shape['strand']}> (stage P of the partition path)"
         note = ("stage P streams the packed set once (codes + validity), derives k-mer starts and conflict candidates and "
-                "partitions 16-bit keys into class buckets; ALU-pipe bound (ncu: pipe_alu 75 %), see DESIGN.md")
+                "partitions 16-bit keys into class buckets; bound by the ALU pipe and issue (ncu: pipe_alu 59 %, issue active 55 %, "
+                "8 warps per scheduler), see DESIGN.md")
     else:
         kname = f"k_count_global<{W},{shape['strand']}>" if W >= 10 else "k_count_smem"
         note = "one L2 atomic per counted k-mer: atomic-throughput-bound far below the HBM roof (DESIGN.md)"
