@@ -44,10 +44,11 @@ static inline void chunk_scalar(const uint8_t* p, uint32_t n, bool ascii, uint64
   v = vv;
 }
 
-__attribute__((target("avx512f,avx512bw"))) static inline void chunk_avx512(const uint8_t* p, uint32_t n, bool ascii, uint64_t& lo,
+template <bool ascii>
+__attribute__((target("avx512f,avx512bw"))) static inline void chunk_avx512(const uint8_t* p, uint32_t n, uint64_t& lo,
                                                                             uint64_t& hi, uint64_t& v) {
   const __mmask64 lm = n >= 64 ? ~(__mmask64)0 : (((__mmask64)1 << n) - 1);
-  const __m512i z = _mm512_maskz_loadu_epi8(lm, p);
+  const __m512i z = n >= 64 ? _mm512_loadu_si512((const void*)p) : _mm512_maskz_loadu_epi8(lm, p);
   __mmask64 ok;
   __m512i code;
   if (ascii) {
@@ -88,20 +89,10 @@ struct BitWriter {
     lo = hi = v = 0;
     first_partial = fill != 0;
   }
-  inline void emit() {
-    if (first_partial) {
-      out->push_back(Partial{blk, lo, hi, v});
-      first_partial = false;
-    } else {
-      codes[2 * (blk - blk0)] = lo;
-      codes[2 * (blk - blk0) + 1] = hi;
-      valid[blk - blk0] = v;
-    }
-    blk++;
-    lo = hi = v = 0;
-  }
-  // n in 1..64 positions; the bits of c_lo / c_hi / vv behind position n are zero.  Branch-free up to the block test:
-  // the alignment changes with every sequence, so tests on `fill` would mispredict.
+  uint64_t scratch[3];  // where the stores of a block entered in the middle go (it leaves as a Partial)
+  // n in 1..64 positions; the bits of c_lo / c_hi / vv behind position n are zero.  Branch-free: the alignment changes
+  // with every sequence, so neither tests on `fill` nor the "block complete" test would predict.  The current block is
+  // stored after every append (same cache line again and again); completing it only moves the pointers on.
   inline void append(uint64_t c_lo, uint64_t c_hi, uint64_t vv, uint32_t n) {
     typedef unsigned __int128 u128;
     const u128 c = ((u128)c_hi << 64) | c_lo;
@@ -113,15 +104,44 @@ struct BitWriter {
     v |= vv << fill;
     const uint64_t over_v = (vv >> 1) >> (63 - fill);
     const uint32_t tot = fill + n;
-    if (tot >= 64) {
-      emit();
-      lo = (uint64_t)over;
-      hi = (uint64_t)(over >> 64);
-      v = over_v;
-      fill = tot - 64;
-    } else {
-      fill = tot;
+    const bool adv = tot >= 64;
+    uint64_t* cp = first_partial ? scratch : codes + 2 * (blk - blk0);
+    uint64_t* vp = first_partial ? scratch + 2 : valid + (blk - blk0);
+    cp[0] = lo;
+    cp[1] = hi;
+    vp[0] = v;
+    if (__builtin_expect(adv && first_partial, 0)) {
+      out->push_back(Partial{blk, lo, hi, v});
+      first_partial = false;
     }
+    blk += adv;
+    const uint64_t m = (uint64_t)0 - (uint64_t)adv;  // all ones: the block is complete, carry on with what fell out
+    lo = ((uint64_t)over & m) | (lo & ~m);
+    hi = ((uint64_t)(over >> 64) & m) | (hi & ~m);
+    v = (over_v & m) | (v & ~m);
+    fill = tot & 63u;
+  }
+  // a whole chunk of 64 positions: the current block is completed whatever its fill, which stays as it is
+  inline void append64(uint64_t c_lo, uint64_t c_hi, uint64_t vv) {
+    typedef unsigned __int128 u128;
+    const u128 c = ((u128)c_hi << 64) | c_lo;
+    const uint32_t sh = 2 * fill;
+    const u128 in = c << sh;
+    const u128 over = (c >> 1) >> (127 - sh);
+    const uint64_t b_lo = lo | (uint64_t)in, b_hi = hi | (uint64_t)(in >> 64), b_v = v | (vv << fill);
+    uint64_t* cp = first_partial ? scratch : codes + 2 * (blk - blk0);
+    uint64_t* vp = first_partial ? scratch + 2 : valid + (blk - blk0);
+    cp[0] = b_lo;
+    cp[1] = b_hi;
+    vp[0] = b_v;
+    if (__builtin_expect(first_partial, 0)) {
+      out->push_back(Partial{blk, b_lo, b_hi, b_v});
+      first_partial = false;
+    }
+    blk++;
+    lo = (uint64_t)over;
+    hi = (uint64_t)(over >> 64);
+    v = (vv >> 1) >> (63 - fill);
   }
   void zeros(uint64_t n) {
     while (n) {
@@ -135,20 +155,46 @@ struct BitWriter {
   }
 };
 
-__attribute__((target("avx512f,avx512bw"))) static void run_avx512(const Share& sh, BitWriter& w) {
-  for (uint64_t s = sh.s_begin; s < sh.s_end; s++) {
-    const uint8_t* p = sh.src + sh.offsets[s];
-    const uint64_t L = sh.offsets[s + 1] - sh.offsets[s];
-    uint32_t sep = 2;  // the two separator positions (core_seq.cuh) ride on the last chunk where they fit
-    for (uint64_t i = 0; i < L; i += 64) {
-      uint32_t n = (uint32_t)std::min<uint64_t>(64, L - i);
+// the writer is worked on as a local copy: through the reference its state would live in memory (a store-to-load
+// forward per append) instead of registers
+template <bool ascii>
+__attribute__((target("avx512f,avx512bw"))) static void run_avx512_t(const Share& sh, BitWriter& w_io) {
+  BitWriter w = w_io;
+  const uint8_t* const src = sh.src;
+  const uint64_t* const offsets = sh.offsets;
+  const uint64_t s_end = sh.s_end;
+  uint64_t o0 = offsets[sh.s_begin];
+  for (uint64_t s = sh.s_begin; s < s_end; s++) {
+    const uint8_t* p = src + o0;
+    const uint64_t o1 = offsets[s + 1];
+    const uint64_t L = o1 - o0;
+    o0 = o1;
+    uint64_t i = 0;
+    for (; i + 64 <= L; i += 64) {  // whole chunks
       uint64_t lo, hi, v;
-      chunk_avx512(p + i, n, sh.ascii, lo, hi, v);
-      if (i + 64 >= L && n <= 62) { n += 2; sep = 0; }
-      w.append(lo, hi, v, n);
+      chunk_avx512<ascii>(p + i, 64, lo, hi, v);
+      w.append64(lo, hi, v);
     }
-    if (sep) w.append(0, 0, 0, 2);
+    // the rest of the sequence (0 .. 63 letters) and the two separator positions (core_seq.cuh), in one append where
+    // they fit
+    const uint32_t n = (uint32_t)(L - i);
+    if (n) {
+      uint64_t lo, hi, v;
+      chunk_avx512<ascii>(p + i, n, lo, hi, v);
+      if (n <= 62) {
+        w.append(lo, hi, v, n + 2);
+      } else {
+        w.append(lo, hi, v, n);
+        w.append(0, 0, 0, 2);
+      }
+    } else {
+      w.append(0, 0, 0, 2);
+    }
   }
+  w_io = w;
+}
+static void run_avx512(const Share& sh, BitWriter& w) {
+  if (sh.ascii) run_avx512_t<true>(sh, w); else run_avx512_t<false>(sh, w);
 }
 static void run_scalar(const Share& sh, BitWriter& w) {
   for (uint64_t s = sh.s_begin; s < sh.s_end; s++) {

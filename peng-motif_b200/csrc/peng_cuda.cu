@@ -49,6 +49,8 @@ struct peng_cuda_ctx {
   uint8_t* pin[2] = {nullptr, nullptr};    // pinned staging buffers of the streaming FASTA ingest
   cudaEvent_t pin_ev[2] = {nullptr, nullptr};
   std::vector<uint64_t> h_offsets;
+  uint64_t* pin_offs = nullptr;    // pinned copy of the offsets for the H2D copy (hybrid ingest), grow-only
+  size_t pin_offs_cap = 0;
 
   // ---- count table ----
   int W = 0, strand = PENG_STRAND_BOTH;
@@ -1576,6 +1578,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   for (int i = 0; i < 2; i++) if (h->copy_ev[i]) cudaEventDestroy(h->copy_ev[i]);
   for (int i = 0; i < 2; i++) if (h->pin[i]) cudaFreeHost(h->pin[i]);
+  if (h->pin_offs) cudaFreeHost(h->pin_offs);
   for (int i = 0; i < 2; i++) if (h->pin_ev[i]) cudaEventDestroy(h->pin_ev[i]);
   dev_free(&h->d_planes);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
@@ -1665,6 +1668,7 @@ static void seq_lengths(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq
 struct BookTask {
   const uint64_t* offsets;
   uint64_t* dst;
+  uint64_t* dst2;  // optional second copy (pinned, for the DMA engine)
   uint64_t n_seq;
   int n_tasks;
   uint32_t mn[64], mx[64];
@@ -1681,13 +1685,15 @@ static void book_task(int i, void* arg) {
   b.mn[i] = mn;
   b.mx[i] = mx;
   memcpy(b.dst + s0, b.offsets + s0, (s1 - s0 + (i == b.n_tasks - 1 ? 1 : 0)) * sizeof(uint64_t));
+  if (b.dst2) memcpy(b.dst2 + s0, b.offsets + s0, (s1 - s0 + (i == b.n_tasks - 1 ? 1 : 0)) * sizeof(uint64_t));
 }
-static void host_bookkeeping_parallel(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq) {
+static void host_bookkeeping_parallel(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq, uint64_t* pinned_copy = nullptr) {
   if (h->h_offsets.size() != n_seq + 1) h->h_offsets.resize(n_seq + 1);
   peng_hostpack::Pool& pool = peng_hostpack::global_pool();
   BookTask b;
   b.offsets = offsets;
   b.dst = h->h_offsets.data();
+  b.dst2 = pinned_copy;
   b.n_seq = n_seq;
   b.n_tasks = std::min(pool.size(), 64);
   pool.run(b.n_tasks, book_task, &b);
@@ -1732,6 +1738,9 @@ static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64
 }
 
 #define PENG_PIN_BYTES (16u << 20)
+#ifndef PENG_PHASE_MB_DEFAULT
+#define PENG_PHASE_MB_DEFAULT 16
+#endif
 static int need_copy_stream_and_pins(peng_handle_t h, bool pins) {
   if (!h->copy_stream) {
     CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -1762,6 +1771,8 @@ __global__ void k_sstart_scatter(const uint64_t* __restrict__ offsets, uint64_t 
 // plain path.
 static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
   using namespace peng_hostpack;
+  const double t_entry = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  double t_marks[4] = {0, 0, 0, 0};
   const uint64_t total = n_seq ? offsets[n_seq] : 0;
   if (h->ingest_mode == 1) return 1;
   const bool force = h->ingest_mode == 2;
@@ -1771,7 +1782,8 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   h->last_ingest_packed = 0;
   double f = 1.0;
   if (!force) {
-    const double rh = 3.75 * pool.size(), rp = 46.0;  // Gbases/s: measured packing rate per thread (60 at 16), PCIe rate
+    // Gbases/s: measured packing rate (5.7 per thread up to 8 threads, 63 at 16: tools/probe/host_pack_bench.cpp), PCIe rate
+    const double rh = 5.7 * std::min(pool.size(), 8) + 2.2 * std::max(0, pool.size() - 8), rp = 46.0;
     f = rh / (rp + 0.625 * rh);
     if (h->ingest_fraction >= 0) f = h->ingest_fraction;
     f = std::min(1.0, std::max(0.0, f));
@@ -1781,7 +1793,14 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   uint64_t s_split = n_seq;
   if (f < 1.0) s_split = (uint64_t)(std::upper_bound(offsets, offsets + n_seq + 1, (uint64_t)(f * (double)total)) - offsets) - 1;
   if (s_split == 0) return 1;
-  const uint64_t max_blocks = PENG_PIN_BYTES / 24;  // 16 B of codes + 8 B of validity per block of 64 positions
+  // 16 B of codes + 8 B of validity per block of 64 positions.  A phase fills at most PENG_PHASE_MB of its staging
+  // buffer: the copy of the LAST phase cannot hide behind packing, so phases are kept shorter than the buffers allow
+  static const uint64_t phase_bytes = [] {
+    const char* e = getenv("PENG_PHASE_MB");
+    const uint64_t mb = e ? (uint64_t)atoi(e) : PENG_PHASE_MB_DEFAULT;
+    return std::min<uint64_t>(PENG_PIN_BYTES, std::max<uint64_t>(1, mb) << 20);
+  }();
+  const uint64_t max_blocks = phase_bytes / 24;
   // every phase must hold at least one sequence
   {
     uint64_t s = 0;
@@ -1793,41 +1812,46 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
       first = false;
     }
   }
+  auto mark = [&](int i) { t_marks[i] = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count() - t_entry; };
+  mark(0);
   CU(h, cudaSetDevice(h->device));
   TRY(prepare_ingest(h, offsets, n_seq));
   TRY(need_copy_stream_and_pins(h, true));
+  mark(1);
   const uint64_t q_total = ((h->n_words32 * 32 + 63) / 64) * 64;
   const uint64_t n_blocks = q_total / 64;
   const uint64_t q_split = PENG_FRONT_PAD + offsets[s_split] + 2 * s_split;
   const uint64_t blk_split = s_split < n_seq ? (q_split >> 6) : n_blocks;
   const uint64_t b_lo = s_split < n_seq ? offsets[s_split] - std::min<uint64_t>(offsets[s_split], 128) : total;
   if (s_split < n_seq) TRY(need_scratch(h, (size_t)(total - b_lo) + 16));
+  if (h->pin_offs_cap < n_seq + 1) {
+    if (h->pin_offs) cudaFreeHost(h->pin_offs);
+    h->pin_offs = nullptr;
+    h->pin_offs_cap = 0;
+    CU(h, cudaHostAlloc((void**)&h->pin_offs, (n_seq + 1 + (n_seq >> 2)) * sizeof(uint64_t), cudaHostAllocDefault));
+    h->pin_offs_cap = n_seq + 1 + (n_seq >> 2);
+  }
   CU(h, cudaEventRecord(h->copy_ev[0], h->stream));
   CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
-  CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+  mark(2);
   // ---- the raw rest: queued first, the DMA engine works on it while the host packs ----
   if (s_split < n_seq) {
-    const uint8_t* d_src = (const uint8_t*)h->d_scratch - b_lo;  // indexed by absolute base offset, never read below b_lo
     const uint64_t chunk = 32ull << 20;
-    uint64_t t_done = blk_split * 2, s_hint = s_split;
-    int flip = 0;
     for (uint64_t b0 = b_lo; b0 < total; b0 += chunk) {
       const uint64_t b1 = std::min(total, b0 + chunk);
       CU(h, cudaMemcpyAsync((uint8_t*)h->d_scratch + (b0 - b_lo), src + b0, b1 - b0, cudaMemcpyHostToDevice, h->copy_stream));
-      CU(h, cudaEventRecord(h->copy_ev[flip], h->copy_stream));
-      CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[flip], 0));
-      flip ^= 1;
-      uint64_t t_end = h->n_words32;
-      if (b1 < total) {
-        const uint64_t* it = std::upper_bound(offsets + s_hint, offsets + n_seq + 1, b1);
-        s_hint = (uint64_t)(it - offsets) - 1;
-        t_end = (PENG_FRONT_PAD + b1 + 2 * s_hint) / 32;
-      }
-      if (t_end > t_done) {
-        TRY(launch_pack(h, d_src, ascii, t_done, t_end));
-        t_done = t_end;
-      }
     }
+  }
+  // ---- the offsets: a cudaMemcpyAsync out of the caller's pageable array would block this thread for the whole copy
+  // (0.38 ms per 10^6 sequences), so the pool's threads copy them into a pinned buffer — in the same pass that keeps the
+  // host copy and finds the shortest / longest sequence — and the DMA engine takes them from there
+  host_bookkeeping_parallel(h, offsets, n_seq, h->pin_offs);
+  CU(h, cudaMemcpyAsync(h->d_offsets, h->pin_offs, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+  if (s_split < n_seq) {  // raw bytes and offsets have arrived: the device packs the rest in one go
+    const uint8_t* d_src = (const uint8_t*)h->d_scratch - b_lo;  // indexed by absolute base offset, never read below b_lo
+    CU(h, cudaEventRecord(h->copy_ev[0], h->copy_stream));
+    CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[0], 0));
+    TRY(launch_pack(h, d_src, ascii, blk_split * 2, h->n_words32));
   }
   // ---- the packed part, phase by phase through the two pinned staging buffers ----
   bool has_carry = false;
@@ -1838,6 +1862,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   double t_pack = 0, t_wait = 0, t_issue = 0;
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   const double t_start = now();
+  mark(3);
   for (uint64_t s = 0;;) {
     uint64_t e = std::min(s_split, plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks - 4));
     // the last phase of a fully packed set also writes the tail pad; if that does not fit, the tail gets a phase of its own
@@ -1878,9 +1903,11 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   k_sstart_scatter<<<grid_for(std::max<uint64_t>(n_seq, 1), 256), 256, 0, h->stream>>>(h->d_offsets, n_seq, t_split, h->d_sstart);
   LAUNCH_CHECK(h);
   const double t_loop = now();
-  host_bookkeeping_parallel(h, offsets, n_seq);
   const double t_book = now();
   CU(h, cudaStreamSynchronize(h->stream));
+  if (dbg)
+    fprintf(stderr, "[ingest] before the phases: plan %.2f, prepare %.2f, offsets copy issued %.2f, raw rest issued %.2f ms\n",
+            1e3 * t_marks[0], 1e3 * (t_marks[1] - t_marks[0]), 1e3 * (t_marks[2] - t_marks[1]), 1e3 * (t_marks[3] - t_marks[2]));
   if (dbg)
     fprintf(stderr, "[ingest] threads %d split %.2f: phases %.2f ms (pack %.2f, wait %.2f, issue %.2f), bookkeeping %.2f, final sync %.2f\n",
             pool.size(), (double)offsets[s_split] / (double)std::max<uint64_t>(total, 1), 1e3 * (t_loop - t_start), 1e3 * t_pack,
