@@ -92,6 +92,7 @@ struct peng_cuda_ctx {
   double ingest_fraction = -1;     // share of the bases packed on the host (< 0: from the thread count)
   uint64_t last_ingest_packed = 0; // sequences the host packed in the last ingest
   int part_cfg = 0;                // stage-P geometry (tuning knob, PENG_PART_CFG)
+  bool fold_untiled = false;       // PENG_FOLD_UNTILED: one-thread-per-id fold / mirror at every W (A/B)
   uint2* d_slow_list = nullptr;
   size_t slow_list_elems = 0;
   unsigned int* d_slow_count = nullptr;
@@ -965,6 +966,106 @@ __global__ void k_fold_first(uint32_t* __restrict__ hist, uint64_t* __restrict__
   }
 }
 
+// ---- tiled fold / mirror for tables beyond the L2 (W >= 12) -----------------------------------------------------------
+// One thread per id reads its partner at revcomp(id): neighbouring ids have partners 4^(W-1) apart, every partner read
+// (and mirror write) moves a whole 32-byte sector for 4 or 8 bytes (W = 14, BOTH: fold 7.9 ms + mirror 3.9 ms).  Written
+// as id = (a, m, b) with a = top 3 letters, b = low 3 letters, m = the W-6 letters between them,
+//     revcomp(a, m, b) = (revcomp3(b), revcomp(m), revcomp3(a)):
+// the 64 x 64 ids of a middle m ("tile": 64 rows of 64 consecutive ids) have their partners exactly in the tile of
+// revcomp(m).  A CTA loads the two tiles row by row, pairs them through shared memory and writes rows: every global
+// access is a 256- or 512-byte run.
+#define FOLD_TS 64  // ids per tile row = 4^3
+__global__ void k_mirror(uint64_t* __restrict__ counts, int W, uint64_t n);
+__device__ __forceinline__ uint32_t revcomp3(uint32_t x) { return revcomp_id(x, 3); }
+// FIRST: the 64-bit table is written (= pair sum at canonical ids, at the others too with MIRROR, else 0); otherwise the
+// pair sums are added at the canonical ids.  The uint32 table is cleared either way.
+template <bool FIRST, bool MIRROR>
+__global__ void __launch_bounds__(256) k_fold_canon_tiled(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, int W) {
+  __shared__ uint32_t tA[FOLD_TS * FOLD_TS], tB[FOLD_TS * FOLD_TS];
+  const uint32_t m = blockIdx.x, mp = revcomp_id(m, W - 6);
+  if (m > mp) return;  // the pair of tiles belongs to the CTA of the smaller middle
+  const bool self = m == mp;
+  const int sh_a = 2 * W - 6;
+  for (uint32_t e = threadIdx.x; e < FOLD_TS * FOLD_TS; e += 256) {
+    const uint32_t a = e >> 6, b = e & 63u;
+    tA[e] = hist[((uint64_t)a << sh_a) | ((uint64_t)m << 6) | b];
+    if (!self) tB[e] = hist[((uint64_t)a << sh_a) | ((uint64_t)mp << 6) | b];
+  }
+  __syncthreads();
+  for (uint32_t e = threadIdx.x; e < FOLD_TS * FOLD_TS; e += 256) {
+    const uint32_t a = e >> 6, b = e & 63u;
+    const uint32_t pe = revcomp3(b) * FOLD_TS + revcomp3(a);  // where the partner sits in the other tile
+#pragma unroll
+    for (int t = 0; t < 2; t++) {
+      if (t == 1 && self) break;
+      const uint32_t mid = t ? mp : m, pmid = t ? m : mp;
+      const uint64_t j = ((uint64_t)a << sh_a) | ((uint64_t)mid << 6) | b;
+      const uint64_t rj = ((uint64_t)(pe >> 6) << sh_a) | ((uint64_t)pmid << 6) | (pe & 63u);
+      const uint32_t own = t ? tB[e] : tA[e];
+      const uint32_t other = (t || self) ? tA[pe] : tB[pe];
+      const uint64_t v = j == rj ? (uint64_t)own : (uint64_t)own + other;
+      if (FIRST) acc[j] = (j <= rj || MIRROR) ? v : 0ull;
+      else if (j <= rj && v) acc[j] += v;
+      if (own) hist[j] = 0;
+    }
+  }
+}
+// the pair count of every canonical id copied to its reverse complement (k_mirror), tile by tile
+__global__ void __launch_bounds__(256) k_mirror_tiled(uint64_t* __restrict__ counts, int W) {
+  extern __shared__ uint64_t tiles[];  // two tiles of 64 x 64
+  uint64_t* tA = tiles;
+  uint64_t* tB = tiles + FOLD_TS * FOLD_TS;
+  const uint32_t m = blockIdx.x, mp = revcomp_id(m, W - 6);
+  if (m > mp) return;
+  const bool self = m == mp;
+  const int sh_a = 2 * W - 6;
+  for (uint32_t e = threadIdx.x; e < FOLD_TS * FOLD_TS; e += 256) {
+    const uint32_t a = e >> 6, b = e & 63u;
+    tA[e] = counts[((uint64_t)a << sh_a) | ((uint64_t)m << 6) | b];
+    if (!self) tB[e] = counts[((uint64_t)a << sh_a) | ((uint64_t)mp << 6) | b];
+  }
+  __syncthreads();
+  for (uint32_t e = threadIdx.x; e < FOLD_TS * FOLD_TS; e += 256) {
+    const uint32_t a = e >> 6, b = e & 63u;
+    const uint32_t pe = revcomp3(b) * FOLD_TS + revcomp3(a);
+#pragma unroll
+    for (int t = 0; t < 2; t++) {
+      if (t == 1 && self) break;
+      const uint32_t mid = t ? mp : m, pmid = t ? m : mp;
+      const uint64_t j = ((uint64_t)a << sh_a) | ((uint64_t)mid << 6) | b;
+      const uint64_t rj = ((uint64_t)(pe >> 6) << sh_a) | ((uint64_t)pmid << 6) | (pe & 63u);
+      if (j > rj) counts[j] = (t || self) ? tA[pe] : tB[pe];
+    }
+  }
+}
+#define FOLD_TILED_MIN_W 12
+static int launch_fold_canon(peng_handle_t h, int W, bool first, bool mirror) {
+  const uint64_t n = h->n_patterns;
+  if (W >= FOLD_TILED_MIN_W && !h->fold_untiled) {
+    const unsigned grid = 1u << (2 * (W - 6));
+    if (first && mirror) k_fold_canon_tiled<true, true><<<grid, 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W);
+    else if (first) k_fold_canon_tiled<true, false><<<grid, 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W);
+    else k_fold_canon_tiled<false, false><<<grid, 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W);
+  } else {
+    if (first && mirror) k_fold_canon_first<true><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+    else if (first) k_fold_canon_first<false><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+    else k_fold_canon<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+  }
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+static int launch_mirror(peng_handle_t h) {
+  if (h->W >= FOLD_TILED_MIN_W && !h->fold_untiled) {
+    const size_t smem = 2 * FOLD_TS * FOLD_TS * sizeof(uint64_t);
+    CU(h, cudaFuncSetAttribute(k_mirror_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_mirror_tiled<<<1u << (2 * (h->W - 6)), 256, smem, h->stream>>>(h->d_counts, h->W);
+  } else {
+    k_mirror<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_counts, h->W, h->n_patterns);
+  }
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
+
 // 32-bit exchange (peng_cuda_count_local32 / _finish32): ltot rides in word n of the uint32 table
 __global__ void k_ltot_to32(const uint64_t* __restrict__ ltot64, uint32_t* __restrict__ word) { *word = (uint32_t)*ltot64; }
 __global__ void k_ltot_from32(uint32_t* __restrict__ word, uint64_t* __restrict__ ltot64) {
@@ -1546,6 +1647,7 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
     return PENG_E_CUDA;
   }
   if (const char* e = getenv("PENG_PART_CFG")) h->part_cfg = atoi(e);
+  h->fold_untiled = getenv("PENG_FOLD_UNTILED") != nullptr;
   if (const char* e = getenv("PENG_INGEST_MODE")) h->ingest_mode = !strcmp(e, "raw") ? 1 : !strcmp(e, "packed") ? 2 : 0;
   if (const char* e = getenv("PENG_HOST_PACK_FRACTION")) h->ingest_fraction = atof(e);
   if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
@@ -2270,7 +2372,7 @@ static int launch_count_partition(peng_handle_t h, bool both) {
     CU(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
     if (ub == 0) MARK(h, 7);
     if (ue < n_units) {
-      if (both) k_fold_canon<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, h->n_patterns);
+      if (both) TRY(launch_fold_canon(h, W, false, false));
       else k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
       LAUNCH_CHECK(h);
     }
@@ -2353,7 +2455,7 @@ static int launch_count_deep(peng_handle_t h, bool both) {
   for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
     const uint64_t ue = std::min(n_units, ub + units_per_chunk);
     if (pos_since_fold + (ue - ub) * 32 > 0xFFFFFFFFull) {  // a uint32 bin could overflow: fold first
-      if (both) k_fold_canon<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, h->n_patterns);
+      if (both) TRY(launch_fold_canon(h, W, false, false));
       else k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
       LAUNCH_CHECK(h);
       pos_since_fold = 0;
@@ -2471,13 +2573,16 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   h->counts_final = false;
   h->stats_ready = false;
   CU(h, cudaMemsetAsync(h->d_hist32, 0, (n + 4) * 4, h->stream));
-  // up to 2^30 stream positions (pads included) every path folds exactly once, at the end: that fold writes the whole 64-bit table
-  const bool single_fold = h->n_words32 <= (1ull << 25);  // one chunk of every path
+  const bool both = strand == PENG_STRAND_BOTH;
+  const bool partition = use_partition(h, W);
+  // up to 2^30 stream positions (pads included) every path folds exactly once, at the end; the deep partition path
+  // (W >= 12) folds between its chunks only when a uint32 bin could overflow, i.e. never below 2^32 positions.  A single
+  // fold WRITES the whole 64-bit table: no clearing pass, no read of the old values, the mirror copy in the same kernel.
+  const bool single_chunk = h->n_words32 <= (1ull << 25);
+  const bool single_fold = single_chunk || (partition && W >= 12 && h->n_words32 * 32 <= 0xFFFFFFFFull);
   if (single_fold) CU(h, cudaMemsetAsync(h->d_counts + n, 0, 8, h->stream));
   else CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
   h->mirrored = false;
-  const bool both = strand == PENG_STRAND_BOTH;
-  const bool partition = use_partition(h, W);
   h->used_partition = false;
   MARK(h, 0);
   if (!partition) {  // the partition path derives the k-mer starts inside its first stage
@@ -2501,18 +2606,16 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   TRY(rc);
   MARK(h, 4);
   h->fold_deferred = false;
-  if (h->defer_fold && single_fold) {
+  if (h->defer_fold && single_chunk) {
     // 32-bit exchange: the caller sums the uint32 table (+ ltot in word n) over the ranks, peng_cuda_count_finish32 folds
     k_ltot_to32<<<1, 1, 0, h->stream>>>(h->d_counts + n, h->d_hist32 + n);
     LAUNCH_CHECK(h);
     h->fold_deferred = true;
   } else if (h->used_partition && both) {
     if (single_fold && h->fuse_mirror) {
-      k_fold_canon_first<true><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
+      TRY(launch_fold_canon(h, W, true, true));
       h->mirrored = true;
-    } else if (single_fold) k_fold_canon_first<false><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
-    else k_fold_canon<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, W, n);
-    LAUNCH_CHECK(h);
+    } else TRY(launch_fold_canon(h, W, single_fold, false));
   } else {
     if (single_fold) k_fold_first<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
     else k_fold<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
@@ -2563,12 +2666,12 @@ extern "C" int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot) {
   k_ltot_from32<<<1, 1, 0, h->stream>>>(h->d_hist32 + n, h->d_counts + n);
   LAUNCH_CHECK(h);
   if (h->used_partition && h->strand == PENG_STRAND_BOTH) {
-    k_fold_canon_first<true><<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->W, n);
+    TRY(launch_fold_canon(h, h->W, true, true));
     h->mirrored = true;
   } else {
     k_fold_first<<<grid_for(n, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, n);
+    LAUNCH_CHECK(h);
   }
-  LAUNCH_CHECK(h);
   h->fold_deferred = false;
   return peng_cuda_count_finish(h, ltot);
 }
@@ -2579,8 +2682,7 @@ extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
   CU(h, cudaSetDevice(h->device));
   if (!h->counts_final) {
     if (h->strand == PENG_STRAND_BOTH && !h->mirrored) {
-      k_mirror<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_counts, h->W, h->n_patterns);
-      LAUNCH_CHECK(h);
+      TRY(launch_mirror(h));
     }
     CU(h, cudaMemcpyAsync(&h->ltot, h->d_counts + h->n_patterns, 8, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
