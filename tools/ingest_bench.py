@@ -6,6 +6,11 @@ import _pkg
 pkg = _pkg.load()
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 g = pkg.PengCuda(0)
+if os.environ.get("PENG_TOOL_STREAM") == "legacy":  # what a caller on torch's default stream hands over
+    g.set_stream(torch.cuda.current_stream().cuda_stream)
+elif os.environ.get("PENG_TOOL_STREAM") == "torch":
+    _s = torch.cuda.Stream()
+    g.set_stream(_s.cuda_stream)
 g.ingest_synthetic(n, 200, 1234, 0, "TGCTGASTCAGCA", 0.3, 0.0)
 codes, offs = g.export_codes()
 pin = torch.from_numpy(codes).pin_memory()
