@@ -1885,7 +1885,8 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   double f = 1.0;
   if (!force) {
     // Gbases/s: measured packing rate (5.7 per thread up to 8 threads, 63 at 16: tools/probe/host_pack_bench.cpp), PCIe rate
-    const double rh = 5.7 * std::min(pool.size(), 8) + 2.2 * std::max(0, pool.size() - 8), rp = 46.0;
+    // x 0.8: the packing runs beside the DMA traffic and behind the bookkeeping pass (measured optimum at 16 threads: 0.65)
+    const double rh = 0.8 * (5.7 * std::min(pool.size(), 8) + 2.2 * std::max(0, pool.size() - 8)), rp = 46.0;
     f = rh / (rp + 0.625 * rh);
     if (h->ingest_fraction >= 0) f = h->ingest_fraction;
     f = std::min(1.0, std::max(0.0, f));
@@ -1961,12 +1962,22 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   int buf = 0;
   bool first = true;
   static const bool dbg = getenv("PENG_INGEST_DEBUG") != nullptr;
+  static const bool taper = getenv("PENG_NO_TAPER") == nullptr;
   double t_pack = 0, t_wait = 0, t_issue = 0;
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   const double t_start = now();
   mark(3);
   for (uint64_t s = 0;;) {
-    uint64_t e = std::min(s_split, plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks - 4));
+    // the copy of the LAST phase cannot hide behind packing: towards the end every phase takes half of what is left
+    // (down to 2 MiB of blocks), so that the tail of the DMA queue is short
+    uint64_t cap = max_blocks - 4;
+    if (taper) {
+      const uint64_t blk_here = first ? 0 : (PENG_FRONT_PAD + offsets[s] + 2 * s) >> 6;
+      const uint64_t remaining = blk_split > blk_here ? blk_split - blk_here : 0;
+      if (remaining < 2 * cap) cap = std::min(cap, std::max<uint64_t>((2u << 20) / 24, remaining / 2));
+    }
+    uint64_t e = std::min(s_split, plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, cap));
+    if (e == s) e = std::min(s_split, plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks - 4));  // a long sequence
     // the last phase of a fully packed set also writes the tail pad; if that does not fit, the tail gets a phase of its own
     bool last = false;
     if (s_split == n_seq && e == n_seq) {
