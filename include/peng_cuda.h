@@ -47,7 +47,10 @@ enum {                                                         /* tables of Base
   PENG_TABLE_BGPROB = 0,   /* pattern_bg_probabilities[order] */
   PENG_TABLE_EXPECTED = 1, /* expected_counts */
   PENG_TABLE_ZSCORE = 2,   /* pattern_zscore */
-  PENG_TABLE_LOGP = 3      /* pattern_logp */
+  PENG_TABLE_LOGP = 3      /* pattern_logp; PENG_F32REF: the one table that is NOT bit-identical to the reference — its
+                            * log() is the device's, not glibc's (<= 4 differing float entries per 10^5, checked at float
+                            * resolution); unused on the default path (MUTUAL_INFO), the host driver recomputes the logp of
+                            * the selected seeds with glibc */
 };
 
 /* ---- lifetime ------------------------------------------------------------------------------------- */
@@ -136,6 +139,19 @@ int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot);
 int peng_cuda_count_local32(peng_handle_t h, int W, int strand);
 int peng_cuda_count_buffer32(peng_handle_t h, void** device_ptr, uint64_t* n_u32);
 int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot);
+/* Id-sliced tables for the long pattern lengths on several GPUs (BASELINE configs[4]; the reference's tables are one
+ * float array per order plus expected / z / logp over all 4^W ids, src/base_pattern.h:116-120 — at W = 16 more than one
+ * GPU holds).  Rank `part` of `n_parts` keeps the ids [lo, hi) (whole tiles of 1024 ids, peng_cuda_table_slice) of every
+ * table peng_cuda_stats builds; peng_cuda_get_table returns the slice, _gather_table / _gather_counts accept ids of the
+ * slice, peng_cuda_iupac_aggregate (PENG_F64) and _iupac_count return this rank's PARTIAL sums (the caller adds them
+ * over the ranks), the EM session must be opened with the same (part, n_parts).  The float32 arm's sequential sums and
+ * seed selection need whole tables and refuse.  n_parts = 1 switches slicing off.
+ * peng_cuda_count_finish32_sliced (PLUS strand) is the matching finish of the 32-bit exchange: the caller reduce-scatters
+ * the 4^W uint32 bins in place (ncclReduceScatter with recvbuff = sendbuff + lo) and all-reduces word 4^W (ltot); only
+ * the slice of the 64-bit table is then written and valid. */
+int peng_cuda_set_table_slice(peng_handle_t h, int part, int n_parts);
+int peng_cuda_table_slice(peng_handle_t h, uint64_t* lo, uint64_t* hi); /* after a count: this rank's id range */
+int peng_cuda_count_finish32_sliced(peng_handle_t h, uint64_t* ltot);
 /* Sparse read-back for tables that are too large to copy (W >= 14): the bins at `ids`, and the sum of all bins. */
 int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uint64_t n, uint64_t* out);
 int peng_cuda_counts_total(peng_handle_t h, uint64_t* total);

@@ -77,6 +77,9 @@ _PROTOS = {
     "peng_cuda_count_local32": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_count_buffer32": (C.c_int, [H, C.POINTER(C.c_void_p), u64p]),
     "peng_cuda_count_finish32": (C.c_int, [H, u64p]),
+    "peng_cuda_set_table_slice": (C.c_int, [H, C.c_int, C.c_int]),
+    "peng_cuda_table_slice": (C.c_int, [H, u64p, u64p]),
+    "peng_cuda_count_finish32_sliced": (C.c_int, [H, u64p]),
     "peng_cuda_gather_counts": (C.c_int, [H, C.c_void_p, C.c_uint64, C.c_void_p]),
     "peng_cuda_counts_total": (C.c_int, [H, u64p]),
     "peng_cuda_set_counts": (C.c_int, [H, C.c_int, C.c_int, C.c_void_p, C.c_uint64]),
@@ -327,6 +330,27 @@ class PengCuda:
         self._ck(self.lib.peng_cuda_count_finish32(self.h, C.byref(ltot)))
         return ltot.value
 
+    # id-sliced tables (long pattern lengths on several GPUs)
+    def set_table_slice(self, part=0, n_parts=1):
+        self._ck(self.lib.peng_cuda_set_table_slice(self.h, int(part), int(n_parts)))
+        self._sliced = n_parts > 1
+
+    def table_slice(self):
+        lo, hi = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.peng_cuda_table_slice(self.h, C.byref(lo), C.byref(hi)))
+        return lo.value, hi.value
+
+    def count_finish32_sliced(self):
+        ltot = C.c_uint64()
+        self._ck(self.lib.peng_cuda_count_finish32_sliced(self.h, C.byref(ltot)))
+        return ltot.value
+
+    def _table_len(self):
+        if getattr(self, "_sliced", False):
+            lo, hi = self.table_slice()
+            return hi - lo
+        return 4 ** self.W
+
     def get_counts(self):
         out = np.zeros(4 ** self.W, np.uint64)
         self._ck(self.lib.peng_cuda_get_counts(self.h, _ptr(out)))
@@ -358,7 +382,7 @@ class PengCuda:
         self._ck(self.lib.peng_cuda_stats(self.h, K, _ptr(a32), _ptr(a64), k, max_k))
 
     def get_table(self, table, precision=F32REF, order=0):
-        out = np.zeros(4 ** self.W, np.float32 if precision == F32REF else np.float64)
+        out = np.zeros(self._table_len(), np.float32 if precision == F32REF else np.float64)
         self._ck(self.lib.peng_cuda_get_table(self.h, table, order, precision, _ptr(out)))
         return out
 

@@ -236,6 +236,135 @@ inline std::vector<uint64_t> select_base_patterns(const float* z, const uint64_t
   return selected;
 }
 
+// ---- seed selection with the top partition levels on the device -----------------------------------------
+// The 4^W-element introsort above spends nearly all of its time in the first few partition passes, which touch the whole
+// index array only to throw the right part away (its pivot lies below the threshold).  One pass of libstdc++'s
+//   std::__unguarded_partition(first + 1, last, pivot = *first)       [after std::__move_median_to_first]
+// is data-parallel: with  A = positions (ascending) whose element stops the left scan  (!(z > z_pivot)),
+//                         B = positions (descending) whose element stops the right scan (!(z_pivot > z)),
+// the k-th swap exchanges A[k] and B[k] for every k < m, m = #{k : A[k] < B[k]} (the predicate is monotone), and the cut is
+// min(A[m], B[m - 1]): while k < m the left pointer has only seen original elements in front of B[k] and the right
+// pointer only original elements behind A[k], so the sequential scans stop exactly at the list entries.  The device runs
+// these passes on its resident z table (flags -> scan -> compact -> pair swap, peng_cuda.cu: k_sel_*), follows the left
+// part while it is long, and hands the host only the short leading range — as (z, id) pairs, so that the host needs no
+// 4^W table at all — to finish with libstdc++'s own steps as above.  `Engine` is the device (peng_cuda.cu) or, for the
+// GPU-less tests, a host restatement of the same list formulation (tests/sim/sim_kernels.cpp).
+struct ZId {
+  float z;
+  uint32_t id;
+};
+struct ZIdDescending {
+  bool operator()(const ZId& a, const ZId& b) const { return a.z > b.z; }
+};
+
+// the list formulation of one partition pass on order[0 .. n) (host restatement of k_sel_pivot / _flags / _compact /
+// _find / _swap; n > 16 as in the introsort loop): returns the cut, *pivot_z = z of the pivot (left at order[0])
+inline size_t partition_level_lists(uint32_t* order, const float* z, size_t n, float* pivot_z) {
+  auto gt = [&](size_t i, size_t j) { return z[order[i]] > z[order[j]]; };
+  const size_t a = 1, b = n / 2, c = n - 1;
+  size_t sel;
+  if (gt(a, b)) sel = gt(b, c) ? b : (gt(a, c) ? c : a);
+  else sel = gt(a, c) ? a : (gt(b, c) ? c : b);
+  std::swap(order[0], order[sel]);
+  const float zp = z[order[0]];
+  *pivot_z = zp;
+  std::vector<uint32_t> A, B;
+  for (size_t i = 1; i < n; i++)
+    if (!(z[order[i]] > zp)) A.push_back((uint32_t)i);
+  for (size_t i = n - 1; i >= 1; i--)
+    if (!(zp > z[order[i]])) B.push_back((uint32_t)i);
+  size_t lo = 0, hi = std::min(A.size(), B.size());  // m = number of k with A[k] < B[k]
+  while (lo < hi) {
+    const size_t mid = (lo + hi) / 2;
+    if (A[mid] < B[mid]) lo = mid + 1; else hi = mid;
+  }
+  const size_t m = lo;
+  for (size_t k = 0; k < m; k++) std::swap(order[A[k]], order[B[k]]);
+  size_t cut = (size_t)-1;
+  if (m < A.size()) cut = A[m];
+  if (m >= 1 && B[m - 1] < cut) cut = B[m - 1];
+  return cut;
+}
+
+#if defined(__GLIBCXX__)
+template <typename Comp>
+inline void pruned_introsort_loop_pairs(ZId* first, ZId* last, long depth_limit, Comp comp, float threshold, ZId** cold_begin) {
+  while (last - first > 16) {
+    if (depth_limit == 0) {
+      std::__partial_sort(first, last, last, comp);
+      return;
+    }
+    --depth_limit;
+    ZId* cut = std::__unguarded_partition_pivot(first, last, comp);  // pivot is left at *first
+    if (first->z < threshold) {
+      if (cut < *cold_begin) *cold_begin = cut;
+    } else {
+      pruned_introsort_loop_pairs(cut, last, depth_limit, comp, threshold, cold_begin);
+    }
+    last = cut;
+  }
+}
+
+// Engine: size_t level(size_t n_cur, float* pivot_z)   one partition pass on the leading n_cur positions -> cut
+//         void   fetch(size_t n, ZId* out)            the leading n positions as (z, id) pairs
+// -> lead[0 .. returned) is what std::sort over all n ids leaves in front, every id behind it has z < threshold.
+// n > 4096, no NaN in the table (the caller checks).
+template <typename Engine>
+inline size_t sort_leading_by_levels(Engine& eng, size_t n, float threshold, size_t stop_below, std::vector<ZId>* lead) {
+  struct Range { size_t b, e; long depth; };
+  std::vector<Range> todo;  // right parts that may hold an id above the threshold: sorted on the host with the depth they had
+  long depth = (long)std::__lg((long)n) * 2;
+  size_t n_cur = n, cold = n;
+  while (n_cur > stop_below && n_cur > 16 && depth > 0) {
+    --depth;
+    float pz;
+    const size_t cut = eng.level(n_cur, &pz);
+    if (pz < threshold) { if (cut < cold) cold = cut; }
+    else todo.push_back(Range{cut, n_cur, depth});
+    n_cur = cut;
+  }
+  lead->resize(cold);
+  eng.fetch(cold, lead->data());
+  auto comp = __gnu_cxx::__ops::__iter_comp_iter(ZIdDescending{});
+  ZId* first = lead->data();
+  ZId* cold_begin = first + cold;
+  for (const Range& r : todo) pruned_introsort_loop_pairs(first + r.b, first + r.e, r.depth, comp, threshold, &cold_begin);
+  pruned_introsort_loop_pairs(first, first + n_cur, depth, comp, threshold, &cold_begin);
+  const size_t n_lead = (size_t)(cold_begin - first);
+  if (n_lead > 16) {
+    std::__insertion_sort(first, first + 16, comp);
+    std::__unguarded_insertion_sort(first + 16, first + n_lead, comp);
+  } else {
+    std::__insertion_sort(first, first + n_lead, comp);
+  }
+  return n_lead;
+}
+#endif
+
+// the walk of select_base_patterns over the sorted leading ids whose z >= threshold (src/base_pattern.cpp:470-515);
+// counts[r] = count of sorted[r].id
+inline std::vector<uint64_t> select_walk(const ZId* sorted, const uint64_t* counts, size_t n_candidates, int W,
+                                         uint64_t count_threshold, bool single_stranded, bool filter_neighbors) {
+  const size_t n = (size_t)1 << (2 * W);
+  std::vector<bool> seen(n, false);
+  std::vector<uint64_t> selected;
+  for (size_t r = 0; r < n_candidates; r++) {
+    const size_t id = sorted[r].id;
+    if (counts[r] < count_threshold) continue;
+    if (seen[id]) continue;
+    if (!single_stranded && seen[revcomp_id64(id, W)]) continue;
+    selected.push_back(id);
+    seen[id] = true;
+    if (filter_neighbors) {
+      for (int p = 0; p < W; p++) {
+        const size_t masked = id & ~((size_t)3 << (2 * p));
+        for (size_t c = 0; c < 4; c++) seen[masked | (c << (2 * p))] = true;
+      }
+    }
+  }
+  return selected;
+}
+
 // IUPAC id (sum c_p 11^p, A,C,G,T,S,W,R,Y,M,K,N = 0..10; src/iupac_pattern.h:26-30) -> nibble p = set of
 // bases the letter at position p stands for (representative_iupac_nucleotides, src/iupac_alphabet.cpp:138-180)
 inline bool iupac_letter_mask(uint64_t iupac_id, int W, uint64_t* mask) {

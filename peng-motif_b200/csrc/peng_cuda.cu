@@ -77,6 +77,13 @@ struct peng_cuda_ctx {
   float *d_exp32 = nullptr, *d_z32 = nullptr, *d_logp32 = nullptr;
   double *d_exp64 = nullptr, *d_z64 = nullptr, *d_logp64 = nullptr;
   bool stats_ready = false;
+  // ---- id-sliced tables (multi-GPU long k-mers, peng_cuda_set_table_slice): this rank keeps [slice_lo, slice_hi) of every
+  // float table and — after peng_cuda_count_finish32_sliced — of the 64-bit count table.  A sliced buffer is addressed
+  // through a pointer moved back by slice_lo elements, so that kernels keep indexing by the absolute id.
+  int slice_part = 0, slice_parts = 1;
+  uint64_t slice_lo = 0, slice_hi = 0;  // valid after a count (slice_hi = 0: not yet derived)
+  bool counts_sliced = false;
+  uint64_t tab_lo = 0, tab_hi = 0;      // what the float tables hold (set by peng_cuda_stats)
 
   // ---- partition path (W = 10) ----
   int count_path = 0;              // 0 auto, 1 L2-atomic path, 2 partition path
@@ -110,6 +117,9 @@ struct peng_cuda_ctx {
   // ---- scratch ----
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
+  uint32_t* d_sel = nullptr;       // seed selection: order | list A | list B | block counts | state
+  size_t sel_words = 0;
+  bool select_on_host = false;     // PENG_SELECT_HOST: whole-table host replay (A/B, tests)
 
   // ---- EM session (multi-GPU protocol) ----
   struct {
@@ -118,6 +128,8 @@ struct peng_cuda_ctx {
     double sat = 0, thr = 0;
     double *d_old = nullptr, *d_acc = nullptr, *d_part = nullptr, *d_change = nullptr;
     int *d_iter = nullptr, *d_active = nullptr, *d_nactive = nullptr;
+    double2* d_pairs = nullptr;  // {(double) count, bgprob} of the ids of this rank's slice (k_em_pairs)
+    uint32_t ub = 0, ue = 0;     // the slice in units of 256 ids
   } em;
 };
 
@@ -179,6 +191,23 @@ static int need_scratch(peng_handle_t h, size_t bytes) {
   } while (0)
 
 static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+
+// id-sliced tables: a buffer that holds [lo, hi) is addressed through a pointer moved back by lo, so that kernels index by
+// the absolute id (never dereferenced outside [lo, hi))
+template <typename T>
+static inline T* vbase(T* p, uint64_t lo) { return p ? p - lo : nullptr; }
+// this rank's slice of the id range: whole tiles of 1024 ids (the EM slices of peng_cuda_em_begin use the same cut)
+static void slice_range(peng_handle_t h, uint64_t* lo, uint64_t* hi) {
+  const uint64_t n = h->n_patterns;
+  if (h->slice_parts <= 1 || n < 1024) { *lo = 0; *hi = n; return; }
+  const uint64_t n_tiles = n >> 10;
+  *lo = (n_tiles * (uint64_t)h->slice_part / (uint64_t)h->slice_parts) << 10;
+  *hi = (n_tiles * (uint64_t)(h->slice_part + 1) / (uint64_t)h->slice_parts) << 10;
+}
+// the ids the count table is valid for
+static inline uint64_t counts_lo(peng_handle_t h) { return h->counts_sliced ? h->slice_lo : 0; }
+static inline uint64_t counts_hi(peng_handle_t h) { return h->counts_sliced ? h->slice_hi : h->n_patterns; }
+static inline bool tables_whole(peng_handle_t h) { return !h->counts_sliced && h->tab_lo == 0 && h->tab_hi == h->n_patterns; }
 
 // =====================================================================================================
 // kernels: ingest
@@ -266,7 +295,7 @@ struct EmitShared {
 template <int W, bool BOTH>
 __global__ void __launch_bounds__(256) k_count_smem(const uint32_t* __restrict__ codes,
                                                     const uint32_t* __restrict__ kstart,
-                                                    uint32_t* __restrict__ hist, uint64_t n_chunks,
+                                                    uint32_t* __restrict__ hist, uint64_t first_chunk, uint64_t n_chunks,
                                                     uint32_t words_per_chunk) {
   extern __shared__ uint32_t sh[];
   constexpr uint32_t NB = 1u << (2 * W);
@@ -274,7 +303,7 @@ __global__ void __launch_bounds__(256) k_count_smem(const uint32_t* __restrict__
   __syncthreads();
   for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_chunks;
        c += (uint64_t)gridDim.x * blockDim.x) {
-    const uint64_t e0 = PENG_FRONT_PAD + c * 16ull * words_per_chunk;
+    const uint64_t e0 = PENG_FRONT_PAD + (first_chunk + c) * 16ull * words_per_chunk;
     count_chunk<W, BOTH>(codes, kstart, e0, words_per_chunk, EmitShared{sh});
   }
   __syncthreads();
@@ -305,7 +334,7 @@ struct EmitShared16 {
 template <int W, bool BOTH>
 __global__ void __launch_bounds__(512) k_count_smem16(const uint32_t* __restrict__ codes,
                                                       const uint32_t* __restrict__ kstart,
-                                                      uint32_t* __restrict__ hist, uint64_t n_chunks,
+                                                      uint32_t* __restrict__ hist, uint64_t first_chunk, uint64_t n_chunks,
                                                       uint32_t words_per_chunk) {
   extern __shared__ uint32_t sh[];
   constexpr uint32_t NW = 1u << (2 * W - 1);  // packed words
@@ -313,7 +342,7 @@ __global__ void __launch_bounds__(512) k_count_smem16(const uint32_t* __restrict
   __syncthreads();
   for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_chunks;
        c += (uint64_t)gridDim.x * blockDim.x) {
-    const uint64_t e0 = PENG_FRONT_PAD + c * 16ull * words_per_chunk;
+    const uint64_t e0 = PENG_FRONT_PAD + (first_chunk + c) * 16ull * words_per_chunk;
     count_chunk<W, BOTH>(codes, kstart, e0, words_per_chunk, EmitShared16{sh, hist});
   }
   __syncthreads();
@@ -1125,22 +1154,23 @@ __global__ void __launch_bounds__(256) k_bg_counts(const uint32_t* __restrict__ 
 // =====================================================================================================
 // kernels: tables
 // =====================================================================================================
+// ids [lo, lo + n); every table pointer is indexed by the absolute id (sliced tables: moved back by the slice start)
 template <typename R>
-__global__ void k_bgprob(const R* __restrict__ v, int W, int order, int both, R* __restrict__ out, uint64_t n) {
+__global__ void k_bgprob(const R* __restrict__ v, int W, int order, int both, R* __restrict__ out, uint64_t lo, uint64_t n) {
   extern __shared__ unsigned char shv_raw[];
   R* shv = reinterpret_cast<R*>(shv_raw);
   const uint32_t nv = v_offset(order + 1);
   for (uint32_t i = threadIdx.x; i < nv; i += blockDim.x) shv[i] = v[i];
   __syncthreads();
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) out[i] = bg_prob_entry<R>(shv, W, order, (uint32_t)i, both != 0);
+  if (i < n) out[lo + i] = bg_prob_entry<R>(shv, W, order, (uint32_t)(lo + i), both != 0);
 }
 
 template <typename R>
 __global__ void k_stats(const uint64_t* __restrict__ counts, const R* __restrict__ bg, uint64_t ltot,
-                        R* __restrict__ expected, R* __restrict__ z, R* __restrict__ logp, uint64_t n) {
-  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) stats_of<R>(counts[i], bg[i], ltot, expected + i, z + i, logp + i);
+                        R* __restrict__ expected, R* __restrict__ z, R* __restrict__ logp, uint64_t lo, uint64_t n) {
+  const uint64_t i = lo + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < lo + n) stats_of<R>(counts[i], bg[i], ltot, expected + i, z + i, logp + i);
 }
 
 // =====================================================================================================
@@ -1161,7 +1191,7 @@ __global__ void __launch_bounds__(256) k_iupac_any(const uint64_t* __restrict__ 
                                                    const uint64_t* __restrict__ counts, const R* __restrict__ bg,
                                                    const R* __restrict__ expected,
                                                    unsigned long long* __restrict__ out_n, double* __restrict__ out_bg,
-                                                   double* __restrict__ out_exp) {
+                                                   double* __restrict__ out_exp, uint64_t id_lo, uint64_t id_hi) {
   const uint64_t mask = masks[blockIdx.x];
   const IupacShape shape = iupac_shape(mask, W);
   const uint64_t N = 1ull << shape.total_bits;
@@ -1169,6 +1199,7 @@ __global__ void __launch_bounds__(256) k_iupac_any(const uint64_t* __restrict__ 
   double sb = 0, se = 0;
   for (uint64_t t = threadIdx.x; t < N; t += blockDim.x) {
     const uint32_t e = iupac_expansion_any(mask, W, shape, t);
+    if (e < id_lo || e >= id_hi) continue;  // id-sliced tables: this rank's partial sum
     if (BOTH && !iupac_is_representative(mask, W, e)) continue;
     sn += counts[e];  // counts / bgprob / expected hold the pair value at both ids of a pair
     if (WITH_FLOATS) {
@@ -1300,134 +1331,178 @@ __global__ void __launch_bounds__(IUPAC_TILE_WORDS) k_iupac_f32_both(const uint6
 // kernels: EM, FP64 (fast path)
 // =====================================================================================================
 // new_pwm[p][a] = sum over ids with digit_p = a of  cnt*s / (1 + s/odds),  odds = prod_p pwm[p][digit_p] / bg
-//              = sum cnt*s*prob / (prob + s*bg).
-// A warp owns a tile of 1024 consecutive ids (positions 0..4 take all values, positions >= 5 are fixed).
-// Lane l handles ids  tile + l + 32 j, j = 0..31:
-//   positions 0,1 : fixed by the lane (l & 3, (l >> 2) & 3)
-//   position 2    : digit = (l >> 4) | ((j & 1) << 1)
-//   position 3    : digit = (j >> 1) & 3          position 4 : digit = (j >> 3) & 3
-// so the per-digit partial sums live in 11 statically indexed registers and are combined across lanes with
-// warp shuffles once per tile; per-warp accumulators in shared memory, one deterministic block reduction,
-// one partial-sum row per CTA in global memory (reduced in fixed order by k_em_reduce).
-#define EM_WARPS 8
-__device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+//              = s * sum cnt*prob' / (prob' + bg),   prob' = prob / s
+// (the common factor s cancels in the row normalisation that follows and is dropped from the accumulators).
+//
+// ONE pass over the table per iteration for ALL PWMs (16 B per bin and iteration, whatever the number of
+// PWMs).  The work is laid out PWM-per-thread, not id-per-thread:
+//   * k_em_pairs (once per EM call) writes {(double) count, bg} per id — the two operands every (id, PWM) term needs,
+//     one 16-byte load;
+//   * a CTA of 256 threads hosts R = 256 / P "slots"; thread (r, m) = (t / P, t % P) evaluates PWM m on the ids of slot
+//     r.  A slot is a contiguous range of units of 256 ids (the low 4 letters), handed out evenly over all slots of the
+//     grid; every 16-id block of every slot of the CTA arrives in shared memory through a 4-stage cp.async pipeline
+//     (each table byte crosses HBM -> SM once) and is read by the P threads of its slot as a broadcast;
+//   * because a thread owns a PWM for a whole id range, NOTHING is reduced across lanes inside the loop: the sums for
+//     positions 0 and 1 sit in 8 statically indexed registers (the 16 ids of a block are unrolled), those of the other
+//     positions in a private shared-memory column that takes one add per block (positions 2, 3) or per unit (>= 4);
+//     the prefix product over the positions >= 2 is formed once per block, so a term costs 1 multiply for its
+//     probability, 1 add for the denominator, the reciprocal (1 MUFU seed + 2 Newton steps = 4 FMA, 1-2 ulp; the IEEE
+//     division is 9+ instructions and a slow path), 2 multiplies and ~1.6 adds: ~10.6 FP64 instructions, against 23
+//     (+ 108 shuffles per tile and PWM) in the id-per-lane kernel this replaces;
+//   * blocks / groups of 4 ids whose counts are all zero are skipped (sparse long-k-mer tables);
+//   * at the end the R slots of a PWM are added in fixed order: one partial row per CTA and PWM, reduced in fixed order
+//     by k_em_reduce* -> deterministic.
+#define EM_NT 256
+#define EM_STAGES 4
+#define EM_MAX_R 32
+#define EM_MAX_GROUP 64  // PWMs per launch (larger batches run group after group)
+#define EM_UNIT_BITS 8   // 256 ids per unit
+
+__device__ __forceinline__ double em_rcp(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));  // ~2^-20 relative (the seed looks at the upper 32 bits)
+  double e = fma(-d, r, 1.0);
+  r = fma(r, e, r);  // 2^-40
+  e = fma(-d, r, 1.0);
+  r = fma(r, e, r);  // below the rounding error of a double
+  return r;
+}
+
+__global__ void k_em_pairs(const uint64_t* __restrict__ counts, const double* __restrict__ bg, uint64_t id_begin, uint64_t n,
+                           double2* __restrict__ pairs) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) pairs[i] = make_double2((double)counts[id_begin + i], bg[id_begin + i]);
+}
 
 template <int W>
-__global__ void __launch_bounds__(EM_WARPS * 32, 2) k_em_accumulate_f64(
-    const uint64_t* __restrict__ counts, const double* __restrict__ bg, const double* __restrict__ pwms,
-    const int* __restrict__ active, double saturation, uint32_t tile_begin, uint32_t tile_end,
-    double* __restrict__ partials /* [n_pwm][gridDim.x][W*4] */) {
-  static_assert(W >= 6, "tile layout needs positions 0..4 plus at least one fixed position");
-  const int m = blockIdx.y;
-  if (!active[m]) return;
-  __shared__ double spwm[W * 4];
-  __shared__ double sacc[EM_WARPS][W * 4];
-  for (int i = threadIdx.x; i < W * 4; i += blockDim.x) spwm[i] = pwms[(size_t)m * W * 4 + i];
-  for (int i = threadIdx.x; i < EM_WARPS * W * 4; i += blockDim.x) (&sacc[0][0])[i] = 0.0;
-  __syncthreads();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t d0 = lane & 3, d1 = (lane >> 2) & 3, d2lo = lane >> 4;
-  const double p01 = spwm[d0] * spwm[4 + d1];
-  double p2[2], p3[4], p4[4];
-  p2[0] = spwm[8 + d2lo];
-  p2[1] = spwm[8 + d2lo + 2];
+__global__ void __launch_bounds__(EM_NT, 1) k_em_accumulate_all(
+    const double2* __restrict__ pairs /* indexed by id - (unit_begin << 8) */, const double* __restrict__ pwms /* [P][W*4] */,
+    const int* __restrict__ active, int P, int R, double inv_saturation, uint32_t unit_begin, uint32_t unit_end,
+    double* __restrict__ partials /* [P][nbx][W*4] */, int nbx) {
+  static_assert(W >= 4, "a unit is the 256 ids of the low 4 positions");
+  constexpr int WA = W * 4;
+  extern __shared__ __align__(16) unsigned char em_smem[];
+  double2* stage = reinterpret_cast<double2*>(em_smem);      // [EM_STAGES][R][16]
+  double* spw = reinterpret_cast<double*>(stage + EM_STAGES * R * 16);  // [WA][P]: entry-major, the PWMs of a warp side by side
+  double* sacc = spw + WA * P;                                // [WA][EM_NT]: one private column per thread
+  const int t = threadIdx.x;
+  const int r = t / P, m = t - r * P;
+  const bool worker = r < R;
+  const bool live = worker && active[m] != 0;
+  if (!__syncthreads_or(live)) return;  // every PWM of this launch has converged
+  for (int i = t; i < WA * P; i += EM_NT) {
+    const int mm = i / WA, e = i - mm * WA;
+    spw[e * P + mm] = pwms[i];
+  }
+#pragma unroll 4
+  for (int e = 0; e < WA; e++) sacc[e * EM_NT + t] = 0.0;
+  // ---- slots: slot s of S = gridDim.x * R owns the units [lo(s), lo(s + 1)) ----
+  const uint32_t S = gridDim.x * (uint32_t)R, n_units = unit_end - unit_begin;
+  auto slot_lo = [&](uint32_t s) { return (uint32_t)((uint64_t)n_units * s / S); };  // relative to unit_begin
+  const uint32_t s0 = blockIdx.x * (uint32_t)R;
+  uint32_t n_steps = 0;
+  for (int rr = 0; rr < R; rr++) n_steps = max(n_steps, (slot_lo(s0 + rr + 1) - slot_lo(s0 + rr)) << 4);
+  // loader role: thread t copies 16-byte piece (t & 15) of the blocks of slots (t >> 4) and (t >> 4) + 16
+  uint32_t ld_lo[2], ld_n[2];
 #pragma unroll
-  for (int a = 0; a < 4; a++) { p3[a] = spwm[12 + a]; p4[a] = spwm[16 + a]; }
-
-  for (uint32_t tile = tile_begin + blockIdx.x * EM_WARPS + warp; tile < tile_end; tile += gridDim.x * EM_WARPS) {
-    // product over the tile-fixed positions 5..W-1
-    double pfix = p01;
+  for (int j = 0; j < 2; j++) {
+    const int lr = (t >> 4) + 16 * j;
+    const uint32_t lo = lr < R ? slot_lo(s0 + lr) : 0u, hi = lr < R ? slot_lo(s0 + lr + 1) : 0u;
+    ld_lo[j] = lo;
+    ld_n[j] = (hi - lo) << 4;
+  }
+  const uint32_t stage_s = (uint32_t)__cvta_generic_to_shared(stage);
+  auto issue = [&](uint32_t k) {
 #pragma unroll
-    for (int q = 5; q < W; q++) pfix *= spwm[q * 4 + ((tile >> (2 * (q - 5))) & 3u)];
-    const uint64_t id0 = ((uint64_t)tile << 10) + lane;
-    double a2[2] = {0, 0}, a3[4] = {0, 0, 0, 0}, a4[4] = {0, 0, 0, 0};
-    // The 32 ids of a lane are read in four batches of 8 (count and background probability of every id, unconditionally),
-    // the loads of the next batch issued before the arithmetic of the current one: at W >= 12 the tables live in HBM and
-    // a load -> test -> dependent load chain per id left the kernel latency-bound (ncu: long scoreboard 32 stalls per
-    // issue, FP64 pipe 9 %, DRAM 2 %).
-    uint64_t cn[2][8];
-    double bn[2][8];
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      cn[0][k] = __ldg(counts + id0 + 32 * k);
-      bn[0][k] = __ldg(bg + id0 + 32 * k);
-    }
-#pragma unroll
-    for (int g = 0; g < 4; g++) {
-      if (g < 3) {
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-          cn[(g + 1) & 1][k] = __ldg(counts + id0 + 32 * (8 * (g + 1) + k));
-          bn[(g + 1) & 1][k] = __ldg(bg + id0 + 32 * (8 * (g + 1) + k));
-        }
-      }
-      // A batch whose 256 ids are all empty (the usual case in a sparse long-k-mer table) is skipped by the whole warp;
-      // otherwise all 8 terms are evaluated without a per-id branch, so that the 8 dependent FP64 chains (3 multiplies,
-      // the division's Newton steps) overlap.
-      uint64_t any = 0;
-#pragma unroll
-      for (int k = 0; k < 8; k++) any |= cn[g & 1][k];
-      if (__any_sync(0xffffffffu, any != 0)) {
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-          const int j = 8 * g + k;
-          const double prob = pfix * p2[j & 1] * p3[(j >> 1) & 3] * p4[(j >> 3) & 3];
-          const double sb = saturation * bn[g & 1][k];
-          // an empty bin contributes 0; its quotient is formed with numerator count 1 because a zero numerator sends the
-          // FP64 division to its slow path (subroutine call), which at 50 % empty bins doubled the kernel time
-          const uint64_t cnt = cn[g & 1][k];
-          const double q = ((double)(cnt | (uint64_t)(cnt == 0)) * saturation) * prob / (prob + sb);
-          const double term = cnt ? q : 0.0;
-          a2[j & 1] += term;
-          a3[(j >> 1) & 3] += term;
-          a4[(j >> 3) & 3] += term;
-        }
+    for (int j = 0; j < 2; j++) {
+      if (k < ld_n[j]) {
+        const int lr = (t >> 4) + 16 * j;
+        const double2* src = pairs + (((uint64_t)ld_lo[j] << EM_UNIT_BITS) + ((uint64_t)k << 4) + (t & 15));
+        const uint32_t dst = stage_s + (uint32_t)((((k % EM_STAGES) * R + lr) * 16 + (t & 15)) * sizeof(double2));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
       }
     }
-    const double tot = a2[0] + a2[1];
-    // position 0: classes = lane bits 0-1, reduce over bits 2,3,4
-    double r0 = tot;
-    r0 += shfl_xor_d(r0, 4); r0 += shfl_xor_d(r0, 8); r0 += shfl_xor_d(r0, 16);
-    // position 1: classes = lane bits 2-3, reduce over bits 0,1,4
-    double r1 = tot;
-    r1 += shfl_xor_d(r1, 1); r1 += shfl_xor_d(r1, 2); r1 += shfl_xor_d(r1, 16);
-    // position 2: digit = (lane >> 4) | (jbit << 1): reduce over lane bits 0-3, classes = lane bit 4 x jbit
-    double r2a = a2[0], r2b = a2[1];
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  __syncthreads();  // spw complete
+  // compute role
+  const uint32_t my_lo = worker ? slot_lo(s0 + r) : 0u;
+  const uint32_t my_n = live ? ((slot_lo(s0 + r + 1) - my_lo) << 4) : 0u;
+  double pw0[4], pw1[4], acc0[4] = {0, 0, 0, 0}, acc1[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int o = 1; o < 16; o <<= 1) { r2a += shfl_xor_d(r2a, o); r2b += shfl_xor_d(r2b, o); }
-    // positions 3, 4 and the tile total: full warp sums
-    double r3[4], r4[4];
+  for (int a = 0; a < 4; a++) {
+    pw0[a] = live ? spw[a * P + m] : 0.0;
+    pw1[a] = live ? spw[(4 + a) * P + m] : 0.0;
+  }
+  double pre4 = 0.0, unit_total = 0.0;
+#pragma unroll 1
+  for (uint32_t k = 0; k < EM_STAGES - 1; k++) issue(k);
+#pragma unroll 1
+  for (uint32_t k = 0; k < n_steps; k++) {
+    asm volatile("cp.async.wait_group %0;" :: "n"(EM_STAGES - 2) : "memory");
+    __syncthreads();  // block k of every slot has landed; everybody is done with block k - 1, whose buffer is refilled now
+    issue(k + EM_STAGES - 1);
+    if (k < my_n) {
+      const uint32_t b = k & 15u, u = unit_begin + my_lo + (k >> 4);
+      if (b == 0) {
+        pre4 = inv_saturation;
 #pragma unroll
-    for (int a = 0; a < 4; a++) {
-      r3[a] = a3[a];
-      r4[a] = a4[a];
+        for (int q = 4; q < W; q++) pre4 *= spw[(q * 4 + ((u >> (2 * (q - 4))) & 3u)) * P + m];
+        unit_total = 0.0;
+      }
+      const uint32_t d2 = b & 3u, d3 = b >> 2;
+      const double2* src = stage + ((k % EM_STAGES) * R + r) * 16;
+      double2 v[16];
+      unsigned long long any = 0;
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) { r3[a] += shfl_xor_d(r3[a], o); r4[a] += shfl_xor_d(r4[a], o); }
+      for (int i = 0; i < 16; i++) {
+        v[i] = src[i];
+        any |= (unsigned long long)__double_as_longlong(v[i].x);
+      }
+      if (any) {  // counts are >= 0: the bit pattern is zero exactly for an empty bin
+        const double pre2 = pre4 * spw[(12 + d3) * P + m] * spw[(8 + d2) * P + m];
+        double blk = 0.0;
+#pragma unroll
+        for (int d1 = 0; d1 < 4; d1++) {
+          const unsigned long long any4 = (unsigned long long)__double_as_longlong(v[4 * d1].x) | (unsigned long long)__double_as_longlong(v[4 * d1 + 1].x) |
+                                          (unsigned long long)__double_as_longlong(v[4 * d1 + 2].x) | (unsigned long long)__double_as_longlong(v[4 * d1 + 3].x);
+          if (any4) {
+            const double p1 = pre2 * pw1[d1];
+            double tt[4];
+#pragma unroll
+            for (int d0 = 0; d0 < 4; d0++) {
+              const double prob = p1 * pw0[d0];
+              const double2 cb = v[4 * d1 + d0];
+              tt[d0] = (cb.x * prob) * em_rcp(prob + cb.y);
+              acc0[d0] += tt[d0];
+            }
+            const double g = (tt[0] + tt[1]) + (tt[2] + tt[3]);
+            acc1[d1] += g;
+            blk += g;
+          }
+        }
+        sacc[(8 + d2) * EM_NT + t] += blk;
+        sacc[(12 + d3) * EM_NT + t] += blk;
+        unit_total += blk;
+      }
+      if (b == 15u) {
+#pragma unroll
+        for (int q = 4; q < W; q++) sacc[(q * 4 + ((u >> (2 * (q - 4))) & 3u)) * EM_NT + t] += unit_total;
+      }
     }
-    const double all = r3[0] + r3[1] + r3[2] + r3[3];
-    double* acc = sacc[warp];
-    if (lane < 4) acc[lane] += r0;                      // position 0, digit = lane
-    if ((lane & 0x13) == 0) acc[4 + (lane >> 2)] += r1; // position 1, digit = lane >> 2 (lanes 0,4,8,12)
-    if ((lane & 15) == 0) {                             // lanes 0 and 16: position 2
-      acc[8 + (lane >> 4)] += r2a;
-      acc[8 + (lane >> 4) + 2] += r2b;
-    }
-    if (lane == 1) {
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
-      for (int a = 0; a < 4; a++) { acc[12 + a] += r3[a]; acc[16 + a] += r4[a]; }
-    }
-    if (lane == 2) {
-#pragma unroll
-      for (int q = 5; q < W; q++) acc[q * 4 + ((tile >> (2 * (q - 5))) & 3u)] += all;
-    }
-    __syncwarp();
+  for (int a = 0; a < 4; a++) {
+    sacc[a * EM_NT + t] = acc0[a];
+    sacc[(4 + a) * EM_NT + t] = acc1[a];
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < W * 4; i += blockDim.x) {
-    double s = 0;
-#pragma unroll
-    for (int w = 0; w < EM_WARPS; w++) s += sacc[w][i];
-    partials[((size_t)m * gridDim.x + blockIdx.x) * (W * 4) + i] = s;
+  for (int i = t; i < P * WA; i += EM_NT) {
+    const int mm = i / WA, e = i - mm * WA;
+    double sum = 0.0;
+    for (int rr = 0; rr < R; rr++) sum += sacc[e * EM_NT + rr * P + mm];
+    partials[((size_t)mm * nbx + blockIdx.x) * WA + e] = sum;
   }
 }
 
@@ -1488,6 +1563,39 @@ __global__ void k_em_update_f64(const double* __restrict__ acc, double* __restri
     active[m] = still;
     if (still) atomicAdd(n_active, 1);
   }
+}
+
+// single-GPU iteration tail: k_em_reduce + k_em_update_f64 in one launch (one block per PWM)
+__global__ void __launch_bounds__(64) k_em_reduce_update(const double* __restrict__ partials, int nbx, double* __restrict__ acc,
+                                                         double* __restrict__ old_pwm, double* __restrict__ change,
+                                                         int* __restrict__ iters, int* __restrict__ active, int W, double threshold,
+                                                         int max_iterations, int* __restrict__ n_active) {
+  const int m = blockIdx.x, i = threadIdx.x, WA = W * 4;
+  if (!active[m]) return;
+  __shared__ double sh[PENG_MAX_W * 4];
+  if (i < WA) {
+    double s = 0;
+    for (int b = 0; b < nbx; b++) s += partials[((size_t)m * nbx + b) * WA + i];
+    sh[i] = s;
+    acc[(size_t)m * WA + i] = s;
+  }
+  __syncthreads();
+  if (i != 0) return;
+  double ch = 0;
+  for (int p = 0; p < W; p++) {
+    double s = 0;
+    for (int a = 0; a < 4; a++) s += sh[p * 4 + a];
+    for (int a = 0; a < 4; a++) {
+      const double nv = sh[p * 4 + a] / s;
+      ch += fabs(nv - old_pwm[(size_t)m * WA + p * 4 + a]);
+      old_pwm[(size_t)m * WA + p * 4 + a] = nv;
+    }
+  }
+  change[m] = ch;
+  iters[m] += 1;
+  const int still = !(ch <= threshold || iters[m] >= max_iterations);
+  active[m] = still;
+  if (still) atomicAdd(n_active, 1);
 }
 
 __global__ void k_em_init(double* __restrict__ change, int* __restrict__ iters, int* __restrict__ active, int n, int W,
@@ -1651,6 +1759,7 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
   if (const char* e = getenv("PENG_INGEST_MODE")) h->ingest_mode = !strcmp(e, "raw") ? 1 : !strcmp(e, "packed") ? 2 : 0;
   if (const char* e = getenv("PENG_HOST_PACK_FRACTION")) h->ingest_fraction = atof(e);
   if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
+  h->select_on_host = getenv("PENG_SELECT_HOST") != nullptr;
   *out = h;
   return PENG_OK;
 }
@@ -1664,6 +1773,7 @@ static void free_tables(peng_handle_t h) {
 static void free_em(peng_handle_t h) {
   dev_free(&h->em.d_old); dev_free(&h->em.d_acc); dev_free(&h->em.d_part); dev_free(&h->em.d_change);
   dev_free(&h->em.d_iter); dev_free(&h->em.d_active); dev_free(&h->em.d_nactive);
+  dev_free(&h->em.d_pairs);
   h->em.open = false;
 }
 
@@ -1677,6 +1787,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   free_tables(h);
   free_em(h);
   if (h->d_scratch) cudaFree(h->d_scratch);
+  dev_free(&h->d_sel);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
   for (int i = 0; i < 2; i++) if (h->copy_ev[i]) cudaEventDestroy(h->copy_ev[i]);
   for (int i = 0; i < 2; i++) if (h->pin[i]) cudaFreeHost(h->pin[i]);
@@ -2529,22 +2640,33 @@ static int launch_count_W(peng_handle_t h, bool both) {
   while (wpc > 1 && n_words16 / wpc < (uint64_t)h->sm_count * 1024) wpc >>= 1;
   const uint64_t n_chunks = (n_words16 + wpc - 1) / wpc;
   constexpr size_t bins_bytes = (size_t)4 << (2 * W);
-  if constexpr (W <= 6) {
-    const unsigned block = 256;
-    const unsigned grid = (unsigned)std::min<uint64_t>(grid_for(n_chunks, block), (uint64_t)h->sm_count * 8);
-    if (both) k_count_smem<W, true><<<grid, block, bins_bytes, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
-    else k_count_smem<W, false><<<grid, block, bins_bytes, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
-    LAUNCH_CHECK(h);
-    return PENG_OK;
-  } else if constexpr (W == 8) {
-    const unsigned block = 512;
-    const size_t smem = bins_bytes / 2;  // 128 KB of packed 16-bit bins
-    if (both) CU(h, cudaFuncSetAttribute(k_count_smem16<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    else CU(h, cudaFuncSetAttribute(k_count_smem16<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned grid = (unsigned)std::min<uint64_t>(grid_for(n_chunks, block), (uint64_t)h->sm_count);
-    if (both) k_count_smem16<W, true><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
-    else k_count_smem16<W, false><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, n_chunks, wpc);
-    LAUNCH_CHECK(h);
+  // every launch covers at most 2^31 positions and is followed by a fold, so that no uint32 bin can wrap (few bins at
+  // small W: one bin may take a large share of a multi-Gbp set)
+  const uint64_t max_chunks_per_launch = (1ull << 31) / (16ull * wpc);
+  if constexpr (W <= 8) {
+    constexpr bool PACKED = W == 8;  // 128 KB of packed 16-bit bins
+    const unsigned block = PACKED ? 512 : 256;
+    const size_t smem = PACKED ? bins_bytes / 2 : bins_bytes;
+    if constexpr (PACKED) {
+      if (both) CU(h, cudaFuncSetAttribute(k_count_smem16<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      else CU(h, cudaFuncSetAttribute(k_count_smem16<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    for (uint64_t first = 0; first < n_chunks; first += max_chunks_per_launch) {
+      const uint64_t nc = std::min(max_chunks_per_launch, n_chunks - first);
+      const unsigned grid = (unsigned)std::min<uint64_t>(grid_for(nc, block), (uint64_t)h->sm_count * (PACKED ? 1 : 8));
+      if constexpr (PACKED) {
+        if (both) k_count_smem16<W, true><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, first, nc, wpc);
+        else k_count_smem16<W, false><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, first, nc, wpc);
+      } else {
+        if (both) k_count_smem<W, true><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, first, nc, wpc);
+        else k_count_smem<W, false><<<grid, block, smem, h->stream>>>(h->d_codes, h->d_kstart, h->d_hist32, first, nc, wpc);
+      }
+      LAUNCH_CHECK(h);
+      if (first + nc < n_chunks) {
+        k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
+        LAUNCH_CHECK(h);
+      }
+    }
     return PENG_OK;
   } else {
   if constexpr (W == 10) {
@@ -2553,7 +2675,6 @@ static int launch_count_W(peng_handle_t h, bool both) {
     if (use_partition(h, W)) return launch_count_deep<W>(h, both);
   }
   // W >= 10: global atomics; a uint32 bin cannot overflow within 2^32 positions, so split and fold
-  const uint64_t max_chunks_per_launch = (1ull << 31) / (16ull * wpc);
   for (uint64_t first = 0; first < n_chunks; first += max_chunks_per_launch) {
     const uint64_t nc = std::min(max_chunks_per_launch, n_chunks - first);
     const unsigned block = 128;
@@ -2585,6 +2706,7 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   h->n_patterns = n;
   h->counts_final = false;
   h->stats_ready = false;
+  h->counts_sliced = false;
   CU(h, cudaMemsetAsync(h->d_hist32, 0, (n + 4) * 4, h->stream));
   const bool both = strand == PENG_STRAND_BOTH;
   const bool partition = use_partition(h, W);
@@ -2678,7 +2800,10 @@ extern "C" int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot) {
   const uint64_t n = h->n_patterns;
   k_ltot_from32<<<1, 1, 0, h->stream>>>(h->d_hist32 + n, h->d_counts + n);
   LAUNCH_CHECK(h);
-  if (h->used_partition && h->strand == PENG_STRAND_BOTH) {
+  // The summed table may mix the two bin conventions (ranks choose their counting path from their own shard size: the
+  // partition paths leave fast W-mers in their forward-id bin, the others count at the canonical id): the pair fold is
+  // right for both — a canonical-only table has 0 at the partner bin — so BOTH strands always take it.
+  if (h->strand == PENG_STRAND_BOTH) {
     TRY(launch_fold_canon(h, h->W, true, true));
     h->mirrored = true;
   } else {
@@ -2687,6 +2812,44 @@ extern "C" int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot) {
   }
   h->fold_deferred = false;
   return peng_cuda_count_finish(h, ltot);
+}
+
+// Sliced finish of the 32-bit exchange (PLUS strand): the caller has reduce-scattered the uint32 table in place (this
+// rank's slice [lo, hi) of it holds the sum over the ranks) and all-reduced the ltot word; only the slice is folded into
+// the 64-bit table, and every later table pass (stats, IUPAC sums, EM) works on the slice.
+extern "C" int peng_cuda_count_finish32_sliced(peng_handle_t h, uint64_t* ltot) {
+  if (!h || !h->d_hist32 || !h->fold_deferred) return fail(h, PENG_E_INVALID, "count_finish32_sliced: no unfolded table (peng_cuda_count_local32 first)");
+  if (h->slice_parts <= 1) return fail(h, PENG_E_INVALID, "count_finish32_sliced: no table slice set (peng_cuda_set_table_slice)");
+  if (h->strand != PENG_STRAND_PLUS)
+    return fail(h, PENG_E_INVALID, "count_finish32_sliced: both strands pair ids of different slices — sum the whole table (peng_cuda_count_finish32)");
+  CU(h, cudaSetDevice(h->device));
+  const uint64_t n = h->n_patterns;
+  slice_range(h, &h->slice_lo, &h->slice_hi);
+  k_ltot_from32<<<1, 1, 0, h->stream>>>(h->d_hist32 + n, h->d_counts + n);
+  LAUNCH_CHECK(h);
+  const uint64_t ns = h->slice_hi - h->slice_lo;
+  k_fold_first<<<grid_for(ns, 256), 256, 0, h->stream>>>(h->d_hist32 + h->slice_lo, h->d_counts + h->slice_lo, ns);
+  LAUNCH_CHECK(h);
+  h->fold_deferred = false;
+  h->counts_sliced = true;
+  h->mirrored = true;  // nothing to mirror
+  return peng_cuda_count_finish(h, ltot);
+}
+
+extern "C" int peng_cuda_set_table_slice(peng_handle_t h, int part, int n_parts) {
+  if (!h || n_parts < 1 || part < 0 || part >= n_parts) return fail(h, PENG_E_INVALID, "set_table_slice: bad slice %d/%d", part, n_parts);
+  h->slice_part = part;
+  h->slice_parts = n_parts;
+  h->stats_ready = false;
+  return PENG_OK;
+}
+extern "C" int peng_cuda_table_slice(peng_handle_t h, uint64_t* lo, uint64_t* hi) {
+  if (!h || !h->n_patterns) return fail(h, PENG_E_INVALID, "table_slice: nothing counted");
+  uint64_t a, b;
+  slice_range(h, &a, &b);
+  if (lo) *lo = a;
+  if (hi) *hi = b;
+  return PENG_OK;
 }
 
 extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
@@ -2716,7 +2879,8 @@ extern "C" int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* lto
 extern "C" int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts) {
   if (!h || !h->d_counts || !h->counts_final) return fail(h, PENG_E_INVALID, "get_counts: count table not final");
   CU(h, cudaSetDevice(h->device));
-  CU(h, cudaMemcpyAsync(counts, h->d_counts, h->n_patterns * 8, cudaMemcpyDeviceToHost, h->stream));
+  // sliced count table: the slice only (out holds hi - lo elements, peng_cuda_table_slice)
+  CU(h, cudaMemcpyAsync(counts, h->d_counts + counts_lo(h), (counts_hi(h) - counts_lo(h)) * 8, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
   return PENG_OK;
 }
@@ -2725,7 +2889,7 @@ extern "C" int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uin
   if (!h || !h->d_counts || !h->counts_final || (n && (!ids || !out))) return fail(h, PENG_E_INVALID, "gather_counts: count table not final");
   if (n == 0) return PENG_OK;
   for (uint64_t i = 0; i < n; i++)
-    if (ids[i] >= h->n_patterns) return fail(h, PENG_E_INVALID, "gather_counts: id out of range");
+    if (ids[i] < counts_lo(h) || ids[i] >= counts_hi(h)) return fail(h, PENG_E_INVALID, "gather_counts: id out of range (of this rank's slice)");
   CU(h, cudaSetDevice(h->device));
   TRY(need_scratch(h, n * 16));
   uint64_t* d_ids = (uint64_t*)h->d_scratch;
@@ -2743,7 +2907,7 @@ extern "C" int peng_cuda_counts_total(peng_handle_t h, uint64_t* total) {
   CU(h, cudaSetDevice(h->device));
   TRY(need_scratch(h, 8));
   CU(h, cudaMemsetAsync(h->d_scratch, 0, 8, h->stream));
-  k_sum_u64<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_counts, h->n_patterns, (unsigned long long*)h->d_scratch);
+  k_sum_u64<<<h->sm_count * 8, 256, 0, h->stream>>>(h->d_counts + counts_lo(h), counts_hi(h) - counts_lo(h), (unsigned long long*)h->d_scratch);
   LAUNCH_CHECK(h);
   CU(h, cudaMemcpyAsync(total, h->d_scratch, 8, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
@@ -2768,6 +2932,7 @@ extern "C" int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const ui
   CU(h, cudaStreamSynchronize(h->stream));
   h->ltot = ltot;
   h->counts_final = true;
+  h->counts_sliced = false;
   h->stats_ready = false;
   return PENG_OK;
 }
@@ -2826,21 +2991,28 @@ extern "C" int peng_cuda_stats(peng_handle_t h, int K, const float* v32, const d
     return fail(h, PENG_E_INVALID, "stats: bad orders K=%d k=%d max_k=%d (W=%d)", K, k, max_k, h->W);
   if (!v32 && !v64) return fail(h, PENG_E_INVALID, "stats: no background model given");
   CU(h, cudaSetDevice(h->device));
-  const uint64_t n = h->n_patterns;
   const uint32_t nv = v_offset(K + 1);
   const int both = h->strand == PENG_STRAND_BOTH;
   const unsigned block = 256;
   free_tables(h);
+  // id-sliced tables (peng_cuda_set_table_slice): only this rank's ids are computed and kept
+  uint64_t lo, hi;
+  slice_range(h, &lo, &hi);
+  if (h->counts_sliced && (lo != h->slice_lo || hi != h->slice_hi)) return fail(h, PENG_E_INVALID, "stats: the table slice changed since the sliced count");
+  const uint64_t n = hi - lo;
+  h->tab_lo = lo;
+  h->tab_hi = hi;
   if (v32) {
     TRY(dev_alloc(h, &h->d_v32, (size_t)nv));
     CU(h, cudaMemcpyAsync(h->d_v32, v32, nv * 4, cudaMemcpyHostToDevice, h->stream));
     for (int o = 0; o <= max_k; o++) {
       TRY(dev_alloc(h, &h->d_bg32[o], n));
-      k_bgprob<float><<<grid_for(n, block), block, v_offset(o + 1) * 4, h->stream>>>(h->d_v32, h->W, o, both, h->d_bg32[o], n);
+      k_bgprob<float><<<grid_for(n, block), block, v_offset(o + 1) * 4, h->stream>>>(h->d_v32, h->W, o, both, vbase(h->d_bg32[o], lo), lo, n);
       LAUNCH_CHECK(h);
     }
     TRY(dev_alloc(h, &h->d_exp32, n)); TRY(dev_alloc(h, &h->d_z32, n)); TRY(dev_alloc(h, &h->d_logp32, n));
-    k_stats<float><<<grid_for(n, block), block, 0, h->stream>>>(h->d_counts, h->d_bg32[k], h->ltot, h->d_exp32, h->d_z32, h->d_logp32, n);
+    k_stats<float><<<grid_for(n, block), block, 0, h->stream>>>(h->d_counts, vbase(h->d_bg32[k], lo), h->ltot, vbase(h->d_exp32, lo),
+                                                                vbase(h->d_z32, lo), vbase(h->d_logp32, lo), lo, n);
     LAUNCH_CHECK(h);
   }
   if (v64) {
@@ -2848,11 +3020,12 @@ extern "C" int peng_cuda_stats(peng_handle_t h, int K, const float* v32, const d
     CU(h, cudaMemcpyAsync(h->d_v64, v64, nv * 8, cudaMemcpyHostToDevice, h->stream));
     for (int o = 0; o <= max_k; o++) {
       TRY(dev_alloc(h, &h->d_bg64[o], n));
-      k_bgprob<double><<<grid_for(n, block), block, v_offset(o + 1) * 8, h->stream>>>(h->d_v64, h->W, o, both, h->d_bg64[o], n);
+      k_bgprob<double><<<grid_for(n, block), block, v_offset(o + 1) * 8, h->stream>>>(h->d_v64, h->W, o, both, vbase(h->d_bg64[o], lo), lo, n);
       LAUNCH_CHECK(h);
     }
     TRY(dev_alloc(h, &h->d_exp64, n)); TRY(dev_alloc(h, &h->d_z64, n)); TRY(dev_alloc(h, &h->d_logp64, n));
-    k_stats<double><<<grid_for(n, block), block, 0, h->stream>>>(h->d_counts, h->d_bg64[k], h->ltot, h->d_exp64, h->d_z64, h->d_logp64, n);
+    k_stats<double><<<grid_for(n, block), block, 0, h->stream>>>(h->d_counts, vbase(h->d_bg64[k], lo), h->ltot, vbase(h->d_exp64, lo),
+                                                                 vbase(h->d_z64, lo), vbase(h->d_logp64, lo), lo, n);
     LAUNCH_CHECK(h);
   }
   CU(h, cudaStreamSynchronize(h->stream));  // v32 / v64 host buffers may go away
@@ -2882,7 +3055,7 @@ extern "C" int peng_cuda_get_table(peng_handle_t h, int table, int order, int pr
   if (!p) return fail(h, PENG_E_INVALID, "get_table: table %d order %d precision %d not available", table, order, precision);
   CU(h, cudaSetDevice(h->device));
   const size_t es = precision == PENG_F32REF ? 4 : 8;
-  CU(h, cudaMemcpyAsync(out, p, h->n_patterns * es, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaMemcpyAsync(out, p, (h->tab_hi - h->tab_lo) * es, cudaMemcpyDeviceToHost, h->stream));  // sliced tables: the slice
   CU(h, cudaStreamSynchronize(h->stream));
   return PENG_OK;
 }
@@ -2901,18 +3074,213 @@ extern "C" int peng_cuda_gather_table(peng_handle_t h, int table, int order, int
   if (!p) return fail(h, PENG_E_INVALID, "gather_table: table %d order %d precision %d not available", table, order, precision);
   if (n == 0) return PENG_OK;
   for (uint64_t i = 0; i < n; i++)
-    if (ids[i] >= h->n_patterns) return fail(h, PENG_E_INVALID, "gather_table: id out of range");
+    if (ids[i] < h->tab_lo || ids[i] >= h->tab_hi) return fail(h, PENG_E_INVALID, "gather_table: id out of range (of this rank's slice)");
   CU(h, cudaSetDevice(h->device));
   const size_t es = precision == PENG_F32REF ? 4 : 8;
   TRY(need_scratch(h, n * 8 + n * es));
   uint64_t* d_ids = (uint64_t*)h->d_scratch;
   void* d_out = (void*)(d_ids + n);
   CU(h, cudaMemcpyAsync(d_ids, ids, n * 8, cudaMemcpyHostToDevice, h->stream));
-  if (precision == PENG_F32REF) k_gather_real<float><<<grid_for(n, 256), 256, 0, h->stream>>>((const float*)p, d_ids, n, (float*)d_out);
-  else k_gather_real<double><<<grid_for(n, 256), 256, 0, h->stream>>>((const double*)p, d_ids, n, (double*)d_out);
+  if (precision == PENG_F32REF) k_gather_real<float><<<grid_for(n, 256), 256, 0, h->stream>>>(vbase((const float*)p, h->tab_lo), d_ids, n, (float*)d_out);
+  else k_gather_real<double><<<grid_for(n, 256), 256, 0, h->stream>>>(vbase((const double*)p, h->tab_lo), d_ids, n, (double*)d_out);
   LAUNCH_CHECK(h);
   CU(h, cudaMemcpyAsync(out, d_out, n * es, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
+// ---- seed selection: the top partition levels of libstdc++'s introsort on the device (host_ingest.h explains the list
+// formulation; tests/test_kernel_logic_sim.py checks it against std::__unguarded_partition_pivot) ----
+struct SelState {
+  float pivot_z;
+  uint32_t nan, total_a, total_b, m, cut;
+};
+#define SEL_NT 256
+#define SEL_PER 8
+#define SEL_BLOCK (SEL_NT * SEL_PER)
+
+__global__ void k_sel_init(uint32_t* __restrict__ order, const float* __restrict__ z, uint32_t n, SelState* __restrict__ st) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    order[i] = i;
+    const float v = z[i];
+    if (v != v) st->nan = 1u;
+  }
+}
+// std::__move_median_to_first(first, first + 1, first + n / 2, last - 1) with comp(a, b) = z[a] > z[b]
+__global__ void k_sel_pivot(uint32_t* __restrict__ order, const float* __restrict__ z, uint32_t n_cur, SelState* __restrict__ st) {
+  const uint32_t a = 1, b = n_cur / 2, c = n_cur - 1;
+  const float za = z[order[a]], zb = z[order[b]], zc = z[order[c]];
+  uint32_t sel;
+  if (za > zb) sel = zb > zc ? b : (za > zc ? c : a);
+  else sel = za > zc ? a : (zb > zc ? c : b);
+  const uint32_t t = order[0];
+  order[0] = order[sel];
+  order[sel] = t;
+  st->pivot_z = z[order[0]];
+}
+// flags of the 8 consecutive positions of a thread: bit j = position stops the left scan (A), bit 8 + j = the right scan (B)
+__device__ __forceinline__ uint32_t sel_flags(const uint32_t* __restrict__ order, const float* __restrict__ z, uint32_t n_cur, float zp,
+                                              uint32_t i0) {
+  uint32_t f = 0;
+#pragma unroll
+  for (int j = 0; j < SEL_PER; j++) {
+    const uint32_t i = i0 + j;
+    if (i >= 1 && i < n_cur) {
+      const float v = z[order[i]];
+      f |= (!(v > zp) ? 1u : 0u) << j;
+      f |= (!(zp > v) ? 1u : 0u) << (8 + j);
+    }
+  }
+  return f;
+}
+__device__ __forceinline__ uint2 sel_block_sum(uint32_t ca, uint32_t cb, uint2* warp_tot) {  // -> exclusive prefix of (ca, cb) within the CTA
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t ia = ca, ib = cb;
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t ya = __shfl_up_sync(0xffffffffu, ia, o), yb = __shfl_up_sync(0xffffffffu, ib, o);
+    if (lane >= (uint32_t)o) { ia += ya; ib += yb; }
+  }
+  if (lane == 31) warp_tot[warp] = make_uint2(ia, ib);
+  __syncthreads();
+  uint32_t oa = ia - ca, ob = ib - cb;
+  for (uint32_t w = 0; w < warp; w++) { oa += warp_tot[w].x; ob += warp_tot[w].y; }
+  return make_uint2(oa, ob);
+}
+__global__ void __launch_bounds__(SEL_NT) k_sel_flags(const uint32_t* __restrict__ order, const float* __restrict__ z, uint32_t n_cur,
+                                                      const SelState* __restrict__ st, uint32_t* __restrict__ block_a,
+                                                      uint32_t* __restrict__ block_b) {
+  __shared__ uint2 warp_tot[SEL_NT / 32];
+  const uint32_t f = sel_flags(order, z, n_cur, st->pivot_z, blockIdx.x * SEL_BLOCK + threadIdx.x * SEL_PER);
+  const uint2 off = sel_block_sum(__popc(f & 0xFFu), __popc(f >> 8), warp_tot);
+  if (threadIdx.x == SEL_NT - 1) {
+    block_a[blockIdx.x] = off.x + __popc(f & 0xFFu);
+    block_b[blockIdx.x] = off.y + __popc(f >> 8);
+  }
+}
+// exclusive scan of the per-block counts, in place (one CTA; a thread takes a contiguous run of blocks)
+__global__ void __launch_bounds__(1024) k_sel_scan(uint32_t* __restrict__ block_a, uint32_t* __restrict__ block_b, uint32_t n_blocks,
+                                                   SelState* __restrict__ st) {
+  __shared__ uint2 warp_tot[32];
+  const uint32_t per = (n_blocks + 1023) / 1024, b0 = threadIdx.x * per, b1 = min(n_blocks, b0 + per);
+  uint32_t ca = 0, cb = 0;
+  for (uint32_t b = b0; b < b1; b++) { ca += block_a[b]; cb += block_b[b]; }
+  const uint2 off = sel_block_sum(ca, cb, warp_tot);
+  uint32_t ra = off.x, rb = off.y;
+  for (uint32_t b = b0; b < b1; b++) {
+    const uint32_t va = block_a[b], vb = block_b[b];
+    block_a[b] = ra;
+    block_b[b] = rb;
+    ra += va;
+    rb += vb;
+  }
+  if (threadIdx.x == 1023) { st->total_a = ra; st->total_b = rb; }
+}
+__global__ void __launch_bounds__(SEL_NT) k_sel_compact(const uint32_t* __restrict__ order, const float* __restrict__ z, uint32_t n_cur,
+                                                        const SelState* __restrict__ st, const uint32_t* __restrict__ block_a,
+                                                        const uint32_t* __restrict__ block_b, uint32_t* __restrict__ list_a,
+                                                        uint32_t* __restrict__ list_b) {
+  __shared__ uint2 warp_tot[SEL_NT / 32];
+  const uint32_t i0 = blockIdx.x * SEL_BLOCK + threadIdx.x * SEL_PER;
+  const uint32_t f = sel_flags(order, z, n_cur, st->pivot_z, i0);
+  const uint2 off = sel_block_sum(__popc(f & 0xFFu), __popc(f >> 8), warp_tot);
+  uint32_t ra = block_a[blockIdx.x] + off.x, rb = block_b[blockIdx.x] + off.y;
+  const uint32_t last_b = st->total_b - 1u;
+#pragma unroll
+  for (int j = 0; j < SEL_PER; j++) {
+    if ((f >> j) & 1u) list_a[ra++] = i0 + j;                // ascending positions
+    if ((f >> (8 + j)) & 1u) list_b[last_b - rb++] = i0 + j;  // descending positions
+  }
+}
+// m = #{k : A[k] < B[k]} (monotone), cut = min(A[m], B[m - 1])
+__global__ void k_sel_find(const uint32_t* __restrict__ list_a, const uint32_t* __restrict__ list_b, SelState* __restrict__ st) {
+  uint32_t lo = 0, hi = min(st->total_a, st->total_b);
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (list_a[mid] < list_b[mid]) lo = mid + 1; else hi = mid;
+  }
+  uint32_t cut = 0xFFFFFFFFu;
+  if (lo < st->total_a) cut = list_a[lo];
+  if (lo >= 1) cut = min(cut, list_b[lo - 1]);
+  st->m = lo;
+  st->cut = cut;
+}
+__global__ void k_sel_swap(uint32_t* __restrict__ order, const uint32_t* __restrict__ list_a, const uint32_t* __restrict__ list_b,
+                           const SelState* __restrict__ st) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < st->m) {
+    const uint32_t i = list_a[k], j = list_b[k];
+    const uint32_t t = order[i];
+    order[i] = order[j];
+    order[j] = t;
+  }
+}
+__global__ void k_sel_pairs(const uint32_t* __restrict__ order, const float* __restrict__ z, uint32_t n, peng_host::ZId* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t id = order[i];
+    out[i] = peng_host::ZId{z[id], id};
+  }
+}
+
+struct DeviceLevelEngine {
+  peng_handle_t h;
+  uint32_t *order, *list_a, *list_b, *block_a, *block_b;
+  SelState* st;
+  int rc = PENG_OK;
+  bool nan = false;
+  int run_level(size_t n_cur, SelState* out) {
+    const uint32_t n = (uint32_t)n_cur, nb = (n + SEL_BLOCK - 1) / SEL_BLOCK;
+    k_sel_pivot<<<1, 1, 0, h->stream>>>(order, h->d_z32, n, st);
+    k_sel_flags<<<nb, SEL_NT, 0, h->stream>>>(order, h->d_z32, n, st, block_a, block_b);
+    k_sel_scan<<<1, 1024, 0, h->stream>>>(block_a, block_b, nb, st);
+    k_sel_compact<<<nb, SEL_NT, 0, h->stream>>>(order, h->d_z32, n, st, block_a, block_b, list_a, list_b);
+    k_sel_find<<<1, 1, 0, h->stream>>>(list_a, list_b, st);
+    k_sel_swap<<<grid_for(n / 2 + 1, 256), 256, 0, h->stream>>>(order, list_a, list_b, st);
+    h->launches += 5;
+    LAUNCH_CHECK(h);
+    CU(h, cudaMemcpyAsync(out, st, sizeof(SelState), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return PENG_OK;
+  }
+  size_t level(size_t n_cur, float* pivot_z) {
+    SelState s{};
+    if (rc == PENG_OK) rc = run_level(n_cur, &s);
+    if (rc != PENG_OK || s.nan) {  // stop the walk down the spine; the caller looks at rc / nan
+      nan = s.nan != 0;
+      *pivot_z = 0.f;
+      return 0;
+    }
+    *pivot_z = s.pivot_z;
+    return s.cut;
+  }
+  int run_fetch(size_t n, peng_host::ZId* out) {
+    if (n == 0) return PENG_OK;
+    TRY(need_scratch(h, n * sizeof(peng_host::ZId)));
+    k_sel_pairs<<<grid_for(n, 256), 256, 0, h->stream>>>(order, h->d_z32, (uint32_t)n, (peng_host::ZId*)h->d_scratch);
+    LAUNCH_CHECK(h);
+    CU(h, cudaMemcpyAsync(out, h->d_scratch, n * sizeof(peng_host::ZId), cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return PENG_OK;
+  }
+  void fetch(size_t n, peng_host::ZId* out) {
+    if (rc == PENG_OK && !nan) rc = run_fetch(n, out);
+  }
+};
+
+// how far down the left spine the device goes: a level costs ~6 launches + one 24-byte read-back whatever its length, the
+// host's pass over a range of n ids ~2.5 ns * n
+#define SEL_STOP_BELOW 16384
+
+static int select_host_whole_table(peng_handle_t h, float z_threshold, uint64_t count_threshold, int single_stranded,
+                                   int filter_neighbors, std::vector<uint64_t>* sel) {
+  std::vector<float> z(h->n_patterns);
+  std::vector<uint64_t> counts(h->n_patterns);
+  CU(h, cudaMemcpyAsync(z.data(), h->d_z32, h->n_patterns * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaMemcpyAsync(counts.data(), h->d_counts, h->n_patterns * 8, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  *sel = peng_host::select_base_patterns(z.data(), counts.data(), h->W, z_threshold, count_threshold, single_stranded != 0,
+                                         filter_neighbors != 0);
   return PENG_OK;
 }
 
@@ -2920,14 +3288,54 @@ extern "C" int peng_cuda_select_base_patterns(peng_handle_t h, float z_threshold
                                               int single_stranded, int filter_neighbors, uint64_t* out, uint64_t cap,
                                               uint64_t* n_selected) {
   if (!h || !h->stats_ready || !h->d_z32) return fail(h, PENG_E_INVALID, "select: float32 stats not computed");
+  if (!tables_whole(h)) return fail(h, PENG_E_INVALID, "select: needs the whole z table on one device (id-sliced tables are set)");
   CU(h, cudaSetDevice(h->device));
-  std::vector<float> z(h->n_patterns);
-  std::vector<uint64_t> counts(h->n_patterns);
-  CU(h, cudaMemcpyAsync(z.data(), h->d_z32, h->n_patterns * 4, cudaMemcpyDeviceToHost, h->stream));
-  CU(h, cudaMemcpyAsync(counts.data(), h->d_counts, h->n_patterns * 8, cudaMemcpyDeviceToHost, h->stream));
-  CU(h, cudaStreamSynchronize(h->stream));
-  std::vector<uint64_t> sel = peng_host::select_base_patterns(z.data(), counts.data(), h->W, z_threshold, count_threshold,
-                                                              single_stranded != 0, filter_neighbors != 0);
+  const uint64_t n = h->n_patterns;
+  std::vector<uint64_t> sel;
+  bool on_device = false;
+#if defined(__GLIBCXX__)
+  // the device path indexes positions with 32 bits (W <= 14) and is the pruned replay of libstdc++'s introsort
+  on_device = n > 4096 && h->W <= 14 && z_threshold == z_threshold && !h->select_on_host;
+#endif
+  if (on_device) {
+#if defined(__GLIBCXX__)
+    const uint32_t nb = (uint32_t)((n + SEL_BLOCK - 1) / SEL_BLOCK);
+    const size_t words = 3 * (size_t)n + 2 * (size_t)nb + 16;
+    if (h->sel_words < words) {
+      TRY(dev_alloc(h, &h->d_sel, words));
+      h->sel_words = words;
+    }
+    DeviceLevelEngine eng;
+    eng.h = h;
+    eng.order = h->d_sel;
+    eng.list_a = eng.order + n;
+    eng.list_b = eng.list_a + n;
+    eng.block_a = eng.list_b + n;
+    eng.block_b = eng.block_a + nb;
+    eng.st = reinterpret_cast<SelState*>(eng.block_b + nb);
+    CU(h, cudaMemsetAsync(eng.st, 0, sizeof(SelState), h->stream));
+    k_sel_init<<<grid_for(n, 256), 256, 0, h->stream>>>(eng.order, h->d_z32, (uint32_t)n, eng.st);
+    LAUNCH_CHECK(h);
+    std::vector<peng_host::ZId> lead;
+    const size_t n_lead = peng_host::sort_leading_by_levels(eng, (size_t)n, z_threshold, SEL_STOP_BELOW, &lead);
+    if (h->sel_words > ((size_t)64 << 20)) {  // long pattern lengths: give the 12 bytes per id back
+      dev_free(&h->d_sel);
+      h->sel_words = 0;
+    }
+    TRY(eng.rc);
+    if (eng.nan) {
+      on_device = false;  // a NaN z-score: std::sort's behaviour on it is only reproduced by the plain sort of the whole table
+    } else {
+      size_t k = 0;
+      while (k < n_lead && !(lead[k].z < z_threshold)) k++;
+      std::vector<uint64_t> ids(k), cnt(k);
+      for (size_t r = 0; r < k; r++) ids[r] = lead[r].id;
+      if (k) TRY(peng_cuda_gather_counts(h, ids.data(), k, cnt.data()));
+      sel = peng_host::select_walk(lead.data(), cnt.data(), k, h->W, count_threshold, single_stranded != 0, filter_neighbors != 0);
+    }
+#endif
+  }
+  if (!on_device) TRY(select_host_whole_table(h, z_threshold, count_threshold, single_stranded, filter_neighbors, &sel));
   if (n_selected) *n_selected = sel.size();
   if (out) std::copy(sel.begin(), sel.begin() + std::min<uint64_t>(cap, sel.size()), out);
   return PENG_OK;
@@ -2961,9 +3369,9 @@ extern "C" int peng_cuda_iupac_count(peng_handle_t h, const uint64_t* iupac_ids,
   TRY(iupac_masks_to_device(h, iupac_ids, n, &d_masks, (size_t)n * 8, &extra));
   unsigned long long* d_out = (unsigned long long*)extra;
   if (h->strand == PENG_STRAND_BOTH)
-    k_iupac_any<float, true, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_out, nullptr, nullptr);
+    k_iupac_any<float, true, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_out, nullptr, nullptr, counts_lo(h), counts_hi(h));
   else
-    k_iupac_any<float, false, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_out, nullptr, nullptr);
+    k_iupac_any<float, false, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_out, nullptr, nullptr, counts_lo(h), counts_hi(h));
   LAUNCH_CHECK(h);
   CU(h, cudaMemcpyAsync(counts_out, d_out, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
@@ -2986,8 +3394,9 @@ extern "C" int peng_cuda_iupac_aggregate(peng_handle_t h, const uint64_t* iupac_
     unsigned long long* d_n = (unsigned long long*)extra;
     double* d_b = (double*)(extra + (size_t)n * 8);
     double* d_e = (double*)(extra + (size_t)n * 16);
-    if (both) k_iupac_any<double, true, true><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, h->d_bg64[k], h->d_exp64, d_n, d_b, d_e);
-    else k_iupac_any<double, false, true><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, h->d_bg64[k], h->d_exp64, d_n, d_b, d_e);
+    // id-sliced tables: the sums over this rank's ids (the caller adds the ranks' partial sums)
+    if (both) k_iupac_any<double, true, true><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, vbase(h->d_bg64[k], h->tab_lo), vbase(h->d_exp64, h->tab_lo), d_n, d_b, d_e, h->tab_lo, h->tab_hi);
+    else k_iupac_any<double, false, true><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, vbase(h->d_bg64[k], h->tab_lo), vbase(h->d_exp64, h->tab_lo), d_n, d_b, d_e, h->tab_lo, h->tab_hi);
     LAUNCH_CHECK(h);
     CU(h, cudaMemcpyAsync(n_sites, d_n, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaMemcpyAsync(bg_p, d_b, (size_t)n * 8, cudaMemcpyDeviceToHost, h->stream));
@@ -2996,6 +3405,7 @@ extern "C" int peng_cuda_iupac_aggregate(peng_handle_t h, const uint64_t* iupac_
     return PENG_OK;
   }
   if (!h->d_bg32[k]) return fail(h, PENG_E_INVALID, "iupac_aggregate: float32 tables not computed");
+  if (!tables_whole(h)) return fail(h, PENG_E_INVALID, "iupac_aggregate: the float32 arm adds in the reference's order and needs whole tables (id-sliced tables: PENG_F64)");
   const size_t bm_words = h->W >= 3 ? ((size_t)1 << (2 * h->W - 5)) : 1;
   const size_t out_bytes = (size_t)n * 16;
   const size_t bm_bytes = both ? (size_t)n * bm_words * 4 : 0;
@@ -3005,12 +3415,12 @@ extern "C" int peng_cuda_iupac_aggregate(peng_handle_t h, const uint64_t* iupac_
   float* d_e = (float*)(extra + (size_t)n * 12);
   uint32_t* d_bm = (uint32_t*)(extra + ((out_bytes + 255) & ~(size_t)255));
   if (both) {
-    k_iupac_any<float, true, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_n, nullptr, nullptr);
+    k_iupac_any<float, true, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_n, nullptr, nullptr, 0, h->n_patterns);
     LAUNCH_CHECK(h);
     k_iupac_f32_both<<<n, IUPAC_TILE_WORDS, 0, h->stream>>>(d_masks, h->W, h->d_bg32[k], h->d_exp32, d_bm, d_b, d_e);
     LAUNCH_CHECK(h);
   } else {
-    k_iupac_any<float, false, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_n, nullptr, nullptr);
+    k_iupac_any<float, false, false><<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_counts, nullptr, nullptr, d_n, nullptr, nullptr, 0, h->n_patterns);
     LAUNCH_CHECK(h);
     k_iupac_f32_plus<<<n, 256, 0, h->stream>>>(d_masks, h->W, h->d_bg32[k], h->d_exp32, d_b, d_e);
     LAUNCH_CHECK(h);
@@ -3025,10 +3435,30 @@ extern "C" int peng_cuda_iupac_aggregate(peng_handle_t h, const uint64_t* iupac_
 // =====================================================================================================
 // C ABI: EM
 // =====================================================================================================
+// geometry of k_em_accumulate_all for a group of P PWMs
+struct EmGeom {
+  int R;
+  unsigned grid;
+  size_t smem;
+};
+static EmGeom em_geom(peng_handle_t h, int P, uint32_t n_units) {
+  EmGeom g;
+  g.R = std::max(1, std::min(EM_MAX_R, EM_NT / P));
+  g.grid = (unsigned)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)h->sm_count, (n_units + g.R - 1) / g.R));
+  g.smem = (size_t)EM_STAGES * g.R * 16 * sizeof(double2) + (size_t)h->W * 4 * P * 8 + (size_t)h->W * 4 * EM_NT * 8;
+  return g;
+}
 template <int W>
-static void launch_em_acc(peng_handle_t h, dim3 grid, const double* bg, uint32_t tb, uint32_t te) {
-  k_em_accumulate_f64<W><<<grid, EM_WARPS * 32, 0, h->stream>>>(h->d_counts, bg, h->em.d_old, h->em.d_active, h->em.sat, tb,
-                                                               te, h->em.d_part);
+static int launch_em_acc(peng_handle_t h, int first, int P, uint32_t ub, uint32_t ue) {
+  auto& E = h->em;
+  const EmGeom g = em_geom(h, P, ue - ub);
+  auto kern = k_em_accumulate_all<W>;
+  CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+  const int WA = W * 4;
+  kern<<<g.grid, EM_NT, g.smem, h->stream>>>(E.d_pairs, E.d_old + (size_t)first * WA, E.d_active + first, P, g.R, 1.0 / E.sat, ub, ue,
+                                           E.d_part + (size_t)first * E.nbx * WA, E.nbx);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
 }
 
 extern "C" int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm_in, double saturation, double threshold,
@@ -3036,20 +3466,31 @@ extern "C" int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm
   if (!h || !h->stats_ready || !pwm_in || n_pwms <= 0) return fail(h, PENG_E_INVALID, "em: bad call (stats must be computed first)");
   if (bg_order < 0 || bg_order > h->max_k || !h->d_bg64[bg_order]) return fail(h, PENG_E_INVALID, "em: FP64 bgprob of order %d not available", bg_order);
   if (n_parts < 1 || part < 0 || part >= n_parts) return fail(h, PENG_E_INVALID, "em: bad partition %d/%d", part, n_parts);
+  if (!tables_whole(h)) {  // id-sliced tables: the EM slice is the table slice
+    if (part != h->slice_part || n_parts != h->slice_parts) return fail(h, PENG_E_INVALID, "em: partition %d/%d is not this rank's table slice %d/%d", part, n_parts, h->slice_part, h->slice_parts);
+    if (h->W < 6) return fail(h, PENG_E_INVALID, "em: id-sliced tables need W >= 6");
+  }
   CU(h, cudaSetDevice(h->device));
   free_em(h);
   auto& E = h->em;
   const int WA = h->W * 4;
   E.n = n_pwms; E.max_it = max_iterations; E.order = bg_order; E.part = part; E.n_parts = n_parts;
   E.sat = saturation; E.thr = threshold;
+  E.nbx = 1;
   if (h->W >= 6) {
+    // this rank's slice of the id range, in tiles of 1024 ids (= 4 units)
     const uint32_t n_tiles = (uint32_t)(h->n_patterns >> 10);
-    const uint32_t my_tiles = std::max<uint32_t>(1, n_tiles / n_parts);
-    uint32_t nbx = (my_tiles + EM_WARPS - 1) / EM_WARPS;
-    const uint32_t want = std::max<uint32_t>(1, (uint32_t)(h->sm_count * 4 + n_pwms - 1) / n_pwms);
-    E.nbx = (int)std::max<uint32_t>(1, std::min(nbx, want));
-  } else {
-    E.nbx = 1;
+    E.ub = 4u * (uint32_t)((uint64_t)n_tiles * part / n_parts);
+    E.ue = 4u * (uint32_t)((uint64_t)n_tiles * (part + 1) / n_parts);
+    E.nbx = (int)em_geom(h, std::min(n_pwms, EM_MAX_GROUP), E.ue - E.ub).grid;  // the largest grid of any group
+    for (int first = 0; first < n_pwms; first += EM_MAX_GROUP)
+      E.nbx = std::max(E.nbx, (int)em_geom(h, std::min(EM_MAX_GROUP, n_pwms - first), E.ue - E.ub).grid);
+    const uint64_t n_ids = (uint64_t)(E.ue - E.ub) << EM_UNIT_BITS;
+    TRY(dev_alloc(h, &E.d_pairs, (size_t)std::max<uint64_t>(n_ids, 1)));
+    if (n_ids) {
+      k_em_pairs<<<grid_for(n_ids, 256), 256, 0, h->stream>>>(h->d_counts, vbase(h->d_bg64[bg_order], h->tab_lo), (uint64_t)E.ub << EM_UNIT_BITS, n_ids, E.d_pairs);
+      LAUNCH_CHECK(h);
+    }
   }
   TRY(dev_alloc(h, &E.d_old, (size_t)n_pwms * WA));
   TRY(dev_alloc(h, &E.d_acc, (size_t)n_pwms * WA));
@@ -3060,6 +3501,7 @@ extern "C" int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm
   TRY(dev_alloc(h, &E.d_nactive, (size_t)1));
   CU(h, cudaMemcpyAsync(E.d_old, pwm_in, (size_t)n_pwms * WA * 8, cudaMemcpyHostToDevice, h->stream));
   CU(h, cudaMemsetAsync(E.d_acc, 0, (size_t)n_pwms * WA * 8, h->stream));
+  CU(h, cudaMemsetAsync(E.d_part, 0, (size_t)n_pwms * WA * E.nbx * 8, h->stream));  // groups with a smaller grid leave rows unwritten
   k_em_init<<<grid_for(n_pwms, 64), 64, 0, h->stream>>>(E.d_change, E.d_iter, E.d_active, n_pwms, h->W, threshold, max_iterations);
   LAUNCH_CHECK(h);
   CU(h, cudaStreamSynchronize(h->stream));
@@ -3068,33 +3510,38 @@ extern "C" int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm
   return PENG_OK;
 }
 
+// the per-CTA partial rows of one iteration (everything of peng_cuda_em_accumulate but the final reduction)
+static int em_accumulate_partials(peng_handle_t h) {
+  auto& E = h->em;
+  if (h->W >= 6) {
+    for (int first = 0; first < E.n; first += EM_MAX_GROUP) {
+      const int P = std::min(EM_MAX_GROUP, E.n - first);
+      int rc = PENG_OK;
+      switch (h->W) {
+        case 6: rc = launch_em_acc<6>(h, first, P, E.ub, E.ue); break;
+        case 8: rc = launch_em_acc<8>(h, first, P, E.ub, E.ue); break;
+        case 10: rc = launch_em_acc<10>(h, first, P, E.ub, E.ue); break;
+        case 12: rc = launch_em_acc<12>(h, first, P, E.ub, E.ue); break;
+        case 14: rc = launch_em_acc<14>(h, first, P, E.ub, E.ue); break;
+        case 16: rc = launch_em_acc<16>(h, first, P, E.ub, E.ue); break;
+      }
+      TRY(rc);
+    }
+  } else {
+    const uint32_t n = (uint32_t)h->n_patterns;
+    const uint32_t ib = (uint32_t)((uint64_t)n * E.part / E.n_parts), ie = (uint32_t)((uint64_t)n * (E.part + 1) / E.n_parts);
+    k_em_accumulate_small<<<E.n, 64, 0, h->stream>>>(h->d_counts, h->d_bg64[E.order], E.d_old, E.d_active, h->W, E.sat, ib, ie, E.d_part);
+    LAUNCH_CHECK(h);
+  }
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_em_accumulate(peng_handle_t h) {
   if (!h || !h->em.open) return fail(h, PENG_E_INVALID, "em_accumulate: no EM session");
   CU(h, cudaSetDevice(h->device));
   auto& E = h->em;
-  const double* bg = h->d_bg64[E.order];
-  const int WA = h->W * 4;
-  if (h->W >= 6) {
-    const uint32_t n_tiles = (uint32_t)(h->n_patterns >> 10);
-    const uint32_t tb = (uint32_t)((uint64_t)n_tiles * E.part / E.n_parts);
-    const uint32_t te = (uint32_t)((uint64_t)n_tiles * (E.part + 1) / E.n_parts);
-    dim3 grid(E.nbx, E.n);
-    switch (h->W) {
-      case 6: launch_em_acc<6>(h, grid, bg, tb, te); break;
-      case 8: launch_em_acc<8>(h, grid, bg, tb, te); break;
-      case 10: launch_em_acc<10>(h, grid, bg, tb, te); break;
-      case 12: launch_em_acc<12>(h, grid, bg, tb, te); break;
-      case 14: launch_em_acc<14>(h, grid, bg, tb, te); break;
-      case 16: launch_em_acc<16>(h, grid, bg, tb, te); break;
-    }
-    LAUNCH_CHECK(h);
-  } else {
-    const uint32_t n = (uint32_t)h->n_patterns;
-    const uint32_t ib = (uint32_t)((uint64_t)n * E.part / E.n_parts), ie = (uint32_t)((uint64_t)n * (E.part + 1) / E.n_parts);
-    k_em_accumulate_small<<<E.n, 64, 0, h->stream>>>(h->d_counts, bg, E.d_old, E.d_active, h->W, E.sat, ib, ie, E.d_part);
-    LAUNCH_CHECK(h);
-  }
-  k_em_reduce<<<E.n, 64, 0, h->stream>>>(E.d_part, E.d_active, E.nbx, WA, E.d_acc);
+  TRY(em_accumulate_partials(h));
+  k_em_reduce<<<E.n, 64, 0, h->stream>>>(E.d_part, E.d_active, E.nbx, h->W * 4, E.d_acc);
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
@@ -3130,6 +3577,7 @@ extern "C" int peng_cuda_em_end(peng_handle_t h, double* pwm_out, int* iteration
 static int em_f32ref(peng_handle_t h, int n_pwms, const float* pwm_in, float saturation, float threshold, int max_iterations,
                      int bg_order, float* pwm_out, int* iterations_out) {
   if (!h->d_bg32[bg_order]) return fail(h, PENG_E_INVALID, "em: float32 bgprob of order %d not available", bg_order);
+  if (!tables_whole(h)) return fail(h, PENG_E_INVALID, "em: the float32 arm adds in the reference's order and needs whole tables (id-sliced tables: PENG_F64)");
   const int W = h->W, WA = W * 4;
   const uint64_t n = h->n_patterns;
   // terms buffer: n floats per PWM; batch the PWMs if that would exceed ~8 GB
@@ -3186,12 +3634,22 @@ extern "C" int peng_cuda_em(peng_handle_t h, int n_pwms, const void* pwm_in, int
   if (precision == PENG_F32REF)
     return em_f32ref(h, n_pwms, (const float*)pwm_in, (float)saturation, (float)threshold, max_iterations, bg_order,
                      (float*)pwm_out, iterations_out);
+  if (!tables_whole(h))
+    return fail(h, PENG_E_INVALID, "em: id-sliced tables — run peng_cuda_em_begin / _em_accumulate / (sum over the ranks) / _em_update on every rank");
   TRY(peng_cuda_em_begin(h, n_pwms, (const double*)pwm_in, saturation, threshold, max_iterations, bg_order, 0, 1, nullptr));
+  auto& E = h->em;
   for (int it = 0; it < max_iterations; it++) {
-    TRY(peng_cuda_em_accumulate(h));
-    int na = -1;
-    TRY(peng_cuda_em_update(h, (it & 3) == 3 ? &na : nullptr));  // sync on the convergence flags every 4th iteration
-    if (na == 0) break;
+    TRY(em_accumulate_partials(h));
+    CU(h, cudaMemsetAsync(E.d_nactive, 0, 4, h->stream));
+    k_em_reduce_update<<<E.n, 64, 0, h->stream>>>(E.d_part, E.nbx, E.d_acc, E.d_old, E.d_change, E.d_iter, E.d_active, h->W, E.thr,
+                                                  E.max_it, E.d_nactive);
+    LAUNCH_CHECK(h);
+    if ((it & 3) == 3) {  // look at the convergence flags every 4th iteration only (converged PWMs cost nothing meanwhile)
+      int na = -1;
+      CU(h, cudaMemcpyAsync(&na, E.d_nactive, 4, cudaMemcpyDeviceToHost, h->stream));
+      CU(h, cudaStreamSynchronize(h->stream));
+      if (na == 0) break;
+    }
   }
   return peng_cuda_em_end(h, (double*)pwm_out, iterations_out);
 }

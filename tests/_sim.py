@@ -236,3 +236,23 @@ def sort_leading(z, threshold):
     lib.sim_sort_leading.restype = C.c_uint64
     lead = lib.sim_sort_leading(_p(z, f32p), C.c_uint64(len(z)), C.c_float(threshold), _p(a, u64p), _p(b, u64p))
     return int(lead), a, b
+
+
+def partition_level_agrees(z):
+    """host_ingest.h: partition_level_lists (the device's list formulation of a partition pass) == libstdc++'s pass"""
+    z = np.ascontiguousarray(z, np.float32)
+    lib.sim_partition_level_agrees.restype = C.c_int
+    return bool(lib.sim_partition_level_agrees(_p(z, f32p), C.c_uint64(len(z))))
+
+
+def select_levels(z, counts, W, z_threshold=10.0, count_threshold=3, single_stranded=False, filter_neighbors=True, stop_below=64):
+    """host_ingest.h: sort_leading_by_levels + select_walk with a host engine -> (selected ids, partition levels run)"""
+    z = np.ascontiguousarray(z, np.float32)
+    counts = np.ascontiguousarray(counts, np.uint64)
+    out = np.zeros(len(z), np.uint64)
+    lv = C.c_uint64()
+    lib.sim_select_levels.restype = C.c_uint64
+    n = lib.sim_select_levels(_p(z, f32p), _p(counts, u64p), C.c_int(W), C.c_float(z_threshold), C.c_uint64(count_threshold),
+                              C.c_int(int(single_stranded)), C.c_int(int(filter_neighbors)), C.c_uint64(stop_below), _p(out, u64p),
+                              C.c_uint64(len(out)), C.byref(lv))
+    return out[:n].copy(), lv.value

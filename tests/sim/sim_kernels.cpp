@@ -366,6 +366,59 @@ uint64_t sim_sort_leading(const float* z, uint64_t n, float threshold, uint64_t*
 }
 }
 
+// ---- seed selection through partition levels in the device's list formulation (host_ingest.h: sort_leading_by_levels with a
+// host engine that runs partition_level_lists) ----
+struct HostLevelEngine {
+  std::vector<uint32_t> order;
+  const float* z;
+  size_t levels = 0;
+  size_t level(size_t n_cur, float* pivot_z) {
+    levels++;
+    return peng_host::partition_level_lists(order.data(), z, n_cur, pivot_z);
+  }
+  void fetch(size_t n, peng_host::ZId* out) {
+    for (size_t i = 0; i < n; i++) out[i] = peng_host::ZId{z[order[i]], order[i]};
+  }
+};
+extern "C" {
+// one pass: list formulation vs std::__unguarded_partition_pivot on the same array; returns 1 when cut and arrays agree
+int sim_partition_level_agrees(const float* z, uint64_t n) {
+  std::vector<uint32_t> a(n);
+  std::vector<size_t> b(n);
+  for (size_t i = 0; i < n; i++) a[i] = (uint32_t)i, b[i] = i;
+  // a few nested levels on the shrinking left part, as the device runs them
+  size_t na = n;
+  while (na > 16) {
+    float pz;
+    const size_t cut_a = peng_host::partition_level_lists(a.data(), z, na, &pz);
+    auto comp = __gnu_cxx::__ops::__iter_comp_iter(peng_host::ByZDescending{z});
+    size_t* cut_b = std::__unguarded_partition_pivot(b.data(), b.data() + na, comp);
+    if ((size_t)(cut_b - b.data()) != cut_a || pz != z[b[0]]) return 0;
+    for (size_t i = 0; i < na; i++) if (a[i] != b[i]) return 0;
+    na = cut_a;
+  }
+  return 1;
+}
+uint64_t sim_select_levels(const float* z, const uint64_t* counts, int W, float z_threshold, uint64_t count_threshold, int single_stranded,
+                           int filter_neighbors, uint64_t stop_below, uint64_t* out, uint64_t cap, uint64_t* levels) {
+  const size_t n = (size_t)1 << (2 * W);
+  HostLevelEngine eng;
+  eng.order.resize(n);
+  for (size_t i = 0; i < n; i++) eng.order[i] = (uint32_t)i;
+  eng.z = z;
+  std::vector<peng_host::ZId> lead;
+  const size_t n_lead = peng_host::sort_leading_by_levels(eng, n, z_threshold, stop_below, &lead);
+  size_t k = 0;
+  while (k < n_lead && !(lead[k].z < z_threshold)) k++;
+  std::vector<uint64_t> c(k);
+  for (size_t r = 0; r < k; r++) c[r] = counts[lead[r].id];
+  std::vector<uint64_t> sel = peng_host::select_walk(lead.data(), c.data(), k, W, count_threshold, single_stranded != 0, filter_neighbors != 0);
+  for (size_t i = 0; i < sel.size() && i < cap; i++) out[i] = sel[i];
+  if (levels) *levels = eng.levels;
+  return sel.size();
+}
+}
+
 // ---- host half of the packed ingest (host_pack.cpp): all phases into one host image of the device arrays ----------------
 #include "../../peng-motif_b200/csrc/host_pack.cpp"
 extern "C" {

@@ -140,10 +140,14 @@ def test_composition_skew_at_scale(gpu, pkg):
     assert gpu.count(10, 1) == lt and np.array_equal(gpu.get_counts(), ref)
 
 
-@pytest.mark.parametrize("W_,both,n", [(10, True, 40_000), (10, False, 40_000), (8, True, 4_000), (12, True, 4_000), (14, False, 100_000)])
-def test_sharded_sum32_matches_whole(gpu, pkg, W_, both, n):
+@pytest.mark.parametrize("shard_path", [0, 2], ids=["auto", "partition"])
+@pytest.mark.parametrize("W_,both,n", [(10, True, 40_000), (10, False, 40_000), (8, True, 4_000), (12, True, 4_000), (12, False, 4_000),
+                                       (14, True, 100_000), (14, False, 100_000)])
+def test_sharded_sum32_matches_whole(gpu, pkg, W_, both, n, shard_path):
     """The 32-bit exchange: unfolded uint32 tables (+ ltot in word 4^W) of 4 shards summed as the all-reduce would, written
-    back, folded once by count_finish32 — equals the whole-set table, on the partition paths and on the L2-atomic path."""
+    back, folded once by count_finish32 — equals the whole-set table.  shard_path 0: the shards are small and take the
+    L2-atomic / shared-memory kernels (canonical bins); shard_path 2: the shards are FORCED onto the partition / deep
+    partition paths (fast W-mers in their forward-id bin), the combination bench.py times at N > 1."""
     import torch
 
     gpu.set_count_path(0)
@@ -152,15 +156,52 @@ def test_sharded_sum32_matches_whole(gpu, pkg, W_, both, n):
     ids = np.random.RandomState(1).randint(0, 4 ** W_, 1 << 16, dtype=np.int64).astype(np.uint64)
     whole, total = gpu.gather_counts(ids), gpu.counts_total()
     acc = None
-    for r in range(4):
-        gpu.ingest_synthetic(n // 4, 200, 7, r * (n // 4), "TGCTGASTCAGCA", 0.3, 0.01)
-        gpu.count_local32(W_, int(both))
-        gpu.synchronize()  # the handle works on its own stream, torch on another
-        buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
-        acc = buf.clone() if acc is None else acc + buf
-        with pytest.raises(pkg.PengCudaError):
-            gpu.count_finish()  # the 64-bit finish must refuse an unfolded table
+    gpu.set_count_path(shard_path)
+    try:
+        for r in range(4):
+            gpu.ingest_synthetic(n // 4, 200, 7, r * (n // 4), "TGCTGASTCAGCA", 0.3, 0.01)
+            gpu.count_local32(W_, int(both))
+            if shard_path == 2:
+                assert gpu.last_count_path == (2 if W_ >= 10 else 1)
+            gpu.synchronize()  # the handle works on its own stream, torch on another
+            buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
+            acc = buf.clone() if acc is None else acc + buf
+            with pytest.raises(pkg.PengCudaError):
+                gpu.count_finish()  # the 64-bit finish must refuse an unfolded table
+    finally:
+        gpu.set_count_path(0)
     buf.copy_(acc)  # what the all-reduce leaves on every rank
     torch.cuda.synchronize()
     assert gpu.count_finish32() == ltot
     assert np.array_equal(gpu.gather_counts(ids), whole) and gpu.counts_total() == total
+
+
+@pytest.mark.parametrize("W_,last_on_partition", [(10, False), (10, True), (12, False), (12, True)])
+def test_sum32_of_mixed_paths(gpu, pkg, W_, last_on_partition):
+    """Ranks choose their counting path from their OWN shard size, so base-balanced shards that straddle a threshold mix
+    the two bin conventions in one summed table (partition paths: fast W-mers in the forward-id bin; L2 / shared-memory
+    kernels: everything in the canonical bin).  count_finish32 must fold such a sum correctly whichever path the
+    finishing rank took itself: one partition-path shard + one L2-path shard, BOTH strands, against the oracle."""
+    import torch
+
+    n = 6_000
+    gpu.ingest_synthetic(2 * n, 200, 21, 0, "TGCTGASTCAGCA", 0.3, 0.01)
+    codes, offs = gpu.export_codes()
+    ref, lt = O.count(codes, offs, W_, True)
+    order = [(0, 2), (1, 1)] if not last_on_partition else [(1, 1), (0, 2)]  # (shard, path); the last one finishes
+    acc = None
+    try:
+        for shard, path in order:
+            gpu.set_count_path(path)
+            gpu.ingest_synthetic(n, 200, 21, shard * n, "TGCTGASTCAGCA", 0.3, 0.01)
+            gpu.count_local32(W_, pkg.STRAND_BOTH)
+            assert gpu.last_count_path == path
+            gpu.synchronize()
+            buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
+            acc = buf.clone() if acc is None else acc + buf
+    finally:
+        gpu.set_count_path(0)
+    buf.copy_(acc)
+    torch.cuda.synchronize()
+    assert gpu.count_finish32() == lt
+    assert np.array_equal(gpu.get_counts(), ref)

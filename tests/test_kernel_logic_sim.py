@@ -315,6 +315,34 @@ def test_select_matches_oracle(seed):
         assert np.array_equal(S.select(z, counts, W, thr, ct, single, fn), O.f32.select(z, counts, W, thr, ct, single, fn))
 
 
+@pytest.mark.parametrize("seed", range(16))
+def test_partition_pass_list_formulation_equals_libstdcxx(seed):
+    """The data-parallel restatement of a partition pass (two position lists, pairwise swaps, cut = min(A[m], B[m-1])) that
+    the device runs for seed selection leaves the same array and the same cut as std::__unguarded_partition_pivot, level
+    after level down the left spine — ties, plateaus, sorted and reversed inputs included."""
+    for n in (17, 100, 4 ** 6, 4 ** 8):
+        z = _z_tables(seed, max(n, 512))[:n].copy()
+        assert S.partition_level_agrees(z), (seed, n)
+    assert S.partition_level_agrees(np.zeros(1000, np.float32))  # every element ties with the pivot
+    assert S.partition_level_agrees(np.arange(1000, dtype=np.float32))
+    assert S.partition_level_agrees(-np.arange(1000, dtype=np.float32))
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_select_by_device_levels_matches_oracle(seed):
+    """Seed selection with the top partition levels run in the device's formulation and the rest on (z, id) pairs
+    (host_ingest.h: sort_leading_by_levels) == the oracle's std::sort-based list."""
+    W = 8 if seed % 2 else 9  # 4^8 and 4^9 ids
+    n = 4 ** W
+    z = _z_tables(seed, n)
+    counts = np.random.RandomState(100 + seed).randint(0, 8, n).astype(np.uint64)
+    for thr, ct, single, fn in ((10.0, 3, False, True), (3.0, 1, True, False), (0.5, 2, False, False), (-100.0, 0, True, False)):
+        for stop in (16, 64, 5000):
+            got, levels = S.select_levels(z, counts, W, thr, ct, single, fn, stop)
+            assert levels >= 1
+            assert np.array_equal(got, O.f32.select(z, counts, W, thr, ct, single, fn)), (thr, stop)
+
+
 def test_select_with_nan_falls_back_to_plain_sort():
     W = 8
     z = _z_tables(1, 4 ** W)
