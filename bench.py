@@ -51,6 +51,12 @@ def workload_shape(name, n_gpus):
     raise SystemExit(f"unknown workload {name}")
 
 
+def bench_config(shape, world):
+    """The `config` object of the JSON line — the same keys and values in both arms (`--impl b200` and `--impl reference`)."""
+    return {"workload": shape["label"], "W": shape["W"], "strand": shape["strand"], "n_seq_per_gpu": shape["n_seq_per_gpu"],
+            "seq_len": shape["seq_len"], "seed": 1234, "motif": MOTIF, "plant_fraction": 0.3, "n_gpus": world}
+
+
 # ---------------------------------------------------------------------------------------------------------
 # clocks sampling (B200_PROFILING.md "clocks DURING the timed region")
 # ---------------------------------------------------------------------------------------------------------
@@ -162,20 +168,9 @@ def run_reference_arm(args, shape):
     if rank != 0:
         return
     n_sample = min(shape["n_seq_per_gpu"], args.ref_sample)
-    codes = offs = None
-    try:
-        import _pkg
-
-        pkg = _pkg.load()
-        if pkg.load_library().peng_cuda_device_count() > 0:
-            g = pkg.PengCuda(0)
-            g.ingest_synthetic(n_sample, shape["seq_len"], 1234, 0, MOTIF, 0.3, 0.0)
-            codes, offs = g.export_codes()
-            g.close()
-    except Exception:
-        codes = None
-    if codes is None:
-        codes, offs = sample_codes_host(shape, n_sample)
+    # the reference arm never loads libpeng_cuda.so: the sample comes from the host build of the generator (tests/sim,
+    # the same counter-based generator the device runs: identical sequences)
+    codes, offs = sample_codes_host(shape, n_sample)
     bases = int(offs[-1])
     times, kind, cores = [], None, 1
     ref = CpuReference(codes, offs, shape["W"], shape["strand"])
@@ -191,7 +186,7 @@ def run_reference_arm(args, shape):
     line = {"impl": "reference", "metric": "kmer_count_gbases_per_s", "value": value, "unit": "Gbases/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot / len(times), "higher_is_better": True,
             "scaling": shape["scaling"], "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": shape["label"], "W": shape["W"], "strand": shape["strand"]},
+            "config": bench_config(shape, args.gpus),
             "cpu_baseline": {"value": value, "unit": "Gbases/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -231,6 +226,106 @@ def end_to_end_cli():
     return out
 
 
+def fp64_peak_tflops():
+    """B200 FP64 vector peak: 148 SMs x 64 FMA lanes x 2 flop x the SM clock of MEASURED_PEAKS.json (no measured FP64 number
+    exists in that file, so this is the nominal pipe rate at the measured clock — said so in the line)."""
+    mhz = 1965.0
+    try:
+        mhz = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["sm_max_mhz"])
+    except Exception:
+        pass
+    return 148 * 64 * 2 * mhz * 1e6 / 1e12
+
+
+def em_roofline(g, pkg, W, pw, hbm_peak_gbs, fp64_peak):
+    """One EM iteration of all PWMs = ONE pass over {count, bgprob} (16 B per bin) + ~10.6 FP64 instructions (~17 flop: the
+    fused multiply-adds count twice) per (bin, PWM).  Which roof binds depends on the number of PWMs: HBM (or L2, W <= 10)
+    below ~4 PWMs, the FP64 pipe above."""
+    import torch
+
+    P = len(pw)
+    g.em(pw, pkg.F64, 1e4, 0.0, 2)
+    torch.cuda.synchronize()
+    its_n = 10
+    t0 = time.perf_counter()
+    _, its = g.em(pw, pkg.F64, 1e4, 0.0, its_n)
+    dt = time.perf_counter() - t0
+    # the call also pays the one-off pair table (k_em_pairs) and allocation: time a 1-iteration call and take the difference
+    t0 = time.perf_counter()
+    g.em(pw, pkg.F64, 1e4, 0.0, 1)
+    dt1 = time.perf_counter() - t0
+    per_it = max(1e-9, (dt - dt1) / (its_n - 1))
+    bins = 4 ** W
+    flop = 17.0 * bins * P
+    return {"ms_per_iteration_all_pwms": 1e3 * per_it, "pwm_iterations_per_s_steady": P / per_it,
+            "roofline": {"bound": "fp64" if P >= 4 else "hbm", "table_bytes_per_iteration": 16 * bins,
+                         "table_GBps": 16 * bins / per_it / 1e9, "hbm_peak_GBps": hbm_peak_gbs, "hbm_frac": 16 * bins / per_it / 1e9 / hbm_peak_gbs,
+                         "fp64_tflops": flop / per_it / 1e12, "fp64_peak_tflops": fp64_peak, "fp64_frac": flop / per_it / 1e12 / fp64_peak,
+                         "fp64_peak_source": "nominal: 148 SMs x 64 FMA/clk x SM clock of MEASURED_PEAKS.json",
+                         "flop_per_bin_and_pwm": 17}}
+
+
+def em_cpu_baseline():
+    """The reference's own Peng::em_optimize_pwms (src/peng.cpp:48-178), timed inside oracle/_ref/ref_dump on configs[1]
+    (MafK.fasta, W = 10, the PWMs its own hill climb produced), EM threshold 0 so that every PWM runs all 10 iterations."""
+    ref_dump = os.path.join(ROOT, "oracle", "_ref", "ref_dump")
+    if not os.path.exists(ref_dump):
+        return {"unavailable": "oracle/_ref/ref_dump not built"}
+    d = tempfile.mkdtemp(prefix="peng_em_")
+    try:
+        cores = os.cpu_count() or 1
+        r = subprocess.run([ref_dump, os.path.join(ROOT, "tests", "golden", "data", "MafK.fasta"), "10", "BOTH", d, "--em-threshold", "0"],
+                           capture_output=True, text=True, env=dict(os.environ, OMP_NUM_THREADS=str(cores)))
+        if r.returncode != 0:
+            return {"unavailable": r.stderr[-200:]}
+        meta = dict(l.split() for l in open(os.path.join(d, "meta.txt")))
+        n, t = int(meta["n_em_pwms"]), float(meta["t_em_s"])
+        return {"kind": "reference", "cores": cores, "pwms": n, "iterations": 10, "W": 10, "seconds": t,
+                "pwm_iterations_per_s": n * 10 / t, "sample": "configs[1]: MafK.fasta, W = 10, both strands; the loop over PWMs is an OpenMP "
+                "loop in the reference (src/peng.cpp:60-61), the table pass inside a PWM is serial"}
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
+def configs3_run(pkg, torch, dist, rank, world, local, steps=3):
+    """BASELINE configs[3]: 50 M x 500 bp (25 Gbp) split over the GPUs (strong scaling): > 2^30 positions per GPU (several
+    chunks of the partition path), 2.5e10 > 2^32 in total -> 64-bit exchange (ncclAllReduce of the canonical uint64 table
+    + ltot, mirror afterwards).  Device-timed, max over ranks; ltot checked in closed form."""
+    n_seq, L, W = 50_000_000, 500, 10
+    first, n_local = pkg.shard_synthetic(n_seq, rank, world)
+    g = pkg.PengCuda(local)
+    g.set_stream(torch.cuda.current_stream().cuda_stream)  # main() made a non-default stream current
+    g.ingest_synthetic(n_local, L, 1234, first, MOTIF, 0.3, 0.0)
+
+    def step():
+        if world == 1:
+            return g.count(W, pkg.STRAND_BOTH)
+        g.count_local(W, pkg.STRAND_BOTH)
+        dist.all_reduce(torch.as_tensor(g.count_buffer(), device="cuda"))
+        return g.count_finish()
+
+    lt = step()
+    ok = int(lt) == n_seq * (L - W + 1)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        step()
+    b.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    g.close()
+    return {"workload": "configs[3]: synthetic 50M x 500 bp (25 Gbp) split over the GPUs, W=10, both strands", "n_gpus": world,
+            "steps": steps, "ms_per_step": ms, "gbases_per_s": n_seq * L / (ms * 1e-3) / 1e9, "scaling": "strong",
+            "exchange": "ncclAllReduce of 4^10 uint64 + ltot (the set has more than 2^32 positions)" if world > 1 else None,
+            "ltot_ok": ok}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -240,6 +335,9 @@ def main():
     ap.add_argument("--workload", default="cfg3")
     ap.add_argument("--ref-sample", type=int, default=250_000, help="sequences per CPU-reference step")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1, sets below 2^32 positions: fused sum + fold over NVLink peer memory (k_peer_exchange32) or "
+                         "ncclAllReduce of the uint32 table + fold")
     ap.add_argument("--kernels-only", action="store_true",
                     help="short run for ncu: resident steps only (no time-based warm-up, e2e, CPU baseline, extras)")
     args = ap.parse_args()
@@ -276,7 +374,10 @@ def main():
     first_seq = rank * n_local
     bases_local = n_local * L
     g = pkg.PengCuda(local)
-    stream = torch.cuda.current_stream()
+    # One stream for everything that is timed: torch's DEFAULT stream is the NULL stream, which peng_cuda_set_stream takes
+    # as "the handle's own stream" — the library's kernels would then run beside the L2 flush and outside the torch events.
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     g.set_stream(stream.cuda_stream)  # the library launches on torch's current stream: torch events see its kernels
     g.ingest_synthetic(n_local, L, 1234, first_seq, MOTIF, 0.3, 0.0)
     g.enable_timing(True)
@@ -286,7 +387,7 @@ def main():
     # table (half the bytes of the uint64 one) and fold once, after the sum
     exchange32 = world > 1 and (bases_local + 2 * n_local) * world < 2 ** 32 - 2 ** 20 and bases_local + 2 * n_local < 2 ** 30 - 2 ** 12
 
-    def count_multi():
+    def count_multi_nccl():
         if exchange32:
             g.count_local32(W, strand)
             buf = torch.as_tensor(g.count_buffer32(), device="cuda")
@@ -297,10 +398,54 @@ def main():
         dist.all_reduce(buf)  # per-GPU histograms + ltot -> global table (NCCL over NVLink)
         return g.count_finish()
 
+    # Peer group: the ranks exchange CUDA IPC handles of their tables once (NCCL is the bootstrap only); every step then
+    # runs ONE kernel per rank that sums the uint32 tables over NVLink peer memory, folds, mirrors and publishes the
+    # finished table on every rank (k_peer_exchange32) — no library collective in the data path, no host synchronisation.
+    peer, peer_note = False, None
+    if world > 1 and exchange32 and args.exchange == "peer" and W >= 8:
+        try:
+            blob = torch.from_numpy(g.peer_export(W)).cuda()
+            blobs = [torch.empty_like(blob) for _ in range(world)]
+            dist.all_gather(blobs, blob)
+            g.peer_attach(rank, world, torch.stack(blobs).cpu().numpy())
+            peer = True
+        except Exception as e:  # e.g. no IPC between the ranks' containers: the NCCL path still measures the step
+            peer_note = f"peer attach failed ({e!r}): NCCL all-reduce path"
+        ok = torch.tensor([1 if peer else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if peer and not int(ok.item()):
+            g.peer_detach()
+            peer = False
+
+    def count_multi(want_ltot=False):
+        if peer:
+            g.count_local32(W, strand)
+            return g.count_exchange32(want_ltot)
+        return count_multi_nccl()
+
     def step_resident():
         if world > 1:
             return count_multi()
-        return g.count(W, strand)
+        return g.count(W, strand, want_ltot=False)  # ltot stays on the device: no read-back, no host synchronisation per step
+
+    # ---- the counted result is checked, not only timed: ltot in closed form (no N in the set: every sequence gives
+    # L - W + 1 W-mers), and for N > 1 the peer exchange against the NCCL path on 2^16 bins + the sum of all bins ----
+    expect_ltot = n_local * world * (L - W + 1)
+    checks = {}
+    if world > 1:
+        ids = np.random.RandomState(5).randint(0, 4 ** W, 1 << 16, dtype=np.int64).astype(np.uint64)
+        lt_n = count_multi_nccl()
+        ref_bins, ref_total = g.gather_counts(ids), g.counts_total()
+        checks["ltot_nccl_path"] = int(lt_n) == expect_ltot
+        if peer:
+            lt_p = count_multi(True)
+            checks["ltot_peer_path"] = int(lt_p) == expect_ltot
+            checks["peer_equals_nccl_bins"] = bool(np.array_equal(g.gather_counts(ids), ref_bins)) and g.counts_total() == ref_total
+    else:
+        checks["ltot"] = int(g.count(W, strand)) == expect_ltot
+        checks["bins_sum_le_ltot"] = g.counts_total() <= (2 if strand == pkg.STRAND_BOTH else 1) * expect_ltot
+    if not all(checks.values()):
+        raise SystemExit(f"bench.py: counted result failed its checks on rank {rank}: {checks}")
 
     # ---- resident throughput ("value") ----
     sampler = ClockSampler(local)
@@ -328,6 +473,9 @@ def main():
     barrier()
     t_wall = time.perf_counter() - t_wall
     launches = g.launches - launches0
+    checks["ltot_after_timed_steps"] = int(g.count_finish()) == expect_ltot
+    if not checks["ltot_after_timed_steps"]:
+        raise SystemExit(f"bench.py: ltot after the timed steps is wrong on rank {rank}")
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -358,8 +506,8 @@ def main():
         if world > 1:
             count_multi()
         else:
-            g.count(W, strand)
-        g._ck(g.lib.peng_cuda_get_counts(g.h, counts_host.data_ptr()))  # D2H of the 4^W table
+            g.count(W, strand, want_ltot=False)
+        g._ck(g.lib.peng_cuda_get_counts(g.h, counts_host.data_ptr()))  # D2H of the 4^W table (fetches ltot with it)
 
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
@@ -388,6 +536,18 @@ def main():
     if world == 1:
         t0 = time.perf_counter(); g._ck(g.lib.peng_cuda_get_counts(g.h, counts_host.data_ptr()))
         e2e_phases["get_counts_ms"] = 1e3 * (time.perf_counter() - t0)
+
+    if peer:  # every rank closes its mappings of the peers' tables before anybody frees or re-allocates them
+        g.peer_detach()
+        barrier()
+
+    # ---- BASELINE configs[3] (the set north_star quotes the scaling target on): every rank takes part ----
+    cfg3_extra = None
+    if not args.no_extras and args.workload == "cfg3":
+        try:
+            cfg3_extra = configs3_run(pkg, torch, dist, rank, world, local)
+        except Exception as e:
+            cfg3_extra = {"error": repr(e)}
 
     if rank != 0:
         if dist is not None:
@@ -449,6 +609,8 @@ def main():
 
     # ---- extras: the other two BASELINE metrics on the same table ----
     extra = {}
+    if cfg3_extra is not None:
+        extra["configs3_25gbp"] = cfg3_extra
     if not args.no_extras:
         try:
             t0 = time.perf_counter()
@@ -473,6 +635,18 @@ def main():
                 dt = time.perf_counter() - t0
                 extra[name] = {"pwm_iterations_per_s": float(its.sum()) / dt, "pwms": 17, "iterations": 10, "W": W,
                                "seconds": dt, "bytes_per_bin_per_iteration": 16}
+            extra["em_fp64"].update(em_roofline(g, pkg, W, pw, peak, fp64_peak_tflops()))
+            # the long-k-mer point of the EM metric (BASELINE configs[4]): W = 14, PLUS, the same set
+            g.count(14, pkg.STRAND_PLUS)
+            g.stats(None, v64, K=2)
+            pw14 = rng.dirichlet(np.ones(4), (17, 14)) * 0.3
+            for m in range(17):
+                for p in range(14):
+                    pw14[m, p, "ACGT".index("TGCTGACTCAGCA"[(m + p) % 13])] += 0.7
+            pw14 /= pw14.sum(2, keepdims=True)
+            extra["em_fp64_W14"] = {"pwms": 17, "W": 14, **em_roofline(g, pkg, 14, pw14, peak, fp64_peak_tflops())}
+            g.count(W, strand)  # back to the headline table
+            extra["em_cpu_baseline"] = em_cpu_baseline()
             # third BASELINE metric: end-to-end seconds of the whole CLI run on configs[1] (MafK.fasta, W = 10, defaults),
             # the host driver on this GPU vs the reference binary on this box's host cores, MEME files compared
             if rank == 0:
@@ -483,10 +657,15 @@ def main():
     line = {"metric": "kmer_count_gbases_per_s", "value": value, "unit": "Gbases/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": shape["scaling"],
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": shape["label"], "W": W, "strand": shape["strand"], "n_seq_per_gpu": n_local, "seq_len": L,
-                       "seed": 1234, "motif": MOTIF, "plant_fraction": 0.3,
-                       "l2": "256 MiB buffer written between timed iterations (inputs smaller than L2)",
-                       "parallelism": f"sequence-sharded x{world}" + ((", 1 NCCL all_reduce of 4^W u32 + ltot per step (32-bit exchange)" if exchange32 else ", 1 NCCL all_reduce of 4^W u64 + ltot per step") if world > 1 else "")},
+            "config": bench_config(shape, world),
+            "timing": {"l2": "256 MiB buffer written between timed iterations (inputs smaller than L2)",
+                       "parallelism": f"sequence-sharded x{world}" + (
+                           (", per step ONE fused kernel per rank: sum of the uint32 tables over NVLink peer memory + fold + mirror + "
+                            "publication on every rank (k_peer_exchange32; NCCL only bootstraps the IPC handles)" if peer else
+                            ", 1 NCCL all_reduce of 4^W u32 + ltot per step (32-bit exchange)" if exchange32 else
+                            ", 1 NCCL all_reduce of 4^W u64 + ltot per step") if world > 1 else ""),
+                       "data_plane": ("peer memory (own kernel)" if peer else "nccl") if world > 1 else None,
+                       "note": peer_note, "result_checks": checks},
             "e2e": {"value": e2e_value, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "path": "peng_cuda_ingest_codes (pinned host codes; hybrid: host threads pack part of the set into the 2-bit layout, "
                             "the DMA engine moves the raw rest for the device to pack) -> peng_cuda_count -> peng_cuda_get_counts",

@@ -90,6 +90,13 @@ int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, const uint64_t
 int peng_cuda_set_ingest_mode(peng_handle_t h, int mode, double host_fraction);
 uint64_t peng_cuda_last_ingest_host_packed(peng_handle_t h); /* sequences packed by the host in the last ingest */
 int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets, uint64_t n_seq);
+/* Count prefetch: BasePattern's constructor counts right after the sequences exist (src/base_pattern.cpp:36-80), so a
+ * binding knows W and the strand before it hands the sequences over.  Armed with them, peng_cuda_ingest_codes runs the
+ * first stage of that count (stage P of the W = 10 partition path) unit range by unit range as the data lands on the
+ * device, under the DMA of the rest; the next peng_cuda_count[_local / _local32] with the same (W, strand) only runs what is
+ * left (slow units, stage H, fold).  Same table bit for bit.  Other pattern lengths / small sets: the hint is ignored.
+ * W = 0 disarms. */
+int peng_cuda_set_count_prefetch(peng_handle_t h, int W, int strand);
 /* Synthetic ChIP-seq-like set generated on the device (BASELINE.json configs[2..4]): n_seq sequences of
  * seq_len i.i.d. uniform bases from a counter-based generator (seed, base index), motif (base codes 0..3,
  * motif_len <= 32, may be NULL) planted in ~plant_fraction of the sequences at a uniform offset;
@@ -119,6 +126,9 @@ int peng_cuda_background_finish(peng_handle_t h, int K, const float* alpha, int 
  * ltot = number of W-mers looked at (BasePattern::getLtot). */
 int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* ltot);
 int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts /* 4^W */); /* BasePattern::getPatternCounter */
+/* The same table as uint32 (half the bytes over PCIe) — for sets of fewer than 2^32 positions, where no bin can exceed
+ * 32 bits (the reference's own position counter is `unsigned int`, src/base_pattern.cpp:335-336); fails otherwise. */
+int peng_cuda_get_counts32(peng_handle_t h, uint32_t* counts /* 4^W */);
 /* Counting kernel family for W >= 10: 0 = automatic (partition path from 2^22 / 2^25 / 2^24 / 2^28 stream positions on for W = 10 / 12 / 14 / 16), 1 = one L2 atomic
  * per counted W-mer (k_count_global), 2 = partition path (W = 10: k_count_part / k_count_slow / k_hist_part, shared-
  * memory histograms per id range; W = 12, 14, 16: the deep path k_count_part / k_count_slow / k_part2 / k_hist_leaf),
@@ -139,6 +149,24 @@ int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot);
 int peng_cuda_count_local32(peng_handle_t h, int W, int strand);
 int peng_cuda_count_buffer32(peng_handle_t h, void** device_ptr, uint64_t* n_u32);
 int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot);
+/* Peer group: the multi-GPU counting step without a library collective in the data path.  After peng_cuda_count_local32
+ * on every rank, peng_cuda_count_exchange32 runs ONE kernel per rank that sums the ranks' uint32 launch tables over NVLink
+ * peer memory (each rank reduces the units it owns with 16-byte peer loads), folds reverse-complement pairs and writes the
+ * finished 64-bit table — mirror copy included (src/base_pattern.cpp:387-392) — into every rank's table with peer stores;
+ * arrival / departure of the ranks are flag words in peer memory, nothing passes through the host.  Replaces
+ * count_buffer32 -> ncclAllReduce -> count_finish32 (kept: NCCL remains the portable path and carries the 64-bit exchange).
+ *   peng_cuda_peer_export : allocates the tables of pattern length W (8 .. 16) and writes PENG_PEER_BLOB_BYTES describing
+ *                           them (CUDA IPC handles; raw pointers for handles of the same process);
+ *   peng_cuda_peer_attach : blobs = the exports of all `world` (<= 8) ranks in rank order — gathered by the caller with
+ *                           whatever it has (torch.distributed / MPI / threads of one process);
+ *   peng_cuda_peer_detach : before the pattern length changes or the handle goes away (destroy detaches).
+ * ltot == NULL in peng_cuda_count_exchange32 (and in peng_cuda_count): no read-back and no synchronisation — the table is
+ * complete in stream order and peng_cuda_count_finish(h, &ltot), or the first call that needs the table, fetches ltot. */
+#define PENG_PEER_BLOB_BYTES 256
+int peng_cuda_peer_export(peng_handle_t h, int W, void* blob);
+int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const void* blobs);
+int peng_cuda_peer_detach(peng_handle_t h);
+int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot);
 /* Id-sliced tables for the long pattern lengths on several GPUs (BASELINE configs[4]; the reference's tables are one
  * float array per order plus expected / z / logp over all 4^W ids, src/base_pattern.h:116-120 — at W = 16 more than one
  * GPU holds).  Rank `part` of `n_parts` keeps the ids [lo, hi) (whole tiles of 1024 ids, peng_cuda_table_slice) of every

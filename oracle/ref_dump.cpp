@@ -51,7 +51,8 @@ int main(int argc, char** argv) {
   if (argc < 5) {
     fprintf(stderr,
             "usage: ref_dump FASTA W BOTH|PLUS OUTDIR [--no-em] [--tables-only] [--counts-only]\n"
-            "               [--iupac-file F] [--max-seeds N] [-t Z] [--count-threshold C]\n");
+            "               [--iupac-file F] [--max-seeds N] [-t Z] [--count-threshold C]\n"
+            "               [--em-threshold T] [--em-iterations N]   (bench: T = 0 makes every PWM run all N iterations)\n");
     return 2;
   }
   std::string fasta = argv[1];
@@ -63,6 +64,8 @@ int main(int argc, char** argv) {
   size_t max_seeds = 50;
   REAL zthr = 10;
   size_t cthr = 3;
+  REAL em_thr = 0.08;
+  int em_its = 10;
   for (int i = 5; i < argc; i++) {
     if (!strcmp(argv[i], "--no-em")) use_em = false;
     else if (!strcmp(argv[i], "--tables-only")) tables_only = true;
@@ -71,6 +74,8 @@ int main(int argc, char** argv) {
     else if (!strcmp(argv[i], "--max-seeds") && i + 1 < argc) max_seeds = atol(argv[++i]);
     else if (!strcmp(argv[i], "-t") && i + 1 < argc) zthr = atof(argv[++i]);
     else if (!strcmp(argv[i], "--count-threshold") && i + 1 < argc) cthr = atol(argv[++i]);
+    else if (!strcmp(argv[i], "--em-threshold") && i + 1 < argc) em_thr = atof(argv[++i]);
+    else if (!strcmp(argv[i], "--em-iterations") && i + 1 < argc) em_its = atoi(argv[++i]);
   }
 
   Alphabet::init("STANDARD");
@@ -176,7 +181,7 @@ int main(int argc, char** argv) {
   if (use_em) {
     std::vector<IUPACPattern*> opt;
     t0 = now_s();
-    peng.em_optimize_pwms(unopt, bp, 1e4, 0.08, 10, bp->getBackgroundProb(bp->max_k), opt);
+    peng.em_optimize_pwms(unopt, bp, 1e4, em_thr, em_its, bp->getBackgroundProb(bp->max_k), opt);
     t_em = now_s() - t0;
     std::vector<REAL> em;
     for (auto p : opt)
@@ -186,8 +191,8 @@ int main(int argc, char** argv) {
   }
   {
     FILE* f = fopen((out + "/meta.txt").c_str(), "a");
-    fprintf(f, "t_select_s %.6f\nt_optimize_iupac_s %.6f\nt_em_s %.6f\nn_em_pwms %zu\n", t_sel, t_opt, t_em,
-            unopt.size());
+    fprintf(f, "t_select_s %.6f\nt_optimize_iupac_s %.6f\nt_em_s %.6f\nn_em_pwms %zu\nem_threshold %g\nem_max_iterations %d\n", t_sel,
+            t_opt, t_em, unopt.size(), (double)em_thr, em_its);
     fclose(f);
   }
   return 0;

@@ -69,6 +69,8 @@ _PROTOS = {
     "peng_cuda_background_finish": (C.c_int, [H, C.c_int, f32p, C.c_int, C.c_int, C.c_void_p]),
     "peng_cuda_count": (C.c_int, [H, C.c_int, C.c_int, u64p]),
     "peng_cuda_get_counts": (C.c_int, [H, C.c_void_p]),
+    "peng_cuda_get_counts32": (C.c_int, [H, C.c_void_p]),
+    "peng_cuda_set_count_prefetch": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_count_local": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_set_count_path": (C.c_int, [H, C.c_int]),
     "peng_cuda_last_count_path": (C.c_int, [H]),
@@ -77,6 +79,10 @@ _PROTOS = {
     "peng_cuda_count_local32": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_count_buffer32": (C.c_int, [H, C.POINTER(C.c_void_p), u64p]),
     "peng_cuda_count_finish32": (C.c_int, [H, u64p]),
+    "peng_cuda_peer_export": (C.c_int, [H, C.c_int, C.c_void_p]),
+    "peng_cuda_peer_attach": (C.c_int, [H, C.c_int, C.c_int, C.c_void_p]),
+    "peng_cuda_peer_detach": (C.c_int, [H]),
+    "peng_cuda_count_exchange32": (C.c_int, [H, u64p]),
     "peng_cuda_set_table_slice": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_table_slice": (C.c_int, [H, u64p, u64p]),
     "peng_cuda_count_finish32_sliced": (C.c_int, [H, u64p]),
@@ -287,11 +293,33 @@ class PengCuda:
         return (v, n) if return_counts else v
 
     # ---- (b) counting ----
-    def count(self, W, strand=STRAND_BOTH):
+    def count(self, W, strand=STRAND_BOTH, want_ltot=True):
+        """want_ltot=False: nothing is read back, nothing waits (count_finish() fetches ltot later)."""
         ltot = C.c_uint64()
-        self._ck(self.lib.peng_cuda_count(self.h, W, strand, C.byref(ltot)))
+        self._ck(self.lib.peng_cuda_count(self.h, W, strand, C.byref(ltot) if want_ltot else None))
         self.W, self.strand = W, strand
-        return ltot.value
+        return ltot.value if want_ltot else None
+
+    # peer group: fused cross-GPU sum + fold over NVLink peer memory
+    PEER_BLOB_BYTES = 256
+
+    def peer_export(self, W):
+        blob = np.zeros(self.PEER_BLOB_BYTES, np.uint8)
+        self._ck(self.lib.peng_cuda_peer_export(self.h, W, _ptr(blob)))
+        self.W = W
+        return blob
+
+    def peer_attach(self, rank, world, blobs):
+        blobs = np.ascontiguousarray(blobs, np.uint8).reshape(world, self.PEER_BLOB_BYTES)
+        self._ck(self.lib.peng_cuda_peer_attach(self.h, rank, world, _ptr(blobs)))
+
+    def peer_detach(self):
+        self._ck(self.lib.peng_cuda_peer_detach(self.h))
+
+    def count_exchange32(self, want_ltot=True):
+        ltot = C.c_uint64()
+        self._ck(self.lib.peng_cuda_count_exchange32(self.h, C.byref(ltot) if want_ltot else None))
+        return ltot.value if want_ltot else None
 
     def set_count_path(self, path):
         """0 auto, 1 L2-atomic kernel, 2 partition path (W >= 10), 3 partition path with L2-RED second stage (W >= 12)."""
@@ -355,6 +383,15 @@ class PengCuda:
         out = np.zeros(4 ** self.W, np.uint64)
         self._ck(self.lib.peng_cuda_get_counts(self.h, _ptr(out)))
         return out
+
+    def get_counts32(self):
+        out = np.zeros(4 ** self.W, np.uint32)
+        self._ck(self.lib.peng_cuda_get_counts32(self.h, _ptr(out)))
+        return out
+
+    def set_count_prefetch(self, W=0, strand=STRAND_BOTH):
+        """Arm ingest_codes to run stage P of the count (W = 10 partition path) while the data is still arriving."""
+        self._ck(self.lib.peng_cuda_set_count_prefetch(self.h, int(W), int(strand)))
 
     def gather_counts(self, ids):
         ids = np.ascontiguousarray(ids, np.uint64)

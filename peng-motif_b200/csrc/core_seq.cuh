@@ -84,7 +84,7 @@ PENG_HD bool bit_at(const uint32_t* mask, uint64_t q) { return (ldg(mask + (q >>
 template <bool ASCII>
 PENG_HD void pack_word(uint64_t t, const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets,
                        uint64_t n_seq, uint32_t* __restrict__ codes, uint32_t* __restrict__ valid,
-                       uint32_t* __restrict__ sstart) {
+                       uint32_t* __restrict__ sstart, uint32_t* code_words_out = nullptr) {
   const uint64_t q0 = t * 32;
   uint32_t c0 = 0, c1 = 0, v = 0, ss = 0;
   const uint64_t total = n_seq ? offsets[n_seq] : 0;
@@ -132,6 +132,7 @@ PENG_HD void pack_word(uint64_t t, const uint8_t* __restrict__ src, const uint64
   codes[2 * t + 1] = c1;
   valid[t] = v;
   sstart[t] = ss;
+  if (code_words_out) { code_words_out[0] = c0; code_words_out[1] = c1; }  // for the caller's bit planes
 }
 
 // inverse of pack_word for one base (tests / CPU baseline export): reference letter code 0..4
@@ -186,7 +187,7 @@ PENG_HD uint32_t synth_base(const SynthParams& P, uint64_t g, uint32_t i, uint32
 }
 
 PENG_HD void synth_word(uint64_t t, const SynthParams& P, uint32_t* __restrict__ codes,
-                        uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart) {
+                        uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart, uint32_t* code_words_out = nullptr) {
   const uint64_t q0 = t * 32;
   const uint64_t stride = (uint64_t)P.seq_len + 2;
   const uint64_t stream_end = PENG_FRONT_PAD + P.n_seq * stride;
@@ -208,6 +209,7 @@ PENG_HD void synth_word(uint64_t t, const SynthParams& P, uint32_t* __restrict__
   codes[2 * t + 1] = c1;
   valid[t] = v;
   sstart[t] = ss;
+  if (code_words_out) { code_words_out[0] = c0; code_words_out[1] = c1; }  // for the caller's bit planes
 }
 
 // ---- (b1) which W-mers does the reference look at? -----------------------------------------------------

@@ -4,6 +4,8 @@
 // element-wise table passes, small reductions).  The per-thread bodies live in core_seq.cuh / core_tab.cuh.
 #include <cuda_runtime.h>
 
+#include <unistd.h>
+
 #include <algorithm>
 #include <chrono>
 #include <cstdarg>
@@ -91,6 +93,7 @@ struct peng_cuda_ctx {
   uint2* d_planes = nullptr;       // bit planes of d_codes, {bit 1, bit 0} per 32 positions (ensure_planes)
   size_t cap_planes = 0;
   bool planes_valid = false;
+  uint64_t planes_from = 0;        // words [planes_from, n_words32) were written by the packing kernel of the ingest, the rest is missing
   uint16_t* d_part_buckets = nullptr;
   size_t part_bucket_elems = 0;
   uint32_t* d_part_fill = nullptr;
@@ -120,6 +123,26 @@ struct peng_cuda_ctx {
   uint32_t* d_sel = nullptr;       // seed selection: order | list A | list B | block counts | state
   size_t sel_words = 0;
   bool select_on_host = false;     // PENG_SELECT_HOST: whole-table host replay (A/B, tests)
+
+  // ---- peer group: fused cross-GPU sum + fold over NVLink peer memory (peng_cuda_peer_*, peng_cuda_count_exchange32) ----
+  struct {
+    bool attached = false;
+    int rank = 0, world = 1, W = 0;
+    uint32_t* hist[8] = {};      // every rank's uint32 launch table (own entry: d_hist32)
+    uint64_t* counts[8] = {};    // every rank's 64-bit table
+    uint32_t* flags[8] = {};     // every rank's flag words
+    void* opened[3][8] = {};     // IPC mappings to close on detach
+    uint32_t* d_flags = nullptr; // own: [0 .. 7] arrival epoch per rank, [8] CTAs done, [9] error
+    uint32_t epoch = 0;
+  } peer;
+  bool count_pending = false;    // a count has run and its ltot has not been fetched yet (lazy finish)
+  // count prefetch (peng_cuda_set_count_prefetch): stage P of the W = 10 partition path runs inside peng_cuda_ingest_codes,
+  // unit range by unit range as the packed blocks land, under the DMA of the later ones
+  struct {
+    int W = 0, strand = 0;       // armed for this count (W = 0: off)
+    bool done = false;           // the current ingest ran stage P for (W, strand): the next matching count skips it
+  } pre;
+  bool hist_clean = false;       // every bin of the uint32 launch table is 0 (each complete fold leaves it so): no clearing pass
 
   // ---- EM session (multi-GPU protocol) ----
   struct {
@@ -191,6 +214,21 @@ static int need_scratch(peng_handle_t h, size_t bytes) {
   } while (0)
 
 static inline unsigned grid_for(uint64_t n, unsigned block) { return (unsigned)((n + block - 1) / block); }
+static bool use_partition(peng_handle_t h, int W);
+static int ensure_count_tables(peng_handle_t h, int W);
+static int ensure_planes(peng_handle_t h);
+static int make_planes(peng_handle_t h, uint64_t begin, uint64_t end);
+struct PrefetchRun;
+static int prefetch_begin(peng_handle_t h, PrefetchRun* pr);
+static int prefetch_range(peng_handle_t h, PrefetchRun* pr, uint64_t ub, uint64_t ue);
+struct PrefetchRun {
+  bool on = false, first = true;
+  unsigned grid_p = 0;
+  uint32_t region_cap = 0;
+  size_t smem_h = 0;
+  uint64_t done_u = 0;      // units [0, done_u) of the host-packed front have been through stage P
+  uint64_t planes_done = 0; // words [0, planes_done) of the host-packed front have their bit planes
+};
 
 // id-sliced tables: a buffer that holds [lo, hi) is addressed through a pointer moved back by lo, so that kernels index by
 // the absolute id (never dereferenced outside [lo, hi))
@@ -212,18 +250,33 @@ static inline bool tables_whole(peng_handle_t h) { return !h->counts_sliced && h
 // =====================================================================================================
 // kernels: ingest
 // =====================================================================================================
+// The packing kernels also write the bit planes of the words they produce (uint2 {bit 1, bit 0} per 32 positions, read by
+// stage P's conflict scan): the codes are in registers anyway, so the planes cost 8 more bytes written per 32 positions
+// and no pass of their own (k_make_planes, 26 us + 100 MB of traffic on configs[2], only runs for words the HOST packed).
 template <bool ASCII>
 __global__ void k_pack(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets, uint64_t n_seq,
                        uint32_t* __restrict__ codes, uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart,
-                       uint64_t t_begin, uint64_t t_end) {
+                       uint2* __restrict__ planes, uint64_t t_begin, uint64_t t_end) {
   const uint64_t t = t_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < t_end) pack_word<ASCII>(t, src, offsets, n_seq, codes, valid, sstart);
+  if (t < t_end) {
+    uint32_t c[2];
+    pack_word<ASCII>(t, src, offsets, n_seq, codes, valid, sstart, c);
+    uint2 o;
+    planes_of_unit(c[0], c[1], &o.x, &o.y);
+    planes[t] = o;
+  }
 }
 
 __global__ void k_synth(SynthParams P, uint32_t* __restrict__ codes, uint32_t* __restrict__ valid,
-                        uint32_t* __restrict__ sstart, uint64_t n_words32) {
+                        uint32_t* __restrict__ sstart, uint2* __restrict__ planes, uint64_t n_words32) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n_words32) synth_word(t, P, codes, valid, sstart);
+  if (t < n_words32) {
+    uint32_t c[2];
+    synth_word(t, P, codes, valid, sstart, c);
+    uint2 o;
+    planes_of_unit(c[0], c[1], &o.x, &o.y);
+    planes[t] = o;
+  }
 }
 
 // one thread per stream position: write the reference letter code of real bases to out[base index]
@@ -449,7 +502,7 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     const uint32_t* __restrict__ codes, const uint2* __restrict__ planes, const uint32_t* __restrict__ valid, uint32_t* __restrict__ kstart,
     uint64_t n_words32, uint64_t unit_begin, uint64_t unit_end, typename PartGeom<W>::entry_t* __restrict__ buckets, uint32_t region_cap,
     uint32_t* __restrict__ fill_out, uint32_t* __restrict__ hist, unsigned long long* __restrict__ ltot,
-    uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count, uint32_t zero) {
+    uint2* __restrict__ slow_list, unsigned int* __restrict__ slow_count, uint32_t zero, uint32_t carry_fill) {
   static_assert(W >= 10 && W <= 16, "class geometries exist for 4^10 ids (one level) and 4^12 .. 4^16 ids (deep path)");
   typedef PartGeom<W> G;
   typedef typename G::entry_t entry_t;
@@ -462,7 +515,12 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
   __shared__ uint32_t any_ovf, n_slow, slow_base;
   __shared__ uint2 slow_q[PART_SLOWCAP];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x < PART_NCLASS_) { cnt[threadIdx.x] = 0; prev[threadIdx.x] = 0; fill[threadIdx.x] = 0; ovf[threadIdx.x] = 0; }
+  // carry_fill: an earlier launch of the same count (another unit range: the count prefetch of the ingest) left keys in
+  // this CTA's bucket regions — go on behind them
+  if (threadIdx.x < PART_NCLASS_) {
+    cnt[threadIdx.x] = 0; prev[threadIdx.x] = 0; ovf[threadIdx.x] = 0;
+    fill[threadIdx.x] = carry_fill ? fill_out[threadIdx.x * gridDim.x + blockIdx.x] : 0u;
+  }
   if (threadIdx.x == 0) { cnt[PART_NCLASS_] = 0; any_ovf = 0; n_slow = 0; }
   __syncthreads();
   const uint32_t cnt_s = (uint32_t)__cvta_generic_to_shared(cnt), q_s = (uint32_t)__cvta_generic_to_shared(q);
@@ -1102,6 +1160,178 @@ __global__ void k_ltot_from32(uint32_t* __restrict__ word, uint64_t* __restrict_
   *word = 0;
 }
 
+// -----------------------------------------------------------------------------------------------------
+// Fused cross-GPU sum + fold + mirror over NVLink peer memory (multi-GPU counting step).
+//
+// What it replaces: k_ltot_to32 -> ncclAllReduce(4^W uint32) on NCCL's stream -> k_ltot_from32 -> k_fold_canon_first ->
+// read-back — a flat +0.14 ms on a 0.5 ms step, the same at 2 and at 8 GPUs (latency, not bandwidth).  Here ONE kernel
+// per rank does the whole exchange on the handle's stream, two-shot:
+//   arrive  : every rank tells every peer "my launch table is complete" (flag word in the peer's memory, release / acquire
+//             at system scope) and waits for all of them;
+//   reduce  : the rank that owns a unit reads that unit's uint32 bins from ALL ranks' launch tables (16-byte loads over
+//             NVLink), adds them, folds reverse-complement pairs through shared memory, and
+//   publish : writes the finished 64-bit bins — canonical AND mirrored copy — straight into EVERY rank's 64-bit table
+//             (32-byte peer stores): reduce-scatter, fold, mirror and all-gather in one pass;
+//   depart  : the last CTA of a rank tells the peers "my stores have landed" and waits for theirs, so that whatever
+//             follows on the stream sees a complete table and the launch table may be cleared again.
+// BOTH strands: a unit is a quarter of a pair of 64 x 64 tiles (k_fold_canon_tiled's geometry: id = (a, m, b), the partner
+// of (a, m, b) is (revcomp3(b), revcomp(m), revcomp3(a))): the 16 rows a with a & 3 == q of tile m and the 16-column band
+// b >> 4 == 3 - q of tile revcomp(m) hold each other's partners, every access is a 256- or 64-byte run.  Units of a middle
+// m belong to rank m % world.  PLUS: a unit is 1024 consecutive ids.
+// Nothing here can deadlock on a peer that never arrives: the waits give up after ~2 s and raise the error word.
+struct PeerArgs {
+  uint32_t* hist[8];
+  uint64_t* counts[8];
+  uint32_t* flags[8];
+  int rank, world, W;
+  uint32_t epoch;
+  uint64_t n;
+};
+__device__ __forceinline__ void st_release_sys(uint32_t* a, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* a) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer_u4(const uint32_t* p) {  // L1 is not coherent with a peer's writes: read through to L2 / the link
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void peer_wait_all(const uint32_t* my_flags, int world, uint32_t epoch, uint32_t* err) {
+  if ((int)threadIdx.x < world) {
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(my_flags + threadIdx.x) - epoch) < 0) {
+      if (clock64() - t0 > 4000000000ll) { *err = 1u; break; }  // ~2 s: a peer never arrived
+      __nanosleep(100);
+    }
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void st_peer_4u64(uint64_t* p, uint64_t a, uint64_t b, uint64_t c, uint64_t d) {
+  asm volatile("st.global.v2.u64 [%0], {%1, %2};" :: "l"(p), "l"(a), "l"(b) : "memory");
+  asm volatile("st.global.v2.u64 [%0], {%1, %2};" :: "l"(p + 2), "l"(c), "l"(d) : "memory");
+}
+
+template <bool BOTH>
+__global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
+  __shared__ uint32_t tX[1024], tY[1024];
+  __shared__ uint32_t is_last;
+  uint32_t* my_flags = A.flags[A.rank];
+  uint32_t* err = my_flags + 9;
+  const uint32_t t = threadIdx.x;
+  // ---- arrive ----
+  if (blockIdx.x == 0 && (int)t < A.world) {
+    __threadfence_system();
+    st_release_sys(A.flags[t] + A.rank, A.epoch);
+  }
+  peer_wait_all(my_flags, A.world, A.epoch, err);
+  if (blockIdx.x == 0 && t == 0) {  // ltot rides in word 4^W of every launch table
+    uint64_t lt = 0;
+    for (int p = 0; p < A.world; p++) {
+      uint32_t v;
+      asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(A.hist[p] + A.n) : "memory");
+      lt += v;
+    }
+    A.counts[A.rank][A.n] = lt;
+  }
+  if (BOTH) {
+    const int W = A.W, sh_a = 2 * W - 6;
+    const uint32_t n_units = 4u << (2 * (W - 6));
+    for (uint32_t u = blockIdx.x; u < n_units; u += gridDim.x) {
+      const uint32_t m = u >> 2, q = u & 3u, mp = revcomp_id(m, W - 6);
+      if (m > mp || (int)(m % (uint32_t)A.world) != A.rank) continue;  // CTA-uniform
+      const bool self = m == mp;
+      // X: rows a = 4 rx + q of tile m, thread t -> row rx = t >> 4, ids b0 .. b0 + 3
+      const uint32_t rx = t >> 4, b0 = (t & 15u) * 4u;
+      const uint64_t jX = ((uint64_t)(rx * 4u + q) << sh_a) | ((uint64_t)m << 6) | b0;
+      // Y: the 16-column band 3 - q of tile mp, thread t -> row ay = t >> 2, band columns yl0 .. yl0 + 3
+      const uint32_t ay = t >> 2, yl0 = (t & 3u) * 4u, band = 16u * (3u - q);
+      const uint64_t jY = ((uint64_t)ay << sh_a) | ((uint64_t)mp << 6) | (band + yl0);
+      uint4 vx[8], vy[8];
+#pragma unroll
+      for (int p = 0; p < 8; p++) {
+        if (p < A.world) {
+          vx[p] = ld_peer_u4(A.hist[p] + jX);
+          vy[p] = ld_peer_u4(A.hist[p] + jY);
+        }
+      }
+      uint4 sx = make_uint4(0, 0, 0, 0), sy = make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int p = 0; p < 8; p++) {
+        if (p < A.world) {
+          sx.x += vx[p].x; sx.y += vx[p].y; sx.z += vx[p].z; sx.w += vx[p].w;
+          sy.x += vy[p].x; sy.y += vy[p].y; sy.z += vy[p].z; sy.w += vy[p].w;
+        }
+      }
+      reinterpret_cast<uint4*>(tX)[t] = sx;  // tX[rx * 64 + b]
+      reinterpret_cast<uint4*>(tY)[t] = sy;  // tY[ay * 16 + yl]
+      __syncthreads();
+      // X ids: the partner of (a, b) sits at Y row revcomp3(b), band column (3 - a2) + 4 (3 - a1), a1 = rx & 3, a2 = rx >> 2
+      {
+        const uint32_t ylp = (3u - (rx >> 2)) + 4u * (3u - (rx & 3u));
+        uint64_t o[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const uint32_t b = b0 + i, ayp = revcomp3(b);
+          const uint64_t rj = ((uint64_t)ayp << sh_a) | ((uint64_t)mp << 6) | (band + ylp);
+          const uint32_t own = tX[t * 4 + i], other = tY[ayp * 16 + ylp];
+          o[i] = (jX + i == rj) ? (uint64_t)own : (uint64_t)own + other;
+        }
+#pragma unroll
+        for (int p = 0; p < 8; p++)
+          if (p < A.world) st_peer_4u64(A.counts[p] + jX, o[0], o[1], o[2], o[3]);
+      }
+      if (!self) {  // Y ids: the partner of (ay, band + yl) sits at X row (3 - (yl >> 2)) + 4 (3 - (yl & 3)), column revcomp3(ay)
+        const uint32_t bxp = revcomp3(ay);
+        uint64_t o[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const uint32_t yl = yl0 + i, rxp = (3u - (yl >> 2)) + 4u * (3u - (yl & 3u));
+          o[i] = (uint64_t)tY[t * 4 + i] + tX[rxp * 64 + bxp];
+        }
+#pragma unroll
+        for (int p = 0; p < 8; p++)
+          if (p < A.world) st_peer_4u64(A.counts[p] + jY, o[0], o[1], o[2], o[3]);
+      }
+      __syncthreads();
+    }
+  } else {
+    const uint64_t n_units = A.n >> 10;
+    for (uint64_t u = blockIdx.x; u < n_units; u += gridDim.x) {
+      if ((int)(u % (uint64_t)A.world) != A.rank) continue;
+      const uint64_t j = (u << 10) + t * 4u;
+      uint4 v[8];
+#pragma unroll
+      for (int p = 0; p < 8; p++)
+        if (p < A.world) v[p] = ld_peer_u4(A.hist[p] + j);
+      uint64_t o[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int p = 0; p < 8; p++)
+        if (p < A.world) { o[0] += v[p].x; o[1] += v[p].y; o[2] += v[p].z; o[3] += v[p].w; }
+#pragma unroll
+      for (int p = 0; p < 8; p++)
+        if (p < A.world) st_peer_4u64(A.counts[p] + j, o[0], o[1], o[2], o[3]);
+    }
+  }
+  // ---- depart ----
+  __threadfence_system();
+  __syncthreads();
+  if (t == 0) is_last = atomicAdd(my_flags + 8, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    if (t == 0) my_flags[8] = 0u;
+    if ((int)t < A.world) {
+      __threadfence_system();
+      st_release_sys(A.flags[t] + A.rank, A.epoch + 1u);
+    }
+    peer_wait_all(my_flags, A.world, A.epoch + 1u, err);
+  }
+}
+
 // second copy of the pair count at the reverse-complement id (src/base_pattern.cpp:387-392). Only
 // non-canonical entries are written and only canonical entries are read, so in place is race-free.
 __global__ void k_mirror(uint64_t* __restrict__ counts, int W, uint64_t n) {
@@ -1374,17 +1604,22 @@ __global__ void k_em_pairs(const uint64_t* __restrict__ counts, const double* __
   if (i < n) pairs[i] = make_double2((double)counts[id_begin + i], bg[id_begin + i]);
 }
 
+// rows of the private shared-memory columns: positions 2, 3 (one add per 16-id block) and positions >= 6 (one add per
+// 256-id unit); positions 0, 1 (per id) and 4, 5 (per unit, predicated adds) live in registers.  The same rows are reused
+// at the end to hand the 16 register sums to the cross-slot reduction.
+#define EM_ROWS(W) ((4 * (W) - 16) > 16 ? (4 * (W) - 16) : 16)
+
 template <int W>
-__global__ void __launch_bounds__(EM_NT, 1) k_em_accumulate_all(
+__global__ void __launch_bounds__(EM_NT, 2) k_em_accumulate_all(
     const double2* __restrict__ pairs /* indexed by id - (unit_begin << 8) */, const double* __restrict__ pwms /* [P][W*4] */,
     const int* __restrict__ active, int P, int R, double inv_saturation, uint32_t unit_begin, uint32_t unit_end,
     double* __restrict__ partials /* [P][nbx][W*4] */, int nbx) {
-  static_assert(W >= 4, "a unit is the 256 ids of the low 4 positions");
+  static_assert(W >= 6, "positions 0 .. 5 are handled in registers / per block");
   constexpr int WA = W * 4;
   extern __shared__ __align__(16) unsigned char em_smem[];
   double2* stage = reinterpret_cast<double2*>(em_smem);      // [EM_STAGES][R][16]
   double* spw = reinterpret_cast<double*>(stage + EM_STAGES * R * 16);  // [WA][P]: entry-major, the PWMs of a warp side by side
-  double* sacc = spw + WA * P;                                // [WA][EM_NT]: one private column per thread
+  double* sacc = spw + WA * P;                                // [EM_ROWS(W)][EM_NT]: one private column per thread
   const int t = threadIdx.x;
   const int r = t / P, m = t - r * P;
   const bool worker = r < R;
@@ -1395,7 +1630,7 @@ __global__ void __launch_bounds__(EM_NT, 1) k_em_accumulate_all(
     spw[e * P + mm] = pwms[i];
   }
 #pragma unroll 4
-  for (int e = 0; e < WA; e++) sacc[e * EM_NT + t] = 0.0;
+  for (int e = 0; e < EM_ROWS(W); e++) sacc[e * EM_NT + t] = 0.0;
   // ---- slots: slot s of S = gridDim.x * R owns the units [lo(s), lo(s + 1)) ----
   const uint32_t S = gridDim.x * (uint32_t)R, n_units = unit_end - unit_begin;
   auto slot_lo = [&](uint32_t s) { return (uint32_t)((uint64_t)n_units * s / S); };  // relative to unit_begin
@@ -1428,7 +1663,7 @@ __global__ void __launch_bounds__(EM_NT, 1) k_em_accumulate_all(
   // compute role
   const uint32_t my_lo = worker ? slot_lo(s0 + r) : 0u;
   const uint32_t my_n = live ? ((slot_lo(s0 + r + 1) - my_lo) << 4) : 0u;
-  double pw0[4], pw1[4], acc0[4] = {0, 0, 0, 0}, acc1[4] = {0, 0, 0, 0};
+  double pw0[4], pw1[4], acc0[4] = {0, 0, 0, 0}, acc1[4] = {0, 0, 0, 0}, acc4[4] = {0, 0, 0, 0}, acc5[4] = {0, 0, 0, 0};
 #pragma unroll
   for (int a = 0; a < 4; a++) {
     pw0[a] = live ? spw[a * P + m] : 0.0;
@@ -1452,56 +1687,80 @@ __global__ void __launch_bounds__(EM_NT, 1) k_em_accumulate_all(
       }
       const uint32_t d2 = b & 3u, d3 = b >> 2;
       const double2* src = stage + ((k % EM_STAGES) * R + r) * 16;
-      double2 v[16];
-      unsigned long long any = 0;
+      const double pre2 = pre4 * spw[(12 + d3) * P + m] * spw[(8 + d2) * P + m];
+      double blk = 0.0;
 #pragma unroll
-      for (int i = 0; i < 16; i++) {
-        v[i] = src[i];
-        any |= (unsigned long long)__double_as_longlong(v[i].x);
-      }
-      if (any) {  // counts are >= 0: the bit pattern is zero exactly for an empty bin
-        const double pre2 = pre4 * spw[(12 + d3) * P + m] * spw[(8 + d2) * P + m];
-        double blk = 0.0;
+      for (int half = 0; half < 2; half++) {  // 8 ids at a time: 32 registers of table data in flight
+        double2 v[8];
+        unsigned long long any = 0;
 #pragma unroll
-        for (int d1 = 0; d1 < 4; d1++) {
-          const unsigned long long any4 = (unsigned long long)__double_as_longlong(v[4 * d1].x) | (unsigned long long)__double_as_longlong(v[4 * d1 + 1].x) |
-                                          (unsigned long long)__double_as_longlong(v[4 * d1 + 2].x) | (unsigned long long)__double_as_longlong(v[4 * d1 + 3].x);
-          if (any4) {
-            const double p1 = pre2 * pw1[d1];
-            double tt[4];
+        for (int i = 0; i < 8; i++) {
+          v[i] = src[8 * half + i];
+          any |= (unsigned long long)__double_as_longlong(v[i].x);  // counts are >= 0: the bit pattern is zero exactly for an empty bin
+        }
+        if (any) {
 #pragma unroll
-            for (int d0 = 0; d0 < 4; d0++) {
-              const double prob = p1 * pw0[d0];
-              const double2 cb = v[4 * d1 + d0];
-              tt[d0] = (cb.x * prob) * em_rcp(prob + cb.y);
-              acc0[d0] += tt[d0];
+          for (int dd = 0; dd < 2; dd++) {
+            const int d1 = 2 * half + dd;
+            const unsigned long long any4 = (unsigned long long)__double_as_longlong(v[4 * dd].x) | (unsigned long long)__double_as_longlong(v[4 * dd + 1].x) |
+                                            (unsigned long long)__double_as_longlong(v[4 * dd + 2].x) | (unsigned long long)__double_as_longlong(v[4 * dd + 3].x);
+            if (any4) {
+              const double p1 = pre2 * pw1[d1];
+              double tt[4];
+#pragma unroll
+              for (int d0 = 0; d0 < 4; d0++) {
+                const double prob = p1 * pw0[d0];
+                const double2 cb = v[4 * dd + d0];
+                tt[d0] = (cb.x * prob) * em_rcp(prob + cb.y);
+                acc0[d0] += tt[d0];
+              }
+              const double g = (tt[0] + tt[1]) + (tt[2] + tt[3]);
+              acc1[d1] += g;
+              blk += g;
             }
-            const double g = (tt[0] + tt[1]) + (tt[2] + tt[3]);
-            acc1[d1] += g;
-            blk += g;
           }
         }
-        sacc[(8 + d2) * EM_NT + t] += blk;
-        sacc[(12 + d3) * EM_NT + t] += blk;
-        unit_total += blk;
       }
+      sacc[d2 * EM_NT + t] += blk;
+      sacc[(4 + d3) * EM_NT + t] += blk;
+      unit_total += blk;
       if (b == 15u) {
+        const uint32_t d4 = u & 3u, d5 = (u >> 2) & 3u;
 #pragma unroll
-        for (int q = 4; q < W; q++) sacc[(q * 4 + ((u >> (2 * (q - 4))) & 3u)) * EM_NT + t] += unit_total;
+        for (int a = 0; a < 4; a++) {
+          acc4[a] += d4 == (uint32_t)a ? unit_total : 0.0;
+          acc5[a] += d5 == (uint32_t)a ? unit_total : 0.0;
+        }
+#pragma unroll
+        for (int q = 6; q < W; q++) sacc[(8 + (q - 6) * 4 + ((u >> (2 * (q - 4))) & 3u)) * EM_NT + t] += unit_total;
       }
     }
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  // ---- the R slots of a PWM are added in fixed order: first the shared-memory rows (positions 2, 3, >= 6) ... ----
+  for (int i = t; i < P * (WA - 16); i += EM_NT) {
+    const int mm = i / (WA - 16), row = i - mm * (WA - 16);
+    const int e = row < 8 ? 8 + row : 16 + row;  // row -> entry p * 4 + a: rows 0 .. 7 are positions 2, 3, rows 8 .. are positions 6 ..
+    double sum = 0.0;
+    for (int rr = 0; rr < R; rr++) sum += sacc[row * EM_NT + rr * P + mm];
+    partials[((size_t)mm * nbx + blockIdx.x) * WA + e] = sum;
+  }
+  __syncthreads();
+  // ... then the register sums (positions 0, 1, 4, 5) through the same rows
 #pragma unroll
   for (int a = 0; a < 4; a++) {
     sacc[a * EM_NT + t] = acc0[a];
     sacc[(4 + a) * EM_NT + t] = acc1[a];
+    sacc[(8 + a) * EM_NT + t] = acc4[a];
+    sacc[(12 + a) * EM_NT + t] = acc5[a];
   }
   __syncthreads();
-  for (int i = t; i < P * WA; i += EM_NT) {
-    const int mm = i / WA, e = i - mm * WA;
+  for (int i = t; i < P * 16; i += EM_NT) {
+    const int mm = i >> 4, row = i & 15;
+    const int e = row < 8 ? row : 8 + row;  // rows 8 .. 15 are positions 4, 5
     double sum = 0.0;
-    for (int rr = 0; rr < R; rr++) sum += sacc[e * EM_NT + rr * P + mm];
+    for (int rr = 0; rr < R; rr++) sum += sacc[row * EM_NT + rr * P + mm];
     partials[((size_t)mm * nbx + blockIdx.x) * WA + e] = sum;
   }
 }
@@ -1781,6 +2040,8 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   if (!h) return;
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
+  peng_cuda_peer_detach(h);
+  dev_free(&h->peer.d_flags);
   dev_free(&h->d_codes); dev_free(&h->d_valid); dev_free(&h->d_sstart); dev_free(&h->d_kstart);
   dev_free(&h->d_offsets); dev_free(&h->d_hist32); dev_free(&h->d_counts); dev_free(&h->d_bgcounts);
   dev_free(&h->d_v32); dev_free(&h->d_v64);
@@ -1853,6 +2114,8 @@ static int alloc_stream(peng_handle_t h, uint64_t n_seq, uint64_t total_bases) {
     TRY(dev_alloc(h, &h->d_valid, h->n_words32 + 8));
     TRY(dev_alloc(h, &h->d_sstart, h->n_words32 + 8));
     TRY(dev_alloc(h, &h->d_kstart, h->n_words32 + 8));
+    TRY(dev_alloc(h, &h->d_planes, h->n_words32 + 8));
+    h->cap_planes = h->n_words32 + 8;
     h->cap_words32 = h->n_words32;
   }
   // the few guard words behind n_words32 are read by funnel shifts at the very end of the stream
@@ -1860,6 +2123,9 @@ static int alloc_stream(peng_handle_t h, uint64_t n_seq, uint64_t total_bases) {
   CU(h, cudaMemsetAsync(h->d_valid + h->n_words32, 0, 8 * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_sstart + h->n_words32, 0, 8 * 4, h->stream));
   CU(h, cudaMemsetAsync(h->d_kstart + h->n_words32, 0, 8 * 4, h->stream));  // the rest is written by every count
+  CU(h, cudaMemsetAsync(h->d_planes + h->n_words32, 0, 8 * sizeof(uint2), h->stream));
+  h->planes_from = h->n_words32;  // no word has its planes yet
+  h->pre.done = false;
   h->counts_final = false;
   h->stats_ready = false;
   h->planes_valid = false;
@@ -1921,10 +2187,10 @@ static int launch_pack(peng_handle_t h, const uint8_t* d_src, bool ascii, uint64
   const unsigned block = 256;
   if (ascii)
     k_pack<true><<<grid_for(t_end - t_begin, block), block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid,
-                                                                          h->d_sstart, t_begin, t_end);
+                                                                          h->d_sstart, h->d_planes, t_begin, t_end);
   else
     k_pack<false><<<grid_for(t_end - t_begin, block), block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid,
-                                                                           h->d_sstart, t_begin, t_end);
+                                                                           h->d_sstart, h->d_planes, t_begin, t_end);
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
@@ -1945,6 +2211,7 @@ static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64
   TRY(prepare_ingest(h, offsets, n_seq));
   CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
   TRY(launch_pack(h, d_src, ascii, 0, h->n_words32));
+  h->planes_valid = true;
   h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping in the shadow of the device work
   seq_lengths(h, offsets, n_seq);
   return PENG_OK;
@@ -2045,6 +2312,9 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     CU(h, cudaHostAlloc((void**)&h->pin_offs, (n_seq + 1 + (n_seq >> 2)) * sizeof(uint64_t), cudaHostAllocDefault));
     h->pin_offs_cap = n_seq + 1 + (n_seq >> 2);
   }
+  // count prefetch: stage P of the armed count follows the data as it lands (see PrefetchRun / prefetch_range)
+  PrefetchRun pr;
+  TRY(prefetch_begin(h, &pr));
   CU(h, cudaEventRecord(h->copy_ev[0], h->stream));
   CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
   mark(2);
@@ -2066,6 +2336,9 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     CU(h, cudaEventRecord(h->copy_ev[0], h->copy_stream));
     CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[0], 0));
     TRY(launch_pack(h, d_src, ascii, blk_split * 2, h->n_words32));
+    // the units behind the one that holds the first position of sequence s_split look at k_pack's words only (every
+    // look-back of the k-mer start rule stops at that sequence's start): their stage P runs under the DMA of the phases
+    if (pr.on) TRY(prefetch_range(h, &pr, (q_split >> 5) + 1, h->n_words32));
   }
   // ---- the packed part, phase by phase through the two pinned staging buffers ----
   bool has_carry = false;
@@ -2113,6 +2386,15 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
       CU(h, cudaMemcpyAsync(h->d_valid + blk0 * 2, valid64, (blk1 - blk0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
     }
     CU(h, cudaEventRecord(h->pin_ev[buf], h->copy_stream));
+    if (pr.on && blk1 > blk0) {  // the blocks of this phase once they have landed: bit planes, then stage P up to two units short of the frontier
+      CU(h, cudaStreamWaitEvent(h->stream, h->pin_ev[buf], 0));
+      TRY(make_planes(h, pr.planes_done, blk1 * 2));
+      pr.planes_done = blk1 * 2;
+      if (blk1 * 2 >= 2) {
+        TRY(prefetch_range(h, &pr, pr.done_u, blk1 * 2 - 2));
+        pr.done_u = std::max(pr.done_u, blk1 * 2 - 2);
+      }
+    }
     t_issue += now() - t0;
     buf ^= 1;
     first = false;
@@ -2126,6 +2408,13 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[1], 0));  // the offsets and every staged block have arrived
   k_sstart_scatter<<<grid_for(std::max<uint64_t>(n_seq, 1), 256), 256, 0, h->stream>>>(h->d_offsets, n_seq, t_split, h->d_sstart);
   LAUNCH_CHECK(h);
+  // k_pack wrote the planes of its words; those of the host-packed words follow here (what the prefetch has not made yet)
+  TRY(make_planes(h, pr.planes_done, t_split));
+  h->planes_valid = true;
+  if (pr.on) {  // what is left of stage P: the front's last units and the units around the split
+    TRY(prefetch_range(h, &pr, pr.done_u, s_split < n_seq ? std::min<uint64_t>((q_split >> 5) + 1, h->n_words32) : h->n_words32));
+    h->pre.done = true;
+  }
   const double t_loop = now();
   const double t_book = now();
   CU(h, cudaStreamSynchronize(h->stream));
@@ -2183,6 +2472,7 @@ static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* 
     t_done = std::max(t_done, t_end);
     if (total == 0) break;
   }
+  h->planes_valid = true;
   h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping while the DMA engine works
   seq_lengths(h, offsets, n_seq);
   CU(h, cudaStreamSynchronize(h->stream));  // the caller may free / reuse src
@@ -2306,6 +2596,7 @@ extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_
   CU(h, cudaEventRecord(h->copy_ev[1], h->copy_stream));
   CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[1], 0));
   TRY(launch_pack(h, sink.d_src, true, 0, h->n_words32));
+  h->planes_valid = true;
   seq_lengths(h, sink.offsets.data(), ns);
   h->h_offsets.swap(sink.offsets);
   CU(h, cudaStreamSynchronize(h->stream));
@@ -2343,8 +2634,9 @@ extern "C" int peng_cuda_ingest_synthetic(peng_handle_t h, uint64_t n_seq, uint3
     P.motif_bits |= (uint64_t)c << (2 * i);
   }
   const unsigned block = 256;
-  k_synth<<<grid_for(h->n_words32, block), block, 0, h->stream>>>(P, h->d_codes, h->d_valid, h->d_sstart, h->n_words32);
+  k_synth<<<grid_for(h->n_words32, block), block, 0, h->stream>>>(P, h->d_codes, h->d_valid, h->d_sstart, h->d_planes, h->n_words32);
   LAUNCH_CHECK(h);
+  h->planes_valid = true;
   return PENG_OK;
 }
 
@@ -2381,23 +2673,24 @@ extern "C" int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes, uint64_t*
 // C ABI: counting
 // =====================================================================================================
 // bit planes of the codes (core_seq.cuh: conflict_candidates_planes), once per ingest, by the first count that wants them
-__global__ void __launch_bounds__(256) k_make_planes(const uint2* __restrict__ codes, uint2* __restrict__ planes, uint64_t n_words32) {
-  const uint64_t u = (uint64_t)blockIdx.x * 256 + threadIdx.x;
-  if (u >= n_words32) return;
+__global__ void __launch_bounds__(256) k_make_planes(const uint2* __restrict__ codes, uint2* __restrict__ planes, uint64_t begin, uint64_t end) {
+  const uint64_t u = begin + (uint64_t)blockIdx.x * 256 + threadIdx.x;
+  if (u >= end) return;
   const uint2 c = __ldg(codes + u);
   uint2 o;
   planes_of_unit(c.x, c.y, &o.x, &o.y);
   planes[u] = o;
 }
+// the planes of the words no packing kernel produced (the part of a hybrid ingest the host threads packed)
+static int make_planes(peng_handle_t h, uint64_t begin, uint64_t end) {
+  if (end <= begin) return PENG_OK;
+  k_make_planes<<<grid_for(end - begin, 256), 256, 0, h->stream>>>(reinterpret_cast<const uint2*>(h->d_codes), h->d_planes, begin, end);
+  LAUNCH_CHECK(h);
+  return PENG_OK;
+}
 static int ensure_planes(peng_handle_t h) {
   if (h->planes_valid) return PENG_OK;
-  if (h->cap_planes < h->n_words32 + 8) {
-    TRY(dev_alloc(h, &h->d_planes, h->n_words32 + 8));
-    h->cap_planes = h->n_words32 + 8;
-  }
-  CU(h, cudaMemsetAsync(h->d_planes + h->n_words32, 0, 8 * sizeof(uint2), h->stream));
-  k_make_planes<<<grid_for(h->n_words32, 256), 256, 0, h->stream>>>(reinterpret_cast<const uint2*>(h->d_codes), h->d_planes, h->n_words32);
-  LAUNCH_CHECK(h);
+  TRY(make_planes(h, 0, std::min<uint64_t>(h->planes_from, h->n_words32)));
   h->planes_valid = true;
   return PENG_OK;
 }
@@ -2409,6 +2702,7 @@ struct PartArgs {
   uint32_t region_cap;
   void* buckets;
   uint32_t* fill;
+  uint32_t carry_fill = 0;
 };
 template <int W, bool BOTH, int NT, uint32_t CAP, int PER_SM, bool LINK, bool PL = true>
 static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
@@ -2419,7 +2713,8 @@ static int launch_part_cfg(peng_handle_t h, const PartArgs& a) {
   CU(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p));
   kern<<<a.grid, NT, smem_p, h->stream>>>(h->d_codes, h->d_planes, h->d_valid, h->d_kstart, h->n_words32, a.ub, a.ue,
                                           (typename G::entry_t*)a.buckets, a.region_cap, a.fill, h->d_hist32,
-                                          (unsigned long long*)(h->d_counts + h->n_patterns), h->d_slow_list, h->d_slow_count, 0u);
+                                          (unsigned long long*)(h->d_counts + h->n_patterns), h->d_slow_list, h->d_slow_count, 0u,
+                                          a.carry_fill);
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
@@ -2454,13 +2749,13 @@ static int launch_slow_beside(peng_handle_t h, bool both, bool mark) {
 
 // Partition path driver: stage P (+ fused k-mer start marking), slow units, stage H; chunks of <= 2^30 positions so
 // that a uint32 bin cannot overflow between folds.
-template <int W>
-static int launch_count_partition(peng_handle_t h, bool both) {
-  const uint64_t n_units = h->n_words32;
-  const uint64_t units_per_chunk = 1ull << 25;
-  const int cfg = h->part_cfg;
-  const unsigned grid_p = (unsigned)h->sm_count * part_cfg_per_sm(cfg);
-  const uint64_t chunk_units = std::min(n_units, units_per_chunk);
+struct PartPlan {
+  unsigned grid_p;
+  uint32_t region_cap;
+  size_t smem_h;
+};
+static int part_reserve(peng_handle_t h, uint64_t chunk_units, PartPlan* pl) {
+  const unsigned grid_p = (unsigned)h->sm_count * part_cfg_per_sm(h->part_cfg);
   // private region of (class, stage-P CTA): 2x the expected share (composition skew of real genomes: a class of an AT-rich set takes ~1.6x its uniform share), at least 1024 keys, multiple of 128
   uint64_t region_cap = (chunk_units * 32 * 2) / ((uint64_t)grid_p * PART_NCLASS);
   region_cap = std::max<uint64_t>(1024, (region_cap + 127) & ~127ull);
@@ -2478,23 +2773,52 @@ static int launch_count_partition(peng_handle_t h, bool both) {
     TRY(dev_alloc(h, &h->d_slow_list, (size_t)chunk_units));
     h->slow_list_elems = chunk_units;
   }
-  const size_t smem_h = (size_t)(part_class_start(1) + 1) * 4;
-  CU(h, cudaFuncSetAttribute(k_hist_part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_h));
+  pl->grid_p = grid_p;
+  pl->region_cap = (uint32_t)region_cap;
+  pl->smem_h = (size_t)(part_class_start(1) + 1) * 4;
+  CU(h, cudaFuncSetAttribute(k_hist_part, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem_h));
+  return PENG_OK;
+}
+// stage P on the units [ub, ue); carry: behind the keys an earlier launch of the same count left in the bucket regions
+template <int W>
+static int part_stage_p(peng_handle_t h, bool both, const PartPlan& pl, uint64_t ub, uint64_t ue, bool carry) {
+  if (ue <= ub) return PENG_OK;
+  PartArgs a{ub, ue, pl.grid_p, pl.region_cap, h->d_part_buckets, h->d_part_fill};
+  a.carry_fill = carry ? 1u : 0u;
+  return both ? launch_part<W, true>(h, h->part_cfg, a) : launch_part<W, false>(h, h->part_cfg, a);
+}
+// slow units (side stream) beside stage H, joined
+template <int W>
+static int part_stage_h(peng_handle_t h, bool both, const PartPlan& pl, bool mark) {
+  TRY(launch_slow_beside<W>(h, both, mark));
+  if (mark) MARK(h, 8);
+  k_hist_part<<<PART_NCLASS * PART_CPC, PART_HT, pl.smem_h, h->stream>>>(h->d_part_buckets, pl.region_cap, pl.grid_p, h->d_part_fill,
+                                                                        h->d_hist32);
+  LAUNCH_CHECK(h);
+  CU(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
+  if (mark) MARK(h, 7);
+  return PENG_OK;
+}
+
+template <int W>
+static int launch_count_partition(peng_handle_t h, bool both) {
+  const uint64_t n_units = h->n_words32;
+  const uint64_t units_per_chunk = 1ull << 25;
+  PartPlan pl;
+  TRY(part_reserve(h, std::min(n_units, units_per_chunk), &pl));
+  if (h->pre.done) {  // stage P already ran, range by range, under the DMA of the ingest (peng_cuda_set_count_prefetch)
+    MARK(h, 6); MARK(h, 2);
+    TRY(part_stage_h<W>(h, both, pl, true));
+    h->used_partition = true;
+    return PENG_OK;
+  }
   for (uint64_t ub = 0; ub < n_units; ub += units_per_chunk) {
     const uint64_t ue = std::min(n_units, ub + units_per_chunk);
     CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
-    const PartArgs a{ub, ue, grid_p, (uint32_t)region_cap, h->d_part_buckets, h->d_part_fill};
     if (ub == 0) MARK(h, 6);  // phases 3..5 time the stages of the FIRST chunk (a full one whenever there are several)
-    const int rc_p = both ? launch_part<W, true>(h, cfg, a) : launch_part<W, false>(h, cfg, a);
-    TRY(rc_p);
+    TRY(part_stage_p<W>(h, both, pl, ub, ue, false));
     if (ub == 0) MARK(h, 2);
-    TRY(launch_slow_beside<W>(h, both, ub == 0));
-    if (ub == 0) MARK(h, 8);
-    k_hist_part<<<PART_NCLASS * PART_CPC, PART_HT, smem_h, h->stream>>>(h->d_part_buckets, (uint32_t)region_cap, grid_p,
-                                                                      h->d_part_fill, h->d_hist32);
-    LAUNCH_CHECK(h);
-    CU(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
-    if (ub == 0) MARK(h, 7);
+    TRY(part_stage_h<W>(h, both, pl, ub == 0));
     if (ue < n_units) {
       if (both) TRY(launch_fold_canon(h, W, false, false));
       else k_fold<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
@@ -2505,6 +2829,47 @@ static int launch_count_partition(peng_handle_t h, bool both) {
   return PENG_OK;
 }
 
+
+// Count prefetch inside the hybrid ingest (peng_cuda_set_count_prefetch): tables and buckets of the armed count are set up
+// before the first byte moves; prefetch_range runs stage P on a unit range whose words have landed.
+static int prefetch_begin(peng_handle_t h, PrefetchRun* pr) {
+  h->pre.done = false;
+  pr->on = false;
+  const int W = h->pre.W;
+  if (W != 10 || h->n_words32 > (1ull << 25) || !use_partition(h, W)) return PENG_OK;  // the one-level partition path, one chunk
+  const uint64_t n = 1ull << (2 * W);
+  TRY(ensure_count_tables(h, W));
+  h->counts_final = false;
+  h->count_pending = false;
+  h->stats_ready = false;
+  if (!h->hist_clean) CU(h, cudaMemsetAsync(h->d_hist32, 0, (n + 4) * 4, h->stream));
+  h->hist_clean = false;
+  CU(h, cudaMemsetAsync(h->d_counts + n, 0, 8, h->stream));
+  PartPlan pl;
+  TRY(part_reserve(h, h->n_words32, &pl));
+  CU(h, cudaMemsetAsync(h->d_slow_count, 0, 4, h->stream));
+  pr->grid_p = pl.grid_p;
+  pr->region_cap = pl.region_cap;
+  pr->smem_h = pl.smem_h;
+  pr->on = true;
+  pr->first = true;
+  return PENG_OK;
+}
+static int prefetch_range(peng_handle_t h, PrefetchRun* pr, uint64_t ub, uint64_t ue) {
+  if (ue <= ub) return PENG_OK;
+  const PartPlan pl{pr->grid_p, pr->region_cap, pr->smem_h};
+  TRY(part_stage_p<10>(h, h->pre.strand == PENG_STRAND_BOTH, pl, ub, ue, !pr->first));
+  pr->first = false;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_set_count_prefetch(peng_handle_t h, int W, int strand) {
+  if (!h || (strand != PENG_STRAND_PLUS && strand != PENG_STRAND_BOTH)) return fail(h, PENG_E_INVALID, "set_count_prefetch: bad argument");
+  h->pre.W = W == 10 ? 10 : 0;  // other pattern lengths: the hint is ignored, the count runs in one piece as before
+  h->pre.strand = strand;
+  h->pre.done = false;
+  return PENG_OK;
+}
 
 // Deep partition path driver (W = 12, 14, 16), see k_part2.  Chunks of <= 2^30 positions bound the bucket memory; the
 // uint32 table is folded into the 64-bit one only when a bin could overflow (2^32 positions since the last fold).
@@ -2690,24 +3055,42 @@ static int launch_count_W(peng_handle_t h, bool both) {
   }
 }
 
+// the uint32 launch table and the 64-bit table of pattern length W (kept while W stays the same)
+static int ensure_count_tables(peng_handle_t h, int W) {
+  const uint64_t n = 1ull << (2 * W);
+  if (h->W != W || !h->d_counts) {
+    if (h->peer.attached) return fail(h, PENG_E_INVALID, "the count tables of W = %d are shared with the peer group: peng_cuda_peer_detach first", h->peer.W);
+    free_tables(h);
+    TRY(dev_alloc(h, &h->d_hist32, n + 4));
+    TRY(dev_alloc(h, &h->d_counts, n + 1));
+    h->W = W;
+    h->n_patterns = n;
+    h->counts_final = false;
+    h->count_pending = false;
+    h->hist_clean = false;
+  }
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   if (!h || !h->d_codes) return fail(h, PENG_E_INVALID, "count: no sequences ingested");
   if (W < 2 || W > PENG_MAX_W || (W & 1)) return fail(h, PENG_E_INVALID, "count: pattern length %d must be even and in [2,16]", W);
   if (strand != PENG_STRAND_PLUS && strand != PENG_STRAND_BOTH) return fail(h, PENG_E_INVALID, "count: bad strand");
   CU(h, cudaSetDevice(h->device));
   const uint64_t n = 1ull << (2 * W);
-  if (h->W != W || !h->d_counts) {
-    free_tables(h);
-    TRY(dev_alloc(h, &h->d_hist32, n + 4));
-    TRY(dev_alloc(h, &h->d_counts, n + 1));
-  }
+  TRY(ensure_count_tables(h, W));
   h->W = W;
   h->strand = strand;
   h->n_patterns = n;
   h->counts_final = false;
+  h->count_pending = false;
   h->stats_ready = false;
   h->counts_sliced = false;
-  CU(h, cudaMemsetAsync(h->d_hist32, 0, (n + 4) * 4, h->stream));
+  // stage P of exactly this count already ran inside the ingest: the launch table and the ltot word hold its part
+  const bool prefetched = h->pre.done && h->pre.W == W && h->pre.strand == strand && use_partition(h, W) && h->n_words32 <= (1ull << 25);
+  h->pre.done = prefetched;
+  if (!prefetched && !h->hist_clean) CU(h, cudaMemsetAsync(h->d_hist32, 0, (n + 4) * 4, h->stream));
+  h->hist_clean = false;
   const bool both = strand == PENG_STRAND_BOTH;
   const bool partition = use_partition(h, W);
   // up to 2^30 stream positions (pads included) every path folds exactly once, at the end; the deep partition path
@@ -2715,7 +3098,8 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
   // fold WRITES the whole 64-bit table: no clearing pass, no read of the old values, the mirror copy in the same kernel.
   const bool single_chunk = h->n_words32 <= (1ull << 25);
   const bool single_fold = single_chunk || (partition && W >= 12 && h->n_words32 * 32 <= 0xFFFFFFFFull);
-  if (single_fold) CU(h, cudaMemsetAsync(h->d_counts + n, 0, 8, h->stream));
+  if (prefetched) {}
+  else if (single_fold) CU(h, cudaMemsetAsync(h->d_counts + n, 0, 8, h->stream));
   else CU(h, cudaMemsetAsync(h->d_counts, 0, (n + 1) * 8, h->stream));
   h->mirrored = false;
   h->used_partition = false;
@@ -2757,6 +3141,8 @@ extern "C" int peng_cuda_count_local(peng_handle_t h, int W, int strand) {
     LAUNCH_CHECK(h);
   }
   MARK(h, 5);
+  h->pre.done = false;                // consumed: a second count of the same set starts from scratch
+  h->hist_clean = !h->fold_deferred;  // every fold kernel zeroes the bins it reads
   return PENG_OK;
 }
 
@@ -2811,6 +3197,7 @@ extern "C" int peng_cuda_count_finish32(peng_handle_t h, uint64_t* ltot) {
     LAUNCH_CHECK(h);
   }
   h->fold_deferred = false;
+  h->hist_clean = true;
   return peng_cuda_count_finish(h, ltot);
 }
 
@@ -2852,19 +3239,38 @@ extern "C" int peng_cuda_table_slice(peng_handle_t h, uint64_t* lo, uint64_t* hi
   return PENG_OK;
 }
 
+// device half of the finish: everything that is left to do on the stream (the mirror copy where no earlier kernel wrote it)
+static int count_finish_device(peng_handle_t h) {
+  if (h->strand == PENG_STRAND_BOTH && !h->mirrored) {
+    TRY(launch_mirror(h));
+    h->mirrored = true;
+  }
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
   if (!h || !h->d_counts) return fail(h, PENG_E_INVALID, "count_finish: nothing counted");
   if (h->fold_deferred) return fail(h, PENG_E_INVALID, "count_finish: the table is unfolded (peng_cuda_count_finish32)");
   CU(h, cudaSetDevice(h->device));
   if (!h->counts_final) {
-    if (h->strand == PENG_STRAND_BOTH && !h->mirrored) {
-      TRY(launch_mirror(h));
-    }
+    TRY(count_finish_device(h));
+    uint32_t peer_err = 0;
     CU(h, cudaMemcpyAsync(&h->ltot, h->d_counts + h->n_patterns, 8, cudaMemcpyDeviceToHost, h->stream));
+    if (h->peer.attached) CU(h, cudaMemcpyAsync(&peer_err, h->peer.d_flags + 9, 4, cudaMemcpyDeviceToHost, h->stream));
     CU(h, cudaStreamSynchronize(h->stream));
+    if (peer_err) {
+      cudaMemsetAsync(h->peer.d_flags + 9, 0, 4, h->stream);
+      return fail(h, PENG_E_CUDA, "peer exchange: a rank of the peer group did not arrive within 2 s — the count table is incomplete");
+    }
     h->counts_final = true;
+    h->count_pending = false;
   }
   if (ltot) *ltot = h->ltot;
+  return PENG_OK;
+}
+// consumers of the finished table: fetch ltot now if the count was left pending (ltot == NULL in peng_cuda_count / _count_exchange32)
+static int ensure_final(peng_handle_t h) {
+  if (h && !h->counts_final && h->count_pending && !h->fold_deferred) return peng_cuda_count_finish(h, nullptr);
   return PENG_OK;
 }
 
@@ -2873,10 +3279,134 @@ extern "C" int peng_cuda_count(peng_handle_t h, int W, int strand, uint64_t* lto
   const int rc = peng_cuda_count_local(h, W, strand);
   if (h) h->fuse_mirror = false;
   TRY(rc);
+  if (!ltot) {  // no read-back, no synchronisation: the table is complete in stream order, ltot is fetched by whoever asks first
+    TRY(count_finish_device(h));
+    h->count_pending = true;
+    return PENG_OK;
+  }
+  return peng_cuda_count_finish(h, ltot);
+}
+
+// ---- peer group ---------------------------------------------------------------------------------------------------------
+struct PeerBlob {
+  uint32_t magic;
+  int32_t W, device, pid;
+  uint64_t hist, counts, flags;  // raw device pointers (used when exporter and attacher are the same process)
+  cudaIpcMemHandle_t ipc_hist, ipc_counts, ipc_flags;
+};
+static_assert(sizeof(PeerBlob) <= 256, "PENG_PEER_BLOB_BYTES");
+#define PEER_MAGIC 0x50454E47u
+
+extern "C" int peng_cuda_peer_export(peng_handle_t h, int W, void* blob) {
+  if (!h || !blob) return fail(h, PENG_E_INVALID, "peer_export: NULL argument");
+  if (W < 8 || W > PENG_MAX_W || (W & 1)) return fail(h, PENG_E_INVALID, "peer_export: the fused exchange covers W = 8 .. 16");
+  CU(h, cudaSetDevice(h->device));
+  if (h->peer.attached) return fail(h, PENG_E_INVALID, "peer_export: already attached (peng_cuda_peer_detach first)");
+  TRY(ensure_count_tables(h, W));
+  if (!h->peer.d_flags) {
+    TRY(dev_alloc(h, &h->peer.d_flags, (size_t)64));
+    CU(h, cudaMemsetAsync(h->peer.d_flags, 0, 64 * 4, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+  }
+  PeerBlob b;
+  memset(&b, 0, sizeof b);
+  b.magic = PEER_MAGIC;
+  b.W = W;
+  b.device = h->device;
+  b.pid = (int32_t)getpid();
+  b.hist = (uint64_t)h->d_hist32;
+  b.counts = (uint64_t)h->d_counts;
+  b.flags = (uint64_t)h->peer.d_flags;
+  CU(h, cudaIpcGetMemHandle(&b.ipc_hist, h->d_hist32));
+  CU(h, cudaIpcGetMemHandle(&b.ipc_counts, h->d_counts));
+  CU(h, cudaIpcGetMemHandle(&b.ipc_flags, h->peer.d_flags));
+  memset(blob, 0, 256);
+  memcpy(blob, &b, sizeof b);
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_peer_detach(peng_handle_t h) {
+  if (!h) return PENG_E_INVALID;
+  cudaSetDevice(h->device);
+  if (h->peer.attached) cudaStreamSynchronize(h->stream);
+  for (int k = 0; k < 3; k++)
+    for (int p = 0; p < 8; p++)
+      if (h->peer.opened[k][p]) { cudaIpcCloseMemHandle(h->peer.opened[k][p]); h->peer.opened[k][p] = nullptr; }
+  h->peer.attached = false;
+  h->peer.world = 1;
+  return PENG_OK;
+}
+
+extern "C" int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const void* blobs) {
+  if (!h || !blobs || world < 1 || world > 8 || rank < 0 || rank >= world) return fail(h, PENG_E_INVALID, "peer_attach: bad rank %d / world %d (1 .. 8)", rank, world);
+  if (h->peer.attached) return fail(h, PENG_E_INVALID, "peer_attach: already attached");
+  if (!h->peer.d_flags || !h->d_hist32) return fail(h, PENG_E_INVALID, "peer_attach: peng_cuda_peer_export first");
+  CU(h, cudaSetDevice(h->device));
+  const unsigned char* base = (const unsigned char*)blobs;
+  for (int p = 0; p < world; p++) {
+    PeerBlob b;
+    memcpy(&b, base + (size_t)p * 256, sizeof b);
+    if (b.magic != PEER_MAGIC || b.W != h->W) { peng_cuda_peer_detach(h); return fail(h, PENG_E_INVALID, "peer_attach: blob %d is not a peer export of W = %d", p, h->W); }
+    if (p == rank) {
+      h->peer.hist[p] = h->d_hist32; h->peer.counts[p] = h->d_counts; h->peer.flags[p] = h->peer.d_flags;
+    } else if (b.pid == (int32_t)getpid()) {  // another handle of this process: its pointers are valid here
+      if (b.device != h->device) {
+        const cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { peng_cuda_peer_detach(h); return fail(h, PENG_E_CUDA, "peer_attach: no peer access from device %d to %d: %s", h->device, b.device, cudaGetErrorString(e)); }
+        cudaGetLastError();
+      }
+      h->peer.hist[p] = (uint32_t*)b.hist; h->peer.counts[p] = (uint64_t*)b.counts; h->peer.flags[p] = (uint32_t*)b.flags;
+    } else {
+      void* ptr[3] = {nullptr, nullptr, nullptr};
+      const cudaIpcMemHandle_t* hs[3] = {&b.ipc_hist, &b.ipc_counts, &b.ipc_flags};
+      for (int k = 0; k < 3; k++) {
+        const cudaError_t e = cudaIpcOpenMemHandle(&ptr[k], *hs[k], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { peng_cuda_peer_detach(h); return fail(h, PENG_E_CUDA, "peer_attach: cudaIpcOpenMemHandle(rank %d): %s", p, cudaGetErrorString(e)); }
+        h->peer.opened[k][p] = ptr[k];
+      }
+      h->peer.hist[p] = (uint32_t*)ptr[0]; h->peer.counts[p] = (uint64_t*)ptr[1]; h->peer.flags[p] = (uint32_t*)ptr[2];
+    }
+  }
+  h->peer.rank = rank;
+  h->peer.world = world;
+  h->peer.W = h->W;
+  h->peer.epoch = 0;
+  h->peer.attached = true;
+  return PENG_OK;
+}
+
+// The multi-GPU counting step behind peng_cuda_count_local32: sum over the ranks, fold, mirror and publication of the
+// finished table on every rank in ONE kernel over peer memory (k_peer_exchange32).  Every rank of the group must call it.
+// ltot == NULL: nothing is read back and nothing waits.
+extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
+  if (!h || !h->d_hist32 || !h->fold_deferred) return fail(h, PENG_E_INVALID, "count_exchange32: no unfolded table (peng_cuda_count_local32 first)");
+  if (!h->peer.attached || h->peer.W != h->W) return fail(h, PENG_E_INVALID, "count_exchange32: no peer group for W = %d (peng_cuda_peer_export / _attach)", h->W);
+  CU(h, cudaSetDevice(h->device));
+  PeerArgs A;
+  for (int p = 0; p < 8; p++) { A.hist[p] = h->peer.hist[p]; A.counts[p] = h->peer.counts[p]; A.flags[p] = h->peer.flags[p]; }
+  A.rank = h->peer.rank;
+  A.world = h->peer.world;
+  A.W = h->W;
+  A.n = h->n_patterns;
+  h->peer.epoch += 2;
+  A.epoch = h->peer.epoch - 1;  // arrive = epoch, depart = epoch + 1
+  const bool both = h->strand == PENG_STRAND_BOTH;
+  const uint64_t n_units = both ? (4ull << (2 * (h->W - 6))) : (h->n_patterns >> 10);
+  const unsigned grid = (unsigned)std::min<uint64_t>(n_units, (uint64_t)h->sm_count * 2);
+  if (both) k_peer_exchange32<true><<<grid, 256, 0, h->stream>>>(A);
+  else k_peer_exchange32<false><<<grid, 256, 0, h->stream>>>(A);
+  LAUNCH_CHECK(h);
+  h->fold_deferred = false;
+  h->mirrored = true;
+  if (!ltot) {
+    h->count_pending = true;
+    return PENG_OK;
+  }
   return peng_cuda_count_finish(h, ltot);
 }
 
 extern "C" int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts) {
+  TRY(ensure_final(h));
   if (!h || !h->d_counts || !h->counts_final) return fail(h, PENG_E_INVALID, "get_counts: count table not final");
   CU(h, cudaSetDevice(h->device));
   // sliced count table: the slice only (out holds hi - lo elements, peng_cuda_table_slice)
@@ -2885,7 +3415,26 @@ extern "C" int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts) {
   return PENG_OK;
 }
 
+__global__ void k_narrow_u64(const uint64_t* __restrict__ in, uint32_t* __restrict__ out, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint32_t)in[i];
+}
+extern "C" int peng_cuda_get_counts32(peng_handle_t h, uint32_t* counts) {
+  TRY(ensure_final(h));
+  if (!h || !h->d_counts || !h->counts_final || !counts) return fail(h, PENG_E_INVALID, "get_counts32: count table not final");
+  if (h->counts_sliced) return fail(h, PENG_E_INVALID, "get_counts32: sliced count table (peng_cuda_get_counts)");
+  if (h->ltot > 0xFFFFFFFFull) return fail(h, PENG_E_INVALID, "get_counts32: %llu W-mers were looked at — a bin may exceed 32 bits (peng_cuda_get_counts)", (unsigned long long)h->ltot);
+  CU(h, cudaSetDevice(h->device));
+  TRY(need_scratch(h, h->n_patterns * 4));
+  k_narrow_u64<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_counts, (uint32_t*)h->d_scratch, h->n_patterns);
+  LAUNCH_CHECK(h);
+  CU(h, cudaMemcpyAsync(counts, h->d_scratch, h->n_patterns * 4, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uint64_t n, uint64_t* out) {
+  TRY(ensure_final(h));
   if (!h || !h->d_counts || !h->counts_final || (n && (!ids || !out))) return fail(h, PENG_E_INVALID, "gather_counts: count table not final");
   if (n == 0) return PENG_OK;
   for (uint64_t i = 0; i < n; i++)
@@ -2903,6 +3452,7 @@ extern "C" int peng_cuda_gather_counts(peng_handle_t h, const uint64_t* ids, uin
 }
 
 extern "C" int peng_cuda_counts_total(peng_handle_t h, uint64_t* total) {
+  TRY(ensure_final(h));
   if (!h || !h->d_counts || !h->counts_final || !total) return fail(h, PENG_E_INVALID, "counts_total: count table not final");
   CU(h, cudaSetDevice(h->device));
   TRY(need_scratch(h, 8));
@@ -2919,14 +3469,11 @@ extern "C" int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const ui
   if (W < 2 || W > PENG_MAX_W || (W & 1)) return fail(h, PENG_E_INVALID, "set_counts: bad pattern length %d", W);
   CU(h, cudaSetDevice(h->device));
   const uint64_t n = 1ull << (2 * W);
-  if (h->W != W || !h->d_counts) {
-    free_tables(h);
-    TRY(dev_alloc(h, &h->d_hist32, n + 4));
-    TRY(dev_alloc(h, &h->d_counts, n + 1));
-  }
+  TRY(ensure_count_tables(h, W));
   h->W = W;
   h->strand = strand;
   h->n_patterns = n;
+  h->count_pending = false;
   CU(h, cudaMemcpyAsync(h->d_counts, counts, n * 8, cudaMemcpyHostToDevice, h->stream));
   CU(h, cudaMemcpyAsync(h->d_counts + n, &ltot, 8, cudaMemcpyHostToDevice, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
@@ -2986,6 +3533,7 @@ extern "C" int peng_cuda_background_model(peng_handle_t h, int K, const float* a
 // C ABI: tables
 // =====================================================================================================
 extern "C" int peng_cuda_stats(peng_handle_t h, int K, const float* v32, const double* v64, int k, int max_k) {
+  TRY(ensure_final(h));
   if (!h || !h->counts_final) return fail(h, PENG_E_INVALID, "stats: count table not final");
   if (K < 0 || K > PENG_MAX_ORDER || k < 0 || k > K || max_k < k || max_k > K || max_k > h->W - 1)
     return fail(h, PENG_E_INVALID, "stats: bad orders K=%d k=%d max_k=%d (W=%d)", K, k, max_k, h->W);
@@ -3361,6 +3909,7 @@ static int iupac_masks_to_device(peng_handle_t h, const uint64_t* iupac_ids, int
 }
 
 extern "C" int peng_cuda_iupac_count(peng_handle_t h, const uint64_t* iupac_ids, int n, uint64_t* counts_out) {
+  TRY(ensure_final(h));
   if (!h || !h->counts_final || !iupac_ids || !counts_out || n < 0) return fail(h, PENG_E_INVALID, "iupac_count: bad call");
   if (n == 0) return PENG_OK;
   CU(h, cudaSetDevice(h->device));
@@ -3444,8 +3993,9 @@ struct EmGeom {
 static EmGeom em_geom(peng_handle_t h, int P, uint32_t n_units) {
   EmGeom g;
   g.R = std::max(1, std::min(EM_MAX_R, EM_NT / P));
-  g.grid = (unsigned)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)h->sm_count, (n_units + g.R - 1) / g.R));
-  g.smem = (size_t)EM_STAGES * g.R * 16 * sizeof(double2) + (size_t)h->W * 4 * P * 8 + (size_t)h->W * 4 * EM_NT * 8;
+  g.smem = (size_t)EM_STAGES * g.R * 16 * sizeof(double2) + (size_t)h->W * 4 * P * 8 + (size_t)EM_ROWS(h->W) * EM_NT * 8;
+  const uint32_t per_sm = g.smem + 1024 <= (227u << 10) / 2 ? 2u : 1u;  // two CTAs per SM where their shared memory fits (W <= 14)
+  g.grid = (unsigned)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)h->sm_count * per_sm, (n_units + g.R - 1) / g.R));
   return g;
 }
 template <int W>

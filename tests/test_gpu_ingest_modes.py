@@ -75,3 +75,67 @@ def test_long_sequence_falls_back(g):
     assert g.last_ingest_host_packed == 0  # plain path
     c2, _ = g.export_codes()
     assert np.array_equal(c2, codes)
+
+
+def chain_sequences(seed):
+    """Runs of exactly-W-long segments separated by single Ns (the parity chain of the k-mer start rule walks back through
+    them), tandem repeats and ordinary sequence, in lengths that put sequence boundaries anywhere in a 64-position block."""
+    rng = np.random.RandomState(seed)
+    seqs = []
+    for _ in range(rng.randint(40, 120)):
+        kind = rng.randint(0, 4)
+        if kind == 0:
+            seqs.append("N".join("".join(rng.choice(list("ACGT"), 10)) for _ in range(rng.randint(1, 30))))
+        elif kind == 1:
+            u = "".join(rng.choice(list("ACGT"), rng.randint(1, 7)))
+            seqs.append((u * 60)[: rng.randint(10, 300)])
+        else:
+            seqs.append("".join(rng.choice(list("ACGT"), rng.randint(1, 400))))
+    return seqs
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_count_prefetch_small_sets(g, pkg, seed):
+    """peng_cuda_set_count_prefetch: stage P of the W = 10 partition path runs INSIDE ingest_codes, unit range by unit range
+    (the raw tail first, then every packed phase, then the units around the split) — the table equals the oracle's for every
+    split position, both strands, and a following count with other parameters is not disturbed."""
+    codes, offs = O.encode(chain_sequences(seed))
+    g.set_count_path(2)
+    try:
+        for both in (True, False):
+            ref, lt = O.count(codes, offs, 10, both)
+            for mode, frac in ((0, 0.5), (0, 0.07), (0, 0.93), (2, -1.0), (0, 0.31)):
+                g.set_ingest_mode(mode, frac)
+                g.set_count_prefetch(10, int(both))
+                g.ingest_codes(codes, offs)
+                assert g.count(10, int(both)) == lt and g.last_count_path == 2
+                assert np.array_equal(g.get_counts(), ref), (seed, both, mode, frac)
+                assert np.array_equal(g.get_counts32(), ref.astype(np.uint32))
+                assert g.count(10, int(both)) == lt and np.array_equal(g.get_counts(), ref)  # second count: from scratch
+                g.ingest_codes(codes, offs)  # armed for `both`, counted with the other strand and another W: prefetch dropped
+                r2, l2 = O.count(codes, offs, 10, not both)
+                assert g.count(10, int(not both)) == l2 and np.array_equal(g.get_counts(), r2)
+                g.ingest_codes(codes, offs)
+                r3, l3 = O.count(codes, offs, 8, both)
+                assert g.count(8, int(both)) == l3 and np.array_equal(g.get_counts(), r3)
+    finally:
+        g.set_count_prefetch(0)
+        g.set_count_path(0)
+
+
+def test_count_prefetch_many_phases(g, pkg):
+    """Ragged 120 M bases: several staging phases, tapered tail, automatic partition path; prefetch == plain count == oracle."""
+    rng = np.random.RandomState(12)
+    lens = rng.randint(1, 600, 400_000)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    codes = rng.randint(0, 5, int(offs[-1])).astype(np.uint8)
+    ref, lt = O.count(codes, offs, 10, True)
+    try:
+        for mode, frac in ((0, -1.0), (0, 0.77), (2, -1.0), (1, -1.0)):
+            g.set_ingest_mode(mode, frac)
+            g.set_count_prefetch(10, 1)
+            g.ingest_codes(codes, offs)
+            assert g.count(10, 1) == lt
+            assert np.array_equal(g.get_counts(), ref), (mode, frac)
+    finally:
+        g.set_count_prefetch(0)

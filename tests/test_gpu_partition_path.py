@@ -31,18 +31,6 @@ def check(gpu, codes, offs):
         assert np.array_equal(gpu.get_counts(), ref), both
 
 
-@pytest.mark.parametrize("case", [c for c in _cases.golden_cases() if c["exit"] == 0 and c["W"] == 10], ids=lambda c: c["tag"])
-def test_golden_cases(part, pkg, case):
-    path = _cases.write_fasta(case["fasta"])
-    try:
-        part.ingest_fasta(path)
-    finally:
-        os.unlink(path)
-    ltot = part.count(W, pkg.STRAND_BOTH if case["strand"] == "BOTH" else pkg.STRAND_PLUS)
-    assert part.last_count_path == 2 and ltot == case["ltot"]
-    assert np.array_equal(part.get_counts(), _cases.case_counts(case))
-
-
 @pytest.mark.parametrize("seed", range(16))
 def test_dirty_and_palindrome_rich(part, seed):
     seqs = _cases.dirty_sequences(seed) if seed % 2 else palindrome_rich_sequences(seed)
