@@ -498,8 +498,10 @@ def main():
     # ---- end to end from host buffers through the C ABI ("e2e") ----
     codes_np, offs = g.export_codes()
     codes_pin = torch.from_numpy(codes_np).pin_memory()
-    counts_host = torch.empty(4 ** W, dtype=torch.int64).pin_memory()
-    d2h = counts_host.numel() * 8
+    # the set has fewer than 2^32 positions: the finished table travels back as uint32 (peng_cuda_get_counts32), half the bytes
+    counts_host = torch.empty(4 ** W, dtype=torch.int32).pin_memory()
+    d2h = counts_host.numel() * 4
+    g.set_count_prefetch(W, strand)  # what a binding knows before it hands the sequences over: stage P runs under the ingest's DMA
 
     def step_e2e():
         g.ingest_codes(codes_pin.numpy(), offs)  # H2D of 1 B/base codes + device packing
@@ -507,7 +509,7 @@ def main():
             count_multi()
         else:
             g.count(W, strand, want_ltot=False)
-        g._ck(g.lib.peng_cuda_get_counts(g.h, counts_host.data_ptr()))  # D2H of the 4^W table (fetches ltot with it)
+        g._ck(g.lib.peng_cuda_get_counts32(g.h, counts_host.data_ptr()))  # D2H of the 4^W table (fetches ltot with it)
 
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
@@ -526,6 +528,32 @@ def main():
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = total_bases * e2e_steps / float(t.item()) / 1e9
+    # ---- the same end-to-end step from what a binding inside the reference really has: one PAGEABLE array per sequence
+    # (Sequence::getSequence() / getL()), handed over as a pointer table — peng_cuda_ingest_sequences packs them on the host ----
+    seq_ptrs = (np.uint64(codes_np.ctypes.data) + offs[:-1]).astype(np.uint64)
+    seq_lens = np.diff(offs).astype(np.uint32)
+
+    def step_e2e_pageable():
+        g.ingest_sequences(seq_ptrs, seq_lens)
+        if world > 1:
+            count_multi()
+        else:
+            g.count(W, strand, want_ltot=False)
+        g._ck(g.lib.peng_cuda_get_counts32(g.h, counts_host.data_ptr()))
+
+    step_e2e_pageable()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e_pageable()
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_pageable = {"value": total_bases * e2e_steps / float(t.item()) / 1e9, "unit": "Gbases/s", "steps": e2e_steps,
+                    "h2d_bytes_per_step": int(0.375 * codes_np.size) + offs.nbytes, "d2h_bytes_per_step": int(d2h),
+                    "path": "peng_cuda_ingest_sequences (pointer table over pageable per-sequence arrays; every sequence packed by the "
+                            "host threads) -> peng_cuda_count -> peng_cuda_get_counts32"}
     clocks = sampler.stop() if rank == 0 else None  # sampled over warm-up + timed region + e2e region
     # where the end-to-end time goes (rank 0, one more step, host clock around each C-ABI call)
     e2e_phases = {}
@@ -534,8 +562,13 @@ def main():
     t0 = time.perf_counter(); g.count(W, strand) if world == 1 else g.count_local(W, strand); g.synchronize()
     e2e_phases["count_ms"] = 1e3 * (time.perf_counter() - t0)
     if world == 1:
-        t0 = time.perf_counter(); g._ck(g.lib.peng_cuda_get_counts(g.h, counts_host.data_ptr()))
+        t0 = time.perf_counter(); g._ck(g.lib.peng_cuda_get_counts32(g.h, counts_host.data_ptr()))
         e2e_phases["get_counts_ms"] = 1e3 * (time.perf_counter() - t0)
+    g.set_count_prefetch(0)
+    # the e2e result is checked too: the table that came back is the resident one
+    if world == 1:
+        g.count(W, strand)
+        checks["e2e_table_equals_resident"] = bool(np.array_equal(counts_host.numpy().view(np.uint32), g.get_counts().astype(np.uint32)))
 
     if peer:  # every rank closes its mappings of the peers' tables before anybody frees or re-allocates them
         g.peer_detach()
@@ -667,10 +700,11 @@ def main():
                        "data_plane": ("peer memory (own kernel)" if peer else "nccl") if world > 1 else None,
                        "note": peer_note, "result_checks": checks},
             "e2e": {"value": e2e_value, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "steps": e2e_steps, "path": "peng_cuda_ingest_codes (pinned host codes; hybrid: host threads pack part of the set into the 2-bit layout, "
-                            "the DMA engine moves the raw rest for the device to pack) -> peng_cuda_count -> peng_cuda_get_counts",
+                    "steps": e2e_steps, "path": "peng_cuda_set_count_prefetch + peng_cuda_ingest_codes (pinned host codes; hybrid: host threads pack part of the set "
+                            "into the 2-bit layout, the DMA engine moves the raw rest for the device to pack; stage P of the count runs on "
+                            "the unit ranges that have landed) -> peng_cuda_count -> peng_cuda_get_counts32",
                     "host_packed_fraction": packed_bases / max(1, codes_pin.numel()), "host_bytes_per_step": int(codes_pin.numel() + offs.nbytes),
-                    "phases_ms": e2e_phases},
+                    "phases_ms": e2e_phases, "pageable_per_sequence": e2e_pageable},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
             "wall_s_timed_region": t_wall, "extra": extra}
     print(json.dumps(line), flush=True)

@@ -77,10 +77,20 @@ int peng_cuda_get_timing(peng_handle_t h, int phase, float* milliseconds);
 /* Read a FASTA file with the reference's line rules and pack it on the device. */
 int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, uint64_t* total_bases,
                            uint32_t* min_len, uint32_t* max_len);
+/* Shard `part` of `n_parts` of the same file for a multi-GPU run (one handle per GPU): contiguous runs of records cut by
+ * their position in the file, i.e. balanced by bases; every record lands in exactly one shard, a shard may be empty.
+ * Every shard applies the reference's line rules to the whole file, so errors are reported by all of them. */
+int peng_cuda_ingest_fasta_shard(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq,
+                                 uint64_t* total_bases, uint32_t* min_len, uint32_t* max_len);
 /* Same for sequences the caller already holds in the reference's encoding: what a binding inside the
  * reference passes from Sequence::getSequence()/getL() (src/shared/Sequence.h:18-19). codes = all sequences
  * concatenated, offsets[n_seq+1]. */
 int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, const uint64_t* offsets, uint64_t n_seq);
+/* Same for one array PER SEQUENCE — exactly what the reference holds: SequenceSet::getSequences()[s]->getSequence() and
+ * ->getL() (src/shared/SequenceSet.h, src/shared/Sequence.h:18-19), in ordinary pageable memory.  The host threads pack
+ * the sequences from where they lie into the 2-bit device layout (0.375 B/base cross PCIe); nothing is concatenated or
+ * pinned by the caller. */
+int peng_cuda_ingest_sequences(peng_handle_t h, const uint8_t* const* seqs, const uint32_t* lengths, uint64_t n_seq);
 /* Same, codes/offsets already resident on this handle's device (no host copy). */
 /* How host buffers travel (peng_cuda_ingest_codes): 0 = automatic — with >= 4 host threads and AVX-512 the first part
  * of the set is packed into the 2-bit device layout BY THE HOST THREADS (0.375 B/base over PCIe) while the DMA engine
@@ -114,7 +124,11 @@ int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes /* total_bases */, ui
  * v_out: v[0] (4) | v[1] (16) | ... | v[K] (4^(K+1)), float for PENG_F32REF, double for PENG_F64. */
 int peng_cuda_background_model(peng_handle_t h, int K, const float* alpha /* K+1 */, int interpolate, int precision,
                                void* v_out, int64_t* kmer_counts_out /* may be NULL, same layout */);
-/* Raw (k+1)-mer counts only, left on the device for a cross-GPU sum (see peng_cuda_device_ptr). */
+/* calculateV (src/shared/BackgroundModel.cpp:490-530) on (k+1)-mer counts summed over the shards of a multi-GPU run
+ * (kmer_counts_out of peng_cuda_background_model, added element-wise by the caller). */
+int peng_cuda_background_from_counts(int K, const float* alpha, int interpolate, int precision, const int64_t* kmer_counts,
+                                     void* v_out);
+/* Raw (k+1)-mer counts only, left on the device for a cross-GPU sum. */
 int peng_cuda_background_counts(peng_handle_t h, int K);
 int peng_cuda_background_finish(peng_handle_t h, int K, const float* alpha, int interpolate, int precision,
                                 void* v_out);

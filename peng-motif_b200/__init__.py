@@ -58,8 +58,11 @@ _PROTOS = {
     "peng_cuda_set_ingest_mode": (C.c_int, [H, C.c_int, C.c_double]),
     "peng_cuda_last_ingest_host_packed": (C.c_uint64, [H]),
     "peng_cuda_ingest_fasta": (C.c_int, [H, C.c_char_p, u64p, u64p, u32p, u32p]),
+    "peng_cuda_ingest_fasta_shard": (C.c_int, [H, C.c_char_p, C.c_int, C.c_int, u64p, u64p, u32p, u32p]),
+    "peng_cuda_background_from_counts": (C.c_int, [C.c_int, f32p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "peng_cuda_ingest_codes": (C.c_int, [H, C.c_void_p, u64p, C.c_uint64]),
     "peng_cuda_ingest_codes_device": (C.c_int, [H, C.c_void_p, u64p, C.c_uint64]),
+    "peng_cuda_ingest_sequences": (C.c_int, [H, C.c_void_p, C.c_void_p, C.c_uint64]),
     "peng_cuda_ingest_synthetic": (C.c_int, [H, C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32,
                                              C.c_double, C.c_double]),
     "peng_cuda_sequences_info": (C.c_int, [H, u64p, u64p, u32p, u32p]),
@@ -242,11 +245,25 @@ class PengCuda:
         self.n_seq = n.value
         return dict(n_seq=n.value, total_bases=tot.value, min_len=mn.value, max_len=mx.value)
 
+    def ingest_fasta_shard(self, path, part, n_parts):
+        n, tot, mn, mx = C.c_uint64(), C.c_uint64(), C.c_uint32(), C.c_uint32()
+        self._ck(self.lib.peng_cuda_ingest_fasta_shard(self.h, os.fsencode(path), part, n_parts, C.byref(n), C.byref(tot), C.byref(mn),
+                                                       C.byref(mx)))
+        self.n_seq = n.value
+        return dict(n_seq=n.value, total_bases=tot.value, min_len=mn.value, max_len=mx.value)
+
     def ingest_codes(self, codes, offsets):
         codes = np.ascontiguousarray(codes, np.uint8)
         offsets = np.ascontiguousarray(offsets, np.uint64)
         self._ck(self.lib.peng_cuda_ingest_codes(self.h, _ptr(codes), offsets.ctypes.data_as(u64p), len(offsets) - 1))
         self.n_seq = len(offsets) - 1
+
+    def ingest_sequences(self, seq_ptrs, lengths):
+        """seq_ptrs: uint64 array of host addresses (one per sequence, reference letter codes), lengths: uint32 array."""
+        seq_ptrs = np.ascontiguousarray(seq_ptrs, np.uint64)
+        lengths = np.ascontiguousarray(lengths, np.uint32)
+        self._ck(self.lib.peng_cuda_ingest_sequences(self.h, _ptr(seq_ptrs), _ptr(lengths), len(lengths)))
+        self.n_seq = len(lengths)
 
     def set_ingest_mode(self, mode=0, host_fraction=-1.0):
         """0 automatic (hybrid host / device packing), 1 raw bytes, 2 host packing only."""

@@ -165,7 +165,7 @@ __attribute__((target("avx512f,avx512bw"))) static void run_avx512_t(const Share
   const uint64_t s_end = sh.s_end;
   uint64_t o0 = offsets[sh.s_begin];
   for (uint64_t s = sh.s_begin; s < s_end; s++) {
-    const uint8_t* p = src + o0;
+    const uint8_t* p = sh.seq_ptrs ? sh.seq_ptrs[s] : src + o0;
     const uint64_t o1 = offsets[s + 1];
     const uint64_t L = o1 - o0;
     o0 = o1;
@@ -198,7 +198,7 @@ static void run_avx512(const Share& sh, BitWriter& w) {
 }
 static void run_scalar(const Share& sh, BitWriter& w) {
   for (uint64_t s = sh.s_begin; s < sh.s_end; s++) {
-    const uint8_t* p = sh.src + sh.offsets[s];
+    const uint8_t* p = sh.seq_ptrs ? sh.seq_ptrs[s] : sh.src + sh.offsets[s];
     const uint64_t L = sh.offsets[s + 1] - sh.offsets[s];
     uint32_t sep = 2;  // the two separator positions (core_seq.cuh) ride on the last chunk where they fit
     for (uint64_t i = 0; i < L; i += 64) {
@@ -354,6 +354,7 @@ void phase_task(int i, void* arg) {
   const int n = (int)r.cut.size() - 1;
   Share sh;
   sh.src = ph.src;
+  sh.seq_ptrs = ph.seq_ptrs;
   sh.offsets = ph.offsets;
   sh.s_begin = r.cut[i];
   sh.s_end = r.cut[i + 1];

@@ -38,6 +38,7 @@ struct Share {
   uint64_t* codes64;
   uint64_t* valid64;
   std::vector<Partial>* partials;
+  const uint8_t* const* seq_ptrs = nullptr;  // != NULL: sequence s is read from seq_ptrs[s] (per-sequence arrays) instead of src + offsets[s]
 };
 void pack_share(const Share& sh);
 bool have_avx512();
@@ -72,6 +73,7 @@ struct Phase {
   uint64_t q_total;  // last phase: zeros up to this position (multiple of 64)
   uint64_t* codes64;
   uint64_t* valid64;
+  const uint8_t* const* seq_ptrs = nullptr;  // see Share
 };
 void phase_blocks(const Phase& ph, uint64_t* blk0, uint64_t* blk1);
 // end of the phase that starts with sequence s_begin: the largest s_end whose blocks (the carried one included) fit

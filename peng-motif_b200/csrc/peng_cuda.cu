@@ -134,6 +134,8 @@ struct peng_cuda_ctx {
     void* opened[3][8] = {};     // IPC mappings to close on detach
     uint32_t* d_flags = nullptr; // own: [0 .. 7] arrival epoch per rank, [8] CTAs done, [9] error
     uint32_t epoch = 0;
+    int colocated = 1;           // ranks of the group on THIS device (tests; several handles of one process): their exchange
+                                 // kernels wait for each other and must be resident together
   } peer;
   bool count_pending = false;    // a count has run and its ltot has not been fetched yet (lazy finish)
   // count prefetch (peng_cuda_set_count_prefetch): stage P of the W = 10 partition path runs inside peng_cuda_ingest_codes,
@@ -1200,11 +1202,11 @@ __device__ __forceinline__ uint4 ld_peer_u4(const uint32_t* p) {  // L1 is not c
   asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void peer_wait_all(const uint32_t* my_flags, int world, uint32_t epoch, uint32_t* err) {
+__device__ __forceinline__ void peer_wait_all(const uint32_t* my_flags, int world, uint32_t epoch, uint32_t* err, uint32_t phase) {
   if ((int)threadIdx.x < world) {
     const long long t0 = clock64();
     while ((int32_t)(ld_acquire_sys(my_flags + threadIdx.x) - epoch) < 0) {
-      if (clock64() - t0 > 4000000000ll) { *err = 1u; break; }  // ~2 s: a peer never arrived
+      if (clock64() - t0 > 4000000000ll) { *err = 0x100u | (phase << 4) | threadIdx.x; break; }  // ~2 s: a peer never arrived
       __nanosleep(100);
     }
   }
@@ -1227,7 +1229,7 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
     __threadfence_system();
     st_release_sys(A.flags[t] + A.rank, A.epoch);
   }
-  peer_wait_all(my_flags, A.world, A.epoch, err);
+  peer_wait_all(my_flags, A.world, A.epoch, err, 0u);
   if (blockIdx.x == 0 && t == 0) {  // ltot rides in word 4^W of every launch table
     uint64_t lt = 0;
     for (int p = 0; p < A.world; p++) {
@@ -1328,7 +1330,7 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
       __threadfence_system();
       st_release_sys(A.flags[t] + A.rank, A.epoch + 1u);
     }
-    peer_wait_all(my_flags, A.world, A.epoch + 1u, err);
+    peer_wait_all(my_flags, A.world, A.epoch + 1u, err, 1u);
   }
 }
 
@@ -2249,13 +2251,15 @@ __global__ void k_sstart_scatter(const uint64_t* __restrict__ offsets, uint64_t 
 // that holds the split is written whole by k_pack (the raw copy starts 128 bases early), the host's part of it is dropped.
 // returns 1 when the set does not qualify (few threads, no AVX-512, a sequence longer than a phase): the caller runs the
 // plain path.
-static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
+static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii,
+                              const uint8_t* const* seq_ptrs = nullptr) {
   using namespace peng_hostpack;
   const double t_entry = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   double t_marks[4] = {0, 0, 0, 0};
   const uint64_t total = n_seq ? offsets[n_seq] : 0;
   if (h->ingest_mode == 1) return 1;
-  const bool force = h->ingest_mode == 2;
+  // per-sequence arrays (seq_ptrs): there is no contiguous byte range for the DMA engine to take, the host packs everything
+  const bool force = h->ingest_mode == 2 || seq_ptrs != nullptr;
   Pool& pool = global_pool();
   // automatic choice only where it pays; an explicit mode or fraction is taken as given (tests, tuning)
   if (!force && h->ingest_fraction < 0 && (!have_avx512() || pool.size() < 4 || total < (1ull << 22))) return 1;
@@ -2268,7 +2272,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     f = rh / (rp + 0.625 * rh);
     if (h->ingest_fraction >= 0) f = h->ingest_fraction;
     f = std::min(1.0, std::max(0.0, f));
-  } else if (h->ingest_fraction >= 0) {
+  } else if (h->ingest_fraction >= 0 && !seq_ptrs) {
     f = std::min(1.0, std::max(0.0, h->ingest_fraction));
   }
   uint64_t s_split = n_seq;
@@ -2373,7 +2377,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     t_wait += now() - t0;
     uint64_t* codes64 = (uint64_t*)h->pin[buf];
     uint64_t* valid64 = codes64 + 2 * max_blocks;
-    Phase ph{src, offsets, s, e, ascii, PENG_FRONT_PAD, first, last, q_total, codes64, valid64};
+    Phase ph{src, offsets, s, e, ascii, PENG_FRONT_PAD, first, last, q_total, codes64, valid64, seq_ptrs};
     uint64_t blk0, blk1;
     phase_blocks(ph, &blk0, &blk1);
     t0 = now();
@@ -2484,6 +2488,36 @@ extern "C" int peng_cuda_ingest_codes(peng_handle_t h, const uint8_t* codes, con
   return ingest_host_src(h, codes, offsets, n_seq, false);
 }
 
+// Sequences as the reference holds them: one array per Sequence object (src/shared/Sequence.h:18-19).  The host threads pack
+// them straight from where they lie (pageable memory: nothing is pinned or concatenated); without AVX-512 / threads the
+// arrays are gathered into one buffer for the plain path.
+struct GatherTask {
+  const uint8_t* const* seqs;
+  const uint64_t* offs;
+  uint8_t* dst;
+  uint64_t n_seq;
+  int n_tasks;
+};
+static void gather_task(int i, void* arg) {
+  GatherTask& g = *(GatherTask*)arg;
+  const uint64_t s0 = g.n_seq * (uint64_t)i / g.n_tasks, s1 = g.n_seq * (uint64_t)(i + 1) / g.n_tasks;
+  for (uint64_t s = s0; s < s1; s++) memcpy(g.dst + g.offs[s], g.seqs[s], g.offs[s + 1] - g.offs[s]);
+}
+extern "C" int peng_cuda_ingest_sequences(peng_handle_t h, const uint8_t* const* seqs, const uint32_t* lengths, uint64_t n_seq) {
+  if (!h || (n_seq && (!seqs || !lengths))) return fail(h, PENG_E_INVALID, "ingest_sequences: NULL argument");
+  std::vector<uint64_t> offs(n_seq + 1);
+  offs[0] = 0;
+  for (uint64_t s = 0; s < n_seq; s++) offs[s + 1] = offs[s] + lengths[s];
+  h->last_ingest_packed = 0;
+  const int rc = ingest_host_hybrid(h, nullptr, offs.data(), n_seq, false, seqs);
+  if (rc != 1) return rc;
+  std::vector<uint8_t> buf(offs[n_seq] + 1);
+  peng_hostpack::Pool& pool = peng_hostpack::global_pool();
+  GatherTask g{seqs, offs.data(), buf.data(), n_seq, std::max(1, std::min(pool.size() * 4, 256))};
+  pool.run(g.n_tasks, gather_task, &g);
+  return ingest_host_src(h, buf.data(), offs.data(), n_seq, false);
+}
+
 extern "C" int peng_cuda_set_ingest_mode(peng_handle_t h, int mode, double host_fraction) {
   if (!h || mode < 0 || mode > 2 || host_fraction > 1.0) return fail(h, PENG_E_INVALID, "set_ingest_mode: mode 0..2, fraction <= 1 (< 0: automatic)");
   h->ingest_mode = mode;
@@ -2515,6 +2549,11 @@ struct StagingSink {
   const char* last_header = nullptr;
   size_t last_header_len = 0;
   std::vector<std::pair<const char*, size_t>> last_segments;
+  // sharded ingest (peng_cuda_ingest_fasta_shard): only the records whose first sequence line starts in [keep_lo, keep_hi)
+  // of the file are staged; every shard scans the whole file with the whole rule set, so the cut is the same for all
+  const char* text = nullptr;
+  size_t keep_lo = 0, keep_hi = (size_t)-1;
+  bool cur_keep = true, last_mine = false;
   int flush() {
     if (fill == 0 || rc != PENG_OK) return rc;
     peng_handle_t hh = h;
@@ -2529,7 +2568,9 @@ struct StagingSink {
     return rc;
   }
   void letters(const char* p, size_t n) {
+    if (segments.empty()) cur_keep = (size_t)(p - text) >= keep_lo && (size_t)(p - text) < keep_hi;
     segments.emplace_back(p, n);
+    if (!cur_keep) return;
     while (n && rc == PENG_OK) {
       const size_t m = std::min<size_t>(n, PENG_PIN_BYTES - fill);
       memcpy(h->pin[cur] + fill, p, m);
@@ -2540,18 +2581,34 @@ struct StagingSink {
     }
   }
   void end_record(const char* header, size_t header_len) {
-    offsets.push_back(sent + fill);
-    last_header = header;
-    last_header_len = header_len;
-    last_segments.swap(segments);
+    last_mine = cur_keep;
+    if (cur_keep) {
+      offsets.push_back(sent + fill);
+      last_header = header;
+      last_header_len = header_len;
+      last_segments.swap(segments);
+    }
     segments.clear();
   }
   bool last_kept = false;
   void end_of_file(bool last_record_kept) { last_kept = last_record_kept; }
 };
 
+static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq, uint64_t* total_bases,
+                             uint32_t* min_len, uint32_t* max_len);
 extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, uint64_t* total_bases,
                                       uint32_t* min_len, uint32_t* max_len) {
+  return ingest_fasta_impl(h, path, 0, 1, n_seq, total_bases, min_len, max_len);
+}
+// Shard `part` of `n_parts` of the file for a multi-GPU run: contiguous runs of records, cut by position in the file (i.e.
+// balanced by bases), every record in exactly one shard.  A shard may be empty (n_seq = 0).
+extern "C" int peng_cuda_ingest_fasta_shard(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq,
+                                            uint64_t* total_bases, uint32_t* min_len, uint32_t* max_len) {
+  if (n_parts < 1 || part < 0 || part >= n_parts) return fail(h, PENG_E_INVALID, "ingest_fasta_shard: bad shard %d/%d", part, n_parts);
+  return ingest_fasta_impl(h, path, part, n_parts, n_seq, total_bases, min_len, max_len);
+}
+static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq, uint64_t* total_bases,
+                             uint32_t* min_len, uint32_t* max_len) {
   if (!h || !path) return fail(h, PENG_E_INVALID, "ingest_fasta: NULL argument");
   CU(h, cudaSetDevice(h->device));
   peng_host::MappedFile file;
@@ -2572,6 +2629,11 @@ extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_
   StagingSink sink;
   sink.h = h;
   sink.d_src = (uint8_t*)h->d_scratch;
+  sink.text = file.data;
+  if (n_parts > 1) {
+    sink.keep_lo = (size_t)((unsigned __int128)file.size * (unsigned)part / (unsigned)n_parts);
+    sink.keep_hi = part == n_parts - 1 ? (size_t)-1 : (size_t)((unsigned __int128)file.size * (unsigned)(part + 1) / (unsigned)n_parts);
+  }
   std::string msg;
   const int rc = peng_host::scan_fasta(file.data, file.size, path, sink, &msg);
   if (rc != 0) {
@@ -2582,7 +2644,7 @@ extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_
   TRY(sink.rc);
   const uint64_t ns = sink.offsets.size() - 1;
   // SequenceSet::readFASTA reports undefined letters for the LAST record only (src/shared/SequenceSet.cpp:395-405)
-  if (ns && sink.last_kept) {
+  if (ns && sink.last_kept && sink.last_mine) {
     const std::string name = sink.last_header_len ? std::string(sink.last_header, sink.last_header_len) : std::to_string(ns);
     for (const auto& seg : sink.last_segments)
       for (size_t i = 0; i < seg.second; i++) {
@@ -3260,7 +3322,8 @@ extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
     CU(h, cudaStreamSynchronize(h->stream));
     if (peer_err) {
       cudaMemsetAsync(h->peer.d_flags + 9, 0, 4, h->stream);
-      return fail(h, PENG_E_CUDA, "peer exchange: a rank of the peer group did not arrive within 2 s — the count table is incomplete");
+      return fail(h, PENG_E_CUDA, "peer exchange: rank %u of the peer group did not arrive within 2 s (%s of the exchange) — the count table is incomplete",
+                  peer_err & 15u, (peer_err >> 4) & 1u ? "end" : "start");
     }
     h->counts_final = true;
     h->count_pending = false;
@@ -3367,6 +3430,13 @@ extern "C" int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const
       h->peer.hist[p] = (uint32_t*)ptr[0]; h->peer.counts[p] = (uint64_t*)ptr[1]; h->peer.flags[p] = (uint32_t*)ptr[2];
     }
   }
+  h->peer.colocated = 0;
+  for (int p = 0; p < world; p++) {
+    PeerBlob b;
+    memcpy(&b, base + (size_t)p * 256, sizeof b);
+    if (b.pid == (int32_t)getpid() && b.device == h->device) h->peer.colocated++;
+  }
+  h->peer.colocated = std::max(1, h->peer.colocated);
   h->peer.rank = rank;
   h->peer.world = world;
   h->peer.W = h->W;
@@ -3392,7 +3462,12 @@ extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
   A.epoch = h->peer.epoch - 1;  // arrive = epoch, depart = epoch + 1
   const bool both = h->strand == PENG_STRAND_BOTH;
   const uint64_t n_units = both ? (4ull << (2 * (h->W - 6))) : (h->n_patterns >> 10);
-  const unsigned grid = (unsigned)std::min<uint64_t>(n_units, (uint64_t)h->sm_count * 2);
+  // One rank per device (the product): two CTAs per SM (128 registers x 256 threads).  Several ranks on ONE device (tests,
+  // handles of one process): their exchange kernels spin until the slowest rank has finished counting, so together they
+  // may hold at most half of the SMs — the counting kernels of the late ranks (1024-thread CTAs) need whole SMs to run.
+  const uint64_t cta_budget = h->peer.colocated > 1 ? std::max<uint64_t>(1, (uint64_t)h->sm_count / (2 * (uint64_t)h->peer.colocated))
+                                                    : (uint64_t)h->sm_count * 2;
+  const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(n_units, cta_budget));
   if (both) k_peer_exchange32<true><<<grid, 256, 0, h->stream>>>(A);
   else k_peer_exchange32<false><<<grid, 256, 0, h->stream>>>(A);
   LAUNCH_CHECK(h);
@@ -3512,6 +3587,17 @@ extern "C" int peng_cuda_background_finish(peng_handle_t h, int K, const float* 
   std::vector<uint64_t> n(n_bins);
   CU(h, cudaMemcpyAsync(n.data(), h->d_bgcounts, n_bins * 8, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
+  if (precision == PENG_F32REF) peng_host::calculate_v<float>(n.data(), K, alpha, interpolate != 0, (float*)v_out);
+  else peng_host::calculate_v<double>(n.data(), K, alpha, interpolate != 0, (double*)v_out);
+  return PENG_OK;
+}
+
+// calculateV on (k+1)-mer counts the caller has summed over the shards of a multi-GPU run (pure host arithmetic)
+extern "C" int peng_cuda_background_from_counts(int K, const float* alpha, int interpolate, int precision, const int64_t* kmer_counts,
+                                                void* v_out) {
+  if (K < 0 || K > PENG_MAX_ORDER || !alpha || !kmer_counts || !v_out) return PENG_E_INVALID;
+  const uint32_t n_bins = v_offset(K + 1);
+  std::vector<uint64_t> n(kmer_counts, kmer_counts + n_bins);
   if (precision == PENG_F32REF) peng_host::calculate_v<float>(n.data(), K, alpha, interpolate != 0, (float*)v_out);
   else peng_host::calculate_v<double>(n.data(), K, alpha, interpolate != 0, (double*)v_out);
   return PENG_OK;

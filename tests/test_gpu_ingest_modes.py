@@ -139,3 +139,25 @@ def test_count_prefetch_many_phases(g, pkg):
             assert np.array_equal(g.get_counts(), ref), (mode, frac)
     finally:
         g.set_count_prefetch(0)
+
+
+@pytest.mark.parametrize("seed", range(3))
+def test_ingest_sequences_per_sequence_arrays(g, seed):
+    """peng_cuda_ingest_sequences: one pageable array per sequence (what Sequence::getSequence() / getL() give) — the same
+    device buffers as the concatenated ingest, in every mode (host packing from the pointers, gather + plain path)."""
+    seqs = _cases.dirty_sequences(seed, n_max=60, len_max=700)
+    codes, offs = O.encode(seqs)
+    arrays = [np.ascontiguousarray(codes[int(offs[i]):int(offs[i + 1])].copy()) for i in range(len(seqs))]
+    rng = np.random.RandomState(seed)
+    keep = [arrays[i] for i in rng.permutation(len(arrays))]  # separate allocations, not one buffer in order
+    ptrs = np.array([a.ctypes.data for a in arrays], np.uint64)
+    lens = np.array([len(a) for a in arrays], np.uint32)
+    g.set_ingest_mode(1, -1.0)
+    g.ingest_codes(codes, offs)
+    ref = fingerprint(g, codes, offs)
+    for mode in (0, 1, 2):
+        g.set_ingest_mode(mode, -1.0)
+        g.ingest_sequences(ptrs, lens)
+        got = fingerprint(g, codes, offs)
+        assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and np.array_equal(got[2], ref[2]), mode
+    del keep

@@ -190,6 +190,7 @@ def test_sliced_protocol_equals_whole_tables_w12(gpu, pkg):
         gpu.synchronize()
         buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
         acc = buf.clone() if acc is None else acc + buf
+        torch.cuda.synchronize()  # torch's stream has read the table before the handle's stream reuses it
     sites = np.zeros(len(ids), np.uint64); bgs = np.zeros(len(ids)); exs = np.zeros(len(ids))
     em_acc, state = None, []
     try:

@@ -154,6 +154,7 @@ def test_sharded_sum32_matches_whole(gpu, pkg, W_, both, n, shard_path):
             gpu.synchronize()  # the handle works on its own stream, torch on another
             buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
             acc = buf.clone() if acc is None else acc + buf
+            torch.cuda.synchronize()  # torch's stream has read the table before the handle's stream reuses it
             with pytest.raises(pkg.PengCudaError):
                 gpu.count_finish()  # the 64-bit finish must refuse an unfolded table
     finally:
@@ -187,6 +188,7 @@ def test_sum32_of_mixed_paths(gpu, pkg, W_, last_on_partition):
             gpu.synchronize()
             buf = torch.as_tensor(gpu.count_buffer32(), device="cuda")
             acc = buf.clone() if acc is None else acc + buf
+            torch.cuda.synchronize()  # torch's stream has read the table before the handle's stream reuses it
     finally:
         gpu.set_count_path(0)
     buf.copy_(acc)
