@@ -157,6 +157,7 @@ Options parse_command_line(int argc, char** argv) {
       // this driver only
       {"--device", true, "--device", as_int(&Options::device)},
       {"--timings", false, "", set_flag(&Options::timings, true)},
+      {"--gpus", true, "--gpus", as_int(&Options::gpus)},
   };
 
   for (int i = 2; i < argc; i++) {

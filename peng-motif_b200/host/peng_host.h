@@ -54,6 +54,7 @@ struct Options {
   // additions of this driver (not options of the reference; all default to the reference's behaviour)
   int device = 0;          // --device N
   bool timings = false;    // --timings: per-phase wall clock on stderr
+  int gpus = 1;            // --gpus N: ingest + counting sharded over the devices [device, device + N)
 };
 
 // Parses argv like Global::readArguments; prints help / version and exits where the reference does.

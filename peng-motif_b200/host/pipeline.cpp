@@ -18,6 +18,7 @@
 #include <iostream>
 #include <memory>
 #include <set>
+#include <thread>
 #include <unordered_map>
 #include <unordered_set>
 
@@ -354,15 +355,122 @@ void filter_redundancy(float merge_bit_factor, const float* v0, std::vector<Moti
 
 }  // namespace
 
+// ---- --gpus N: the data-parallel front of the run (ingest, background counts, k-mer counts) sharded over N devices ----
+// One handle and one host thread per device (the ABI's rule).  Every device reads its shard of the FASTA file
+// (peng_cuda_ingest_fasta_shard: contiguous runs of records, balanced by bases), counts it, and the per-device tables are
+// combined by the fused exchange over peer memory (peng_cuda_count_exchange32: all handles live in this process, so their
+// device pointers are exchanged directly) — or, for sets the 32-bit exchange does not cover, on the host.  Every device ends
+// with the complete table; the table passes, the hill climb and EM then run on the first device as in a single-GPU run
+// (4^W-sized work, "replicas only").  Integer sums: the result is bit-identical to the single-GPU run.
+struct MultiGpu {
+  std::vector<std::unique_ptr<Device>> extra;  // devices 1 .. N-1 (device 0 is the run's main handle)
+  std::vector<peng_handle_t> hs;               // all N handles, rank order
+  template <typename F>
+  void parallel(F f) {  // f(rank) on one thread per handle; rank 0 on the caller
+    std::vector<std::thread> th;
+    for (size_t r = 1; r < hs.size(); r++) th.emplace_back([&, r] { f((int)r); });
+    f(0);
+    for (auto& t : th) t.join();
+  }
+};
+
+static void multi_count(MultiGpu& mg, const Device& dev, int W, int strand, uint64_t total_positions, uint64_t max_shard_positions,
+                        uint64_t* ltot) {
+  const int N = (int)mg.hs.size();
+  std::vector<int> rc((size_t)N, PENG_OK);
+  auto first_error = [&]() {
+    for (int r = 0; r < N; r++)
+      if (rc[(size_t)r] != PENG_OK) {
+        std::cerr << peng_cuda_last_error(mg.hs[(size_t)r]) << std::endl;
+        exit(1);
+      }
+  };
+  const bool exchange32 = W >= 8 && total_positions < ((uint64_t)1 << 32) - ((uint64_t)1 << 20) && max_shard_positions < ((uint64_t)1 << 30) - 4096;
+  if (exchange32) {
+    std::vector<unsigned char> blobs((size_t)N * PENG_PEER_BLOB_BYTES);
+    for (int r = 0; r < N; r++) rc[(size_t)r] = peng_cuda_peer_export(mg.hs[(size_t)r], W, blobs.data() + (size_t)r * PENG_PEER_BLOB_BYTES);
+    first_error();
+    for (int r = 0; r < N; r++) rc[(size_t)r] = peng_cuda_peer_attach(mg.hs[(size_t)r], r, N, blobs.data());
+    first_error();
+    std::vector<uint64_t> lt((size_t)N, 0);
+    mg.parallel([&](int r) {
+      rc[(size_t)r] = peng_cuda_count_local32(mg.hs[(size_t)r], W, strand);
+      if (rc[(size_t)r] == PENG_OK) rc[(size_t)r] = peng_cuda_count_exchange32(mg.hs[(size_t)r], &lt[(size_t)r]);
+    });
+    first_error();
+    for (int r = 0; r < N; r++) peng_cuda_peer_detach(mg.hs[(size_t)r]);
+    *ltot = lt[0];
+    return;
+  }
+  // general case (> 2^32 positions, or W < 8): canonical 64-bit tables summed on the host, loaded into the main handle
+  const uint64_t n = (uint64_t)1 << (2 * W);
+  std::vector<std::vector<uint64_t>> tab((size_t)N);
+  std::vector<uint64_t> lt((size_t)N, 0);
+  mg.parallel([&](int r) {
+    tab[(size_t)r].resize((size_t)n);
+    rc[(size_t)r] = peng_cuda_count(mg.hs[(size_t)r], W, strand, &lt[(size_t)r]);  // per-shard table, mirrored: the sum of mirrored tables is the mirrored sum
+    if (rc[(size_t)r] == PENG_OK) rc[(size_t)r] = peng_cuda_get_counts(mg.hs[(size_t)r], tab[(size_t)r].data());
+  });
+  first_error();
+  uint64_t total = 0;
+  for (int r = 0; r < N; r++) total += lt[(size_t)r];
+  for (int r = 1; r < N; r++)
+    for (uint64_t i = 0; i < n; i++) tab[0][(size_t)i] += tab[(size_t)r][(size_t)i];
+  dev.check(peng_cuda_set_counts(dev.h, W, strand, tab[0].data(), total));
+  *ltot = total;
+}
+
 int run(const Options& opt) {
   Stopwatch watch{opt.timings};
   Device dev(opt.device);
+  MultiGpu mg;
+  mg.hs.push_back(dev.h);
+  // PENG_GPUS_SAME_DEVICE=1 (tests on a one-GPU box): all N handles on --device; the whole multi-GPU protocol runs, the
+  // exchange kernels meet through the same flag words and pointers as over NVLink
+  const bool same_device = getenv("PENG_GPUS_SAME_DEVICE") != nullptr;
+  if (opt.gpus > 1) {
+    if (!same_device && opt.device + opt.gpus > peng_cuda_device_count()) {
+      std::cerr << "Error: --gpus " << opt.gpus << " from device " << opt.device << " on, but only " << peng_cuda_device_count() << " CUDA devices are visible" << std::endl;
+      exit(1);
+    }
+    mg.extra.resize((size_t)opt.gpus - 1);
+    mg.hs.resize((size_t)opt.gpus);
+    mg.parallel([&](int r) {
+      if (r == 0) return;
+      mg.extra[(size_t)r - 1] = std::make_unique<Device>(same_device ? opt.device : opt.device + r);
+      mg.hs[(size_t)r] = mg.extra[(size_t)r - 1]->h;
+    });
+  }
+  const int N = (int)mg.hs.size();
   watch.lap("CUDA context");
 
   // ---- Global::init (src/Global.cpp:60-79): the input set, and the background set if it is another file ----
   uint64_t n_seq = 0, total_bases = 0;
   uint32_t min_len = 0, max_len = 0;
-  dev.check(peng_cuda_ingest_fasta(dev.h, opt.input_fasta.c_str(), &n_seq, &total_bases, &min_len, &max_len));
+  std::vector<uint64_t> shard_positions((size_t)N, 0);
+  if (N == 1) {
+    dev.check(peng_cuda_ingest_fasta(dev.h, opt.input_fasta.c_str(), &n_seq, &total_bases, &min_len, &max_len));
+  } else {
+    std::vector<uint64_t> ns((size_t)N, 0), tb((size_t)N, 0);
+    std::vector<uint32_t> mn((size_t)N, 0), mx((size_t)N, 0);
+    std::vector<int> rc((size_t)N, PENG_OK);
+    mg.parallel([&](int r) {
+      rc[(size_t)r] = peng_cuda_ingest_fasta_shard(mg.hs[(size_t)r], opt.input_fasta.c_str(), r, N, &ns[(size_t)r], &tb[(size_t)r], &mn[(size_t)r], &mx[(size_t)r]);
+    });
+    for (int r = 0; r < N; r++)
+      if (rc[(size_t)r] != PENG_OK) {  // every shard applies the line rules to the whole file: one message is enough
+        std::cerr << peng_cuda_last_error(mg.hs[(size_t)r]) << std::endl;
+        exit(1);
+      }
+    min_len = 0xFFFFFFFFu;
+    for (int r = 0; r < N; r++) {
+      n_seq += ns[(size_t)r];
+      total_bases += tb[(size_t)r];
+      shard_positions[(size_t)r] = tb[(size_t)r] + 2 * ns[(size_t)r];
+      if (ns[(size_t)r]) { min_len = std::min(min_len, mn[(size_t)r]); max_len = std::max(max_len, mx[(size_t)r]); }
+    }
+    if (!n_seq) min_len = 0;
+  }
   watch.lap("ingest");
 
   // ---- background model (src/main.cpp:21-26) ----
@@ -385,8 +493,24 @@ int run(const Options& opt) {
       other->check(peng_cuda_ingest_fasta(other->h, opt.background_fasta.c_str(), &n, &t, &a, &b));
       bg_dev = other.get();
     }
-    bg_dev->check(peng_cuda_background_model(bg_dev->h, K, alpha.data(), opt.interpolate_bg, PENG_F32REF, v32.data(), nullptr));
-    bg_dev->check(peng_cuda_background_model(bg_dev->h, K, alpha.data(), opt.interpolate_bg, PENG_F64, v64.data(), nullptr));
+    if (N > 1 && opt.background_fasta.empty()) {
+      // sharded input set: the (k+1)-mer counts of the shards add up (no k-mer crosses a sequence), calculateV runs once
+      std::vector<std::vector<int64_t>> cnt((size_t)N, std::vector<int64_t>(v_len));
+      std::vector<int> rc((size_t)N, PENG_OK);
+      mg.parallel([&](int r) {
+        std::vector<float> scratch(v_len);
+        rc[(size_t)r] = peng_cuda_background_model(mg.hs[(size_t)r], K, alpha.data(), opt.interpolate_bg, PENG_F32REF, scratch.data(), cnt[(size_t)r].data());
+      });
+      for (int r = 0; r < N; r++) {
+        if (rc[(size_t)r] != PENG_OK) { std::cerr << peng_cuda_last_error(mg.hs[(size_t)r]) << std::endl; exit(1); }
+        if (r) for (size_t i = 0; i < v_len; i++) cnt[0][i] += cnt[(size_t)r][i];
+      }
+      dev.check(peng_cuda_background_from_counts(K, alpha.data(), opt.interpolate_bg, PENG_F32REF, cnt[0].data(), v32.data()));
+      dev.check(peng_cuda_background_from_counts(K, alpha.data(), opt.interpolate_bg, PENG_F64, cnt[0].data(), v64.data()));
+    } else {
+      bg_dev->check(peng_cuda_background_model(bg_dev->h, K, alpha.data(), opt.interpolate_bg, PENG_F32REF, v32.data(), nullptr));
+      bg_dev->check(peng_cuda_background_model(bg_dev->h, K, alpha.data(), opt.interpolate_bg, PENG_F64, v64.data(), nullptr));
+    }
   }
   const float* v0 = v32.data();
   watch.lap("background model");
@@ -411,7 +535,12 @@ int run(const Options& opt) {
   print_status("Finding overrepresented kmers (base patterns)", false);
   const int current_k = std::min(W - 1, k), current_k_max = std::min(W - 1, max_k);
   uint64_t ltot = 0;
-  dev.check(peng_cuda_count(dev.h, W, opt.strand, &ltot));
+  if (N == 1) {
+    dev.check(peng_cuda_count(dev.h, W, opt.strand, &ltot));
+  } else {
+    multi_count(mg, dev, W, opt.strand, total_bases + 2 * n_seq, *std::max_element(shard_positions.begin(), shard_positions.end()), &ltot);
+    mg.extra.clear();  // the other devices are done: everything that follows is 4^W-sized work on the main handle
+  }
   watch.lap("count k-mers");
   dev.check(peng_cuda_stats(dev.h, K, v32.data(), v64.data(), current_k, current_k_max));
   watch.lap("background / z-score tables");

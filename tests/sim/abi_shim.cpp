@@ -4,13 +4,16 @@
 // reference's recorded console report and MEME file on a machine without a GPU (tests/test_host_driver.py builds
 // tests/sim/peng_motif_sim from the driver's sources + this file).  Never linked into the product: the shipped
 // peng_motif links libpeng_cuda.so and stops without a CUDA device.
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/peng_cuda.h"
 #include "../../oracle/peng_oracle.h"
+#include "../../peng-motif_b200/csrc/host_ingest.h"  // calculate_v (host arithmetic of the product, no device code)
 
 struct peng_cuda_ctx {
   std::vector<uint8_t> codes;
@@ -22,6 +25,11 @@ struct peng_cuda_ctx {
   std::vector<std::vector<float>> bgprob;  // per order
   std::vector<float> expected, z, logp, v;
   std::string err;
+  // --gpus N on the shim: the ranks are threads of this process; the "exchange" adds the ranks' tables behind a barrier
+  std::vector<peng_cuda_ctx*> group;
+  std::vector<uint64_t> local;
+  uint64_t local_ltot = 0;
+  std::atomic<int> arrived{0}, departed{0};
 };
 static std::string g_err;
 
@@ -145,6 +153,100 @@ int peng_cuda_em(peng_handle_t h, int n_pwms, const void* pwm_in, int precision,
                              (float)saturation, (float)threshold, max_iterations, (float*)pwm_out + (size_t)i * W * 4);
     if (iterations_out) iterations_out[i] = it;
   }
+  return PENG_OK;
+}
+
+int peng_cuda_device_count(void) { return 8; }
+
+int peng_cuda_ingest_fasta_shard(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq, uint64_t* total,
+                                 uint32_t* min_len, uint32_t* max_len) {
+  uint64_t n = 0, t = 0;
+  uint32_t a = 0, b = 0;
+  const int rc = peng_cuda_ingest_fasta(h, path, &n, &t, &a, &b);
+  if (rc != PENG_OK) return rc;
+  // contiguous runs of records (the product cuts by file position; any cut gives the same sums)
+  const uint64_t s0 = n * (uint64_t)part / (uint64_t)n_parts, s1 = n * (uint64_t)(part + 1) / (uint64_t)n_parts;
+  std::vector<uint8_t> codes(h->codes.begin() + (long)h->offsets[s0], h->codes.begin() + (long)h->offsets[s1]);
+  std::vector<uint64_t> offs;
+  uint32_t mn = 0xFFFFFFFFu, mx = 0;
+  for (uint64_t s = s0; s <= s1; s++) offs.push_back(h->offsets[s] - h->offsets[s0]);
+  for (uint64_t s = s0; s < s1; s++) {
+    const uint32_t L = (uint32_t)(h->offsets[s + 1] - h->offsets[s]);
+    mn = L < mn ? L : mn;
+    mx = L > mx ? L : mx;
+  }
+  if (codes.empty()) codes.push_back(0);
+  h->codes.swap(codes);
+  h->offsets.swap(offs);
+  h->n_seq = s1 - s0;
+  if (n_seq) *n_seq = s1 - s0;
+  if (total) *total = h->offsets.back();
+  if (min_len) *min_len = s1 > s0 ? mn : 0;
+  if (max_len) *max_len = mx;
+  return PENG_OK;
+}
+
+int peng_cuda_background_from_counts(int K, const float* alpha, int interpolate, int precision, const int64_t* kmer_counts, void* v_out) {
+  const size_t nv = (((size_t)1 << (2 * (K + 2))) - 4) / 3;
+  std::vector<uint64_t> n(kmer_counts, kmer_counts + nv);
+  if (precision == PENG_F32REF) peng_host::calculate_v<float>(n.data(), K, alpha, interpolate != 0, (float*)v_out);
+  else peng_host::calculate_v<double>(n.data(), K, alpha, interpolate != 0, (double*)v_out);
+  return PENG_OK;
+}
+
+int peng_cuda_get_counts(peng_handle_t h, uint64_t* counts) {
+  memcpy(counts, h->counts.data(), h->counts.size() * 8);
+  return PENG_OK;
+}
+int peng_cuda_set_counts(peng_handle_t h, int W, int strand, const uint64_t* counts, uint64_t ltot) {
+  h->W = W;
+  h->strand = strand;
+  h->counts.assign(counts, counts + ((size_t)1 << (2 * W)));
+  h->ltot = ltot;
+  return PENG_OK;
+}
+
+int peng_cuda_peer_export(peng_handle_t h, int W, void* blob) {
+  h->W = W;
+  memset(blob, 0, PENG_PEER_BLOB_BYTES);
+  memcpy(blob, &h, sizeof h);
+  return PENG_OK;
+}
+int peng_cuda_peer_attach(peng_handle_t h, int, int world, const void* blobs) {
+  h->group.clear();
+  for (int p = 0; p < world; p++) {
+    peng_cuda_ctx* q;
+    memcpy(&q, (const unsigned char*)blobs + (size_t)p * PENG_PEER_BLOB_BYTES, sizeof q);
+    h->group.push_back(q);
+  }
+  return PENG_OK;
+}
+int peng_cuda_peer_detach(peng_handle_t h) {
+  h->group.clear();
+  return PENG_OK;
+}
+int peng_cuda_count_local32(peng_handle_t h, int W, int strand) {
+  h->W = W;
+  h->strand = strand;
+  h->local.assign((size_t)1 << (2 * W), 0);
+  po_count(h->codes.data(), h->offsets.data(), h->n_seq, W, strand == PENG_STRAND_BOTH, h->local.data(), &h->local_ltot);
+  return PENG_OK;
+}
+int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
+  const int world = (int)h->group.size();
+  for (auto* q : h->group) q->arrived++;             // "my table is complete", told to every rank
+  while (h->arrived.load() < world) std::this_thread::yield();
+  h->counts.assign(h->local.size(), 0);
+  h->ltot = 0;
+  for (auto* q : h->group) {
+    for (size_t i = 0; i < h->counts.size(); i++) h->counts[i] += q->local[i];
+    h->ltot += q->local_ltot;
+  }
+  for (auto* q : h->group) q->departed++;            // "I have read your table"
+  while (h->departed.load() < world) std::this_thread::yield();
+  h->arrived = 0;
+  h->departed = 0;
+  if (ltot) *ltot = h->ltot;
   return PENG_OK;
 }
 

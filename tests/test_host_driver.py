@@ -129,3 +129,55 @@ def test_gpu_cli_case(gpu_binary, name, tmp_path):
 @pytest.mark.parametrize("name", sorted(CONFIG_CASES))
 def test_gpu_config(gpu_binary, name, tmp_path):
     check_config_case(gpu_binary, name, tmp_path)
+
+
+# ---- --gpus N: sharded ingest + counting, combined by the fused peer exchange (or on the host), same bytes out ----------
+def run_gpus(binary, name, n, tmp_path, same_device):
+    fasta, args = CONFIG_CASES[name]
+    env = dict(os.environ)
+    if same_device:
+        env["PENG_GPUS_SAME_DEVICE"] = "1"
+    meme = str(tmp_path / "o.meme")
+    r = subprocess.run([binary, os.path.join(DATA, fasta), *args, "--gpus", str(n), "-o", meme], capture_output=True, text=True, env=env)
+    assert r.returncode == 0, r.stderr
+    assert r.stdout == open(os.path.join(GOLDEN, name + "_stdout.txt")).read()
+    assert open(meme).read() == open(os.path.join(GOLDEN, name + ".meme")).read()
+
+
+@pytest.mark.parametrize("n", [2, 5])
+@pytest.mark.parametrize("name", ["cfg1_W8_BOTH", "cfg1_W8_PLUS"])
+def test_host_logic_multi_gpu(sim_binary, name, n, tmp_path):
+    """The driver's --gpus bookkeeping (one thread per handle, FASTA shards, summed background counts, exchange protocol)
+    on the CPU shim: same console report and MEME as the single-handle run and the reference."""
+    run_gpus(sim_binary, name, n, tmp_path, False)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [2, 3])
+@pytest.mark.parametrize("name", sorted(CONFIG_CASES))
+def test_gpu_multi_handle_one_device(gpu_binary, name, n, tmp_path):
+    """N handles on ONE device (PENG_GPUS_SAME_DEVICE): FASTA shards, summed background counts, count_local32 +
+    peer exchange (W = 8, 10) — console report and MEME byte-identical to the reference's."""
+    run_gpus(gpu_binary, name, n, tmp_path, True)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(CONFIG_CASES))
+def test_gpu_multi_device(gpu_binary, pkg, name, tmp_path):
+    n = pkg.load_library().peng_cuda_device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 CUDA devices (the multi-handle protocol itself runs in test_gpu_multi_handle_one_device)")
+    run_gpus(gpu_binary, name, min(n, 8), tmp_path, False)
+
+
+@pytest.mark.gpu
+def test_gpu_multi_handle_small_w_host_sum(gpu_binary, tmp_path):
+    """W = 6 is outside the fused exchange: per-shard tables are added on the host; output identical to one GPU."""
+    fasta = os.path.join(DATA, "MafK_100seqs.fasta")
+    outs = []
+    for extra in ([], ["--gpus", "2"]):
+        r = subprocess.run([gpu_binary, fasta, "-w", "6", *extra, "-o", str(tmp_path / "x.meme")], capture_output=True, text=True,
+                           env=dict(os.environ, PENG_GPUS_SAME_DEVICE="1"))
+        assert r.returncode == 0, r.stderr
+        outs.append((r.stdout, open(tmp_path / "x.meme").read()))
+    assert outs[0] == outs[1]
