@@ -326,6 +326,129 @@ def configs3_run(pkg, torch, dist, rank, world, local, steps=3):
             "ltot_ok": ok}
 
 
+def run_cfg5_sliced(args, pkg, torch, dist, rank, world, local):
+    """BASELINE configs[4] as north_star states it: 10 M x 300 bp, --strand PLUS, the MAXIMUM pattern length W = 16
+    (src/peng.cpp:325-330 of the reference) with the long-k-mer tables, on 8 GPUs.  The 4^16 tables do not fit one GPU (six FP64
+    tables of 32 GiB), so every rank keeps 1/N of the id range: count_local32 (deep partition path) -> ncclReduceScatter of
+    the uint32 table (+ all-reduce of the ltot word) -> count_finish32_sliced -> stats on the slice -> EM over the slice,
+    accumulators all-reduced.  Checked: ltot in closed form, and 2048 occupied bins against an independent path (the
+    L2-atomic kernel per rank + an all-reduce of the gathered bins)."""
+    import numpy as np
+
+    W, L, n_seq = int(os.environ.get("PENG_CFG5_W", "16")), 300, int(os.environ.get("PENG_CFG5_NSEQ", "10000000"))  # env: functional checks of this flow at a small scale
+    first, n_local = pkg.shard_synthetic(n_seq, rank, world)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    g = pkg.PengCuda(local)
+    g.set_stream(stream.cuda_stream)
+    g.set_table_slice(rank, world)
+    g.ingest_synthetic(n_local, L, 1234, first, MOTIF, 0.3, 0.0)
+    n = 4 ** W
+
+    def barrier():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- reference bins through another path: first W-mers of 256 sequences per rank, counted by the L2-atomic kernel ----
+    codes, offs = None, None
+    sample_n = 256
+    gs = pkg.PengCuda(local)
+    gs.ingest_synthetic(sample_n, L, 1234, first, MOTIF, 0.3, 0.0)
+    sc, so = gs.export_codes()
+    gs.close()
+    ids_local = np.array([sum((int(c) - 1) << (2 * p) for p, c in enumerate(sc[int(o):int(o) + W])) for o in so[:-1]], np.int64)
+    ids_t = torch.from_numpy(ids_local).cuda()
+    all_ids = [torch.empty_like(ids_t) for _ in range(world)]
+    dist.all_gather(all_ids, ids_t)
+    ids = torch.cat(all_ids).cpu().numpy().astype(np.uint64)
+    g.set_table_slice(0, 1)
+    g.set_count_path(1)
+    g.count(W, pkg.STRAND_PLUS)
+    ref = torch.from_numpy(g.gather_counts(ids).astype(np.int64)).cuda()
+    dist.all_reduce(ref)
+    ref = ref.cpu().numpy().astype(np.uint64)
+    g.set_count_path(0)
+    g.set_table_slice(rank, world)
+
+    scratch = None
+
+    def step():
+        nonlocal scratch
+        g.count_local32(W, pkg.STRAND_PLUS)
+        buf = torch.as_tensor(g.count_buffer32(), device="cuda")
+        lo, hi = g.table_slice()
+        if scratch is None:
+            scratch = torch.empty(hi - lo, dtype=torch.int32, device="cuda")
+        dist.reduce_scatter_tensor(scratch, buf[:n])
+        buf[lo:hi].copy_(scratch)
+        dist.all_reduce(buf[n:])
+        return g.count_finish32_sliced()
+
+    lt = step()
+    lo, hi = g.table_slice()
+    mine = (ids >= lo) & (ids < hi)
+    ok_bins = bool(np.array_equal(g.gather_counts(ids[mine]), ref[mine])) and bool(ref.min() >= 1)
+    ok = torch.tensor([1 if (ok_bins and int(lt) == n_seq * (L - W + 1)) else 0], device="cuda")
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    barrier()
+    steps = max(2, min(args.steps, 5))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        step()
+    b.record()
+    barrier()
+    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / steps
+    # ---- table pass + one EM iteration on the slices ----
+    v64 = g.background_model(2, precision=pkg.F64)
+    vt = torch.from_numpy(v64).cuda()
+    dist.broadcast(vt, 0)  # one model for all ranks (rank 0's shard; the timing does not depend on the values)
+    v64 = vt.cpu().numpy()
+    barrier()
+    t0 = time.perf_counter()
+    g.stats(None, v64, K=2, k=2, max_k=2)
+    g.synchronize()
+    stats_ms = 1e3 * (time.perf_counter() - t0)
+    rng = np.random.RandomState(0)
+    pw = rng.dirichlet(np.ones(4), (17, W)) * 0.3
+    for m in range(17):
+        for p in range(W):
+            pw[m, p, "ACGT".index("TGCTGACTCAGCA"[(m + p) % 13])] += 0.7
+    pw /= pw.sum(2, keepdims=True)
+    acc = torch.as_tensor(g.em_begin(pw, 1e4, 0.0, 3, 2, rank, world), device="cuda")
+    em_ms = []
+    for it in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        g.em_accumulate()
+        g.synchronize()
+        dist.all_reduce(acc)
+        g.em_update(False)
+        barrier()
+        em_ms.append(1e3 * (time.perf_counter() - t0))
+    out, its = g.em_end()
+    em_ok = bool(np.isfinite(out).all()) and bool(np.allclose(out.sum(2), 1.0))
+    if rank == 0:
+        line = {"metric": "kmer_count_gbases_per_s", "value": n_seq * L / (ms * 1e-3) / 1e9, "unit": "Gbases/s", "n_gpus": world,
+                "steps": steps, "warmup": 1, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "u32", "data": "synthetic",
+                "config": {"workload": f"configs[4]: synthetic {n_seq} x 300 bp, --strand PLUS, " + ("MAXIMUM pattern length W=16" if W == 16 else f"W={W}") + ", id-sliced long-k-mer tables",
+                           "W": W, "strand": "PLUS", "n_seq_per_gpu": n_local, "seq_len": L, "seed": 1234, "motif": MOTIF, "plant_fraction": 0.3,
+                           "n_gpus": world},
+                "timing": {"exchange": f"ncclReduceScatter of 4^{W} uint32 + all-reduce of the ltot word, sliced finish",
+                           "result_checks": {"ltot_and_2048_bins_vs_l2_atomic_path_all_ranks": bool(int(ok.item()))}},
+                "extra": {"stats_slice_ms_fp64": stats_ms, "em_fp64": {"pwms": 17, "W": W, "ms_per_iteration_all_pwms": min(em_ms),
+                                                                       "iterations_timed": em_ms, "pwms_valid": em_ok,
+                                                                       "protocol": "em_accumulate on the id slice -> ncclAllReduce of 17 x 16 x 4 doubles -> em_update"},
+                          "slice_ids_per_gpu": int(hi - lo)}}
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    g.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -368,6 +491,9 @@ def main():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
+
+    if args.workload == "cfg5" and (world >= 8 or (world > 1 and "PENG_CFG5_W" in os.environ)):
+        return run_cfg5_sliced(args, pkg, torch, dist, rank, world, local)
 
     W, strand = shape["W"], pkg.STRAND_BOTH if shape["strand"] == "BOTH" else pkg.STRAND_PLUS
     n_local, L = shape["n_seq_per_gpu"], shape["seq_len"]
@@ -612,8 +738,8 @@ def main():
     elif partition:
         kname = f"k_count_part<{W},{shape['strand']}> (stage P of the partition path)"
         note = ("stage P streams the packed set once (codes + validity), derives k-mer starts and conflict candidates and "
-                "partitions 16-bit keys into class buckets; bound by the ALU pipe and issue (ncu: pipe_alu 59 %, issue active 55 %, "
-                "8 warps per scheduler), see DESIGN.md")
+                "partitions 16-bit keys into class buckets; bound by the ALU pipe and issue, not by bytes (counters: the ncu extract "
+                "named in roofline.traffic_source), see DESIGN.md")
     else:
         kname = f"k_count_global<{W},{shape['strand']}>" if W >= 10 else "k_count_smem"
         note = "one L2 atomic per counted k-mer: atomic-throughput-bound far below the HBM roof (DESIGN.md)"
@@ -626,7 +752,13 @@ def main():
     tr = os.path.join(ROOT, "profiles", "count_kernel_traffic.json")
     if os.path.exists(tr):
         try:
-            roofline["traffic"] = json.load(open(tr)).get(args.workload)
+            tj = json.load(open(tr))
+            roofline["traffic"] = tj.get(args.workload)
+            roofline["traffic_source"] = tj.get("source", {}).get(args.workload)
+            # distance to the ceiling that actually binds the two-stage design: one shared-memory atomic per counted W-mer in
+            # each stage (2.4e12/s chip-wide, profiles/r1_atomic_microbench.txt) -> bases / 2.4e12 s per stage
+            if partition and W == 10:
+                roofline["smem_atomic_ceiling_frac"] = (bases_local / 2.4e12) / (dev_ms / args.steps * 1e-3)
         except Exception:
             pass
 

@@ -134,6 +134,7 @@ struct peng_cuda_ctx {
     void* opened[3][8] = {};     // IPC mappings to close on detach
     uint32_t* d_flags = nullptr; // own: [0 .. 7] arrival epoch per rank, [8] CTAs done, [9] error
     uint32_t epoch = 0;
+    double timeout_ms = 20000.0; // PENG_PEER_TIMEOUT_MS
     int colocated = 1;           // ranks of the group on THIS device (tests; several handles of one process): their exchange
                                  // kernels wait for each other and must be resident together
   } peer;
@@ -144,6 +145,7 @@ struct peng_cuda_ctx {
     int W = 0, strand = 0;       // armed for this count (W = 0: off)
     bool done = false;           // the current ingest ran stage P for (W, strand): the next matching count skips it
   } pre;
+  uint64_t table_gen = 1;        // generation of {count table, float tables}: consumers that cache derived data compare it
   bool hist_clean = false;       // every bin of the uint32 launch table is 0 (each complete fold leaves it so): no clearing pass
 
   // ---- EM session (multi-GPU protocol) ----
@@ -154,6 +156,12 @@ struct peng_cuda_ctx {
     double *d_old = nullptr, *d_acc = nullptr, *d_part = nullptr, *d_change = nullptr;
     int *d_iter = nullptr, *d_active = nullptr, *d_nactive = nullptr;
     double2* d_pairs = nullptr;  // {(double) count, bgprob} of the ids of this rank's slice (k_em_pairs)
+    // the buffers are kept between sessions (cudaMalloc / cudaFree cost more than an EM iteration at W = 10) and the pair
+    // table is reused while the tables it was made from stand (table_gen: bumped by every count / stats)
+    size_t cap_small = 0, cap_part = 0, cap_pairs = 0;
+    uint64_t pairs_gen = 0;
+    int pairs_order = -1;
+    uint32_t pairs_ub = 0, pairs_ue = 0;
     uint32_t ub = 0, ue = 0;     // the slice in units of 256 ids
   } em;
 };
@@ -1180,7 +1188,8 @@ __global__ void k_ltot_from32(uint32_t* __restrict__ word, uint64_t* __restrict_
 // of (a, m, b) is (revcomp3(b), revcomp(m), revcomp3(a))): the 16 rows a with a & 3 == q of tile m and the 16-column band
 // b >> 4 == 3 - q of tile revcomp(m) hold each other's partners, every access is a 256- or 64-byte run.  Units of a middle
 // m belong to rank m % world.  PLUS: a unit is 1024 consecutive ids.
-// Nothing here can deadlock on a peer that never arrives: the waits give up after ~2 s and raise the error word.
+// Nothing here can deadlock on a peer that never arrives: the waits give up after PENG_PEER_TIMEOUT_MS (default 20 s:
+// ranks may legitimately arrive far apart — uneven shards, a first-touch allocation) and raise the error word.
 struct PeerArgs {
   uint32_t* hist[8];
   uint64_t* counts[8];
@@ -1188,6 +1197,7 @@ struct PeerArgs {
   int rank, world, W;
   uint32_t epoch;
   uint64_t n;
+  long long timeout_cycles;  // how long a rank waits for the others before it gives up and raises the error word
 };
 __device__ __forceinline__ void st_release_sys(uint32_t* a, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a), "r"(v) : "memory");
@@ -1202,11 +1212,12 @@ __device__ __forceinline__ uint4 ld_peer_u4(const uint32_t* p) {  // L1 is not c
   asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-__device__ __forceinline__ void peer_wait_all(const uint32_t* my_flags, int world, uint32_t epoch, uint32_t* err, uint32_t phase) {
+__device__ __forceinline__ void peer_wait_all(const uint32_t* my_flags, int world, uint32_t epoch, uint32_t* err, uint32_t phase,
+                                              long long timeout_cycles) {
   if ((int)threadIdx.x < world) {
     const long long t0 = clock64();
     while ((int32_t)(ld_acquire_sys(my_flags + threadIdx.x) - epoch) < 0) {
-      if (clock64() - t0 > 4000000000ll) { *err = 0x100u | (phase << 4) | threadIdx.x; break; }  // ~2 s: a peer never arrived
+      if (clock64() - t0 > timeout_cycles) { *err = 0x100u | (phase << 4) | threadIdx.x; break; }  // a peer never arrived
       __nanosleep(100);
     }
   }
@@ -1229,7 +1240,7 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
     __threadfence_system();
     st_release_sys(A.flags[t] + A.rank, A.epoch);
   }
-  peer_wait_all(my_flags, A.world, A.epoch, err, 0u);
+  peer_wait_all(my_flags, A.world, A.epoch, err, 0u, A.timeout_cycles);
   if (blockIdx.x == 0 && t == 0) {  // ltot rides in word 4^W of every launch table
     uint64_t lt = 0;
     for (int p = 0; p < A.world; p++) {
@@ -1330,7 +1341,7 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
       __threadfence_system();
       st_release_sys(A.flags[t] + A.rank, A.epoch + 1u);
     }
-    peer_wait_all(my_flags, A.world, A.epoch + 1u, err, 1u);
+    peer_wait_all(my_flags, A.world, A.epoch + 1u, err, 1u, A.timeout_cycles);
   }
 }
 
@@ -2021,6 +2032,7 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
   if (const char* e = getenv("PENG_HOST_PACK_FRACTION")) h->ingest_fraction = atof(e);
   if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
   h->select_on_host = getenv("PENG_SELECT_HOST") != nullptr;
+  if (const char* e = getenv("PENG_PEER_TIMEOUT_MS")) h->peer.timeout_ms = std::max(1.0, atof(e));
   *out = h;
   return PENG_OK;
 }
@@ -2030,11 +2042,18 @@ static void free_tables(peng_handle_t h) {
   dev_free(&h->d_exp32); dev_free(&h->d_z32); dev_free(&h->d_logp32);
   dev_free(&h->d_exp64); dev_free(&h->d_z64); dev_free(&h->d_logp64);
   h->stats_ready = false;
+  h->table_gen++;
+  dev_free(&h->em.d_pairs);  // as large as two tables: not kept across table changes
+  h->em.cap_pairs = 0;
 }
-static void free_em(peng_handle_t h) {
+static void free_em_buffers(peng_handle_t h) {
   dev_free(&h->em.d_old); dev_free(&h->em.d_acc); dev_free(&h->em.d_part); dev_free(&h->em.d_change);
   dev_free(&h->em.d_iter); dev_free(&h->em.d_active); dev_free(&h->em.d_nactive);
   dev_free(&h->em.d_pairs);
+  h->em.cap_small = h->em.cap_part = h->em.cap_pairs = 0;
+  h->em.pairs_gen = 0;
+}
+static void free_em(peng_handle_t h) {  // closes the session; the buffers stay for the next one
   h->em.open = false;
 }
 
@@ -2048,7 +2067,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   dev_free(&h->d_offsets); dev_free(&h->d_hist32); dev_free(&h->d_counts); dev_free(&h->d_bgcounts);
   dev_free(&h->d_v32); dev_free(&h->d_v64);
   free_tables(h);
-  free_em(h);
+  free_em_buffers(h);
   if (h->d_scratch) cudaFree(h->d_scratch);
   dev_free(&h->d_sel);
   if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
@@ -3322,8 +3341,8 @@ extern "C" int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
     CU(h, cudaStreamSynchronize(h->stream));
     if (peer_err) {
       cudaMemsetAsync(h->peer.d_flags + 9, 0, 4, h->stream);
-      return fail(h, PENG_E_CUDA, "peer exchange: rank %u of the peer group did not arrive within 2 s (%s of the exchange) — the count table is incomplete",
-                  peer_err & 15u, (peer_err >> 4) & 1u ? "end" : "start");
+      return fail(h, PENG_E_CUDA, "peer exchange: rank %u of the peer group did not arrive within %.0f ms (%s of the exchange) — the count table is incomplete",
+                  peer_err & 15u, h->peer.timeout_ms, (peer_err >> 4) & 1u ? "end" : "start");
     }
     h->counts_final = true;
     h->count_pending = false;
@@ -3458,6 +3477,7 @@ extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
   A.world = h->peer.world;
   A.W = h->W;
   A.n = h->n_patterns;
+  A.timeout_cycles = (long long)(h->peer.timeout_ms * 1.9e6);  // SM clock ~1.9 GHz
   h->peer.epoch += 2;
   A.epoch = h->peer.epoch - 1;  // arrive = epoch, depart = epoch + 1
   const bool both = h->strand == PENG_STRAND_BOTH;
@@ -4122,19 +4142,31 @@ extern "C" int peng_cuda_em_begin(peng_handle_t h, int n_pwms, const double* pwm
     for (int first = 0; first < n_pwms; first += EM_MAX_GROUP)
       E.nbx = std::max(E.nbx, (int)em_geom(h, std::min(EM_MAX_GROUP, n_pwms - first), E.ue - E.ub).grid);
     const uint64_t n_ids = (uint64_t)(E.ue - E.ub) << EM_UNIT_BITS;
-    TRY(dev_alloc(h, &E.d_pairs, (size_t)std::max<uint64_t>(n_ids, 1)));
-    if (n_ids) {
+    if (E.cap_pairs < n_ids) {
+      TRY(dev_alloc(h, &E.d_pairs, (size_t)std::max<uint64_t>(n_ids, 1)));
+      E.cap_pairs = (size_t)std::max<uint64_t>(n_ids, 1);
+      E.pairs_gen = 0;
+    }
+    if (n_ids && (E.pairs_gen != h->table_gen || E.pairs_order != bg_order || E.pairs_ub != E.ub || E.pairs_ue != E.ue)) {
       k_em_pairs<<<grid_for(n_ids, 256), 256, 0, h->stream>>>(h->d_counts, vbase(h->d_bg64[bg_order], h->tab_lo), (uint64_t)E.ub << EM_UNIT_BITS, n_ids, E.d_pairs);
       LAUNCH_CHECK(h);
+      E.pairs_gen = h->table_gen; E.pairs_order = bg_order; E.pairs_ub = E.ub; E.pairs_ue = E.ue;
     }
   }
-  TRY(dev_alloc(h, &E.d_old, (size_t)n_pwms * WA));
-  TRY(dev_alloc(h, &E.d_acc, (size_t)n_pwms * WA));
-  TRY(dev_alloc(h, &E.d_part, (size_t)n_pwms * WA * E.nbx));
-  TRY(dev_alloc(h, &E.d_change, (size_t)n_pwms));
-  TRY(dev_alloc(h, &E.d_iter, (size_t)n_pwms));
-  TRY(dev_alloc(h, &E.d_active, (size_t)n_pwms));
-  TRY(dev_alloc(h, &E.d_nactive, (size_t)1));
+  if (E.cap_small < (size_t)n_pwms * WA) {
+    const size_t c = (size_t)n_pwms * WA;  // (n_pwms <= c for the per-PWM arrays)
+    TRY(dev_alloc(h, &E.d_old, c));
+    TRY(dev_alloc(h, &E.d_acc, c));
+    TRY(dev_alloc(h, &E.d_change, c));
+    TRY(dev_alloc(h, &E.d_iter, c));
+    TRY(dev_alloc(h, &E.d_active, c));
+    TRY(dev_alloc(h, &E.d_nactive, (size_t)1));
+    E.cap_small = c;
+  }
+  if (E.cap_part < (size_t)n_pwms * WA * E.nbx) {
+    TRY(dev_alloc(h, &E.d_part, (size_t)n_pwms * WA * E.nbx));
+    E.cap_part = (size_t)n_pwms * WA * E.nbx;
+  }
   CU(h, cudaMemcpyAsync(E.d_old, pwm_in, (size_t)n_pwms * WA * 8, cudaMemcpyHostToDevice, h->stream));
   CU(h, cudaMemsetAsync(E.d_acc, 0, (size_t)n_pwms * WA * 8, h->stream));
   CU(h, cudaMemsetAsync(E.d_part, 0, (size_t)n_pwms * WA * E.nbx * 8, h->stream));  // groups with a smaller grid leave rows unwritten

@@ -393,10 +393,14 @@ static void multi_count(MultiGpu& mg, const Device& dev, int W, int strand, uint
     for (int r = 0; r < N; r++) rc[(size_t)r] = peng_cuda_peer_attach(mg.hs[(size_t)r], r, N, blobs.data());
     first_error();
     std::vector<uint64_t> lt((size_t)N, 0);
+    // two passes: the exchange kernels spin on the device until every rank has arrived, so nothing that may block on the
+    // host (first-use kernel loading, allocation) is left to do once the first of them is launched
     mg.parallel([&](int r) {
       rc[(size_t)r] = peng_cuda_count_local32(mg.hs[(size_t)r], W, strand);
-      if (rc[(size_t)r] == PENG_OK) rc[(size_t)r] = peng_cuda_count_exchange32(mg.hs[(size_t)r], &lt[(size_t)r]);
+      if (rc[(size_t)r] == PENG_OK) rc[(size_t)r] = peng_cuda_synchronize(mg.hs[(size_t)r]);
     });
+    first_error();
+    mg.parallel([&](int r) { rc[(size_t)r] = peng_cuda_count_exchange32(mg.hs[(size_t)r], &lt[(size_t)r]); });
     first_error();
     for (int r = 0; r < N; r++) peng_cuda_peer_detach(mg.hs[(size_t)r]);
     *ltot = lt[0];

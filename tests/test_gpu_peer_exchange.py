@@ -66,8 +66,9 @@ def test_ranks_in_one_process(pkg, gpu, W, both, world):
             h.close()
 
 
-def test_missing_rank_times_out(pkg):
+def test_missing_rank_times_out(pkg, monkeypatch):
     """A rank that never calls the exchange must not hang the others: the wait gives up and the finish reports it."""
+    monkeypatch.setenv("PENG_PEER_TIMEOUT_MS", "500")  # read by peng_cuda_create (default 20 s)
     hs = [pkg.PengCuda(0) for _ in range(2)]
     try:
         blobs = np.stack([h.peer_export(10) for h in hs])
