@@ -582,6 +582,7 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
     if constexpr (PL) return cs.c | cs.p[0];
     else return cs.c1 | cs.p[0];
   };
+  const uint64_t region_stride = (uint64_t)gridDim.x * region_cap, region0 = (uint64_t)blockIdx.x * region_cap;  // bucket region of (class c, this CTA)
   constexpr bool STEP_PER_PUSH = Steps::N > 16;  // W >= 12: one scan step behind every push instead of every other
   static_assert(Steps::N <= 32, "at most one scan step per push");
   uint32_t un = scan_begin(blockIdx.x);
@@ -626,8 +627,16 @@ __global__ void __launch_bounds__(PART_NT, MINB) k_count_part(
         const uint32_t base = fill[c];
         const entry_t* src = q + c * PART_CAP;
         if (base + nfl <= region_cap) {
-          entry_t* dst = buckets + ((uint64_t)c * gridDim.x + blockIdx.x) * region_cap + base;
-          for (uint32_t i = lane * 4; i < nfl; i += 128) *(vec_t*)(dst + i) = *(const vec_t*)(src + i);
+          // whole 128-entry blocks, 16 bytes per lane and step, at most CAP entries: unrolled, 32-bit offsets (the rolled
+          // loop with its 64-bit address arithmetic was a quarter of stage P's instructions: profiles/r2_count_part source page)
+          unsigned char* d8 = reinterpret_cast<unsigned char*>(buckets + (c * region_stride + region0 + base));
+          const unsigned char* s8 = reinterpret_cast<const unsigned char*>(src);
+          const uint32_t bytes = nfl * (uint32_t)sizeof(entry_t);
+#pragma unroll
+          for (uint32_t k = 0; k < PART_CAP * sizeof(entry_t) / 512; k++) {
+            const uint32_t off = lane * 16u + k * 512u;
+            if (off < bytes) *reinterpret_cast<uint4*>(d8 + off) = *reinterpret_cast<const uint4*>(s8 + off);
+          }
           if (lane == 0) fill[c] = base + nfl;
         } else {  // private bucket region full: straight to the global table
           for (uint32_t i = lane; i < nfl; i += 32) atomicAdd(hist + G::id_of((uint32_t)src[i], c), 1u);
