@@ -220,9 +220,11 @@ def end_to_end_cli():
             out["reference_cpu_seconds"] = time.perf_counter() - t0
             out["reference_threads"] = nthreads
             out["meme_identical"] = open(os.path.join(d, "ours.meme")).read() == open(os.path.join(d, "ref.meme")).read()
-            # with --threads > 1 the reference's "Calculating PWMs" loop is an OpenMP loop whose lines interleave, so the
-            # console reports are compared as multisets of lines here (tests/test_host_driver.py compares them byte for byte)
-            out["stdout_same_lines"] = sorted(r.stdout.splitlines()) == sorted(rr.stdout.splitlines())
+            # with --threads > 1 the reference's "Calculating PWMs" loop is an OpenMP loop whose lines interleave, so the console
+            # report is compared byte for byte against a second, single-threaded run of the reference
+            r1 = subprocess.run([ref, fasta, "-w", "10", "--threads", "1", "-o", os.path.join(d, "ref1.meme")], capture_output=True, text=True)
+            out["stdout_identical_to_reference_threads_1"] = r.stdout == r1.stdout
+            out["stdout_same_lines"] = sorted(r.stdout.splitlines()) == sorted(r1.stdout.splitlines())
     return out
 
 
@@ -595,7 +597,7 @@ def main():
         step_resident()
         b.record()
         kern_ms.append(g.get_timing((6 if W > 10 else 3) if partition else 1))
-        phase_ms.append([g.get_timing(p) for p in range(7)])
+        phase_ms.append([g.get_timing(p) for p in range(7)] + ([g.get_timing(7)] if peer else [0.0]))
     barrier()
     t_wall = time.perf_counter() - t_wall
     launches = g.launches - launches0
@@ -783,7 +785,7 @@ def main():
                 "kernel": kname, "kernel_ms": k_ms, "algorithmic_bytes": algo_bytes, "peak_source": peak_src, "note": note,
                 "step_phases_ms": {"mark": float(ph[0]), "count_total": float(ph[1]), "fold": float(ph[2]),
                                    "stage_P": float(ph[3]), "slow_units": float(ph[4]), "stage_H": float(ph[5]),
-                                   "stage_P2": float(ph[6])},
+                                   "stage_P2": float(ph[6]), "peer_exchange_kernel": float(ph[7])},
                 "whole_step_frac": (ALGO_BYTES_PER_BASE * bases_local + 4.0 * 4 ** W) / (dev_ms / args.steps * 1e-3) / 1e9 / peak}
     tr = os.path.join(ROOT, "profiles", "count_kernel_traffic.json")
     if os.path.exists(tr):

@@ -67,7 +67,8 @@ int peng_cuda_synchronize(peng_handle_t h);
 /* Device-side timing of the phases of the last peng_cuda_count[_local] call (CUDA events on the handle's stream,
  * recorded only while enabled): phase 0 = k-mer start marking (fused into stage P on the partition path),
  * 1 = the counting kernel(s), 2 = fold; partition path only: 3 = stage P, 4 = slow units, 5 = stage H, 6 = stage P2
- * (deep path of W >= 12, else 0) of the first chunk of <= 2^30 stream positions (the only one for sets up to 1 Gbp).
+ * (deep path of W >= 12, else 0) of the first chunk of <= 2^30 stream positions (the only one for sets up to 1 Gbp);
+ * 7 = the last peng_cuda_count_exchange32 kernel (its wait for the slowest rank included).
  * This is how bench.py measures the dominant kernel's duration for the roofline without a profiler. */
 int peng_cuda_enable_timing(peng_handle_t h, int on);
 int peng_cuda_get_timing(peng_handle_t h, int phase, float* milliseconds);

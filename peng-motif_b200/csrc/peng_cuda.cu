@@ -115,7 +115,7 @@ struct peng_cuda_ctx {
 
   // ---- phase timing (bench) ----
   bool timing = false;
-  cudaEvent_t ev[9] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev[11] = {};  // 9, 10: around the peer exchange kernel
 
   // ---- scratch ----
   void* d_scratch = nullptr;
@@ -2087,7 +2087,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   dev_free(&h->d_planes);
   dev_free(&h->d_part_buckets); dev_free(&h->d_part_fill); dev_free(&h->d_slow_list); dev_free(&h->d_slow_count);
   for (int i = 0; i < 3; i++) { dev_free(&h->d_deep_buckets[i]); dev_free(&h->d_deep_fill[i]); }
-  for (int i = 0; i < 8; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  for (int i = 0; i < 11; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   if (h->own_stream) cudaStreamDestroy(h->own_stream);
   if (h->side_stream) cudaStreamDestroy(h->side_stream);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
@@ -2107,13 +2107,18 @@ extern "C" int peng_cuda_enable_timing(peng_handle_t h, int on) {
   if (!h) return PENG_E_INVALID;
   CU(h, cudaSetDevice(h->device));
   if (on && !h->ev[0])
-    for (int i = 0; i < 9; i++) CU(h, cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i < 11; i++) CU(h, cudaEventCreate(&h->ev[i]));
   h->timing = on != 0;
   return PENG_OK;
 }
 extern "C" int peng_cuda_get_timing(peng_handle_t h, int phase, float* ms) {
-  if (!h || !h->ev[0] || phase < 0 || phase > 6 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
+  if (!h || !h->ev[0] || phase < 0 || phase > 7 || !ms) return fail(h, PENG_E_INVALID, "get_timing: timing not enabled");
   CU(h, cudaSetDevice(h->device));
+  if (phase == 7) {  // the last peer exchange kernel (waits for the other ranks included)
+    CU(h, cudaEventSynchronize(h->ev[10]));
+    CU(h, cudaEventElapsedTime(ms, h->ev[9], h->ev[10]));
+    return PENG_OK;
+  }
   CU(h, cudaEventSynchronize(h->ev[5]));
   // events: 0 start | 1 k-mer starts marked | 4 counting done | 5 folded; of the first chunk of the partition path:
   // 6 stage P launched | 2 stage P done | 3 slow units done (side stream, beside stage H / P2) | 8 stage P2 done (deep
@@ -3497,9 +3502,11 @@ extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
   const uint64_t cta_budget = h->peer.colocated > 1 ? std::max<uint64_t>(1, (uint64_t)h->sm_count / (2 * (uint64_t)h->peer.colocated))
                                                     : (uint64_t)h->sm_count * 2;
   const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(n_units, cta_budget));
+  MARK(h, 9);
   if (both) k_peer_exchange32<true><<<grid, 256, 0, h->stream>>>(A);
   else k_peer_exchange32<false><<<grid, 256, 0, h->stream>>>(A);
   LAUNCH_CHECK(h);
+  MARK(h, 10);
   h->fold_deferred = false;
   h->mirrored = true;
   if (!ltot) {
