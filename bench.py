@@ -591,13 +591,16 @@ def main():
     partition = g.last_count_path == 2  # W = 10 on >= 4 M positions: k_count_part / k_count_slow / k_hist_part
     launches0 = g.launches
     t_wall = time.perf_counter()
-    for a, b in ev:
+    for i, (a, b) in enumerate(ev):
         flush.zero_()  # L2 flush between timed iterations (packed set = 75 MB < L2)
         a.record()
         step_resident()
         b.record()
-        kern_ms.append(g.get_timing((6 if W > 10 else 3) if partition else 1))
-        phase_ms.append([g.get_timing(p) for p in range(7)] + ([g.get_timing(7)] if peer else [0.0]))
+        # the library's own events of this step (kernel durations for the roofline), read on every 8th step only: reading
+        # them waits for the step to finish, and a wait per step would leave the GPU idle for a launch latency each time
+        if i % 8 == 7 or i == len(ev) - 1:
+            kern_ms.append(g.get_timing((6 if W > 10 else 3) if partition else 1))
+            phase_ms.append([g.get_timing(p) for p in range(7)] + ([g.get_timing(7)] if peer else [0.0]))
     barrier()
     t_wall = time.perf_counter() - t_wall
     launches = g.launches - launches0
