@@ -614,6 +614,15 @@ def main():
     dev_ms = float(t.item())
     total_bases = bases_local * world
     value = total_bases * args.steps / (dev_ms * 1e-3) / 1e9
+    # per-rank medians of stage P / stage H / exchange kernel: how far apart the ranks run (the exchange waits for the slowest)
+    rank_phases = None
+    if dist is not None:
+        med = np.median(np.array(phase_ms), axis=0)
+        mine = torch.tensor([med[3], med[5], med[7], sum(a.elapsed_time(b) for a, b in ev) / len(ev)], dtype=torch.float64, device="cuda")
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        rank_phases = {"stage_P_ms": [float(x[0]) for x in allr], "stage_H_ms": [float(x[1]) for x in allr],
+                       "exchange_kernel_ms": [float(x[2]) for x in allr], "step_ms": [float(x[3]) for x in allr]}
 
     if args.kernels_only:
         if rank == 0:
@@ -873,7 +882,7 @@ def main():
                             ", 1 NCCL all_reduce of 4^W u32 + ltot per step (32-bit exchange)" if exchange32 else
                             ", 1 NCCL all_reduce of 4^W u64 + ltot per step") if world > 1 else ""),
                        "data_plane": ("peer memory (own kernel)" if peer else "nccl") if world > 1 else None,
-                       "note": peer_note, "result_checks": checks},
+                       "note": peer_note, "result_checks": checks, "per_rank": rank_phases},
             "e2e": {"value": e2e_value, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "path": "peng_cuda_set_count_prefetch + peng_cuda_ingest_codes (pinned host codes; hybrid: host threads pack part of the set "
                             "into the 2-bit layout, the DMA engine moves the raw rest for the device to pack; stage P of the count runs on "

@@ -3501,7 +3501,9 @@ extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
   // may hold at most half of the SMs — the counting kernels of the late ranks (1024-thread CTAs) need whole SMs to run.
   const uint64_t cta_budget = h->peer.colocated > 1 ? std::max<uint64_t>(1, (uint64_t)h->sm_count / (2 * (uint64_t)h->peer.colocated))
                                                     : (uint64_t)h->sm_count * 2;
-  const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(n_units, cta_budget));
+  unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(n_units, cta_budget));
+  static const int grid_env = getenv("PENG_PEER_GRID") ? atoi(getenv("PENG_PEER_GRID")) : 0;  // tuning knob
+  if (grid_env > 0) grid = (unsigned)std::min<uint64_t>(grid, (uint64_t)grid_env);
   MARK(h, 9);
   if (both) k_peer_exchange32<true><<<grid, 256, 0, h->stream>>>(A);
   else k_peer_exchange32<false><<<grid, 256, 0, h->stream>>>(A);
