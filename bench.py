@@ -605,6 +605,7 @@ def main():
     t_wall = time.perf_counter() - t_wall
     launches = g.launches - launches0
     checks["ltot_after_timed_steps"] = int(g.count_finish()) == expect_ltot
+    peer_trace = [round(float(x) / 1e3, 2) for x in g.peer_trace()] if peer else None  # us, last timed step, this rank
     if not checks["ltot_after_timed_steps"]:
         raise SystemExit(f"bench.py: ltot after the timed steps is wrong on rank {rank}")
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
@@ -882,7 +883,9 @@ def main():
                             ", 1 NCCL all_reduce of 4^W u32 + ltot per step (32-bit exchange)" if exchange32 else
                             ", 1 NCCL all_reduce of 4^W u64 + ltot per step") if world > 1 else ""),
                        "data_plane": ("peer memory (own kernel)" if peer else "nccl") if world > 1 else None,
-                       "note": peer_note, "result_checks": checks, "per_rank": rank_phases},
+                       "note": peer_note, "result_checks": checks, "per_rank": rank_phases,
+                       "peer_exchange_trace_us": {"arrived": peer_trace[0], "cta0_units_done": peer_trace[1], "cta0_stores_visible": peer_trace[2],
+                                                  "all_ctas_done": peer_trace[3], "departed": peer_trace[4]} if peer_trace else None},
             "e2e": {"value": e2e_value, "unit": "Gbases/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "path": "peng_cuda_set_count_prefetch + peng_cuda_ingest_codes (pinned host codes; hybrid: host threads pack part of the set "
                             "into the 2-bit layout, the DMA engine moves the raw rest for the device to pack; stage P of the count runs on "

@@ -182,6 +182,9 @@ int peng_cuda_peer_export(peng_handle_t h, int W, void* blob);
 int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const void* blobs);
 int peng_cuda_peer_detach(peng_handle_t h);
 int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot);
+/* Where the last exchange kernel of this rank spent its time (device clock, ns since its start): [0] all ranks arrived,
+ * [1] the units of CTA 0 done, [2] CTA 0's peer stores visible system-wide, [3] all CTAs done, [4] all ranks departed. */
+int peng_cuda_peer_trace(peng_handle_t h, double* out5);
 /* Id-sliced tables for the long pattern lengths on several GPUs (BASELINE configs[4]; the reference's tables are one
  * float array per order plus expected / z / logp over all 4^W ids, src/base_pattern.h:116-120 — at W = 16 more than one
  * GPU holds).  Rank `part` of `n_parts` keeps the ids [lo, hi) (whole tiles of 1024 ids, peng_cuda_table_slice) of every

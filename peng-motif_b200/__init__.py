@@ -86,6 +86,7 @@ _PROTOS = {
     "peng_cuda_peer_attach": (C.c_int, [H, C.c_int, C.c_int, C.c_void_p]),
     "peng_cuda_peer_detach": (C.c_int, [H]),
     "peng_cuda_count_exchange32": (C.c_int, [H, u64p]),
+    "peng_cuda_peer_trace": (C.c_int, [H, f64p]),
     "peng_cuda_set_table_slice": (C.c_int, [H, C.c_int, C.c_int]),
     "peng_cuda_table_slice": (C.c_int, [H, u64p, u64p]),
     "peng_cuda_count_finish32_sliced": (C.c_int, [H, u64p]),
@@ -332,6 +333,11 @@ class PengCuda:
 
     def peer_detach(self):
         self._ck(self.lib.peng_cuda_peer_detach(self.h))
+
+    def peer_trace(self):
+        out = np.zeros(5, np.float64)
+        self._ck(self.lib.peng_cuda_peer_trace(self.h, out.ctypes.data_as(f64p)))
+        return out
 
     def count_exchange32(self, want_ltot=True):
         ltot = C.c_uint64()

@@ -135,6 +135,9 @@ struct peng_cuda_ctx {
     uint32_t* d_flags = nullptr; // own: [0 .. 7] arrival epoch per rank, [8] CTAs done, [9] error
     uint32_t epoch = 0;
     double timeout_ms = 20000.0; // PENG_PEER_TIMEOUT_MS
+    uint32_t* d_units = nullptr; // BOTH strands: the exchange units this rank owns (see k_peer_exchange32)
+    uint32_t n_owned = 0;
+    int units_W = 0, units_rank = -1, units_world = 0;
     int colocated = 1;           // ranks of the group on THIS device (tests; several handles of one process): their exchange
                                  // kernels wait for each other and must be resident together
   } peer;
@@ -1207,6 +1210,8 @@ struct PeerArgs {
   uint32_t epoch;
   uint64_t n;
   long long timeout_cycles;  // how long a rank waits for the others before it gives up and raises the error word
+  const uint32_t* units;     // BOTH: the units (m << 2 | q) this rank owns, n_owned of them (built by the host: even over the CTAs)
+  uint32_t n_owned;
 };
 __device__ __forceinline__ void st_release_sys(uint32_t* a, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(a), "r"(v) : "memory");
@@ -1216,9 +1221,13 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* a) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a) : "memory");
   return v;
 }
-__device__ __forceinline__ uint4 ld_peer_u4(const uint32_t* p) {  // L1 is not coherent with a peer's writes: read through to L2 / the link
+// Table reads from a peer: ordinary (weak) 16-byte loads.  They are ordered behind the acquire of the peer's arrival flag
+// (ld.acquire.sys, which also invalidates this SM's L1: CCTL.IVALL in the SASS), so they see the peer's finished table.
+// `ld.relaxed.sys` here made every lane's 16 bytes a request of its own (LDG.STRONG.SYS is not coalesced): ~150 GB/s over
+// the link and 20 us per unit at N = 2 (profiles/r2_peer_exchange_trace.txt).
+__device__ __forceinline__ uint4 ld_peer_u4(const uint32_t* p) {
   uint4 v;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
 __device__ __forceinline__ void peer_wait_all(const uint32_t* my_flags, int world, uint32_t epoch, uint32_t* err, uint32_t phase,
@@ -1244,12 +1253,17 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
   uint32_t* my_flags = A.flags[A.rank];
   uint32_t* err = my_flags + 9;
   const uint32_t t = threadIdx.x;
+  // trace (words 16 .. 39 of the flag buffer, nanoseconds): CTA 0 stamps start / arrived / units done, the last CTA its end
+  unsigned long long* stamp = reinterpret_cast<unsigned long long*>(my_flags + 16);
+  auto now_ns = [] { unsigned long long v; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v)); return v; };
+  if (blockIdx.x == 0 && t == 0) stamp[0] = now_ns();
   // ---- arrive ----
   if (blockIdx.x == 0 && (int)t < A.world) {
     __threadfence_system();
     st_release_sys(A.flags[t] + A.rank, A.epoch);
   }
   peer_wait_all(my_flags, A.world, A.epoch, err, 0u, A.timeout_cycles);
+  if (blockIdx.x == 0 && t == 0) stamp[1] = now_ns();
   if (blockIdx.x == 0 && t == 0) {  // ltot rides in word 4^W of every launch table
     uint64_t lt = 0;
     for (int p = 0; p < A.world; p++) {
@@ -1261,10 +1275,9 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
   }
   if (BOTH) {
     const int W = A.W, sh_a = 2 * W - 6;
-    const uint32_t n_units = 4u << (2 * (W - 6));
-    for (uint32_t u = blockIdx.x; u < n_units; u += gridDim.x) {
+    for (uint32_t ju = blockIdx.x; ju < A.n_owned; ju += gridDim.x) {
+      const uint32_t u = A.units[ju];
       const uint32_t m = u >> 2, q = u & 3u, mp = revcomp_id(m, W - 6);
-      if (m > mp || (int)(m % (uint32_t)A.world) != A.rank) continue;  // CTA-uniform
       const bool self = m == mp;
       // X: rows a = 4 rx + q of tile m, thread t -> row rx = t >> 4, ids b0 .. b0 + 3
       const uint32_t rx = t >> 4, b0 = (t & 15u) * 4u;
@@ -1321,9 +1334,9 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
       __syncthreads();
     }
   } else {
-    const uint64_t n_units = A.n >> 10;
-    for (uint64_t u = blockIdx.x; u < n_units; u += gridDim.x) {
-      if ((int)(u % (uint64_t)A.world) != A.rank) continue;
+    const uint64_t n_mine = ((A.n >> 10) - (uint64_t)A.rank + (uint64_t)A.world - 1) / (uint64_t)A.world;  // units rank, rank + world, ...
+    for (uint64_t ju = blockIdx.x; ju < n_mine; ju += gridDim.x) {
+      const uint64_t u = (uint64_t)A.rank + ju * (uint64_t)A.world;
       const uint64_t j = (u << 10) + t * 4u;
       uint4 v[8];
 #pragma unroll
@@ -1339,18 +1352,22 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
     }
   }
   // ---- depart ----
+  if (blockIdx.x == 0 && t == 0) stamp[2] = now_ns();
   __threadfence_system();
   __syncthreads();
+  if (blockIdx.x == 0 && t == 0) stamp[3] = now_ns();
   if (t == 0) is_last = atomicAdd(my_flags + 8, 1u) == gridDim.x - 1 ? 1u : 0u;
   __syncthreads();
   if (is_last) {
     __threadfence();
+    if (t == 0) stamp[4] = now_ns();
     if (t == 0) my_flags[8] = 0u;
     if ((int)t < A.world) {
       __threadfence_system();
       st_release_sys(A.flags[t] + A.rank, A.epoch + 1u);
     }
     peer_wait_all(my_flags, A.world, A.epoch + 1u, err, 1u, A.timeout_cycles);
+    if (t == 0) stamp[5] = now_ns();
   }
 }
 
@@ -2072,6 +2089,7 @@ extern "C" void peng_cuda_destroy(peng_handle_t h) {
   cudaStreamSynchronize(h->stream);
   peng_cuda_peer_detach(h);
   dev_free(&h->peer.d_flags);
+  dev_free(&h->peer.d_units);
   dev_free(&h->d_codes); dev_free(&h->d_valid); dev_free(&h->d_sstart); dev_free(&h->d_kstart);
   dev_free(&h->d_offsets); dev_free(&h->d_hist32); dev_free(&h->d_counts); dev_free(&h->d_bgcounts);
   dev_free(&h->d_v32); dev_free(&h->d_v64);
@@ -3433,6 +3451,25 @@ extern "C" int peng_cuda_peer_detach(peng_handle_t h) {
   return PENG_OK;
 }
 
+// BOTH strands: the exchange units this rank owns — the quarter-tile pairs of the middles m <= revcomp(m) with
+// m mod world == rank — listed so that the CTAs take them one by one (a strided walk over all m left half of the CTAs
+// without work: 296 = 4 * 74 keeps m mod 2 fixed per CTA).  Built when the group is attached: nothing that allocates or
+// synchronises is left to do once the first exchange kernel of the group spins on a device.
+static int peer_build_units(peng_handle_t h) {
+  if (h->peer.units_W == h->W && h->peer.units_rank == h->peer.rank && h->peer.units_world == h->peer.world) return PENG_OK;
+  std::vector<uint32_t> units;
+  const uint32_t n_mid = 1u << (2 * (h->W - 6));
+  for (uint32_t m = (uint32_t)h->peer.rank; m < n_mid; m += (uint32_t)h->peer.world)
+    if (m <= (uint32_t)peng_host::revcomp_id64(m, h->W - 6))
+      for (uint32_t q = 0; q < 4; q++) units.push_back(m << 2 | q);
+  TRY(dev_alloc(h, &h->peer.d_units, std::max<size_t>(units.size(), 1)));
+  CU(h, cudaMemcpyAsync(h->peer.d_units, units.data(), units.size() * 4, cudaMemcpyHostToDevice, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  h->peer.n_owned = (uint32_t)units.size();
+  h->peer.units_W = h->W; h->peer.units_rank = h->peer.rank; h->peer.units_world = h->peer.world;
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const void* blobs) {
   if (!h || !blobs || world < 1 || world > 8 || rank < 0 || rank >= world) return fail(h, PENG_E_INVALID, "peer_attach: bad rank %d / world %d (1 .. 8)", rank, world);
   if (h->peer.attached) return fail(h, PENG_E_INVALID, "peer_attach: already attached");
@@ -3475,6 +3512,19 @@ extern "C" int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const
   h->peer.W = h->W;
   h->peer.epoch = 0;
   h->peer.attached = true;
+  TRY(peer_build_units(h));
+  return PENG_OK;
+}
+
+// trace of the last exchange kernel on this rank, nanoseconds relative to its start: arrived (all ranks' tables complete),
+// units of CTA 0 done, CTA 0's stores visible system-wide, all CTAs done, departed (all ranks' stores have landed)
+extern "C" int peng_cuda_peer_trace(peng_handle_t h, double* out5) {
+  if (!h || !h->peer.d_flags || !out5) return fail(h, PENG_E_INVALID, "peer_trace: no peer group");
+  CU(h, cudaSetDevice(h->device));
+  unsigned long long st[6];
+  CU(h, cudaMemcpyAsync(st, h->peer.d_flags + 16, sizeof st, cudaMemcpyDeviceToHost, h->stream));
+  CU(h, cudaStreamSynchronize(h->stream));
+  for (int i = 0; i < 5; i++) out5[i] = (double)(long long)(st[i + 1] - st[0]);
   return PENG_OK;
 }
 
@@ -3495,7 +3545,10 @@ extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
   h->peer.epoch += 2;
   A.epoch = h->peer.epoch - 1;  // arrive = epoch, depart = epoch + 1
   const bool both = h->strand == PENG_STRAND_BOTH;
-  const uint64_t n_units = both ? (4ull << (2 * (h->W - 6))) : (h->n_patterns >> 10);
+  if (both) TRY(peer_build_units(h));
+  A.units = h->peer.d_units;
+  A.n_owned = h->peer.n_owned;
+  const uint64_t n_units = both ? (uint64_t)std::max<uint32_t>(h->peer.n_owned, 1) : ((h->n_patterns >> 10) + h->peer.world - 1) / h->peer.world;
   // One rank per device (the product): two CTAs per SM (128 registers x 256 threads).  Several ranks on ONE device (tests,
   // handles of one process): their exchange kernels spin until the slowest rank has finished counting, so together they
   // may hold at most half of the SMs — the counting kernels of the late ranks (1024-thread CTAs) need whole SMs to run.

@@ -379,11 +379,13 @@ static void multi_count(MultiGpu& mg, const Device& dev, int W, int strand, uint
   const int N = (int)mg.hs.size();
   std::vector<int> rc((size_t)N, PENG_OK);
   auto first_error = [&]() {
+    bool bad = false;
     for (int r = 0; r < N; r++)
       if (rc[(size_t)r] != PENG_OK) {
-        std::cerr << peng_cuda_last_error(mg.hs[(size_t)r]) << std::endl;
-        exit(1);
+        std::cerr << "[device " << r << "] " << peng_cuda_last_error(mg.hs[(size_t)r]) << std::endl;
+        bad = true;
       }
+    if (bad) exit(1);
   };
   const bool exchange32 = W >= 8 && total_positions < ((uint64_t)1 << 32) - ((uint64_t)1 << 20) && max_shard_positions < ((uint64_t)1 << 30) - 4096;
   if (exchange32) {
@@ -400,7 +402,11 @@ static void multi_count(MultiGpu& mg, const Device& dev, int W, int strand, uint
       if (rc[(size_t)r] == PENG_OK) rc[(size_t)r] = peng_cuda_synchronize(mg.hs[(size_t)r]);
     });
     first_error();
-    mg.parallel([&](int r) { rc[(size_t)r] = peng_cuda_count_exchange32(mg.hs[(size_t)r], &lt[(size_t)r]); });
+    // launch everywhere first (ltot = NULL: nothing blocks), then fetch: a blocking read-back of one handle must not sit in
+    // the driver while another handle of the same device still has its kernel to launch
+    mg.parallel([&](int r) { rc[(size_t)r] = peng_cuda_count_exchange32(mg.hs[(size_t)r], nullptr); });
+    first_error();
+    mg.parallel([&](int r) { rc[(size_t)r] = peng_cuda_count_finish(mg.hs[(size_t)r], &lt[(size_t)r]); });
     first_error();
     for (int r = 0; r < N; r++) peng_cuda_peer_detach(mg.hs[(size_t)r]);
     *ltot = lt[0];
