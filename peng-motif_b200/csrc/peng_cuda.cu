@@ -1246,14 +1246,28 @@ __device__ __forceinline__ void st_peer_4u64(uint64_t* p, uint64_t a, uint64_t b
   asm volatile("st.global.v2.u64 [%0], {%1, %2};" :: "l"(p + 2), "l"(c), "l"(d) : "memory");
 }
 
+__device__ __forceinline__ void st_peer_u4(uint32_t* p, uint4 v) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// What crosses the link (second version; the first one published finished 64-bit bins, canonical and mirrored copy: 12 B
+// per bin and rank, and the all-to-all of 16-byte accesses only reaches ~300 GB/s per GPU — 86 us at N = 8): the owner of
+// a unit reads the unit's uint32 bins from all ranks and writes the pair sums back IN PLACE, as uint32, at the unit's HOME
+// positions of every rank's launch table (nobody else reads or writes those positions during the exchange): 4 B read +
+// 2 B written per bin and rank.  Home = the rows a & 3 == q of tile m for m < revcomp(m) (the band of tile revcomp(m) is
+// read, never written), the whole tile for a self-paired middle (one CTA loads it completely before it stores).  The
+// mirror copy and the widening to 64 bits are local work afterwards: k_expand_home_tiled (k_fold_first for PLUS), which
+// also leaves the launch table clean.
 template <bool BOTH>
 __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
-  __shared__ uint32_t tX[1024], tY[1024];
+  __shared__ __align__(16) uint32_t tS[4096];  // normal unit: tX = tS[0 .. 1023], tY = tS[1024 .. 2047]; self-paired middle: the whole tile
   __shared__ uint32_t is_last;
+  uint32_t* tX = tS;
+  uint32_t* tY = tS + 1024;
   uint32_t* my_flags = A.flags[A.rank];
   uint32_t* err = my_flags + 9;
   const uint32_t t = threadIdx.x;
-  // trace (words 16 .. 39 of the flag buffer, nanoseconds): CTA 0 stamps start / arrived / units done, the last CTA its end
+  // trace (words 16 .. of the flag buffer, nanoseconds): CTA 0 stamps start / arrived / units done, the last CTA its end
   unsigned long long* stamp = reinterpret_cast<unsigned long long*>(my_flags + 16);
   auto now_ns = [] { unsigned long long v; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v)); return v; };
   if (blockIdx.x == 0 && t == 0) stamp[0] = now_ns();
@@ -1277,12 +1291,45 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
     const int W = A.W, sh_a = 2 * W - 6;
     for (uint32_t ju = blockIdx.x; ju < A.n_owned; ju += gridDim.x) {
       const uint32_t u = A.units[ju];
-      const uint32_t m = u >> 2, q = u & 3u, mp = revcomp_id(m, W - 6);
-      const bool self = m == mp;
-      // X: rows a = 4 rx + q of tile m, thread t -> row rx = t >> 4, ids b0 .. b0 + 3
+      const uint32_t m = u >> 3, q = u & 7u, mp = revcomp_id(m, W - 6);
+      if (q == 4u) {  // self-paired middle: the 64 x 64 tile holds its own partners
+#pragma unroll 1
+        for (uint32_t k = 0; k < 4; k++) {
+          const uint32_t e0 = 4u * (t + 256u * k);  // elements e0 .. e0 + 3 = (a, b0 .. b0 + 3)
+          const uint64_t j = ((uint64_t)(e0 >> 6) << sh_a) | ((uint64_t)m << 6) | (e0 & 63u);
+          uint4 v[8];
+#pragma unroll
+          for (int p = 0; p < 8; p++)
+            if (p < A.world) v[p] = ld_peer_u4(A.hist[p] + j);
+          uint4 sv = make_uint4(0, 0, 0, 0);
+#pragma unroll
+          for (int p = 0; p < 8; p++)
+            if (p < A.world) { sv.x += v[p].x; sv.y += v[p].y; sv.z += v[p].z; sv.w += v[p].w; }
+          reinterpret_cast<uint4*>(tS)[t + 256u * k] = sv;
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (uint32_t k = 0; k < 4; k++) {
+          const uint32_t e0 = 4u * (t + 256u * k), a = e0 >> 6;
+          const uint64_t j = ((uint64_t)a << sh_a) | ((uint64_t)m << 6) | (e0 & 63u);
+          uint32_t o[4];
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            const uint32_t e = e0 + i, pe = revcomp3(e & 63u) * 64u + revcomp3(a);
+            o[i] = e == pe ? tS[e] : tS[e] + tS[pe];
+          }
+          const uint4 ov = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+          for (int p = 0; p < 8; p++)
+            if (p < A.world) st_peer_u4(A.hist[p] + j, ov);
+        }
+        __syncthreads();
+        continue;
+      }
+      // X (home): rows a = 4 rx + q of tile m, thread t -> row rx = t >> 4, ids b0 .. b0 + 3
       const uint32_t rx = t >> 4, b0 = (t & 15u) * 4u;
       const uint64_t jX = ((uint64_t)(rx * 4u + q) << sh_a) | ((uint64_t)m << 6) | b0;
-      // Y: the 16-column band 3 - q of tile mp, thread t -> row ay = t >> 2, band columns yl0 .. yl0 + 3
+      // Y (partners): the 16-column band 3 - q of tile mp, thread t -> row ay = t >> 2, band columns yl0 .. yl0 + 3
       const uint32_t ay = t >> 2, yl0 = (t & 3u) * 4u, band = 16u * (3u - q);
       const uint64_t jY = ((uint64_t)ay << sh_a) | ((uint64_t)mp << 6) | (band + yl0);
       uint4 vx[8], vy[8];
@@ -1301,38 +1348,23 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
           sy.x += vy[p].x; sy.y += vy[p].y; sy.z += vy[p].z; sy.w += vy[p].w;
         }
       }
-      reinterpret_cast<uint4*>(tX)[t] = sx;  // tX[rx * 64 + b]
       reinterpret_cast<uint4*>(tY)[t] = sy;  // tY[ay * 16 + yl]
       __syncthreads();
-      // X ids: the partner of (a, b) sits at Y row revcomp3(b), band column (3 - a2) + 4 (3 - a1), a1 = rx & 3, a2 = rx >> 2
-      {
-        const uint32_t ylp = (3u - (rx >> 2)) + 4u * (3u - (rx & 3u));
-        uint64_t o[4];
+      if (blockIdx.x == 0 && t == 0 && ju == 0) stamp[6] = now_ns();
+      // the partner of (a, b) sits at Y row revcomp3(b), band column (3 - a2) + 4 (3 - a1), a1 = rx & 3, a2 = rx >> 2
+      const uint32_t ylp = (3u - (rx >> 2)) + 4u * (3u - (rx & 3u));
+      uint4 ov;
+      ov.x = sx.x + tY[revcomp3(b0) * 16 + ylp];
+      ov.y = sx.y + tY[revcomp3(b0 + 1) * 16 + ylp];
+      ov.z = sx.z + tY[revcomp3(b0 + 2) * 16 + ylp];
+      ov.w = sx.w + tY[revcomp3(b0 + 3) * 16 + ylp];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const uint32_t b = b0 + i, ayp = revcomp3(b);
-          const uint64_t rj = ((uint64_t)ayp << sh_a) | ((uint64_t)mp << 6) | (band + ylp);
-          const uint32_t own = tX[t * 4 + i], other = tY[ayp * 16 + ylp];
-          o[i] = (jX + i == rj) ? (uint64_t)own : (uint64_t)own + other;
-        }
-#pragma unroll
-        for (int p = 0; p < 8; p++)
-          if (p < A.world) st_peer_4u64(A.counts[p] + jX, o[0], o[1], o[2], o[3]);
-      }
-      if (!self) {  // Y ids: the partner of (ay, band + yl) sits at X row (3 - (yl >> 2)) + 4 (3 - (yl & 3)), column revcomp3(ay)
-        const uint32_t bxp = revcomp3(ay);
-        uint64_t o[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-          const uint32_t yl = yl0 + i, rxp = (3u - (yl >> 2)) + 4u * (3u - (yl & 3u));
-          o[i] = (uint64_t)tY[t * 4 + i] + tX[rxp * 64 + bxp];
-        }
-#pragma unroll
-        for (int p = 0; p < 8; p++)
-          if (p < A.world) st_peer_4u64(A.counts[p] + jY, o[0], o[1], o[2], o[3]);
-      }
+      for (int p = 0; p < 8; p++)
+        if (p < A.world) st_peer_u4(A.hist[p] + jX, ov);
       __syncthreads();
+      if (blockIdx.x == 0 && t == 0 && ju == 0) stamp[7] = now_ns();
     }
+    (void)tX;
   } else {
     const uint64_t n_mine = ((A.n >> 10) - (uint64_t)A.rank + (uint64_t)A.world - 1) / (uint64_t)A.world;  // units rank, rank + world, ...
     for (uint64_t ju = blockIdx.x; ju < n_mine; ju += gridDim.x) {
@@ -1342,13 +1374,13 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
 #pragma unroll
       for (int p = 0; p < 8; p++)
         if (p < A.world) v[p] = ld_peer_u4(A.hist[p] + j);
-      uint64_t o[4] = {0, 0, 0, 0};
+      uint4 sv = make_uint4(0, 0, 0, 0);
 #pragma unroll
       for (int p = 0; p < 8; p++)
-        if (p < A.world) { o[0] += v[p].x; o[1] += v[p].y; o[2] += v[p].z; o[3] += v[p].w; }
+        if (p < A.world) { sv.x += v[p].x; sv.y += v[p].y; sv.z += v[p].z; sv.w += v[p].w; }
 #pragma unroll
       for (int p = 0; p < 8; p++)
-        if (p < A.world) st_peer_4u64(A.counts[p] + j, o[0], o[1], o[2], o[3]);
+        if (p < A.world) st_peer_u4(A.hist[p] + j, sv);
     }
   }
   // ---- depart ----
@@ -1367,7 +1399,43 @@ __global__ void __launch_bounds__(256) k_peer_exchange32(PeerArgs A) {
       st_release_sys(A.flags[t] + A.rank, A.epoch + 1u);
     }
     peer_wait_all(my_flags, A.world, A.epoch + 1u, err, 1u, A.timeout_cycles);
+    if (t == 0) A.hist[A.rank][A.n] = 0u;  // every rank has read this rank's ltot word
     if (t == 0) stamp[5] = now_ns();
+  }
+}
+
+// Local half of the exchange (BOTH): the launch table holds the pair sums at the HOME positions (tile m of every pair of
+// middles m < revcomp(m), all of a self-paired tile).  One CTA per pair writes tile m as it is and tile revcomp(m) as its
+// transposed copy — (a, b) <-> (revcomp3(b), revcomp3(a)) — into the 64-bit table, and clears both tiles of the launch table.
+__global__ void __launch_bounds__(256) k_expand_home_tiled(uint32_t* __restrict__ hist, uint64_t* __restrict__ acc, int W) {
+  __shared__ __align__(16) uint32_t tA[FOLD_TS * FOLD_TS];
+  const uint32_t m = blockIdx.x, mp = revcomp_id(m, W - 6);
+  if (m > mp) return;
+  const int sh_a = 2 * W - 6;
+  const uint32_t t = threadIdx.x;
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+#pragma unroll
+  for (uint32_t k = 0; k < 4; k++) {
+    const uint32_t e0 = 4u * (t + 256u * k);
+    uint4* src = reinterpret_cast<uint4*>(hist + (((uint64_t)(e0 >> 6) << sh_a) | ((uint64_t)m << 6) | (e0 & 63u)));
+    const uint4 v = *src;
+    reinterpret_cast<uint4*>(tA)[t + 256u * k] = v;
+    *src = zero;
+    ulonglong2* dst = reinterpret_cast<ulonglong2*>(acc + (((uint64_t)(e0 >> 6) << sh_a) | ((uint64_t)m << 6) | (e0 & 63u)));
+    dst[0] = make_ulonglong2(v.x, v.y);
+    dst[1] = make_ulonglong2(v.z, v.w);
+  }
+  if (m == mp) return;
+  __syncthreads();
+#pragma unroll
+  for (uint32_t k = 0; k < 4; k++) {
+    const uint32_t e0 = 4u * (t + 256u * k), ap = e0 >> 6, bp0 = e0 & 63u;  // elements (ap, bp0 .. bp0 + 3) of tile mp
+    const uint64_t j = ((uint64_t)ap << sh_a) | ((uint64_t)mp << 6) | bp0;
+    const uint32_t col = revcomp3(ap);  // source column in tile m; source rows revcomp3(bp)
+    ulonglong2* dst = reinterpret_cast<ulonglong2*>(acc + j);
+    dst[0] = make_ulonglong2(tA[revcomp3(bp0) * 64 + col], tA[revcomp3(bp0 + 1) * 64 + col]);
+    dst[1] = make_ulonglong2(tA[revcomp3(bp0 + 2) * 64 + col], tA[revcomp3(bp0 + 3) * 64 + col]);
+    *reinterpret_cast<uint4*>(hist + j) = zero;
   }
 }
 
@@ -3460,8 +3528,11 @@ static int peer_build_units(peng_handle_t h) {
   std::vector<uint32_t> units;
   const uint32_t n_mid = 1u << (2 * (h->W - 6));
   for (uint32_t m = (uint32_t)h->peer.rank; m < n_mid; m += (uint32_t)h->peer.world)
-    if (m <= (uint32_t)peng_host::revcomp_id64(m, h->W - 6))
-      for (uint32_t q = 0; q < 4; q++) units.push_back(m << 2 | q);
+  {
+    const uint32_t mp = (uint32_t)peng_host::revcomp_id64(m, h->W - 6);
+    if (m < mp) for (uint32_t q = 0; q < 4; q++) units.push_back(m << 3 | q);  // four quarter units
+    else if (m == mp) units.push_back(m << 3 | 4u);                              // self-paired middle: one whole-tile unit
+  }
   TRY(dev_alloc(h, &h->peer.d_units, std::max<size_t>(units.size(), 1)));
   CU(h, cudaMemcpyAsync(h->peer.d_units, units.data(), units.size() * 4, cudaMemcpyHostToDevice, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
@@ -3513,6 +3584,16 @@ extern "C" int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const
   h->peer.epoch = 0;
   h->peer.attached = true;
   TRY(peer_build_units(h));
+  // CUDA loads a kernel at its first launch, and that load can wait for the device to drain — forever, if it is requested
+  // while another rank's exchange kernel spins on this device waiting for THIS rank (seen with several handles of one
+  // process on one device).  Everything launched behind an exchange kernel is therefore loaded now.
+  {
+    cudaFuncAttributes fa;
+    CU(h, cudaFuncGetAttributes(&fa, k_peer_exchange32<true>));
+    CU(h, cudaFuncGetAttributes(&fa, k_peer_exchange32<false>));
+    CU(h, cudaFuncGetAttributes(&fa, k_expand_home_tiled));
+    CU(h, cudaFuncGetAttributes(&fa, k_fold_first));
+  }
   return PENG_OK;
 }
 
@@ -3521,10 +3602,12 @@ extern "C" int peng_cuda_peer_attach(peng_handle_t h, int rank, int world, const
 extern "C" int peng_cuda_peer_trace(peng_handle_t h, double* out5) {
   if (!h || !h->peer.d_flags || !out5) return fail(h, PENG_E_INVALID, "peer_trace: no peer group");
   CU(h, cudaSetDevice(h->device));
-  unsigned long long st[6];
+  unsigned long long st[8];
   CU(h, cudaMemcpyAsync(st, h->peer.d_flags + 16, sizeof st, cudaMemcpyDeviceToHost, h->stream));
   CU(h, cudaStreamSynchronize(h->stream));
   for (int i = 0; i < 5; i++) out5[i] = (double)(long long)(st[i + 1] - st[0]);
+  if (getenv("PENG_PEER_TRACE")) fprintf(stderr, "[peer trace] first unit of CTA 0: loads landed %+.2f us, stores issued %+.2f us (since kernel start)\n",
+                                         1e-3 * (double)(long long)(st[6] - st[0]), 1e-3 * (double)(long long)(st[7] - st[0]));
   return PENG_OK;
 }
 
@@ -3561,9 +3644,14 @@ extern "C" int peng_cuda_count_exchange32(peng_handle_t h, uint64_t* ltot) {
   if (both) k_peer_exchange32<true><<<grid, 256, 0, h->stream>>>(A);
   else k_peer_exchange32<false><<<grid, 256, 0, h->stream>>>(A);
   LAUNCH_CHECK(h);
+  // local half: widen to 64 bits (+ the mirror copy: transposed tiles) and clear the launch table
+  if (both) k_expand_home_tiled<<<1u << (2 * (h->W - 6)), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->W);
+  else k_fold_first<<<grid_for(h->n_patterns, 256), 256, 0, h->stream>>>(h->d_hist32, h->d_counts, h->n_patterns);
+  LAUNCH_CHECK(h);
   MARK(h, 10);
   h->fold_deferred = false;
   h->mirrored = true;
+  h->hist_clean = true;
   if (!ltot) {
     h->count_pending = true;
     return PENG_OK;
