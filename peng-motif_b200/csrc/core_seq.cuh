@@ -81,10 +81,14 @@ PENG_HD bool bit_at(const uint32_t* mask, uint64_t q) { return (ldg(mask + (q >>
 // One thread builds stream positions [32*t, 32*t+32): two code words, one valid word, one sstart word.
 // src holds the sequences concatenated WITHOUT separators, either in the reference's letter codes
 // (0 = other, 1..4 = ACGT; Alphabet::getCode, src/shared/Alphabet.cpp:33-41) or as raw FASTA letters.
-template <bool ASCII>
+// MODE 0: letter codes, one byte per base; 1: FASTA letters; 2: letter codes as NIBBLES (two bases per byte: base
+// src_base + 2 k in the low, src_base + 2 k + 1 in the high nibble of src[k] — the host's cheap half-way packing of the part
+// of a set it does not pack completely, host_pack.h: nibble_pack)
+template <int MODE>
 PENG_HD void pack_word(uint64_t t, const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets,
                        uint64_t n_seq, uint32_t* __restrict__ codes, uint32_t* __restrict__ valid,
-                       uint32_t* __restrict__ sstart, uint32_t* code_words_out = nullptr) {
+                       uint32_t* __restrict__ sstart, uint32_t* code_words_out = nullptr, uint64_t src_base = 0) {
+  constexpr bool ASCII = MODE == 1;
   const uint64_t q0 = t * 32;
   uint32_t c0 = 0, c1 = 0, v = 0, ss = 0;
   const uint64_t total = n_seq ? offsets[n_seq] : 0;
@@ -109,7 +113,13 @@ PENG_HD void pack_word(uint64_t t, const uint8_t* __restrict__ src, const uint64
       }
       const uint64_t i = q - s_start;
       if (i < s_len) {
-        const uint32_t ch = src[offsets[s] + i];
+        uint32_t ch;
+        if (MODE == 2) {
+          const uint64_t rel = offsets[s] + i - src_base;
+          ch = (src[rel >> 1] >> (4 * (rel & 1))) & 15u;
+        } else {
+          ch = src[offsets[s] + i];
+        }
         uint32_t code, ok;
         if (ASCII) {
           const uint32_t up = ch & 0xDFu;  // fold case

@@ -417,4 +417,48 @@ void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry) {
   }
 }
 
+// ---- nibble packing ---------------------------------------------------------------------------------------------------
+namespace {
+__attribute__((target("avx512f,avx512bw"))) void nibble_avx512(const uint8_t* src, uint64_t n, uint8_t* dst) {
+  uint64_t i = 0;
+  const __m512i four = _mm512_set1_epi8(4), w = _mm512_set1_epi16(0x1001);  // even byte * 1 + odd byte * 16
+  for (; i + 64 <= n; i += 64) {
+    const __m512i z = _mm512_loadu_si512((const void*)(src + i));
+    const __m512i c = _mm512_maskz_mov_epi8(_mm512_cmple_epu8_mask(z, four), z);
+    _mm256_storeu_si256((__m256i*)(dst + (i >> 1)), _mm512_cvtepi16_epi8(_mm512_maddubs_epi16(c, w)));
+  }
+  for (; i < n; i += 2) {
+    const uint32_t a = src[i] <= 4 ? src[i] : 0u, b = i + 1 < n && src[i + 1] <= 4 ? src[i + 1] : 0u;
+    dst[i >> 1] = (uint8_t)(a | (b << 4));
+  }
+}
+void nibble_scalar(const uint8_t* src, uint64_t n, uint8_t* dst) {
+  for (uint64_t i = 0; i < n; i += 2) {
+    const uint32_t a = src[i] <= 4 ? src[i] : 0u, b = i + 1 < n && src[i + 1] <= 4 ? src[i + 1] : 0u;
+    dst[i >> 1] = (uint8_t)(a | (b << 4));
+  }
+}
+struct NibbleRun {
+  const uint8_t* src;
+  uint8_t* dst;
+  uint64_t n;
+  int n_tasks;
+};
+void nibble_task(int i, void* arg) {
+  const NibbleRun& r = *(const NibbleRun*)arg;
+  // shares in multiples of 128 bases: every share starts on a whole destination byte (and a 64-byte source chunk)
+  const uint64_t per = ((r.n / (uint64_t)r.n_tasks) + 127) & ~(uint64_t)127;
+  const uint64_t b0 = std::min(r.n, per * (uint64_t)i), b1 = i == r.n_tasks - 1 ? r.n : std::min(r.n, per * (uint64_t)(i + 1));
+  if (b1 <= b0) return;
+  static const bool scalar = getenv("PENG_HOST_PACK_SCALAR") != nullptr;
+  if (have_avx512() && !scalar) nibble_avx512(r.src + b0, b1 - b0, r.dst + (b0 >> 1));
+  else nibble_scalar(r.src + b0, b1 - b0, r.dst + (b0 >> 1));
+}
+}  // namespace
+
+void nibble_pack(Pool& pool, const uint8_t* src, uint64_t n, uint8_t* dst) {
+  NibbleRun r{src, dst, n, std::max(1, std::min(pool.size() * 2, (int)(n / 65536 + 1)))};
+  pool.run(r.n_tasks, nibble_task, &r);
+}
+
 }  // namespace peng_hostpack

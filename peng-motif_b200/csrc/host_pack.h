@@ -43,6 +43,13 @@ struct Share {
 void pack_share(const Share& sh);
 bool have_avx512();
 
+class Pool;
+// Half-way packing for the part of a set the host does not pack completely: letter codes (0 = other, 1..4 = ACGT, anything
+// else counts as other) as NIBBLES, dst[k] = nib(src[2 k]) | nib(src[2 k + 1]) << 4 — four vector instructions per 64 bases
+// (near memcpy speed) and half the bytes over PCIe; the device unpacks them in k_pack<2> (core_seq.cuh: pack_word).
+// n even or the last byte's high nibble 0.  Runs on the pool's threads.
+void nibble_pack(Pool& pool, const uint8_t* src, uint64_t n, uint8_t* dst);
+
 // minimal persistent worker pool: run(n, fn) calls fn(i) for i = 0 .. n-1 on the pool's threads (the caller takes part)
 class Pool {
  public:

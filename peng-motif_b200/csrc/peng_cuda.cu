@@ -49,6 +49,8 @@ struct peng_cuda_ctx {
   cudaStream_t copy_stream = nullptr;       // H2D of ingest chunks, overlapped with packing on `stream`
   cudaEvent_t copy_ev[2] = {nullptr, nullptr};
   uint8_t* pin[2] = {nullptr, nullptr};    // pinned staging buffers of the streaming FASTA ingest
+  size_t pin_cap = 0;                       // their size: as large as the input needs, at most PENG_PIN_BYTES (pinning 2 x 16 MiB
+                                            // costs ~10 ms: most of a 1 MB file's ingest)
   cudaEvent_t pin_ev[2] = {nullptr, nullptr};
   std::vector<uint64_t> h_offsets;
   uint64_t* pin_offs = nullptr;    // pinned copy of the offsets for the H2D copy (hybrid ingest), grow-only
@@ -266,14 +268,14 @@ static inline bool tables_whole(peng_handle_t h) { return !h->counts_sliced && h
 // The packing kernels also write the bit planes of the words they produce (uint2 {bit 1, bit 0} per 32 positions, read by
 // stage P's conflict scan): the codes are in registers anyway, so the planes cost 8 more bytes written per 32 positions
 // and no pass of their own (k_make_planes, 26 us + 100 MB of traffic on configs[2], only runs for words the HOST packed).
-template <bool ASCII>
+template <int MODE>
 __global__ void k_pack(const uint8_t* __restrict__ src, const uint64_t* __restrict__ offsets, uint64_t n_seq,
                        uint32_t* __restrict__ codes, uint32_t* __restrict__ valid, uint32_t* __restrict__ sstart,
-                       uint2* __restrict__ planes, uint64_t t_begin, uint64_t t_end) {
+                       uint2* __restrict__ planes, uint64_t t_begin, uint64_t t_end, uint64_t src_base) {
   const uint64_t t = t_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t < t_end) {
     uint32_t c[2];
-    pack_word<ASCII>(t, src, offsets, n_seq, codes, valid, sstart, c);
+    pack_word<MODE>(t, src, offsets, n_seq, codes, valid, sstart, c, src_base);
     uint2 o;
     planes_of_unit(c[0], c[1], &o.x, &o.y);
     planes[t] = o;
@@ -2303,15 +2305,16 @@ static void host_bookkeeping_parallel(peng_handle_t h, const uint64_t* offsets, 
   h->max_len = mx;
 }
 
-static int launch_pack(peng_handle_t h, const uint8_t* d_src, bool ascii, uint64_t t_begin, uint64_t t_end) {
+// mode 0 / 1 / 2: letter codes / FASTA letters / nibbles relative to base src_base (pack_word)
+static int launch_pack(peng_handle_t h, const uint8_t* d_src, int mode, uint64_t t_begin, uint64_t t_end, uint64_t src_base = 0) {
   if (t_end <= t_begin) return PENG_OK;
-  const unsigned block = 256;
-  if (ascii)
-    k_pack<true><<<grid_for(t_end - t_begin, block), block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid,
-                                                                          h->d_sstart, h->d_planes, t_begin, t_end);
+  const unsigned block = 256, grid = grid_for(t_end - t_begin, block);
+  if (mode == 1)
+    k_pack<1><<<grid, block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid, h->d_sstart, h->d_planes, t_begin, t_end, 0);
+  else if (mode == 2)
+    k_pack<2><<<grid, block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid, h->d_sstart, h->d_planes, t_begin, t_end, src_base);
   else
-    k_pack<false><<<grid_for(t_end - t_begin, block), block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid,
-                                                                           h->d_sstart, h->d_planes, t_begin, t_end);
+    k_pack<0><<<grid, block, 0, h->stream>>>(d_src, h->d_offsets, h->n_seq, h->d_codes, h->d_valid, h->d_sstart, h->d_planes, t_begin, t_end, 0);
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
@@ -2331,7 +2334,7 @@ static int prepare_ingest(peng_handle_t h, const uint64_t* offsets, uint64_t n_s
 static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
   TRY(prepare_ingest(h, offsets, n_seq));
   CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
-  TRY(launch_pack(h, d_src, ascii, 0, h->n_words32));
+  TRY(launch_pack(h, d_src, ascii ? 1 : 0, 0, h->n_words32));
   h->planes_valid = true;
   h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping in the shadow of the device work
   seq_lengths(h, offsets, n_seq);
@@ -2342,16 +2345,23 @@ static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64
 #ifndef PENG_PHASE_MB_DEFAULT
 #define PENG_PHASE_MB_DEFAULT 16
 #endif
+static int need_pins(peng_handle_t h, size_t bytes) {
+  bytes = std::min<size_t>(PENG_PIN_BYTES, std::max<size_t>(bytes, (size_t)64 << 10));
+  if (h->pin_cap >= bytes) return PENG_OK;
+  for (int i = 0; i < 2; i++) {
+    if (h->pin[i]) { CU(h, cudaStreamSynchronize(h->copy_stream ? h->copy_stream : h->stream)); cudaFreeHost(h->pin[i]); h->pin[i] = nullptr; }
+    CU(h, cudaHostAlloc((void**)&h->pin[i], bytes, cudaHostAllocDefault));
+    if (!h->pin_ev[i]) CU(h, cudaEventCreateWithFlags(&h->pin_ev[i], cudaEventDisableTiming));
+  }
+  h->pin_cap = bytes;
+  return PENG_OK;
+}
 static int need_copy_stream_and_pins(peng_handle_t h, bool pins) {
   if (!h->copy_stream) {
     CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 2; i++) CU(h, cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
   }
-  if (pins && !h->pin[0])
-    for (int i = 0; i < 2; i++) {
-      CU(h, cudaHostAlloc((void**)&h->pin[i], PENG_PIN_BYTES, cudaHostAllocDefault));
-      CU(h, cudaEventCreateWithFlags(&h->pin_ev[i], cudaEventDisableTiming));
-    }
+  if (pins) TRY(need_pins(h, PENG_PIN_BYTES));
   return PENG_OK;
 }
 
@@ -2383,8 +2393,23 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   // automatic choice only where it pays; an explicit mode or fraction is taken as given (tests, tuning)
   if (!force && h->ingest_fraction < 0 && (!have_avx512() || pool.size() < 4 || total < (1ull << 22))) return 1;
   h->last_ingest_packed = 0;
+  // PENG_NIBBLE=1 (off by default): the part the host does not pack completely travels as NIBBLES (host_pack.h: nibble_pack,
+  // 0.5 instead of 1 B/base over PCIe).  Measured on the B200 box (16 host threads, tools/ingest_bench.py,
+  // profiles/r2_ingest_nibble_vs_raw.txt): best split 2.94 ms against 2.63 ms for raw bytes straight out of the caller's
+  // buffer — the host threads are the co-bottleneck of the hybrid ingest, and every byte they touch a second time costs
+  // more than the PCIe bytes it saves.  Kept for hosts with more cores per GPU than PCIe bandwidth.
+  static const bool use_nibble = getenv("PENG_NIBBLE") != nullptr;
+  const bool nib = !ascii && !seq_ptrs && use_nibble;
   double f = 1.0;
-  if (!force) {
+  if (!force && nib) {
+    // host: f / rh + (1 - f) / rn of packing, bus: (0.375 f + 0.5 (1 - f)) / rp — equal at
+    //   f = (0.5 / rp - 1 / rn) / (1 / rh - 1 / rn + 0.125 / rp)       (rn = nibble rate: ~3 x the full packing rate)
+    static const double rn_factor = getenv("PENG_NIBBLE_RATE_FACTOR") ? atof(getenv("PENG_NIBBLE_RATE_FACTOR")) : 3.0;
+    const double rh = 0.8 * (5.7 * std::min(pool.size(), 8) + 2.2 * std::max(0, pool.size() - 8)), rn = rn_factor * rh, rp = 46.0;
+    f = (0.5 / rp - 1.0 / rn) / (1.0 / rh - 1.0 / rn + 0.125 / rp);
+    if (h->ingest_fraction >= 0) f = h->ingest_fraction;
+    f = std::min(1.0, std::max(0.0, f));
+  } else if (!force) {
     // Gbases/s: measured packing rate (5.7 per thread up to 8 threads, 63 at 16: tools/probe/host_pack_bench.cpp), PCIe rate
     // x 0.8: the packing runs beside the DMA traffic and behind the bookkeeping pass (measured optimum at 16 threads: 0.65)
     const double rh = 0.8 * (5.7 * std::min(pool.size(), 8) + 2.2 * std::max(0, pool.size() - 8)), rp = 46.0;
@@ -2426,7 +2451,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   const uint64_t n_blocks = q_total / 64;
   const uint64_t q_split = PENG_FRONT_PAD + offsets[s_split] + 2 * s_split;
   const uint64_t blk_split = s_split < n_seq ? (q_split >> 6) : n_blocks;
-  const uint64_t b_lo = s_split < n_seq ? offsets[s_split] - std::min<uint64_t>(offsets[s_split], 128) : total;
+  const uint64_t b_lo = s_split < n_seq ? (offsets[s_split] - std::min<uint64_t>(offsets[s_split], 128)) & ~(uint64_t)1 : total;
   if (s_split < n_seq) TRY(need_scratch(h, (size_t)(total - b_lo) + 16));
   if (h->pin_offs_cap < n_seq + 1) {
     if (h->pin_offs) cudaFreeHost(h->pin_offs);
@@ -2442,7 +2467,19 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
   mark(2);
   // ---- the raw rest: queued first, the DMA engine works on it while the host packs ----
-  if (s_split < n_seq) {
+  int buf = 0;
+  if (s_split < n_seq && nib) {
+    // nibbles through the two pinned staging buffers: the pool packs chunk i while the DMA engine moves chunk i - 1
+    const uint64_t chunk = 2 * (uint64_t)h->pin_cap;  // bases per staging buffer
+    for (uint64_t b0 = b_lo; b0 < total; b0 += chunk) {
+      const uint64_t b1 = std::min(total, b0 + chunk);
+      CU(h, cudaEventSynchronize(h->pin_ev[buf]));  // the previous copy out of this staging buffer is done
+      nibble_pack(pool, src + b0, b1 - b0, h->pin[buf]);
+      CU(h, cudaMemcpyAsync((uint8_t*)h->d_scratch + ((b0 - b_lo) >> 1), h->pin[buf], (size_t)((b1 - b0 + 1) >> 1), cudaMemcpyHostToDevice, h->copy_stream));
+      CU(h, cudaEventRecord(h->pin_ev[buf], h->copy_stream));
+      buf ^= 1;
+    }
+  } else if (s_split < n_seq) {
     const uint64_t chunk = 32ull << 20;
     for (uint64_t b0 = b_lo; b0 < total; b0 += chunk) {
       const uint64_t b1 = std::min(total, b0 + chunk);
@@ -2458,7 +2495,8 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     const uint8_t* d_src = (const uint8_t*)h->d_scratch - b_lo;  // indexed by absolute base offset, never read below b_lo
     CU(h, cudaEventRecord(h->copy_ev[0], h->copy_stream));
     CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[0], 0));
-    TRY(launch_pack(h, d_src, ascii, blk_split * 2, h->n_words32));
+    if (nib) TRY(launch_pack(h, (const uint8_t*)h->d_scratch, 2, blk_split * 2, h->n_words32, b_lo));
+    else TRY(launch_pack(h, d_src, ascii ? 1 : 0, blk_split * 2, h->n_words32));
     // the units behind the one that holds the first position of sequence s_split look at k_pack's words only (every
     // look-back of the k-mer start rule stops at that sequence's start): their stage P runs under the DMA of the phases
     if (pr.on) TRY(prefetch_range(h, &pr, (q_split >> 5) + 1, h->n_words32));
@@ -2466,7 +2504,6 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   // ---- the packed part, phase by phase through the two pinned staging buffers ----
   bool has_carry = false;
   Partial carry{};
-  int buf = 0;
   bool first = true;
   static const bool dbg = getenv("PENG_INGEST_DEBUG") != nullptr;
   static const bool taper = getenv("PENG_NO_TAPER") == nullptr;
@@ -2591,7 +2628,7 @@ static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* 
       s_hint = (uint64_t)(it - offsets) - 1;
       t_end = (PENG_FRONT_PAD + b1 + 2 * s_hint) / 32;
     }
-    TRY(launch_pack(h, d_src, ascii, t_done, t_end));
+    TRY(launch_pack(h, d_src, ascii ? 1 : 0, t_done, t_end));
     t_done = std::max(t_done, t_end);
     if (total == 0) break;
   }
@@ -2691,12 +2728,12 @@ struct StagingSink {
     segments.emplace_back(p, n);
     if (!cur_keep) return;
     while (n && rc == PENG_OK) {
-      const size_t m = std::min<size_t>(n, PENG_PIN_BYTES - fill);
+      const size_t m = std::min<size_t>(n, h->pin_cap - fill);
       memcpy(h->pin[cur] + fill, p, m);
       fill += m;
       p += m;
       n -= m;
-      if (fill == PENG_PIN_BYTES) flush();
+      if (fill == h->pin_cap) flush();
     }
   }
   void end_record(const char* header, size_t header_len) {
@@ -2737,11 +2774,7 @@ static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_
     CU(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 2; i++) CU(h, cudaEventCreateWithFlags(&h->copy_ev[i], cudaEventDisableTiming));
   }
-  if (!h->pin[0])
-    for (int i = 0; i < 2; i++) {
-      CU(h, cudaHostAlloc((void**)&h->pin[i], PENG_PIN_BYTES, cudaHostAllocDefault));
-      CU(h, cudaEventCreateWithFlags(&h->pin_ev[i], cudaEventDisableTiming));
-    }
+  TRY(need_pins(h, file.size + 1));
   // the copy stream must not run ahead of earlier work on the handle's stream that still reads the scratch buffer
   CU(h, cudaEventRecord(h->copy_ev[0], h->stream));
   CU(h, cudaStreamWaitEvent(h->copy_stream, h->copy_ev[0], 0));
@@ -2776,7 +2809,7 @@ static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_
   CU(h, cudaMemcpyAsync(h->d_offsets, sink.offsets.data(), (ns + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
   CU(h, cudaEventRecord(h->copy_ev[1], h->copy_stream));
   CU(h, cudaStreamWaitEvent(h->stream, h->copy_ev[1], 0));
-  TRY(launch_pack(h, sink.d_src, true, 0, h->n_words32));
+  TRY(launch_pack(h, sink.d_src, 1, 0, h->n_words32));
   h->planes_valid = true;
   seq_lengths(h, sink.offsets.data(), ns);
   h->h_offsets.swap(sink.offsets);

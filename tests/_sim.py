@@ -256,3 +256,14 @@ def select_levels(z, counts, W, z_threshold=10.0, count_threshold=3, single_stra
                               C.c_int(int(single_stranded)), C.c_int(int(filter_neighbors)), C.c_uint64(stop_below), _p(out, u64p),
                               C.c_uint64(len(out)), C.byref(lv))
     return out[:n].copy(), lv.value
+
+
+def pack_nibbles(src, offsets, src_base, n_threads=3):
+    """nibble_pack (host) + pack_word<2> (device body) for the words behind src_base -> (Stream, first word written)"""
+    n_seq = len(offsets) - 1
+    st = Stream(n_seq, int(offsets[-1]))
+    src = np.ascontiguousarray(src, np.uint8)
+    fw = C.c_uint64()
+    lib.sim_pack_nibbles(_p(src, u8p), _p(offsets, u64p), C.c_uint64(n_seq), C.c_uint64(src_base), C.c_int(n_threads), _p(st.codes, u32p),
+                         _p(st.valid, u32p), _p(st.sstart, u32p), C.byref(fw))
+    return st, fw.value

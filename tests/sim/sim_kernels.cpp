@@ -80,6 +80,11 @@ void sim_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, int a
   }
 }
 
+// nibble path of the hybrid ingest: the host's nibble_pack of the bases [src_base, total) (host_pack.cpp, the pool's threads)
+// followed by pack_word<2> on every word — must leave what pack_word<0> leaves for the words that hold no base below src_base
+void sim_pack_nibbles(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, uint64_t src_base, int n_threads, uint32_t* codes,
+                      uint32_t* valid, uint32_t* sstart, uint64_t* first_word);
+
 void sim_synth(uint64_t n_seq, uint32_t seq_len, uint64_t seed, uint64_t first_seq, const uint8_t* motif,
                uint32_t motif_len, double plant_fraction, double n_fraction, uint32_t* codes, uint32_t* valid,
                uint32_t* sstart) {
@@ -422,6 +427,21 @@ uint64_t sim_select_levels(const float* z, const uint64_t* counts, int W, float 
 // ---- host half of the packed ingest (host_pack.cpp): all phases into one host image of the device arrays ----------------
 #include "../../peng-motif_b200/csrc/host_pack.cpp"
 extern "C" {
+void sim_pack_nibbles(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, uint64_t src_base, int n_threads, uint32_t* codes,
+                      uint32_t* valid, uint32_t* sstart, uint64_t* first_word) {
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  std::vector<uint8_t> nib((total - src_base + 1) / 2 + 64, 0xEE);
+  peng_hostpack::Pool pool(n_threads);
+  peng_hostpack::nibble_pack(pool, src + src_base, total - src_base, nib.data());
+  // first word whose positions all lie at or behind the first base >= src_base
+  uint64_t s = 0;
+  while (s < n_seq && offsets[s] < src_base) s++;
+  const uint64_t q = PENG_FRONT_PAD + (s < n_seq ? offsets[s] : total) + 2 * s;
+  *first_word = (q + 31) / 32;
+  const uint64_t nw = sim_n_words32(n_seq, total);
+  for (uint64_t t = *first_word; t < nw; t++) pack_word<2>(t, nib.data(), offsets, n_seq, codes, valid, sstart, nullptr, src_base);
+}
+
 // codes32: 2 * n_words32 + 8 words, valid32: n_words32 + 8 words (as the device allocates them); returns the number of
 // phases, or -1 when a sequence does not fit a phase
 int sim_host_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, int ascii, int n_threads, uint64_t max_blocks,

@@ -397,3 +397,21 @@ def test_host_pack_scalar_path_and_oversized_sequence():
     codes = rng.randint(0, 5, 5100).astype(np.uint8)
     assert S.host_pack(codes, offs, False, 2, 16)[3] == -1  # the 4950-letter sequence needs 78 blocks
     _host_pack_matches(codes, offs, False, 2, 200)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_nibble_path_equals_byte_path(seed):
+    """The half-way packing of the hybrid ingest (host: nibble_pack over the pool's threads, device: pack_word<2>) leaves the
+    same code / validity / sequence-start words as the one-byte-per-base path, for every (even) split position; letter codes
+    above 4 count as 'other' in both."""
+    rng = np.random.RandomState(seed)
+    lens = rng.randint(1, 700, rng.randint(5, 400))
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    src = rng.randint(0, 7, int(offs[-1])).astype(np.uint8)  # 5, 6: not letters
+    ref = S.pack(src, offs, False)
+    for s_split in (0, 1, len(lens) // 2, len(lens) - 1):
+        base = (int(offs[s_split]) - min(int(offs[s_split]), 128)) & ~1
+        st, fw = S.pack_nibbles(src, offs, base, n_threads=1 + seed % 4)
+        assert fw <= (64 + int(offs[s_split]) + 2 * s_split + 31) // 32 + 1
+        assert np.array_equal(st.codes[2 * fw:], ref.codes[2 * fw:]) and np.array_equal(st.valid[fw:], ref.valid[fw:])
+        assert np.array_equal(st.sstart[fw:], ref.sstart[fw:])
