@@ -125,6 +125,7 @@ struct peng_cuda_ctx {
   uint32_t* d_sel = nullptr;       // seed selection: order | list A | list B | block counts | state
   size_t sel_words = 0;
   bool select_on_host = false;     // PENG_SELECT_HOST: whole-table host replay (A/B, tests)
+  bool use_nibble = false;         // PENG_NIBBLE: nibble staging of the raw part of the hybrid ingest
 
   // ---- peer group: fused cross-GPU sum + fold over NVLink peer memory (peng_cuda_peer_*, peng_cuda_count_exchange32) ----
   struct {
@@ -2128,6 +2129,7 @@ extern "C" int peng_cuda_create(int device, peng_handle_t* out) {
   if (const char* e = getenv("PENG_HOST_PACK_FRACTION")) h->ingest_fraction = atof(e);
   if (const char* e = getenv("PENG_DEEP_MODE")) h->deep_mode = atoi(e);
   h->select_on_host = getenv("PENG_SELECT_HOST") != nullptr;
+  h->use_nibble = getenv("PENG_NIBBLE") != nullptr;
   if (const char* e = getenv("PENG_PEER_TIMEOUT_MS")) h->peer.timeout_ms = std::max(1.0, atof(e));
   *out = h;
   return PENG_OK;
@@ -2398,8 +2400,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   // profiles/r2_ingest_nibble_vs_raw.txt): best split 2.94 ms against 2.63 ms for raw bytes straight out of the caller's
   // buffer — the host threads are the co-bottleneck of the hybrid ingest, and every byte they touch a second time costs
   // more than the PCIe bytes it saves.  Kept for hosts with more cores per GPU than PCIe bandwidth.
-  static const bool use_nibble = getenv("PENG_NIBBLE") != nullptr;
-  const bool nib = !ascii && !seq_ptrs && use_nibble;
+  const bool nib = !ascii && !seq_ptrs && h->use_nibble;
   double f = 1.0;
   if (!force && nib) {
     // host: f / rh + (1 - f) / rn of packing, bus: (0.375 f + 0.5 (1 - f)) / rp — equal at
