@@ -1150,7 +1150,13 @@ __global__ void __launch_bounds__(256) k_mirror_tiled(uint64_t* __restrict__ cou
     }
   }
 }
-#define FOLD_TILED_MIN_W 12
+// tiled from W = 8 on (2 letters of middle): at W = 10 the one-thread-per-id fold took 23 us of a 0.48 ms step although the
+// table is L2-resident (scattered 4-byte partner reads), the tiled one 256- / 512-byte runs only.  PENG_FOLD_TILED_MIN_W for A/B.
+static int fold_tiled_min_w() {
+  static const int v = getenv("PENG_FOLD_TILED_MIN_W") ? atoi(getenv("PENG_FOLD_TILED_MIN_W")) : 8;
+  return std::max(8, v);
+}
+#define FOLD_TILED_MIN_W fold_tiled_min_w()
 static int launch_fold_canon(peng_handle_t h, int W, bool first, bool mirror) {
   const uint64_t n = h->n_patterns;
   if (W >= FOLD_TILED_MIN_W && !h->fold_untiled) {
