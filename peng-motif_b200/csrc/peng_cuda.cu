@@ -53,6 +53,7 @@ struct peng_cuda_ctx {
                                             // costs ~10 ms: most of a 1 MB file's ingest)
   cudaEvent_t pin_ev[2] = {nullptr, nullptr};
   std::vector<uint64_t> h_offsets;
+  bool offsets_in_pin = false;     // the host's copy of the offsets is pin_offs (hybrid ingest), not h_offsets
   uint64_t* pin_offs = nullptr;    // pinned copy of the offsets for the H2D copy (hybrid ingest), grow-only
   size_t pin_offs_cap = 0;
 
@@ -2294,15 +2295,17 @@ static void book_task(int i, void* arg) {
   }
   b.mn[i] = mn;
   b.mx[i] = mx;
-  memcpy(b.dst + s0, b.offsets + s0, (s1 - s0 + (i == b.n_tasks - 1 ? 1 : 0)) * sizeof(uint64_t));
+  if (b.dst) memcpy(b.dst + s0, b.offsets + s0, (s1 - s0 + (i == b.n_tasks - 1 ? 1 : 0)) * sizeof(uint64_t));
   if (b.dst2) memcpy(b.dst2 + s0, b.offsets + s0, (s1 - s0 + (i == b.n_tasks - 1 ? 1 : 0)) * sizeof(uint64_t));
 }
 static void host_bookkeeping_parallel(peng_handle_t h, const uint64_t* offsets, uint64_t n_seq, uint64_t* pinned_copy = nullptr) {
-  if (h->h_offsets.size() != n_seq + 1) h->h_offsets.resize(n_seq + 1);
+  // with a pinned copy at hand that copy is also the host's record of the offsets (peng_cuda_export_codes): one copy, not two
+  h->offsets_in_pin = pinned_copy != nullptr;
+  if (!pinned_copy && h->h_offsets.size() != n_seq + 1) h->h_offsets.resize(n_seq + 1);
   peng_hostpack::Pool& pool = peng_hostpack::global_pool();
   BookTask b;
   b.offsets = offsets;
-  b.dst = h->h_offsets.data();
+  b.dst = pinned_copy ? nullptr : h->h_offsets.data();
   b.dst2 = pinned_copy;
   b.n_seq = n_seq;
   b.n_tasks = std::min(pool.size(), 64);
@@ -2344,6 +2347,7 @@ static int ingest_device_src(peng_handle_t h, const uint8_t* d_src, const uint64
   CU(h, cudaMemcpyAsync(h->d_offsets, offsets, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->stream));
   TRY(launch_pack(h, d_src, ascii ? 1 : 0, 0, h->n_words32));
   h->planes_valid = true;
+  h->offsets_in_pin = false;
   h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping in the shadow of the device work
   seq_lengths(h, offsets, n_seq);
   return PENG_OK;
@@ -2640,6 +2644,7 @@ static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* 
     if (total == 0) break;
   }
   h->planes_valid = true;
+  h->offsets_in_pin = false;
   h->h_offsets.assign(offsets, offsets + n_seq + 1);  // host bookkeeping while the DMA engine works
   seq_lengths(h, offsets, n_seq);
   CU(h, cudaStreamSynchronize(h->stream));  // the caller may free / reuse src
@@ -2819,6 +2824,7 @@ static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_
   TRY(launch_pack(h, sink.d_src, 1, 0, h->n_words32));
   h->planes_valid = true;
   seq_lengths(h, sink.offsets.data(), ns);
+  h->offsets_in_pin = false;
   h->h_offsets.swap(sink.offsets);
   CU(h, cudaStreamSynchronize(h->stream));
   if (n_seq) *n_seq = h->n_seq;
@@ -2834,6 +2840,7 @@ extern "C" int peng_cuda_ingest_synthetic(peng_handle_t h, uint64_t n_seq, uint3
   if (!h || seq_len == 0 || motif_len > 32) return fail(h, PENG_E_INVALID, "ingest_synthetic: bad argument");
   CU(h, cudaSetDevice(h->device));
   h->fixed_len = seq_len;
+  h->offsets_in_pin = false;
   h->h_offsets.clear();
   dev_free(&h->d_offsets);
   h->cap_offsets = 0;
@@ -2876,6 +2883,7 @@ extern "C" int peng_cuda_export_codes(peng_handle_t h, uint8_t* codes, uint64_t*
   CU(h, cudaSetDevice(h->device));
   if (offsets) {
     if (h->fixed_len) for (uint64_t s = 0; s <= h->n_seq; s++) offsets[s] = s * h->fixed_len;
+    else if (h->offsets_in_pin) std::copy(h->pin_offs, h->pin_offs + h->n_seq + 1, offsets);
     else std::copy(h->h_offsets.begin(), h->h_offsets.end(), offsets);
   }
   if (codes && h->total_bases) {
