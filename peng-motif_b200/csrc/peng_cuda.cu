@@ -1905,15 +1905,25 @@ __global__ void k_em_accumulate_small(const uint64_t* __restrict__ counts, const
   partials[(size_t)m * (W * 4) + c] = s;
 }
 
-// acc[m][i] = sum_b partials[m][b][i] in fixed order
-__global__ void k_em_reduce(const double* __restrict__ partials, const int* __restrict__ active, int nbx, int WA,
-                            double* __restrict__ acc) {
-  const int m = blockIdx.x, i = threadIdx.x;
-  if (i >= WA) return;
+// acc[m][i] = sum_b partials[m][b][i] in fixed order (16 strided part sums per accumulator, then those in order)
+__global__ void __launch_bounds__(PENG_MAX_W * 4 * 16) k_em_reduce(const double* __restrict__ partials, const int* __restrict__ active,
+                                                                   int nbx, int WA, double* __restrict__ acc) {
+  const int m = blockIdx.x;
   if (!active[m]) return;
-  double s = 0;
-  for (int b = 0; b < nbx; b++) s += partials[((size_t)m * nbx + b) * WA + i];
-  acc[(size_t)m * WA + i] = s;
+  __shared__ double part[16][PENG_MAX_W * 4];
+  const int i = threadIdx.x % (PENG_MAX_W * 4), r = threadIdx.x / (PENG_MAX_W * 4);
+  if (i < WA) {
+    double s = 0;
+    for (int b = r; b < nbx; b += 16) s += partials[((size_t)m * nbx + b) * WA + i];
+    part[r][i] = s;
+  }
+  __syncthreads();
+  if (r == 0 && i < WA) {
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s += part[k][i];
+    acc[(size_t)m * WA + i] = s;
+  }
 }
 
 // normalise rows, L1 change, iteration bookkeeping (src/peng.cpp:104-144); one warp per PWM
@@ -1941,22 +1951,33 @@ __global__ void k_em_update_f64(const double* __restrict__ acc, double* __restri
   }
 }
 
-// single-GPU iteration tail: k_em_reduce + k_em_update_f64 in one launch (one block per PWM)
-__global__ void __launch_bounds__(64) k_em_reduce_update(const double* __restrict__ partials, int nbx, double* __restrict__ acc,
-                                                         double* __restrict__ old_pwm, double* __restrict__ change,
-                                                         int* __restrict__ iters, int* __restrict__ active, int W, double threshold,
-                                                         int max_iterations, int* __restrict__ n_active) {
-  const int m = blockIdx.x, i = threadIdx.x, WA = W * 4;
+// single-GPU iteration tail: k_em_reduce + k_em_update_f64 in one launch (one block per PWM).  16 threads per accumulator
+// take every 16th partial row each, their sums are added in fixed order: deterministic, and 296 rows cost 19 dependent
+// loads instead of 296 (the one-thread-per-accumulator version took 37 us per iteration — as long as the table pass at W = 10).
+#define EM_RED_PARTS 16
+__global__ void __launch_bounds__(PENG_MAX_W * 4 * EM_RED_PARTS) k_em_reduce_update(
+    const double* __restrict__ partials, int nbx, double* __restrict__ acc, double* __restrict__ old_pwm, double* __restrict__ change,
+    int* __restrict__ iters, int* __restrict__ active, int W, double threshold, int max_iterations, int* __restrict__ n_active) {
+  const int m = blockIdx.x, WA = W * 4;
   if (!active[m]) return;
+  __shared__ double part[EM_RED_PARTS][PENG_MAX_W * 4];
   __shared__ double sh[PENG_MAX_W * 4];
+  const int i = threadIdx.x % (PENG_MAX_W * 4), r = threadIdx.x / (PENG_MAX_W * 4);
   if (i < WA) {
     double s = 0;
-    for (int b = 0; b < nbx; b++) s += partials[((size_t)m * nbx + b) * WA + i];
+    for (int b = r; b < nbx; b += EM_RED_PARTS) s += partials[((size_t)m * nbx + b) * WA + i];
+    part[r][i] = s;
+  }
+  __syncthreads();
+  if (r == 0 && i < WA) {
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < EM_RED_PARTS; k++) s += part[k][i];
     sh[i] = s;
     acc[(size_t)m * WA + i] = s;
   }
   __syncthreads();
-  if (i != 0) return;
+  if (threadIdx.x != 0) return;
   double ch = 0;
   for (int p = 0; p < W; p++) {
     double s = 0;
@@ -4416,7 +4437,7 @@ extern "C" int peng_cuda_em_accumulate(peng_handle_t h) {
   CU(h, cudaSetDevice(h->device));
   auto& E = h->em;
   TRY(em_accumulate_partials(h));
-  k_em_reduce<<<E.n, 64, 0, h->stream>>>(E.d_part, E.d_active, E.nbx, h->W * 4, E.d_acc);
+  k_em_reduce<<<E.n, PENG_MAX_W * 4 * 16, 0, h->stream>>>(E.d_part, E.d_active, E.nbx, h->W * 4, E.d_acc);
   LAUNCH_CHECK(h);
   return PENG_OK;
 }
@@ -4516,7 +4537,7 @@ extern "C" int peng_cuda_em(peng_handle_t h, int n_pwms, const void* pwm_in, int
   for (int it = 0; it < max_iterations; it++) {
     TRY(em_accumulate_partials(h));
     CU(h, cudaMemsetAsync(E.d_nactive, 0, 4, h->stream));
-    k_em_reduce_update<<<E.n, 64, 0, h->stream>>>(E.d_part, E.nbx, E.d_acc, E.d_old, E.d_change, E.d_iter, E.d_active, h->W, E.thr,
+    k_em_reduce_update<<<E.n, PENG_MAX_W * 4 * EM_RED_PARTS, 0, h->stream>>>(E.d_part, E.nbx, E.d_acc, E.d_old, E.d_change, E.d_iter, E.d_active, h->W, E.thr,
                                                   E.max_it, E.d_nactive);
     LAUNCH_CHECK(h);
     if ((it & 3) == 3) {  // look at the convergence flags every 4th iteration only (converged PWMs cost nothing meanwhile)
