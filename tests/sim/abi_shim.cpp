@@ -157,6 +157,11 @@ int peng_cuda_em(peng_handle_t h, int n_pwms, const void* pwm_in, int precision,
 }
 
 int peng_cuda_device_count(void) { return 8; }
+int peng_cuda_synchronize(peng_handle_t) { return PENG_OK; }
+int peng_cuda_count_finish(peng_handle_t h, uint64_t* ltot) {
+  if (ltot) *ltot = h->ltot;
+  return PENG_OK;
+}
 
 int peng_cuda_ingest_fasta_shard(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq, uint64_t* total,
                                  uint32_t* min_len, uint32_t* max_len) {
