@@ -1749,8 +1749,11 @@ __global__ void __launch_bounds__(EM_NT, 2) k_em_accumulate_all(
 #pragma unroll 4
   for (int e = 0; e < EM_ROWS(W); e++) sacc[e * EM_NT + t] = 0.0;
   // ---- slots: slot s of S = gridDim.x * R owns the units [lo(s), lo(s + 1)) ----
+  // the first `rem` slots take q + 1 units, the others q (no 64-bit divisions per slot: they were microseconds of the
+  // 40 us a whole W = 10 pass takes)
   const uint32_t S = gridDim.x * (uint32_t)R, n_units = unit_end - unit_begin;
-  auto slot_lo = [&](uint32_t s) { return (uint32_t)((uint64_t)n_units * s / S); };  // relative to unit_begin
+  const uint32_t q_units = n_units / S, rem_units = n_units - q_units * S;
+  auto slot_lo = [&](uint32_t s) { return s * q_units + min(s, rem_units); };  // relative to unit_begin
   const uint32_t s0 = blockIdx.x * (uint32_t)R;
   uint32_t n_steps = 0;
   for (int rr = 0; rr < R; rr++) n_steps = max(n_steps, (slot_lo(s0 + rr + 1) - slot_lo(s0 + rr)) << 4);
