@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--n-seq", type=int, default=1_000_000)
     ap.add_argument("--seq-len", type=int, default=200)
     ap.add_argument("--skip-reference", action="store_true")
+    ap.add_argument("--gpus", type=int, nargs="*", default=[], help="also run peng_motif --gpus N for these N and compare with the one-GPU run")
     args = ap.parse_args()
     import _pkg
 
@@ -66,6 +67,18 @@ def main():
         out["b200_seconds_all_runs"] = times
         out["b200_phases_ms"] = {l.split("]")[1].rsplit(None, 2)[0].strip(): float(l.split()[-2]) for l in r.stderr.splitlines()
                                  if l.startswith("[timing]")}
+        for n in args.gpus:  # the sharded front (FASTA shards, summed background counts, fused exchange): same bytes out
+            tn = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                rn = subprocess.run([ours, fasta, "-w", "10", "-o", os.path.join(d, f"ours{n}.meme"), "--timings", "--gpus", str(n)],
+                                    capture_output=True, text=True)
+                tn.append(time.perf_counter() - t0)
+                assert rn.returncode == 0, rn.stderr[-500:]
+            out[f"gpus_{n}"] = {"seconds": min(tn), "stdout_identical_to_one_gpu": rn.stdout == r.stdout,
+                                "meme_identical_to_one_gpu": open(os.path.join(d, f"ours{n}.meme")).read() == open(os.path.join(d, "ours.meme")).read(),
+                                "phases_ms": {l.split("]")[1].rsplit(None, 2)[0].strip(): float(l.split()[-2]) for l in rn.stderr.splitlines()
+                                              if l.startswith("[timing]")}}
         if not args.skip_reference and os.path.exists(ref):
             n = os.cpu_count() or 1
             t0 = time.perf_counter()
