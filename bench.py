@@ -664,7 +664,7 @@ def main():
     # bytes that crossed PCIe per step: the sequences the host threads packed travel as 0.375 B/base (2-bit codes + validity),
     # the rest as 1 B/base for the device to pack, plus the record offsets
     packed_bases = int(offs[g.last_ingest_host_packed])
-    h2d = int(0.375 * packed_bases) + (codes_pin.numel() - packed_bases) + offs.nbytes
+    h2d = g.last_ingest_h2d_bytes  # counted by the library copy by copy (2-bit codes, validity words where they are not implied, raw rest, offsets)
     t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -692,7 +692,7 @@ def main():
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_pageable = {"value": total_bases * e2e_steps / float(t.item()) / 1e9, "unit": "Gbases/s", "steps": e2e_steps,
-                    "h2d_bytes_per_step": int(0.375 * codes_np.size) + offs.nbytes, "d2h_bytes_per_step": int(d2h),
+                    "h2d_bytes_per_step": int(g.last_ingest_h2d_bytes), "d2h_bytes_per_step": int(d2h),
                     "path": "peng_cuda_ingest_sequences (pointer table over pageable per-sequence arrays; every sequence packed by the "
                             "host threads) -> peng_cuda_count -> peng_cuda_get_counts32"}
     clocks = sampler.stop() if rank == 0 else None  # sampled over warm-up + timed region + e2e region

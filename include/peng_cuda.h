@@ -100,6 +100,7 @@ int peng_cuda_ingest_sequences(peng_handle_t h, const uint8_t* const* seqs, cons
  * else hardware threads / LOCAL_WORLD_SIZE.  The device buffers are bit-identical in every mode. */
 int peng_cuda_set_ingest_mode(peng_handle_t h, int mode, double host_fraction);
 uint64_t peng_cuda_last_ingest_host_packed(peng_handle_t h); /* sequences packed by the host in the last ingest */
+uint64_t peng_cuda_last_ingest_h2d_bytes(peng_handle_t h);   /* bytes the last ingest from host buffers sent to the device */
 int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets, uint64_t n_seq);
 /* Count prefetch: BasePattern's constructor counts right after the sequences exist (src/base_pattern.cpp:36-80), so a
  * binding knows W and the strand before it hands the sequences over.  Armed with them, peng_cuda_ingest_codes runs the

@@ -57,6 +57,7 @@ _PROTOS = {
     "peng_cuda_get_timing": (C.c_int, [H, C.c_int, f32p]),
     "peng_cuda_set_ingest_mode": (C.c_int, [H, C.c_int, C.c_double]),
     "peng_cuda_last_ingest_host_packed": (C.c_uint64, [H]),
+    "peng_cuda_last_ingest_h2d_bytes": (C.c_uint64, [H]),
     "peng_cuda_ingest_fasta": (C.c_int, [H, C.c_char_p, u64p, u64p, u32p, u32p]),
     "peng_cuda_ingest_fasta_shard": (C.c_int, [H, C.c_char_p, C.c_int, C.c_int, u64p, u64p, u32p, u32p]),
     "peng_cuda_background_from_counts": (C.c_int, [C.c_int, f32p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
@@ -273,6 +274,10 @@ class PengCuda:
     @property
     def last_ingest_host_packed(self):
         return int(self.lib.peng_cuda_last_ingest_host_packed(self.h))
+
+    @property
+    def last_ingest_h2d_bytes(self):
+        return int(self.lib.peng_cuda_last_ingest_h2d_bytes(self.h))
 
     def ingest_codes_device(self, device_ptr, offsets):
         offsets = np.ascontiguousarray(offsets, np.uint64)

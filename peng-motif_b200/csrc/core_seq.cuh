@@ -145,6 +145,33 @@ PENG_HD void pack_word(uint64_t t, const uint8_t* __restrict__ src, const uint64
   if (code_words_out) { code_words_out[0] = c0; code_words_out[1] = c1; }  // for the caller's bit planes
 }
 
+// The validity word of stream positions [32 t, 32 t + 32) of a set WITHOUT letters other than ACGT: bit b is set iff position
+// 32 t + b holds a letter of a sequence — a function of the offsets alone.  The packed ingest sends validity words only
+// where they differ from this (host_pack.h: ValidExc).
+PENG_HD uint32_t implied_valid_word(uint64_t t, const uint64_t* __restrict__ offsets, uint64_t n_seq) {
+  const uint64_t q0 = t * 32, q1 = q0 + 32;
+  const uint64_t total = n_seq ? offsets[n_seq] : 0;
+  const uint64_t stream_end = PENG_FRONT_PAD + total + 2 * n_seq;
+  if (q1 <= PENG_FRONT_PAD || q0 >= stream_end) return 0;
+  const uint64_t q = q0 < PENG_FRONT_PAD ? PENG_FRONT_PAD : q0;
+  uint64_t lo = 0, hi = n_seq - 1;  // largest s with start(s) <= q
+  while (lo < hi) {
+    const uint64_t mid = (lo + hi + 1) >> 1;
+    if (PENG_FRONT_PAD + offsets[mid] + 2 * mid <= q) lo = mid; else hi = mid - 1;
+  }
+  uint32_t v = 0;
+  uint64_t o = offsets[lo];
+  for (uint64_t s = lo; s < n_seq; s++) {
+    const uint64_t o1 = offsets[s + 1];
+    const uint64_t a = PENG_FRONT_PAD + o + 2 * s, e = a + (o1 - o);  // letters at [a, e)
+    o = o1;
+    if (a >= q1) break;
+    const uint64_t x = a > q0 ? a : q0, y = e < q1 ? e : q1;
+    if (y > x) v |= (0xFFFFFFFFu >> (32 - (uint32_t)(y - x))) << (uint32_t)(x - q0);
+  }
+  return v;
+}
+
 // inverse of pack_word for one base (tests / CPU baseline export): reference letter code 0..4
 PENG_HD uint8_t unpack_code(const uint32_t* codes, const uint32_t* valid, uint64_t q) {
   if (!bit_at(valid, q)) return 0;

@@ -44,36 +44,7 @@ static inline void chunk_scalar(const uint8_t* p, uint32_t n, bool ascii, uint64
   v = vv;
 }
 
-template <bool ascii>
-__attribute__((target("avx512f,avx512bw"))) static inline void chunk_avx512(const uint8_t* p, uint32_t n, uint64_t& lo,
-                                                                            uint64_t& hi, uint64_t& v) {
-  const __mmask64 lm = n >= 64 ? ~(__mmask64)0 : (((__mmask64)1 << n) - 1);
-  const __m512i z = n >= 64 ? _mm512_loadu_si512((const void*)p) : _mm512_maskz_loadu_epi8(lm, p);
-  __mmask64 ok;
-  __m512i code;
-  if (ascii) {
-    const __m512i up = _mm512_and_si512(z, _mm512_set1_epi8((char)0xDF));
-    ok = _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('A')) | _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('C')) |
-         _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('G')) | _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('T'));
-    ok &= lm;
-    __m512i c = _mm512_and_si512(_mm512_srli_epi16(up, 1), _mm512_set1_epi8(3));          // A0 C1 G3 T2
-    c = _mm512_xor_si512(c, _mm512_and_si512(_mm512_srli_epi16(c, 1), _mm512_set1_epi8(1)));  // A0 C1 G2 T3
-    code = _mm512_maskz_mov_epi8(ok, c);
-  } else {
-    const __m512i t = _mm512_sub_epi8(z, _mm512_set1_epi8(1));
-    ok = _mm512_cmplt_epu8_mask(t, _mm512_set1_epi8(4)) & lm;
-    code = _mm512_maskz_mov_epi8(ok, _mm512_and_si512(t, _mm512_set1_epi8(3)));
-  }
-  // 4 letters per byte: b0 + 4 b1 (16-bit lanes), then + 16 (b2 + 4 b3) (32-bit lanes), then the low byte of every lane
-  const __m512i m1 = _mm512_maddubs_epi16(code, _mm512_set1_epi16(0x0401));
-  const __m512i m2 = _mm512_madd_epi16(m1, _mm512_set1_epi32(0x00100001));
-  const __m128i b = _mm512_cvtepi32_epi8(m2);
-  lo = (uint64_t)_mm_cvtsi128_si64(b);
-  hi = (uint64_t)_mm_extract_epi64(b, 1);
-  v = (uint64_t)ok;
-}
-
-// ---- sequential bit writer over 64-position blocks --------------------------------------------------------------------
+// ---- sequential bit writer over 64-position blocks (scalar fallback) --------------------------------------------------------------------
 struct BitWriter {
   uint64_t* codes;
   uint64_t* valid;
@@ -121,28 +92,6 @@ struct BitWriter {
     v = (over_v & m) | (v & ~m);
     fill = tot & 63u;
   }
-  // a whole chunk of 64 positions: the current block is completed whatever its fill, which stays as it is
-  inline void append64(uint64_t c_lo, uint64_t c_hi, uint64_t vv) {
-    typedef unsigned __int128 u128;
-    const u128 c = ((u128)c_hi << 64) | c_lo;
-    const uint32_t sh = 2 * fill;
-    const u128 in = c << sh;
-    const u128 over = (c >> 1) >> (127 - sh);
-    const uint64_t b_lo = lo | (uint64_t)in, b_hi = hi | (uint64_t)(in >> 64), b_v = v | (vv << fill);
-    uint64_t* cp = first_partial ? scratch : codes + 2 * (blk - blk0);
-    uint64_t* vp = first_partial ? scratch + 2 : valid + (blk - blk0);
-    cp[0] = b_lo;
-    cp[1] = b_hi;
-    vp[0] = b_v;
-    if (__builtin_expect(first_partial, 0)) {
-      out->push_back(Partial{blk, b_lo, b_hi, b_v});
-      first_partial = false;
-    }
-    blk++;
-    lo = (uint64_t)over;
-    hi = (uint64_t)(over >> 64);
-    v = (vv >> 1) >> (63 - fill);
-  }
   void zeros(uint64_t n) {
     while (n) {
       const uint32_t k = (uint32_t)std::min<uint64_t>(n, 64u - fill);
@@ -155,46 +104,115 @@ struct BitWriter {
   }
 };
 
-// the writer is worked on as a local copy: through the reference its state would live in memory (a store-to-load
-// forward per append) instead of registers
+// ---- AVX-512 body: driven by the OUTPUT blocks ------------------------------------------------------------------------
+// Block b holds the stream positions [64 b, 64 b + 64).  Its letters are gathered with one unaligned load where the block
+// lies inside a sequence, else with one masked load per sequence that overlaps it (masked-off lanes are neither read nor
+// can they fault; separator and padding positions stay 0 = "other"), converted once and stored where they belong: no bit
+// writer, no shifts that depend on the alignment of a sequence.  Blocks the share covers only in part leave as Partials.
+// Control flow follows the sequences (head in the open block, whole blocks inside, tail opens the next block), so the
+// branches depend on a sequence's length class, not on its alignment.
 template <bool ascii>
-__attribute__((target("avx512f,avx512bw"))) static void run_avx512_t(const Share& sh, BitWriter& w_io) {
-  BitWriter w = w_io;
+__attribute__((target("avx512f,avx512bw"))) static inline void block_convert(const __m512i z, __m128i& codes, __mmask64& ok) {
+  __m512i code;
+  if (ascii) {
+    const __m512i up = _mm512_and_si512(z, _mm512_set1_epi8((char)0xDF));
+    ok = _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('A')) | _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('C')) |
+         _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('G')) | _mm512_cmpeq_epi8_mask(up, _mm512_set1_epi8('T'));
+    __m512i c = _mm512_and_si512(_mm512_srli_epi16(up, 1), _mm512_set1_epi8(3));                // A0 C1 G3 T2
+    c = _mm512_xor_si512(c, _mm512_and_si512(_mm512_srli_epi16(c, 1), _mm512_set1_epi8(1)));  // A0 C1 G2 T3
+    code = _mm512_maskz_mov_epi8(ok, c);
+  } else {
+    const __m512i t = _mm512_sub_epi8(z, _mm512_set1_epi8(1));
+    ok = _mm512_cmplt_epu8_mask(t, _mm512_set1_epi8(4));
+    code = _mm512_maskz_mov_epi8(ok, t);  // t is 0..3 wherever ok
+  }
+  const __m512i m1 = _mm512_maddubs_epi16(code, _mm512_set1_epi16(0x0401));
+  const __m512i m2 = _mm512_madd_epi16(m1, _mm512_set1_epi32(0x00100001));
+  codes = _mm512_cvtepi32_epi8(m2);
+}
+
+// a block that may be one of the two the share covers only in part
+struct EmitCtx {
+  uint64_t q_lo, q_hi;
+  uint64_t *codes, *valid;  // indexed by the absolute block number
+  std::vector<Partial>* partials;
+  std::vector<ValidExc>* exc;
+};
+// zm: the lanes of z that hold a letter of a sequence (the implied validity of the block)
+template <bool ascii>
+__attribute__((target("avx512f,avx512bw,bmi2"), always_inline)) static inline void emit_block(const EmitCtx& cx, const __m512i z, const uint64_t zm,
+                                                                                              const uint64_t Q) {
+  __m128i c;
+  __mmask64 ok;
+  block_convert<ascii>(z, c, ok);
+  if (__builtin_expect(Q >= cx.q_lo && Q + 64 <= cx.q_hi, 1)) {
+    _mm_storeu_si128((__m128i*)(cx.codes + (Q >> 5)), c);
+    cx.valid[Q >> 6] = (uint64_t)ok;
+    if (__builtin_expect((uint64_t)ok != zm, 0) && cx.exc) cx.exc->push_back(ValidExc{Q >> 6, (uint64_t)ok});
+  } else {
+    cx.partials->push_back(Partial{Q >> 6, (uint64_t)_mm_cvtsi128_si64(c), (uint64_t)_mm_extract_epi64(c, 1), (uint64_t)ok});
+  }
+}
+
+template <bool ascii>
+__attribute__((target("avx512f,avx512bw,bmi2"))) static void run_blocks_avx512(const Share& sh, const uint64_t q_lo, const uint64_t q_hi) {
+  if (q_hi <= q_lo) return;
   const uint8_t* const src = sh.src;
+  const uint8_t* const* const seq_ptrs = sh.seq_ptrs;
   const uint64_t* const offsets = sh.offsets;
-  const uint64_t s_end = sh.s_end;
-  uint64_t o0 = offsets[sh.s_begin];
+  const uint64_t s_end = sh.s_end, front_pad = sh.front_pad;
+  uint64_t* const codes = sh.codes64 - 2 * sh.blk0;
+  uint64_t* const valid = sh.valid64 - sh.blk0;
+  const EmitCtx cx{q_lo, q_hi, codes, valid, sh.partials, sh.exc};
+  // the OPEN block [Q, Q + 64): z holds the letters gathered so far, everything else is 0
+  uint64_t Q = q_lo & ~(uint64_t)63;
+  __m512i z = _mm512_setzero_si512();
+  uint64_t zm = 0;
+  uint64_t o = offsets[sh.s_begin];
   for (uint64_t s = sh.s_begin; s < s_end; s++) {
-    const uint8_t* p = sh.seq_ptrs ? sh.seq_ptrs[s] : src + o0;
     const uint64_t o1 = offsets[s + 1];
-    const uint64_t L = o1 - o0;
-    o0 = o1;
-    uint64_t i = 0;
-    for (; i + 64 <= L; i += 64) {  // whole chunks
-      uint64_t lo, hi, v;
-      chunk_avx512<ascii>(p + i, 64, lo, hi, v);
-      w.append64(lo, hi, v);
+    const uint64_t qs = front_pad + o + 2 * s, qe = qs + (o1 - o);  // stream positions of the sequence
+    const uintptr_t base = (uintptr_t)(seq_ptrs ? seq_ptrs[s] : src + o) - (uintptr_t)qs;  // letter of position q at base + q
+    o = o1;
+    while (__builtin_expect(qs >= Q + 64, 0)) {  // front pad of the set
+      emit_block<ascii>(cx, z, zm, Q);
+      z = _mm512_setzero_si512();
+      zm = 0;
+      Q += 64;
     }
-    // the rest of the sequence (0 .. 63 letters) and the two separator positions (core_seq.cuh), in one append where
-    // they fit
-    const uint32_t n = (uint32_t)(L - i);
-    if (n) {
-      uint64_t lo, hi, v;
-      chunk_avx512<ascii>(p + i, n, lo, hi, v);
-      if (n <= 62) {
-        w.append(lo, hi, v, n + 2);
-      } else {
-        w.append(lo, hi, v, n);
-        w.append(0, 0, 0, 2);
+    // head: what of the sequence lies in the open block
+    const uint64_t e = std::min(qe, Q + 64);
+    if (e > qs) {
+      const uint64_t m = _bzhi_u64(~(uint64_t)0 << (qs - Q), (uint32_t)(e - Q));
+      z = _mm512_mask_loadu_epi8(z, (__mmask64)m, (const void*)(base + Q));
+      zm |= m;
+    }
+    if (qe >= Q + 64) {  // the sequence reaches the end of the open block
+      emit_block<ascii>(cx, z, zm, Q);
+      Q += 64;
+      for (const uint64_t Q_int = Q + ((qe - Q) & ~(uint64_t)63); Q < Q_int; Q += 64) {  // blocks inside the sequence: always whole blocks of the share
+        __m128i c;
+        __mmask64 ok;
+        block_convert<ascii>(_mm512_loadu_si512((const void*)(base + Q)), c, ok);
+        _mm_storeu_si128((__m128i*)(codes + (Q >> 5)), c);  // (streaming stores measured: 25 x slower — two 16 / 8-byte streams per thread never fill a write-combining line)
+        valid[Q >> 6] = (uint64_t)ok;
+        if (__builtin_expect((uint64_t)ok != ~(uint64_t)0, 0) && cx.exc) cx.exc->push_back(ValidExc{Q >> 6, (uint64_t)ok});
       }
-    } else {
-      w.append(0, 0, 0, 2);
+      zm = _bzhi_u64(~(uint64_t)0, (uint32_t)(qe - Q));
+      z = _mm512_maskz_loadu_epi8((__mmask64)zm, (const void*)(base + Q));  // tail: 0 .. 63 letters
+    }
+    if (__builtin_expect(qe + 2 >= Q + 64, 0)) {  // the two separator positions end the open block
+      emit_block<ascii>(cx, z, zm, Q);
+      z = _mm512_setzero_si512();
+      zm = 0;
+      Q += 64;
     }
   }
-  w_io = w;
-}
-static void run_avx512(const Share& sh, BitWriter& w) {
-  if (sh.ascii) run_avx512_t<true>(sh, w); else run_avx512_t<false>(sh, w);
+  for (; Q < q_hi; Q += 64) {  // the open block and the padding behind the last sequence
+    emit_block<ascii>(cx, z, zm, Q);
+    z = _mm512_setzero_si512();
+    zm = 0;
+  }
 }
 static void run_scalar(const Share& sh, BitWriter& w) {
   for (uint64_t s = sh.s_begin; s < sh.s_end; s++) {
@@ -212,7 +230,19 @@ static void run_scalar(const Share& sh, BitWriter& w) {
   }
 }
 
+bool lists_exceptions() {
+  static const bool no_avx = getenv("PENG_HOST_PACK_SCALAR") != nullptr;
+  return have_avx512() && !no_avx;
+}
+
 void pack_share(const Share& sh) {
+  if (lists_exceptions()) {
+    const uint64_t q_lo = sh.lead_zero ? 0 : sh.front_pad + sh.offsets[sh.s_begin] + 2 * sh.s_begin;
+    const uint64_t q_seq = sh.front_pad + sh.offsets[sh.s_end] + 2 * sh.s_end;  // behind the separators of the last sequence
+    const uint64_t q_hi = std::max(q_seq, sh.q_end_pad);
+    if (sh.ascii) run_blocks_avx512<true>(sh, q_lo, q_hi); else run_blocks_avx512<false>(sh, q_lo, q_hi);
+    return;
+  }
   BitWriter w;
   w.codes = sh.codes64;
   w.valid = sh.valid64;
@@ -224,8 +254,7 @@ void pack_share(const Share& sh) {
   } else {
     w.begin(sh.front_pad + sh.offsets[sh.s_begin] + 2 * sh.s_begin);
   }
-  static const bool no_avx = getenv("PENG_HOST_PACK_SCALAR") != nullptr;
-  if (have_avx512() && !no_avx) run_avx512(sh, w); else run_scalar(sh, w);
+  run_scalar(sh, w);
   if (sh.q_end_pad) {
     const uint64_t q = (w.blk << 6) + w.fill;
     if (sh.q_end_pad > q) w.zeros(sh.q_end_pad - q);
@@ -283,21 +312,27 @@ Pool::~Pool() {
   for (auto& t : p_->workers) t.join();
   delete p_;
 }
-void Pool::run(int n_tasks, void (*fn)(int, void*), void* arg) {
-  if (n_tasks <= 0) return;
+void Pool::start(int n_tasks, void (*fn)(int, void*), void* arg) {
   {
     std::lock_guard<std::mutex> lk(p_->m);
     p_->fn = fn;
     p_->arg = arg;
-    p_->n_tasks = n_tasks;
+    p_->n_tasks = std::max(0, n_tasks);
     p_->next.store(0, std::memory_order_relaxed);
     p_->busy = (int)p_->workers.size();
     p_->generation++;
   }
   p_->cv_work.notify_all();
+}
+void Pool::finish() {
   p_->drain();  // the caller works too
   std::unique_lock<std::mutex> lk(p_->m);
   p_->cv_done.wait(lk, [&] { return p_->busy == 0; });
+}
+void Pool::run(int n_tasks, void (*fn)(int, void*), void* arg) {
+  if (n_tasks <= 0) return;
+  start(n_tasks, fn, arg);
+  finish();
 }
 
 Pool& global_pool() {
@@ -341,15 +376,17 @@ uint64_t plan_phase(const uint64_t* offsets, uint64_t n_seq, uint64_t s_begin, u
   return lo;
 }
 
-namespace {
-struct PhaseRun {
+struct PhaseJob {
   const Phase* ph;
-  uint64_t blk0;
+  uint64_t blk0, blk1;
+  bool want_exc;
   std::vector<uint64_t> cut;  // share i = sequences [cut[i], cut[i + 1])
   std::vector<std::vector<Partial>> partials;
+  std::vector<std::vector<ValidExc>> exc;
 };
+namespace {
 void phase_task(int i, void* arg) {
-  PhaseRun& r = *(PhaseRun*)arg;
+  PhaseJob& r = *(PhaseJob*)arg;
   const Phase& ph = *r.ph;
   const int n = (int)r.cut.size() - 1;
   Share sh;
@@ -366,17 +403,17 @@ void phase_task(int i, void* arg) {
   sh.codes64 = ph.codes64;
   sh.valid64 = ph.valid64;
   sh.partials = &r.partials[i];
+  sh.exc = r.exc.empty() ? nullptr : &r.exc[i];
   if (sh.s_begin == sh.s_end && !sh.lead_zero && !sh.q_end_pad) return;
   pack_share(sh);
 }
 }  // namespace
 
-void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry) {
-  uint64_t blk0, blk1;
-  phase_blocks(ph, &blk0, &blk1);
-  PhaseRun r;
+PhaseJob* pack_phase_begin(Pool& pool, const Phase& ph) {
+  PhaseJob* job = new PhaseJob;
+  PhaseJob& r = *job;
+  phase_blocks(ph, &r.blk0, &r.blk1);
   r.ph = &ph;
-  r.blk0 = blk0;
   // shares of about equal numbers of bases, cut at sequence boundaries
   const uint64_t b0 = ph.offsets[ph.s_begin], b1 = ph.offsets[ph.s_end];
   // four shares per thread, handed out dynamically: a thread that loses its core for a moment does not hold up the phase
@@ -390,7 +427,20 @@ void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry) {
   }
   r.cut.push_back(ph.s_end);
   r.partials.resize(n);
-  pool.run(n, phase_task, &r);
+  r.want_exc = ph.exc && lists_exceptions();
+  if (ph.exc) ph.exc->clear();
+  if (ph.exc_complete) *ph.exc_complete = r.want_exc;
+  if (r.want_exc) r.exc.resize(n);
+  pool.start(n, phase_task, job);
+  return job;
+}
+
+void pack_phase_end(Pool& pool, PhaseJob* job, bool* has_carry, Partial* carry) {
+  pool.finish();
+  PhaseJob& r = *job;
+  const Phase& ph = *r.ph;
+  const uint64_t blk0 = r.blk0, blk1 = r.blk1;
+  const bool want_exc = r.want_exc;
   // boundary blocks: OR the contributions (at most two per share, plus the carry of the previous phase)
   std::vector<Partial> all;
   if (*has_carry) all.push_back(*carry);
@@ -409,12 +459,22 @@ void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry) {
       ph.codes64[2 * (acc.blk - blk0)] = acc.lo;
       ph.codes64[2 * (acc.blk - blk0) + 1] = acc.hi;
       ph.valid64[acc.blk - blk0] = acc.v;
+      if (want_exc) ph.exc->push_back(ValidExc{acc.blk, acc.v});
     } else {
       *carry = acc;
       *has_carry = true;
     }
     i = j;
   }
+  if (want_exc) {
+    for (auto& v : r.exc) ph.exc->insert(ph.exc->end(), v.begin(), v.end());
+    std::sort(ph.exc->begin(), ph.exc->end(), [](const ValidExc& a, const ValidExc& b) { return a.blk < b.blk; });
+  }
+  delete job;
+}
+
+void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry) {
+  pack_phase_end(pool, pack_phase_begin(pool, ph), has_carry, carry);
 }
 
 // ---- nibble packing ---------------------------------------------------------------------------------------------------

@@ -19,6 +19,13 @@ struct Partial {
   uint64_t blk, lo, hi, v;
 };
 
+// Implied validity: without letters other than ACGT the validity bits of a block follow from the offsets alone (the device
+// rebuilds them, see k_valid_implied), so a phase only has to send the blocks where that is not true — those holding another
+// letter, and the blocks at share boundaries (merged by the caller, listed unconditionally).
+struct ValidExc {
+  uint64_t blk, v;
+};
+
 // One worker's share: sequences [s_begin, s_end) of the set, written as whole 64-position blocks
 //   codes64[2 * (blk - blk0)], codes64[2 * (blk - blk0) + 1]  (position q at bits 2 (q & 63) of the pair)
 //   valid64[blk - blk0]                                        (position q at bit q & 63)
@@ -39,9 +46,11 @@ struct Share {
   uint64_t* valid64;
   std::vector<Partial>* partials;
   const uint8_t* const* seq_ptrs = nullptr;  // != NULL: sequence s is read from seq_ptrs[s] (per-sequence arrays) instead of src + offsets[s]
+  std::vector<ValidExc>* exc = nullptr;      // != NULL: whole blocks whose validity word is not the implied one are listed here (AVX-512 path only)
 };
 void pack_share(const Share& sh);
 bool have_avx512();
+bool lists_exceptions();  // the path pack_share takes fills Share::exc (AVX-512 present and not switched off)
 
 class Pool;
 // Half-way packing for the part of a set the host does not pack completely: letter codes (0 = other, 1..4 = ACGT, anything
@@ -57,6 +66,10 @@ class Pool {
   ~Pool();
   int size() const { return n_; }
   void run(int n_tasks, void (*fn)(int, void*), void* arg);
+  // the same in two steps: start() wakes the workers and returns, finish() lets the caller take part and waits for the last
+  // task — what the caller does in between runs beside the workers (one job at a time)
+  void start(int n_tasks, void (*fn)(int, void*), void* arg);
+  void finish();
 
  private:
   struct Impl;
@@ -81,11 +94,21 @@ struct Phase {
   uint64_t* codes64;
   uint64_t* valid64;
   const uint8_t* const* seq_ptrs = nullptr;  // see Share
+  // != NULL and the AVX-512 path runs: receives every block of [blk0, blk1) whose validity word differs from the implied one
+  // (or may: the merged boundary blocks), sorted by block; *exc_complete says whether the list was made at all
+  std::vector<ValidExc>* exc = nullptr;
+  bool* exc_complete = nullptr;
 };
 void phase_blocks(const Phase& ph, uint64_t* blk0, uint64_t* blk1);
 // end of the phase that starts with sequence s_begin: the largest s_end whose blocks (the carried one included) fit
 // max_blocks; returns s_begin if not even one sequence fits (the caller falls back to the unpacked ingest)
 uint64_t plan_phase(const uint64_t* offsets, uint64_t n_seq, uint64_t s_begin, uint32_t front_pad, bool first, uint64_t max_blocks);
 void pack_phase(Pool& pool, const Phase& ph, bool* has_carry, Partial* carry);
+// the same in two steps (the Phase must stay alive in between): begin() cuts the shares and starts the pool, end() joins the
+// packing, merges the boundary blocks and hands the carry on.  Between the two the caller can queue the copies of the
+// previous phase.
+struct PhaseJob;
+PhaseJob* pack_phase_begin(Pool& pool, const Phase& ph);
+void pack_phase_end(Pool& pool, PhaseJob* job, bool* has_carry, Partial* carry);
 
 }  // namespace peng_hostpack

@@ -104,6 +104,7 @@ struct peng_cuda_ctx {
   int ingest_mode = 0;             // 0 auto (hybrid where it pays), 1 raw bytes + device packing, 2 host packing
   double ingest_fraction = -1;     // share of the bases packed on the host (< 0: from the thread count)
   uint64_t last_ingest_packed = 0; // sequences the host packed in the last ingest
+  uint64_t last_ingest_h2d = 0;    // bytes the last ingest from host buffers sent over PCIe
   int part_cfg = 0;                // stage-P geometry (tuning knob, PENG_PART_CFG)
   bool fold_untiled = false;       // PENG_FOLD_UNTILED: one-thread-per-id fold / mirror at every W (A/B)
   uint2* d_slow_list = nullptr;
@@ -2402,6 +2403,20 @@ static int need_copy_stream_and_pins(peng_handle_t h, bool pins) {
 }
 
 // sequence-start bits of the sequences whose first base lies in front of word t_end (the words are cleared beforehand)
+// Packed ingest, phases without letters other than ACGT: the validity words follow from the offsets (core_seq.cuh:
+// implied_valid_word); the few blocks where they do not (host_pack.h: ValidExc) are listed and written over them.
+__global__ void k_valid_implied(const uint64_t* __restrict__ offsets, uint64_t n_seq, uint64_t t0, uint64_t t1, uint32_t* __restrict__ valid) {
+  const uint64_t t = t0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < t1) valid[t] = implied_valid_word(t, offsets, n_seq);
+}
+__global__ void k_valid_exceptions(const uint64_t* __restrict__ exc, uint32_t n, uint32_t* __restrict__ valid) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t blk = exc[2 * i], v = exc[2 * i + 1];
+  valid[2 * blk] = (uint32_t)v;
+  valid[2 * blk + 1] = (uint32_t)(v >> 32);
+}
+
 __global__ void k_sstart_scatter(const uint64_t* __restrict__ offsets, uint64_t n_seq, uint64_t t_end, uint32_t* __restrict__ sstart) {
   const uint64_t s = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_seq) return;
@@ -2445,10 +2460,14 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     if (h->ingest_fraction >= 0) f = h->ingest_fraction;
     f = std::min(1.0, std::max(0.0, f));
   } else if (!force) {
-    // Gbases/s: measured packing rate (5.7 per thread up to 8 threads, 63 at 16: tools/probe/host_pack_bench.cpp), PCIe rate
-    // x 0.8: the packing runs beside the DMA traffic and behind the bookkeeping pass (measured optimum at 16 threads: 0.65)
-    const double rh = 0.8 * (5.7 * std::min(pool.size(), 8) + 2.2 * std::max(0, pool.size() - 8)), rp = 46.0;
-    f = rh / (rp + 0.625 * rh);
+    // Gbases/s: measured packing rate (tools/probe/host_pack_bench.cpp on the B200 box: 11 / 42 / 73 / 115 with 1 / 4 / 8 / 16
+    // threads — the host's memory system from 8 threads on), PCIe rate; x 0.85: the packing runs beside the DMA traffic
+    // (measured inside the ingest: 104 at 16 threads; optimum of tools/ingest_bench.py's sweep: 0.9)
+    const double rh = 0.85 * (9.5 * std::min(pool.size(), 8) + 5.0 * std::max(0, pool.size() - 8)), rp = 46.0;
+    // packed bytes per base: 0.375, or 0.25 where the validity words are implied (no letters other than ACGT: 256 probes say)
+    bool clean = !ascii && !seq_ptrs && lists_exceptions() && getenv("PENG_NO_IMPLIED_VALID") == nullptr;
+    for (uint64_t i = 0; clean && i < 256; i++) clean = (uint8_t)(src[(total - 1) / 256 * i] - 1u) < 4u;
+    f = rh / (rp + (clean ? 0.75 : 0.625) * rh);
     if (h->ingest_fraction >= 0) f = h->ingest_fraction;
     f = std::min(1.0, std::max(0.0, f));
   } else if (h->ingest_fraction >= 0 && !seq_ptrs) {
@@ -2487,7 +2506,16 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   const uint64_t q_split = PENG_FRONT_PAD + offsets[s_split] + 2 * s_split;
   const uint64_t blk_split = s_split < n_seq ? (q_split >> 6) : n_blocks;
   const uint64_t b_lo = s_split < n_seq ? (offsets[s_split] - std::min<uint64_t>(offsets[s_split], 128)) & ~(uint64_t)1 : total;
-  if (s_split < n_seq) TRY(need_scratch(h, (size_t)(total - b_lo) + 16));
+  // implied validity (see k_valid_implied): a phase lists at most 1/16 of its blocks (+ 64), else it sends its validity words
+  static const bool implied_on = getenv("PENG_NO_IMPLIED_VALID") == nullptr;
+  const bool implied = implied_on && lists_exceptions();
+  const size_t raw_bytes = s_split < n_seq ? (((size_t)(total - b_lo) + 16 + 255) & ~(size_t)255) : 0;
+  const uint64_t exc_cap = implied ? blk_split / 16 + 64 * (blk_split / ((2u << 20) / 24) + 8) : 0;  // entries, all phases together
+  if (raw_bytes + exc_cap) TRY(need_scratch(h, raw_bytes + (size_t)exc_cap * 16));
+  uint64_t* const d_exc = (uint64_t*)((uint8_t*)h->d_scratch + raw_bytes);
+  uint64_t exc_used = 0, h2d = 0;
+  std::vector<ValidExc> exc;
+  bool exc_complete = false;
   if (h->pin_offs_cap < n_seq + 1) {
     if (h->pin_offs) cudaFreeHost(h->pin_offs);
     h->pin_offs = nullptr;
@@ -2511,6 +2539,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
       CU(h, cudaEventSynchronize(h->pin_ev[buf]));  // the previous copy out of this staging buffer is done
       nibble_pack(pool, src + b0, b1 - b0, h->pin[buf]);
       CU(h, cudaMemcpyAsync((uint8_t*)h->d_scratch + ((b0 - b_lo) >> 1), h->pin[buf], (size_t)((b1 - b0 + 1) >> 1), cudaMemcpyHostToDevice, h->copy_stream));
+      h2d += (b1 - b0 + 1) >> 1;
       CU(h, cudaEventRecord(h->pin_ev[buf], h->copy_stream));
       buf ^= 1;
     }
@@ -2519,6 +2548,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     for (uint64_t b0 = b_lo; b0 < total; b0 += chunk) {
       const uint64_t b1 = std::min(total, b0 + chunk);
       CU(h, cudaMemcpyAsync((uint8_t*)h->d_scratch + (b0 - b_lo), src + b0, b1 - b0, cudaMemcpyHostToDevice, h->copy_stream));
+      h2d += b1 - b0;
     }
   }
   // ---- the offsets: a cudaMemcpyAsync out of the caller's pageable array would block this thread for the whole copy
@@ -2526,6 +2556,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   // host copy and finds the shortest / longest sequence — and the DMA engine takes them from there
   host_bookkeeping_parallel(h, offsets, n_seq, h->pin_offs);
   CU(h, cudaMemcpyAsync(h->d_offsets, h->pin_offs, (n_seq + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, h->copy_stream));
+  h2d += (n_seq + 1) * sizeof(uint64_t);
   if (s_split < n_seq) {  // raw bytes and offsets have arrived: the device packs the rest in one go
     const uint8_t* d_src = (const uint8_t*)h->d_scratch - b_lo;  // indexed by absolute base offset, never read below b_lo
     CU(h, cudaEventRecord(h->copy_ev[0], h->copy_stream));
@@ -2539,14 +2570,25 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
   // ---- the packed part, phase by phase through the two pinned staging buffers ----
   bool has_carry = false;
   Partial carry{};
-  bool first = true;
   static const bool dbg = getenv("PENG_INGEST_DEBUG") != nullptr;
   static const bool taper = getenv("PENG_NO_TAPER") == nullptr;
   double t_pack = 0, t_wait = 0, t_issue = 0;
   auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
   const double t_start = now();
   mark(3);
-  for (uint64_t s = 0;;) {
+  // Two phases are in flight: while the pool packs phase i + 1 into one staging buffer, this thread queues the copies and
+  // kernels of phase i out of the other (the packing is the bottleneck of the ingest; nothing else should sit on its path).
+  struct Slot {
+    uint64_t s, e, blk0, blk1;
+    bool first, last;
+    int buf;
+    uint64_t *codes64, *valid64;
+    Phase ph;
+    PhaseJob* job = nullptr;
+    std::vector<ValidExc> exc;
+    bool exc_complete = false;
+  } slots[2];
+  auto begin_phase = [&](Slot& c, uint64_t s, bool first, int buf) -> int {
     // the copy of the LAST phase cannot hide behind packing: towards the end every phase takes half of what is left
     // (down to 2 MiB of blocks), so that the tail of the DMA queue is short
     uint64_t cap = max_blocks - 4;
@@ -2566,21 +2608,59 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
     double t0 = now();
     CU(h, cudaEventSynchronize(h->pin_ev[buf]));  // the previous copy out of this staging buffer is done
     t_wait += now() - t0;
-    uint64_t* codes64 = (uint64_t*)h->pin[buf];
-    uint64_t* valid64 = codes64 + 2 * max_blocks;
-    Phase ph{src, offsets, s, e, ascii, PENG_FRONT_PAD, first, last, q_total, codes64, valid64, seq_ptrs};
-    uint64_t blk0, blk1;
-    phase_blocks(ph, &blk0, &blk1);
-    t0 = now();
-    pack_phase(pool, ph, &has_carry, &carry);
-    t_pack += now() - t0;
-    t0 = now();
-    blk1 = std::min(blk1, blk_split);  // the block of the split belongs to k_pack
+    c.s = s;
+    c.e = e;
+    c.first = first;
+    c.last = last;
+    c.buf = buf;
+    c.codes64 = (uint64_t*)h->pin[buf];
+    c.valid64 = c.codes64 + 2 * max_blocks;
+    c.ph = Phase{src, offsets, s, e, ascii, PENG_FRONT_PAD, first, last, q_total, c.codes64, c.valid64, seq_ptrs};
+    if (implied) {
+      c.ph.exc = &c.exc;
+      c.ph.exc_complete = &c.exc_complete;
+    }
+    c.exc_complete = false;
+    phase_blocks(c.ph, &c.blk0, &c.blk1);
+    c.job = pack_phase_begin(pool, c.ph);
+    return PENG_OK;
+  };
+  auto issue_phase = [&](Slot& c) -> int {
+    const uint64_t blk0 = c.blk0, blk1 = std::min(c.blk1, blk_split);  // the block of the split belongs to k_pack
+    const int buf = c.buf;
+    std::vector<ValidExc>& exc = c.exc;
+    uint32_t n_exc = 0;
+    bool phase_implied = false;
     if (blk1 > blk0) {
-      CU(h, cudaMemcpyAsync(h->d_codes + blk0 * 4, codes64, (blk1 - blk0) * 16, cudaMemcpyHostToDevice, h->copy_stream));
-      CU(h, cudaMemcpyAsync(h->d_valid + blk0 * 2, valid64, (blk1 - blk0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
+      CU(h, cudaMemcpyAsync(h->d_codes + blk0 * 4, c.codes64, (blk1 - blk0) * 16, cudaMemcpyHostToDevice, h->copy_stream));
+      h2d += (blk1 - blk0) * 16;
+      if (implied && c.exc_complete) {
+        while (!exc.empty() && exc.back().blk >= blk1) exc.pop_back();  // sorted by block; the block of the split is k_pack's
+        phase_implied = exc.size() <= (blk1 - blk0) / 16 + 64 && exc_used + exc.size() <= exc_cap;
+      }
+      if (phase_implied) {  // the listed blocks travel through the staging area of the validity words that stay here
+        n_exc = (uint32_t)exc.size();
+        if (n_exc) {
+          memcpy(c.valid64, exc.data(), (size_t)n_exc * 16);
+          CU(h, cudaMemcpyAsync(d_exc + 2 * exc_used, c.valid64, (size_t)n_exc * 16, cudaMemcpyHostToDevice, h->copy_stream));
+          h2d += (uint64_t)n_exc * 16;
+        }
+      } else {
+        CU(h, cudaMemcpyAsync(h->d_valid + blk0 * 2, c.valid64, (blk1 - blk0) * 8, cudaMemcpyHostToDevice, h->copy_stream));
+        h2d += (blk1 - blk0) * 8;
+      }
     }
     CU(h, cudaEventRecord(h->pin_ev[buf], h->copy_stream));
+    if (phase_implied) {  // (the offsets were queued in front of every phase)
+      CU(h, cudaStreamWaitEvent(h->stream, h->pin_ev[buf], 0));
+      k_valid_implied<<<grid_for((blk1 - blk0) * 2, 256), 256, 0, h->stream>>>(h->d_offsets, n_seq, blk0 * 2, blk1 * 2, h->d_valid);
+      LAUNCH_CHECK(h);
+      if (n_exc) {
+        k_valid_exceptions<<<grid_for(n_exc, 256), 256, 0, h->stream>>>(d_exc + 2 * exc_used, n_exc, h->d_valid);
+        LAUNCH_CHECK(h);
+      }
+      exc_used += n_exc;
+    }
     if (pr.on && blk1 > blk0) {  // the blocks of this phase once they have landed: bit planes, then stage P up to two units short of the frontier
       CU(h, cudaStreamWaitEvent(h->stream, h->pin_ev[buf], 0));
       TRY(make_planes(h, pr.planes_done, blk1 * 2));
@@ -2590,11 +2670,37 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
         pr.done_u = std::max(pr.done_u, blk1 * 2 - 2);
       }
     }
-    t_issue += now() - t0;
-    buf ^= 1;
-    first = false;
-    s = e;
-    if (last || (s >= s_split && s_split < n_seq)) break;
+    return PENG_OK;
+  };
+  {
+    int rc = begin_phase(slots[0], 0, true, buf);
+    for (int cur = 0; rc == PENG_OK;) {
+      Slot& c = slots[cur];
+      double t0 = now();
+      pack_phase_end(pool, c.job, &has_carry, &carry);
+      c.job = nullptr;
+      t_pack += now() - t0;
+      const bool more = !(c.last || (c.e >= s_split && s_split < n_seq));
+      // the next phase starts before this one's copies are queued — unless its staging buffer is still being read by the
+      // DMA engine: then the bus is the bottleneck, and this phase's copy goes out first
+      const bool next_free = more && cudaEventQuery(h->pin_ev[c.buf ^ 1]) == cudaSuccess;
+      if (next_free) rc = begin_phase(slots[cur ^ 1], c.e, false, c.buf ^ 1);
+      t0 = now();
+      if (rc == PENG_OK) rc = issue_phase(c);
+      t_issue += now() - t0;
+      if (more && !next_free && rc == PENG_OK) rc = begin_phase(slots[cur ^ 1], c.e, false, c.buf ^ 1);
+      if (!more) break;
+      cur ^= 1;
+    }
+    if (rc != PENG_OK) {  // a job that was started must be joined before its Phase goes away
+      for (Slot& c : slots)
+        if (c.job) {
+          bool hc = false;
+          Partial pc{};
+          pack_phase_end(pool, c.job, &hc, &pc);
+        }
+      return rc;
+    }
   }
   // sequence starts of the packed part (k_pack writes those of its own words)
   const uint64_t t_split = std::min<uint64_t>(blk_split * 2, h->n_words32);
@@ -2621,6 +2727,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
             pool.size(), (double)offsets[s_split] / (double)std::max<uint64_t>(total, 1), 1e3 * (t_loop - t_start), 1e3 * t_pack,
             1e3 * t_wait, 1e3 * t_issue, 1e3 * (t_book - t_loop), 1e3 * (now() - t_book));
   h->last_ingest_packed = s_split;
+  h->last_ingest_h2d = h2d;
   return PENG_OK;
 }
 
@@ -2629,6 +2736,7 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
 // own bookkeeping, hide behind the PCIe transfer.
 static int ingest_host_src(peng_handle_t h, const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, bool ascii) {
   h->last_ingest_packed = 0;
+  h->last_ingest_h2d = (n_seq ? offsets[n_seq] : 0) + (n_seq + 1) * sizeof(uint64_t);  // the plain path; the hybrid one counts its own
   {
     const int rc = ingest_host_hybrid(h, src, offsets, n_seq, ascii);
     if (rc != 1) return rc;  // done (or failed); 1 = not applicable, plain path
@@ -2717,6 +2825,7 @@ extern "C" int peng_cuda_set_ingest_mode(peng_handle_t h, int mode, double host_
   return PENG_OK;
 }
 extern "C" uint64_t peng_cuda_last_ingest_host_packed(peng_handle_t h) { return h ? h->last_ingest_packed : 0; }
+extern "C" uint64_t peng_cuda_last_ingest_h2d_bytes(peng_handle_t h) { return h ? h->last_ingest_h2d : 0; }
 
 extern "C" int peng_cuda_ingest_codes_device(peng_handle_t h, const void* d_codes, const uint64_t* offsets,
                                              uint64_t n_seq) {

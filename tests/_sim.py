@@ -197,8 +197,10 @@ def host_pack(src, offsets, ascii=False, n_threads=4, max_blocks=1 << 14):
     nw = int(lib.sim_n_words32(C.c_uint64(n_seq), C.c_uint64(int(offsets[-1]))))
     codes = np.full(2 * nw + 8, 0xDEADBEEF, np.uint32)
     valid = np.full(nw + 8, 0xDEADBEEF, np.uint32)
+    n_exc = C.c_uint64()
     ph = lib.sim_host_pack(_p(src, u8p), _p(offsets, u64p), C.c_uint64(n_seq), int(ascii), int(n_threads), C.c_uint64(max_blocks),
-                           C.c_uint64(nw), _p(codes, u32p), _p(valid, u32p))
+                           C.c_uint64(nw), _p(codes, u32p), _p(valid, u32p), C.byref(n_exc))
+    host_pack.last_exceptions = int(n_exc.value)  # validity words sent explicitly (the rest is implied by the offsets)
     return codes, valid, nw, ph
 
 

@@ -445,9 +445,10 @@ void sim_pack_nibbles(const uint8_t* src, const uint64_t* offsets, uint64_t n_se
 // codes32: 2 * n_words32 + 8 words, valid32: n_words32 + 8 words (as the device allocates them); returns the number of
 // phases, or -1 when a sequence does not fit a phase
 int sim_host_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, int ascii, int n_threads, uint64_t max_blocks,
-                  uint64_t n_words32, uint32_t* codes32, uint32_t* valid32) {
+                  uint64_t n_words32, uint32_t* codes32, uint32_t* valid32, uint64_t* n_exc) {
   using namespace peng_hostpack;
   Pool pool(n_threads);
+  if (n_exc) *n_exc = 0;
   const uint64_t q_total = ((n_words32 * 32 + 63) / 64) * 64;
   const uint64_t n_blocks = q_total / 64;
   std::vector<uint64_t> sc(2 * max_blocks + 2), sv(max_blocks + 1);
@@ -465,11 +466,25 @@ int sim_host_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, i
     }
     if (e == s && !last) return -1;
     Phase ph{src, offsets, s, e, ascii != 0, PENG_FRONT_PAD, first, last, q_total, sc.data(), sv.data()};
+    std::vector<ValidExc> exc;
+    bool exc_complete = false;
+    ph.exc = &exc;
+    ph.exc_complete = &exc_complete;
     uint64_t blk0, blk1;
     phase_blocks(ph, &blk0, &blk1);
     pack_phase(pool, ph, &has_carry, &carry);
     memcpy(codes32 + blk0 * 4, sc.data(), (blk1 - blk0) * 16);
-    memcpy(valid32 + blk0 * 2, sv.data(), (blk1 - blk0) * 8);
+    if (exc_complete) {  // what the device does with a phase that sends no validity words: implied ones, then the listed blocks
+      for (uint64_t t = blk0 * 2; t < blk1 * 2; t++) valid32[t] = implied_valid_word(t, offsets, n_seq);
+      for (const ValidExc& x : exc) {
+        if (x.blk < blk0 || x.blk >= blk1) return -3;
+        memcpy(valid32 + x.blk * 2, &x.v, 8);
+      }
+      if (n_exc) *n_exc += exc.size();
+      if (memcmp(valid32 + blk0 * 2, sv.data(), (blk1 - blk0) * 8)) return -4;
+    } else {
+      memcpy(valid32 + blk0 * 2, sv.data(), (blk1 - blk0) * 8);
+    }
     phases++;
     if (last) break;
     s = e;

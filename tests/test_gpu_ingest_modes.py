@@ -66,6 +66,34 @@ def test_fixed_length_set_and_automatic_choice(g, pkg):
     assert np.array_equal(g.get_counts(), ref)
 
 
+def test_implied_validity(g):
+    """Phases without letters other than ACGT send no validity words (k_valid_implied rebuilds them from the offsets, the
+    listed blocks — share boundaries, blocks holding another letter — are written over them): a clean set, a set with rare
+    other letters, and a set whose later phases are dirty (those send their validity words as before)."""
+    rng = np.random.RandomState(21)
+    lens = rng.randint(1, 600, 400_000)  # 120 M bases: 3 staging phases
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    total = int(offs[-1])
+    clean = rng.randint(1, 5, total).astype(np.uint8)
+    check_modes(g, clean, offs, [(2, -1.0), (0, 0.7)])
+    g.set_ingest_mode(2, -1.0)
+    g.ingest_codes(clean, offs)
+    packed_all = g.last_ingest_h2d_bytes
+    assert packed_all < 0.26 * total + offs.nbytes + (1 << 20), packed_all  # 2-bit codes + offsets + a few listed blocks
+    rare = clean.copy()
+    rare[rng.choice(total, total // 20_000, replace=False)] = 0
+    check_modes(g, rare, offs, [(2, -1.0), (0, 0.4)])
+    g.set_ingest_mode(2, -1.0)
+    g.ingest_codes(rare, offs)
+    assert packed_all < g.last_ingest_h2d_bytes < packed_all + 32 * (total // 20_000)
+    late = clean.copy()
+    late[int(0.6 * total):] = rng.randint(0, 5, total - int(0.6 * total))
+    check_modes(g, late, offs, [(2, -1.0), (0, 0.9)])
+    g.set_ingest_mode(2, -1.0)
+    g.ingest_codes(late, offs)
+    assert 0.26 * total < g.last_ingest_h2d_bytes - offs.nbytes < 0.375 * total
+
+
 def test_long_sequence_falls_back(g):
     rng = np.random.RandomState(2)
     offs = np.array([0, 1000, 50_001_000, 50_002_000], np.uint64)  # 50 M letters in one record: more than a staging phase

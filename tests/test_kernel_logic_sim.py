@@ -391,6 +391,38 @@ def test_host_pack_many_phases_and_threads():
     _host_pack_matches(np.zeros(0, np.uint8), np.zeros(1, np.uint64), False, 4, 64)
 
 
+@pytest.mark.parametrize("trial", range(6))
+def test_host_pack_block_edges(trial):
+    """The AVX-512 packer works on output blocks (head / whole blocks / tail of every sequence): lengths around the block
+    size, empty sequences, sequences whose separators end a block, many sequences inside one block, codes > 4."""
+    rng = np.random.RandomState(90 + trial)
+    pool = [0, 1, 2, 5, 9] if trial % 3 == 0 else [0, 1, 2, 3, 30, 60, 61, 62, 63, 64, 65, 66, 67, 124, 125, 126, 127, 128, 190,
+                                                   191, 192, 193, 200, 700]
+    lens = rng.choice(pool, 3000 if trial % 3 == 0 else 400)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    codes = rng.randint(0, 7, int(offs[-1])).astype(np.uint8)
+    for n_threads, max_blocks in ((1, 1 << 14), (5, 64), (3, 33)):
+        _host_pack_matches(codes, offs, False, n_threads, max_blocks)
+
+
+def test_host_pack_implied_validity():
+    """A phase whose letters are all ACGT sends no validity words: the device rebuilds them from the offsets
+    (core_seq.cuh: implied_valid_word) and only the listed blocks travel (share boundaries, blocks holding another letter).
+    `S.host_pack` rebuilds every phase that way and compares with the words the packer wrote."""
+    rng = np.random.RandomState(5)
+    lens = rng.randint(1, 400, 4000)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    clean = rng.randint(1, 5, int(offs[-1])).astype(np.uint8)
+    phases = _host_pack_matches(clean, offs, False, 4, 2000)
+    n_blocks = (int(offs[-1]) + 2 * len(lens) + 64) // 64
+    assert S.host_pack.last_exceptions <= phases * (4 * 4 * 2 + 2) < n_blocks // 20  # only the share boundaries
+    dirty = clean.copy()
+    hit = rng.choice(len(dirty), 300, replace=False)
+    dirty[hit] = 0
+    _host_pack_matches(dirty, offs, False, 4, 2000)
+    assert 250 <= S.host_pack.last_exceptions <= 300 + phases * 34
+
+
 def test_host_pack_scalar_path_and_oversized_sequence():
     rng = np.random.RandomState(4)
     offs = np.array([0, 50, 5000, 5100], np.uint64)

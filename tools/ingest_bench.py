@@ -14,7 +14,7 @@ elif os.environ.get("PENG_TOOL_STREAM") == "torch":
 g.ingest_synthetic(n, 200, 1234, 0, "TGCTGASTCAGCA", 0.3, 0.0)
 codes, offs = g.export_codes()
 pin = torch.from_numpy(codes).pin_memory()
-for mode, frac in [(1, -1), (2, -1), (0, -1), (0, 0.0), (0, 0.15), (0, 0.25), (0, 0.35), (0, 0.5), (0, 0.65), (0, 0.8)]:
+for mode, frac in [(1, -1), (2, -1), (0, -1), (0, 0.0), (0, 0.15), (0, 0.25), (0, 0.35), (0, 0.5), (0, 0.65), (0, 0.8), (0, 0.9), (0, 0.95)]:
     g.set_ingest_mode(mode, frac)
     ts = []
     for i in range(8):
