@@ -10,6 +10,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -31,8 +32,9 @@ namespace peng_host {
 // Sink: void letters(const char* p, size_t n)  — next n sequence bytes of the current record
 //       void end_record(const char* header, size_t header_len) — the current record is complete (it had >= 1 byte)
 //       void end_of_file(bool last_record_kept) — whether the file's final record was a complete one
+// warn != NULL: warnings are appended there instead of going to stderr (parallel scan: printed in file order afterwards)
 template <typename Sink>
-inline int scan_fasta(const char* text, size_t size, const char* path, Sink& sink, std::string* msg) {
+inline int scan_fasta(const char* text, size_t size, const char* path, Sink& sink, std::string* msg, std::string* warn = nullptr) {
   bool in_record = false;
   uint64_t record_bytes = 0;
   const char* header = nullptr;
@@ -41,6 +43,7 @@ inline int scan_fasta(const char* text, size_t size, const char* path, Sink& sin
   const char* end = text + size;
   auto close_record = [&]() {
     if (record_bytes) sink.end_record(header, header_len);
+    else if (warn) *warn += std::string("Warning: Ignore FASTA entry without sequence: ") + path + "\n";
     else fprintf(stderr, "Warning: Ignore FASTA entry without sequence: %s\n", path);
   };
   while (p < end) {
@@ -73,14 +76,102 @@ inline int scan_fasta(const char* text, size_t size, const char* path, Sink& sin
   return 0;
 }
 
+// First position >= pos where a line starts with '>' (a record can only begin there), or size.
+inline size_t next_header_line(const char* text, size_t size, size_t pos) {
+  if (pos == 0) return 0;  // whatever the file starts with belongs to the first chunk
+  const char* p = text + pos - 1;  // the line start at pos counts if the byte in front of it is a newline
+  const char* end = text + size;
+  while (p < end) {
+    const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+    if (!nl || nl + 1 >= end) return size;
+    if (nl[1] == '>') return (size_t)(nl + 1 - text);
+    p = nl + 1;
+  }
+  return size;
+}
+
+struct RecordSink {
+  const char* text = nullptr;
+  size_t keep_lo = 0, keep_hi = (size_t)-1;  // shard: records whose first sequence line starts in [keep_lo, keep_hi)
+  std::vector<const uint8_t*> ptrs;
+  std::vector<uint32_t> lens;
+  std::vector<std::unique_ptr<char[]>> arena;
+  std::vector<std::pair<const char*, size_t>> segments, last_segments;
+  const char* last_header = nullptr;
+  size_t last_header_len = 0;
+  bool cur_keep = true, last_mine = false, last_kept = false, too_long = false;
+  void letters(const char* p, size_t n) {
+    if (segments.empty()) cur_keep = (size_t)(p - text) >= keep_lo && (size_t)(p - text) < keep_hi;
+    segments.emplace_back(p, n);
+  }
+  void end_record(const char* header, size_t header_len) {
+    last_mine = cur_keep;
+    if (cur_keep) {
+      size_t total = 0;
+      for (const auto& sg : segments) total += sg.second;
+      if (total > 0xFFFFFFFFull) too_long = true;
+      if (segments.size() == 1) {
+        ptrs.push_back((const uint8_t*)segments[0].first);
+      } else {
+        arena.emplace_back(new char[total + 64]);
+        char* w = arena.back().get();
+        ptrs.push_back((const uint8_t*)w);
+        for (const auto& sg : segments) {
+          memcpy(w, sg.first, sg.second);
+          w += sg.second;
+        }
+      }
+      lens.push_back((uint32_t)total);
+      last_header = header;
+      last_header_len = header_len;
+      last_segments.swap(segments);
+    }
+    segments.clear();
+  }
+  void end_of_file(bool last_record_kept) { last_kept = last_record_kept; }
+};
+struct ChunkedScan {
+  const char* text;
+  const char* path;
+  std::vector<size_t> cut;  // chunk i = [cut[i], cut[i + 1])
+  std::vector<RecordSink> sinks;
+  std::vector<std::string> msgs, warns;
+  std::vector<int> rcs;
+  // n chunks cut at header lines near equal file positions; shard (part, n_parts) as in peng_cuda_ingest_fasta_shard
+  void prepare(const char* text_, size_t size, const char* path_, int n, int part, int n_parts) {
+    text = text_;
+    path = path_;
+    cut.assign(1, 0);
+    for (int i = 1; i < n; i++) cut.push_back(std::max(cut.back(), next_header_line(text, size, size * (size_t)i / (size_t)n)));
+    cut.push_back(size);
+    sinks.clear();
+    sinks.resize((size_t)n);
+    msgs.assign((size_t)n, std::string());
+    warns.assign((size_t)n, std::string());
+    rcs.assign((size_t)n, 0);
+    for (auto& k : sinks) {
+      k.text = text;
+      if (n_parts > 1) {
+        k.keep_lo = (size_t)((unsigned __int128)size * (unsigned)part / (unsigned)n_parts);
+        k.keep_hi = part == n_parts - 1 ? (size_t)-1 : (size_t)((unsigned __int128)size * (unsigned)(part + 1) / (unsigned)n_parts);
+      }
+    }
+  }
+  void scan_chunk(int i) {
+    const size_t a = cut[(size_t)i], b = cut[(size_t)i + 1];
+    rcs[(size_t)i] = b > a ? scan_fasta(text + a, b - a, path, sinks[(size_t)i], &msgs[(size_t)i], &warns[(size_t)i]) : 0;
+  }
+};
+
+
 // The whole file as one read-only mapping (page cache pages, no copy).  An empty file maps to size 0.
 struct MappedFile {
   const char* data = nullptr;
   size_t size = 0;
-  int open_file(const char* path);  // 0 ok, 1 cannot open
+  int open_file(const char* path, bool populate = true);  // 0 ok, 1 cannot open; populate: map every page now (one serial pass)
   ~MappedFile();
 };
-inline int MappedFile::open_file(const char* path) {
+inline int MappedFile::open_file(const char* path, bool populate) {
   const int fd = open(path, O_RDONLY);
   if (fd < 0) return 1;
   struct stat st;
@@ -90,13 +181,13 @@ inline int MappedFile::open_file(const char* path) {
   }
   size = (size_t)st.st_size;
   if (size) {
-    void* m = mmap(nullptr, size, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
+    void* m = mmap(nullptr, size, PROT_READ, MAP_PRIVATE | (populate ? MAP_POPULATE : 0), fd, 0);
     if (m == MAP_FAILED) {
       close(fd);
       size = 0;
       return 1;
     }
-    madvise(m, size, MADV_SEQUENTIAL);
+    if (populate) madvise(m, size, MADV_SEQUENTIAL);
     data = static_cast<const char*>(m);
   }
   close(fd);

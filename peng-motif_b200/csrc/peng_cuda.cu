@@ -14,6 +14,7 @@
 #include <cstring>
 #include <string>
 #include <type_traits>
+#include <memory>
 #include <vector>
 
 #include "../../include/peng_cuda.h"
@@ -105,6 +106,7 @@ struct peng_cuda_ctx {
   double ingest_fraction = -1;     // share of the bases packed on the host (< 0: from the thread count)
   uint64_t last_ingest_packed = 0; // sequences the host packed in the last ingest
   uint64_t last_ingest_h2d = 0;    // bytes the last ingest from host buffers sent over PCIe
+  std::vector<uint64_t> seq_offs;  // peng_cuda_ingest_sequences: offsets built from the lengths (kept between calls)
   int part_cfg = 0;                // stage-P geometry (tuning knob, PENG_PART_CFG)
   bool fold_untiled = false;       // PENG_FOLD_UNTILED: one-thread-per-id fold / mirror at every W (A/B)
   uint2* d_slow_list = nullptr;
@@ -2803,16 +2805,54 @@ static void gather_task(int i, void* arg) {
   const uint64_t s0 = g.n_seq * (uint64_t)i / g.n_tasks, s1 = g.n_seq * (uint64_t)(i + 1) / g.n_tasks;
   for (uint64_t s = s0; s < s1; s++) memcpy(g.dst + g.offs[s], g.seqs[s], g.offs[s + 1] - g.offs[s]);
 }
+struct LengthScan {
+  const uint32_t* lengths;
+  uint64_t* offs;
+  uint64_t n_seq;
+  int n_tasks;
+  std::vector<uint64_t> sums;  // [i + 1] = sum of chunk i, then (after the serial pass) [i] = total in front of chunk i
+};
+static void length_sum_task(int i, void* arg) {
+  LengthScan& sc = *(LengthScan*)arg;
+  const uint64_t a = sc.n_seq * (uint64_t)i / (uint64_t)sc.n_tasks, b = sc.n_seq * (uint64_t)(i + 1) / (uint64_t)sc.n_tasks;
+  uint64_t t = 0;
+  for (uint64_t s = a; s < b; s++) t += sc.lengths[s];
+  sc.sums[(size_t)i + 1] = t;
+}
+static void length_scan_task(int i, void* arg) {
+  LengthScan& sc = *(LengthScan*)arg;
+  const uint64_t a = sc.n_seq * (uint64_t)i / (uint64_t)sc.n_tasks, b = sc.n_seq * (uint64_t)(i + 1) / (uint64_t)sc.n_tasks;
+  uint64_t t = sc.sums[(size_t)i];
+  for (uint64_t s = a; s < b; s++) {
+    sc.offs[s] = t;
+    t += sc.lengths[s];
+  }
+}
+
+// h->seq_offs = prefix sums of the lengths: two passes on the pool (chunk sums, then the chunks' offsets), into a buffer the
+// handle keeps (a fresh 8 MB vector per call costs more in page faults than the sums)
+static int offsets_from_lengths(peng_handle_t h, const uint32_t* lengths, uint64_t n_seq) {
+  peng_hostpack::Pool& pool = peng_hostpack::global_pool();
+  std::vector<uint64_t>& offs = h->seq_offs;
+  if (offs.size() < n_seq + 1) offs.resize(n_seq + 1 + (n_seq >> 3));
+  LengthScan sc{lengths, offs.data(), n_seq, std::max(1, std::min<int>(pool.size() * 2, (int)(n_seq / 65536 + 1))), {}};
+  sc.sums.assign((size_t)sc.n_tasks + 1, 0);
+  pool.run(sc.n_tasks, length_sum_task, &sc);
+  for (int i = 0; i < sc.n_tasks; i++) sc.sums[(size_t)i + 1] += sc.sums[(size_t)i];  // sums[i]: total in front of chunk i
+  pool.run(sc.n_tasks, length_scan_task, &sc);
+  offs[n_seq] = sc.sums[(size_t)sc.n_tasks];
+  return PENG_OK;
+}
+
 extern "C" int peng_cuda_ingest_sequences(peng_handle_t h, const uint8_t* const* seqs, const uint32_t* lengths, uint64_t n_seq) {
   if (!h || (n_seq && (!seqs || !lengths))) return fail(h, PENG_E_INVALID, "ingest_sequences: NULL argument");
-  std::vector<uint64_t> offs(n_seq + 1);
-  offs[0] = 0;
-  for (uint64_t s = 0; s < n_seq; s++) offs[s + 1] = offs[s] + lengths[s];
+  peng_hostpack::Pool& pool = peng_hostpack::global_pool();
+  std::vector<uint64_t>& offs = h->seq_offs;
+  TRY(offsets_from_lengths(h, lengths, n_seq));
   h->last_ingest_packed = 0;
   const int rc = ingest_host_hybrid(h, nullptr, offs.data(), n_seq, false, seqs);
   if (rc != 1) return rc;
   std::vector<uint8_t> buf(offs[n_seq] + 1);
-  peng_hostpack::Pool& pool = peng_hostpack::global_pool();
   GatherTask g{seqs, offs.data(), buf.data(), n_seq, std::max(1, std::min(pool.size() * 4, 256))};
   pool.run(g.n_tasks, gather_task, &g);
   return ingest_host_src(h, buf.data(), offs.data(), n_seq, false);
@@ -2895,6 +2935,74 @@ struct StagingSink {
   void end_of_file(bool last_record_kept) { last_kept = last_record_kept; }
 };
 
+// Parallel FASTA ingest (the default; the streaming path above is the fallback).  The file is cut at header lines into
+// chunks, the pool's threads scan them with the same line rules (scan_fasta), and instead of copying letters a RecordSink
+// notes WHERE every record's sequence lies: single-line records (and those are the long ones of a ChIP-seq peak file) are
+// read in place from the mapping, wrapped records are joined in a side arena.  The pointer table then goes through the
+// packed ingest (ingest_host_hybrid with per-sequence pointers, ASCII): the host threads write the device layout straight
+// from the page cache.
+struct PtrGather {
+  peng_host::ChunkedScan* f;
+  std::vector<uint64_t> first;  // index of chunk i's first record
+  const uint8_t** ptrs;
+  uint32_t* lens;
+};
+static void ptr_gather_task(int i, void* arg) {
+  PtrGather& g = *(PtrGather*)arg;
+  const peng_host::RecordSink& k = g.f->sinks[(size_t)i];
+  if (k.ptrs.empty()) return;
+  memcpy(g.ptrs + g.first[(size_t)i], k.ptrs.data(), k.ptrs.size() * sizeof(const uint8_t*));
+  memcpy(g.lens + g.first[(size_t)i], k.lens.data(), k.lens.size() * sizeof(uint32_t));
+}
+
+// returns 1 when the set does not qualify (the caller takes the streaming path), else a PENG_ code
+static int ingest_fasta_parallel(peng_handle_t h, const char* path, int part, int n_parts) {
+  using namespace peng_hostpack;
+  if (getenv("PENG_FASTA_SERIAL") || !lists_exceptions()) return 1;  // (the masked loads that make reading in place safe are the AVX-512 path's)
+  Pool& pool = global_pool();
+  peng_host::MappedFile file;
+  if (file.open_file(path, false) != 0) return fail(h, PENG_E_IO, "Error: Cannot open FASTA file: %s", path);
+  peng_host::ChunkedScan f;
+  const int n = (int)std::max<size_t>(1, std::min<size_t>((size_t)pool.size() * 4, file.size >> 18));
+  f.prepare(file.data, file.size, path, n, part, n_parts);
+  pool.run(n, [](int i, void* arg) { ((peng_host::ChunkedScan*)arg)->scan_chunk(i); }, &f);
+  // warnings and the first error in file order, as one pass over the file would have printed them
+  for (int i = 0; i < n; i++) {
+    if (!f.warns[(size_t)i].empty()) fputs(f.warns[(size_t)i].c_str(), stderr);
+    if (f.rcs[(size_t)i] != 0) return fail(h, PENG_E_FORMAT, "%s", f.msgs[(size_t)i].c_str());
+  }
+  PtrGather g;
+  g.f = &f;
+  uint64_t ns = 0;
+  int last_chunk = -1;  // the chunk that holds the end of the file
+  for (int i = 0; i < n; i++) {
+    g.first.push_back(ns);
+    ns += f.sinks[(size_t)i].ptrs.size();
+    if (f.sinks[(size_t)i].too_long) return 1;
+    if (f.cut[(size_t)i + 1] > f.cut[(size_t)i]) last_chunk = i;
+  }
+  if (ns == 0) return 1;
+  std::vector<const uint8_t*> ptrs(ns);
+  std::vector<uint32_t> lens(ns);
+  g.ptrs = ptrs.data();
+  g.lens = lens.data();
+  pool.run(n, ptr_gather_task, &g);
+  // SequenceSet::readFASTA reports undefined letters for the LAST record only (src/shared/SequenceSet.cpp:395-405)
+  const peng_host::RecordSink& lastk = f.sinks[(size_t)last_chunk];
+  if (lastk.last_kept && lastk.last_mine) {
+    const std::string name = lastk.last_header_len ? std::string(lastk.last_header, lastk.last_header_len) : std::to_string(ns);
+    for (const auto& seg : lastk.last_segments)
+      for (size_t i = 0; i < seg.second; i++) {
+        const char c = seg.first[i], up = (char)(c & 0xDF);
+        if (up != 'A' && up != 'C' && up != 'G' && up != 'T')
+          fprintf(stderr, "Warning: The FASTA file contains an undefined base: %c at sequence %s\n", c, name.c_str());
+      }
+  }
+  std::vector<uint64_t>& offs = h->seq_offs;
+  TRY(offsets_from_lengths(h, lens.data(), ns));
+  return ingest_host_hybrid(h, nullptr, offs.data(), ns, true, ptrs.data());
+}
+
 static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_parts, uint64_t* n_seq, uint64_t* total_bases,
                              uint32_t* min_len, uint32_t* max_len);
 extern "C" int peng_cuda_ingest_fasta(peng_handle_t h, const char* path, uint64_t* n_seq, uint64_t* total_bases,
@@ -2912,6 +3020,18 @@ static int ingest_fasta_impl(peng_handle_t h, const char* path, int part, int n_
                              uint32_t* min_len, uint32_t* max_len) {
   if (!h || !path) return fail(h, PENG_E_INVALID, "ingest_fasta: NULL argument");
   CU(h, cudaSetDevice(h->device));
+  {
+    const int rc = ingest_fasta_parallel(h, path, part, n_parts);
+    if (rc != 1) {  // done (or failed); 1 = not applicable, streaming path
+      if (rc != PENG_OK) return rc;
+      if (n_seq) *n_seq = h->n_seq;
+      if (total_bases) *total_bases = h->total_bases;
+      if (min_len) *min_len = h->min_len;
+      if (max_len) *max_len = h->max_len;
+      return PENG_OK;
+    }
+  }
+  h->last_ingest_packed = 0;
   peng_host::MappedFile file;
   if (file.open_file(path) != 0) return fail(h, PENG_E_IO, "Error: Cannot open FASTA file: %s", path);
   TRY(need_scratch(h, file.size + 16));  // the sequence bytes are a subset of the file's

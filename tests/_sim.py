@@ -220,6 +220,19 @@ def scan_fasta(path):
     return lut[letters], offsets
 
 
+def scan_fasta_chunked(path, n_chunks, part=0, n_parts=1):
+    """host_ingest.h: ChunkedScan (the parallel ingest's scan, chunk by chunk) -> (raw letters, offsets, warnings, last record reported)"""
+    n_seq, n_let, n_warn, last = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_int()
+    args = (os.fsencode(path), int(n_chunks), int(part), int(n_parts), C.byref(n_seq), C.byref(n_let))
+    rc = lib.sim_scan_fasta_chunked(*args, None, None, C.byref(n_warn), C.byref(last))
+    if rc:
+        raise ValueError(f"scan_fasta rc={rc}")
+    letters = np.zeros(max(n_let.value, 1), np.uint8)
+    offsets = np.zeros(n_seq.value + 1, np.uint64)
+    lib.sim_scan_fasta_chunked(*args, letters.ctypes.data_as(C.c_char_p), _p(offsets, u64p), C.byref(n_warn), C.byref(last))
+    return letters[: n_let.value], offsets, int(n_warn.value), bool(last.value)
+
+
 def select(z, counts, W, z_threshold=10.0, count_threshold=3, single_stranded=False, filter_neighbors=True):
     """host_ingest.h: select_base_patterns (pruned introsort) -> selected ids"""
     z = np.ascontiguousarray(z, np.float32)

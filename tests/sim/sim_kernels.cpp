@@ -351,6 +351,37 @@ int sim_scan_fasta(const char* path, uint64_t* n_seq, uint64_t* n_letters, char*
 }
 }
 
+// the chunked scan of the parallel FASTA ingest (host_ingest.h: ChunkedScan, chunks scanned one after the other here):
+// same return codes / outputs as sim_scan_fasta; *n_warn = warnings collected; shard (part, n_parts)
+extern "C" int sim_scan_fasta_chunked(const char* path, int n_chunks, int part, int n_parts, uint64_t* n_seq, uint64_t* n_letters,
+                                      char* letters, uint64_t* offsets, uint64_t* n_warn, int* last_kept_and_mine) {
+  peng_host::MappedFile f;
+  if (f.open_file(path, false) != 0) return 1;
+  peng_host::ChunkedScan cs;
+  cs.prepare(f.data, f.size, path, n_chunks, part, n_parts);
+  for (int i = 0; i < n_chunks; i++) cs.scan_chunk(i);
+  *n_warn = 0;
+  int last_chunk = -1;
+  for (int i = 0; i < n_chunks; i++) {
+    for (char c : cs.warns[(size_t)i]) *n_warn += c == '\n';
+    if (cs.rcs[(size_t)i]) return cs.rcs[(size_t)i];
+    if (cs.cut[(size_t)i + 1] > cs.cut[(size_t)i]) last_chunk = i;
+  }
+  uint64_t ns = 0, nl = 0;
+  for (auto& k : cs.sinks)
+    for (size_t r = 0; r < k.ptrs.size(); r++) {
+      if (letters) memcpy(letters + nl, k.ptrs[r], k.lens[r]);
+      nl += k.lens[r];
+      ns++;
+      if (offsets) offsets[ns] = nl;
+    }
+  if (offsets) offsets[0] = 0;
+  *n_seq = ns;
+  *n_letters = nl;
+  *last_kept_and_mine = last_chunk >= 0 && cs.sinks[(size_t)last_chunk].last_kept && cs.sinks[(size_t)last_chunk].last_mine;
+  return 0;
+}
+
 // ---- seed selection (host_ingest.h: select_base_patterns with the pruned introsort) and the leading part of the sort ----
 extern "C" {
 uint64_t sim_select(const float* z, const uint64_t* counts, int W, float z_threshold, uint64_t count_threshold, int single_stranded,

@@ -1,6 +1,8 @@
 """peng_cuda_ingest_codes from host buffers: raw bytes + device packing, host packing (host_pack.cpp) and the hybrid of the
 two must leave bit-identical device buffers — checked through everything that reads them: export, k-mer counts (codes +
 validity), background counts (sequence starts)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -92,6 +94,37 @@ def test_implied_validity(g):
     g.set_ingest_mode(2, -1.0)
     g.ingest_codes(late, offs)
     assert 0.26 * total < g.last_ingest_h2d_bytes - offs.nbytes < 0.375 * total
+
+
+def test_fasta_parallel_equals_streaming(g, monkeypatch):
+    """peng_cuda_ingest_fasta: the parallel path (file cut at header lines, records read in place from the mapping by the
+    host packer, wrapped records joined in an arena) against the streaming path (PENG_FASTA_SERIAL=1: one scanning thread,
+    raw letters to the device) and the oracle's reader — a 3 MB file of single-line and wrapped records, lower case, N, CR
+    line ends, blank lines, records without sequence; whole and as shards."""
+    from test_kernel_logic_sim import _random_fasta
+
+    rng = np.random.RandomState(77)
+    text = _random_fasta(rng, 20_000)
+    path = _cases.write_fasta(text)
+    try:
+        assert os.path.getsize(path) > (2 << 20)  # 12 chunks
+        codes, offs, mn, mx = O.read_fasta(path)
+        info = g.ingest_fasta(path)
+        assert g.last_ingest_host_packed == len(offs) - 1  # the parallel path packs on the host
+        assert info == dict(n_seq=len(offs) - 1, total_bases=len(codes), min_len=mn, max_len=mx)
+        c, o = g.export_codes()
+        assert np.array_equal(o, offs) and np.array_equal(c, codes)
+        par = fingerprint(g, codes, offs)
+        shards = [g.ingest_fasta_shard(path, p, 3) and g.export_codes() for p in range(3)]
+        assert np.array_equal(np.concatenate([s[0] for s in shards]), codes)
+        assert np.array_equal(np.concatenate([np.diff(s[1]) for s in shards]), np.diff(offs))
+        monkeypatch.setenv("PENG_FASTA_SERIAL", "1")
+        info2 = g.ingest_fasta(path)
+        assert g.last_ingest_host_packed == 0 and info2 == info
+        ser = fingerprint(g, codes, offs)
+        assert par[0] == ser[0] and np.array_equal(par[1], ser[1]) and np.array_equal(par[2], ser[2])
+    finally:
+        os.unlink(path)
 
 
 def test_long_sequence_falls_back(g):

@@ -268,6 +268,71 @@ def test_scan_fasta_edge_files(text):
     assert np.array_equal(offs, ref_offs) and np.array_equal(codes, ref_codes[: len(codes)])
 
 
+def _random_fasta(rng, n_rec):
+    """records with wrapped and single-line sequences, blank lines, empty records, CR line ends, lower case, N"""
+    out = []
+    for r in range(n_rec):
+        out.append(">r%d some text\n" % r if rng.rand() < 0.9 else ">\n")
+        kind = rng.randint(0, 10)
+        if kind == 0:
+            continue  # record without sequence: ignored with a warning
+        L = int(rng.choice([1, 5, 59, 60, 61, 200, 700]))
+        seq = "".join(rng.choice(list("ACGTacgtNn"), L, p=[0.22, 0.22, 0.22, 0.22, 0.02, 0.02, 0.02, 0.02, 0.02, 0.02]))
+        if kind < 5:
+            out.append(seq + "\n")
+        else:
+            w = int(rng.choice([10, 60, 61]))
+            for i in range(0, L, w):
+                out.append(seq[i:i + w] + ("\r\n" if kind == 9 else "\n"))
+                if rng.rand() < 0.05:
+                    out.append("\n")
+    return "".join(out)
+
+
+@pytest.mark.parametrize("seed", range(5))
+def test_scan_fasta_chunked_equals_serial(seed):
+    """The parallel ingest cuts the file at header lines and scans the chunks independently (ChunkedScan): same records,
+    same warnings, same 'last record' as one pass — for any number of chunks, and sharded like peng_cuda_ingest_fasta_shard."""
+    rng = np.random.RandomState(300 + seed)
+    text = _random_fasta(rng, 400)
+    if seed == 1:
+        text += ">tail\nACGT"  # unterminated last line: dropped, its record ignored
+    if seed == 2:
+        text += ">empty\n"
+    path = _cases.write_fasta(text)
+    try:
+        ref_l, ref_o, ref_w, ref_last = S.scan_fasta_chunked(path, 1)
+        c0, o0 = S.scan_fasta(path)
+        assert np.array_equal(o0, ref_o) and len(c0) == len(ref_l)
+        for n in (2, 3, 7, 16, 64, 500):
+            l, o, w, last = S.scan_fasta_chunked(path, n)
+            assert np.array_equal(o, ref_o) and np.array_equal(l, ref_l) and w == ref_w and last == ref_last, n
+        for n_parts in (2, 3):
+            ls, lens, ws = [], [], 0
+            for part in range(n_parts):
+                l1, o1, w1, _ = S.scan_fasta_chunked(path, 1, part, n_parts)
+                l, o, w, _ = S.scan_fasta_chunked(path, 9, part, n_parts)
+                assert np.array_equal(o, o1) and np.array_equal(l, l1) and w == w1
+                ls.append(l)
+                lens.append(np.diff(o))
+            assert np.array_equal(np.concatenate(ls), ref_l) and np.array_equal(np.concatenate(lens), np.diff(ref_o))
+    finally:
+        os.unlink(path)
+
+
+def test_scan_fasta_chunked_errors():
+    """A sequence line before any header / a space in a sequence line is fatal in whichever chunk it lies."""
+    good = "".join(">r%d\nACGTACGTAC\n" % i for i in range(200))
+    for bad in ("ACGT\n" + good, good + ">x\nAC GT\n", good[:1500] + ">y\nA C\n" + good[1500:]):
+        path = _cases.write_fasta(bad)
+        try:
+            for n in (1, 4, 50):
+                with pytest.raises(ValueError):
+                    S.scan_fasta_chunked(path, n)
+        finally:
+            os.unlink(path)
+
+
 def test_scan_fasta_missing_file():
     with pytest.raises(ValueError):
         S.scan_fasta("/nonexistent/file.fa")
