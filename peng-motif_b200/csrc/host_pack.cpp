@@ -266,6 +266,7 @@ void pack_share(const Share& sh) {
 struct Pool::Impl {
   std::vector<std::thread> workers;
   std::mutex m;
+  std::mutex job;  // held from start() to finish(): callers on several threads (one per device of a multi-GPU run) take turns
   std::condition_variable cv_work, cv_done;
   uint64_t generation = 0;
   bool stop = false;
@@ -313,6 +314,7 @@ Pool::~Pool() {
   delete p_;
 }
 void Pool::start(int n_tasks, void (*fn)(int, void*), void* arg) {
+  p_->job.lock();  // released by finish(), on the same thread
   {
     std::lock_guard<std::mutex> lk(p_->m);
     p_->fn = fn;
@@ -326,8 +328,11 @@ void Pool::start(int n_tasks, void (*fn)(int, void*), void* arg) {
 }
 void Pool::finish() {
   p_->drain();  // the caller works too
-  std::unique_lock<std::mutex> lk(p_->m);
-  p_->cv_done.wait(lk, [&] { return p_->busy == 0; });
+  {
+    std::unique_lock<std::mutex> lk(p_->m);
+    p_->cv_done.wait(lk, [&] { return p_->busy == 0; });
+  }
+  p_->job.unlock();
 }
 void Pool::run(int n_tasks, void (*fn)(int, void*), void* arg) {
   if (n_tasks <= 0) return;

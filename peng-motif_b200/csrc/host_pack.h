@@ -67,7 +67,9 @@ class Pool {
   int size() const { return n_; }
   void run(int n_tasks, void (*fn)(int, void*), void* arg);
   // the same in two steps: start() wakes the workers and returns, finish() lets the caller take part and waits for the last
-  // task — what the caller does in between runs beside the workers (one job at a time)
+  // task — what the caller does in between runs beside the workers.  One job at a time: a second thread's start() waits
+  // until the first has called finish(), so every start() must be followed by finish() on the same thread, and a thread
+  // must not start a second job (or call run()) before it has finished its first
   void start(int n_tasks, void (*fn)(int, void*), void* arg);
   void finish();
 

@@ -2685,7 +2685,12 @@ static int ingest_host_hybrid(peng_handle_t h, const uint8_t* src, const uint64_
       const bool more = !(c.last || (c.e >= s_split && s_split < n_seq));
       // the next phase starts before this one's copies are queued — unless its staging buffer is still being read by the
       // DMA engine: then the bus is the bottleneck, and this phase's copy goes out first
-      const bool next_free = more && cudaEventQuery(h->pin_ev[c.buf ^ 1]) == cudaSuccess;
+      bool next_free = false;
+      if (more) {
+        const cudaError_t q = cudaEventQuery(h->pin_ev[c.buf ^ 1]);
+        next_free = q == cudaSuccess;
+        if (q == cudaErrorNotReady) (void)cudaGetLastError();  // "not ready" is an answer, not an error: do not leave it for the next launch check
+      }
       if (next_free) rc = begin_phase(slots[cur ^ 1], c.e, false, c.buf ^ 1);
       t0 = now();
       if (rc == PENG_OK) rc = issue_phase(c);

@@ -204,6 +204,17 @@ def host_pack(src, offsets, ascii=False, n_threads=4, max_blocks=1 << 14):
     return codes, valid, nw, ph
 
 
+def host_pack_concurrent(src, offsets, n_callers, n_threads, rounds, max_blocks, want_codes):
+    """n_callers threads pack the set through ONE pool at the same time (two phases in flight each) -> callers that went wrong"""
+    src = np.ascontiguousarray(src, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.uint64)
+    n_seq = len(offsets) - 1
+    nw = int(lib.sim_n_words32(C.c_uint64(n_seq), C.c_uint64(int(offsets[-1]))))
+    want = np.ascontiguousarray(want_codes[: 2 * nw], np.uint32)
+    return int(lib.sim_host_pack_concurrent(_p(src, u8p), _p(offsets, u64p), C.c_uint64(n_seq), int(n_callers), int(n_threads), int(rounds),
+                                            C.c_uint64(max_blocks), C.c_uint64(nw), _p(want, u32p)))
+
+
 def scan_fasta(path):
     """host_ingest.h: scan_fasta on a mapped file -> (codes in the reference's encoding, offsets) or raises ValueError."""
     n_seq, n_let = C.c_uint64(), C.c_uint64()

@@ -523,4 +523,74 @@ int sim_host_pack(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, i
   }
   return has_carry ? -2 : phases;
 }
+
+// Several callers on ONE pool at the same time (peng_motif --gpus N: one host thread per device, all of them ingest
+// through the process-wide pool), each with two phases in flight the way ingest_host_hybrid runs them (pack_phase_begin of
+// phase i + 1 before phase i is taken out of its staging buffer).  Every caller packs the whole set `rounds` times and
+// compares its codes with want_codes32 (2 * n_words32 words).  Returns the number of callers that saw a difference or
+// an error.
+int sim_host_pack_concurrent(const uint8_t* src, const uint64_t* offsets, uint64_t n_seq, int n_callers, int n_threads, int rounds,
+                             uint64_t max_blocks, uint64_t n_words32, const uint32_t* want_codes32) {
+  using namespace peng_hostpack;
+  Pool pool(n_threads);
+  const uint64_t q_total = ((n_words32 * 32 + 63) / 64) * 64;
+  const uint64_t n_blocks = q_total / 64;
+  std::vector<int> bad((size_t)n_callers, 0);
+  auto caller = [&](int who) {
+    std::vector<uint32_t> codes32(2 * n_words32 + 8, 0);
+    struct Slot {
+      std::vector<uint64_t> sc, sv;
+      Phase ph;
+      PhaseJob* job = nullptr;
+      uint64_t blk0 = 0, blk1 = 0, e = 0;
+      bool last = false;
+    } slots[2];
+    for (auto& c : slots) { c.sc.resize(2 * max_blocks + 2); c.sv.resize(max_blocks + 1); }
+    for (int r = 0; r < rounds && !bad[(size_t)who]; r++) {
+      std::fill(codes32.begin(), codes32.end(), 0u);
+      bool has_carry = false;
+      Partial carry{};
+      auto begin = [&](Slot& c, uint64_t s, bool first) -> bool {
+        uint64_t e = plan_phase(offsets, n_seq, s, PENG_FRONT_PAD, first, max_blocks);
+        bool last = e == n_seq;
+        if (last) {
+          const uint64_t q0 = first ? 0 : PENG_FRONT_PAD + offsets[s] + 2 * s;
+          if (n_blocks - (q0 >> 6) > max_blocks) last = false;
+        }
+        if (e == s && !last) return false;
+        c.ph = Phase{src, offsets, s, e, false, PENG_FRONT_PAD, first, last, q_total, c.sc.data(), c.sv.data()};
+        c.e = e;
+        c.last = last;
+        phase_blocks(c.ph, &c.blk0, &c.blk1);
+        c.job = pack_phase_begin(pool, c.ph);
+        return true;
+      };
+      if (!begin(slots[0], 0, true)) { bad[(size_t)who] = 1; break; }
+      for (int cur = 0;;) {
+        Slot& c = slots[cur];
+        pack_phase_end(pool, c.job, &has_carry, &carry);
+        c.job = nullptr;
+        const bool more = !c.last;
+        if (more && !begin(slots[cur ^ 1], c.e, false)) { bad[(size_t)who] = 1; break; }
+        memcpy(codes32.data() + c.blk0 * 4, c.sc.data(), (c.blk1 - c.blk0) * 16);  // "issue" of phase i beside the packing of i + 1
+        if (!more) break;
+        cur ^= 1;
+      }
+      for (auto& c : slots)
+        if (c.job) {
+          bool hc = false;
+          Partial pc{};
+          pack_phase_end(pool, c.job, &hc, &pc);
+          c.job = nullptr;
+        }
+      if (has_carry || memcmp(codes32.data(), want_codes32, 2 * n_words32 * 4)) bad[(size_t)who] = 1;
+    }
+  };
+  std::vector<std::thread> ts;
+  for (int i = 0; i < n_callers; i++) ts.emplace_back(caller, i);
+  for (auto& t : ts) t.join();
+  int n_bad = 0;
+  for (int b : bad) n_bad += b;
+  return n_bad;
+}
 }

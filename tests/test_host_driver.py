@@ -51,7 +51,7 @@ def gpu_binary():
 def run_cli(binary, fasta, args, tmp_path):
     meme, js = str(tmp_path / "o.meme"), str(tmp_path / "o.json")
     r = subprocess.run([binary, os.path.join(DATA, fasta), *[a.replace("@DATA@", DATA) for a in args], "-o", meme, "-j", js],
-                       capture_output=True, text=True)
+                       capture_output=True, text=True, timeout=600)
     read = lambda p: open(p).read() if os.path.exists(p) else None
     return r, read(meme), read(js)
 
@@ -87,24 +87,24 @@ def test_host_logic_config(sim_binary, name, tmp_path):
 
 def test_help_and_version(sim_binary):
     """Help text, version lines and exit codes of Global::readArguments (src/Global.cpp:81-96,296-303)."""
-    r = subprocess.run([sim_binary, "-h"], capture_output=True, text=True)
+    r = subprocess.run([sim_binary, "-h"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and " Usage: peng_motif SEQFILE [options] " in r.stdout
     for flag in ("-o,", "-j,", "--background-sequences,", "-t,", "-w,", "--bg-model-order,", "--count-threshold,", "--strand,",
                  "--optimization_score,", "--enrich_pseudocount_factor,", "-b,", "--no-em", "-a,", "--em-threshold,",
                  "--em-max-iterations,", "--no-merging", "--max_merged_length", "--use-default-pwm", "--pseudo-counts,",
                  "--threads,", "--no-neighbor-filtering", "--minimum-processed-patterns", "--version", "--max-optimized-patterns"):
         assert "\n      " + flag in r.stdout, flag
-    r = subprocess.run([sim_binary, "-version"], capture_output=True, text=True)
+    r = subprocess.run([sim_binary, "-version"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and r.stdout == "peng_motif version 1.0.0\n"
-    r = subprocess.run([sim_binary, "x.fa", "--version"], capture_output=True, text=True)
+    r = subprocess.run([sim_binary, "x.fa", "--version"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and r.stdout == "peng_motif 1.0.0\n"
-    r = subprocess.run([sim_binary], capture_output=True, text=True)
+    r = subprocess.run([sim_binary], capture_output=True, text=True, timeout=600)
     assert r.returncode == 255 and "Error: Arguments are missing!" in r.stderr
-    r = subprocess.run([sim_binary, "x.fa", "-w"], capture_output=True, text=True)
+    r = subprocess.run([sim_binary, "x.fa", "-w"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 4 and "No expression following -w" in r.stderr
-    r = subprocess.run([sim_binary, "x.fa", "-w", "7"], capture_output=True, text=True)
+    r = subprocess.run([sim_binary, "x.fa", "-w", "7"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 4 and "multiple of 2" in r.stderr
-    r = subprocess.run([sim_binary, "x.fa", "--strand", "MINUS"], capture_output=True, text=True)
+    r = subprocess.run([sim_binary, "x.fa", "--strand", "MINUS"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 4 and "Unknown expression following --strand" in r.stderr
 
 
@@ -114,7 +114,7 @@ def test_shipped_binary_has_no_cpu_path(gpu_binary, pkg):
     assert "libpeng_cuda.so" in out and "oracle" not in out and "sim" not in out
     if pkg.load_library().peng_cuda_device_count() > 0:
         pytest.skip("a GPU is present")
-    r = subprocess.run([gpu_binary, os.path.join(DATA, "MafK_100seqs.fasta"), "-w", "8"], capture_output=True, text=True)
+    r = subprocess.run([gpu_binary, os.path.join(DATA, "MafK_100seqs.fasta"), "-w", "8"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 1 and "no CPU fallback" in r.stderr and "[STATUS]" not in r.stdout
 
 
@@ -138,7 +138,7 @@ def run_gpus(binary, name, n, tmp_path, same_device):
     if same_device:
         env["PENG_GPUS_SAME_DEVICE"] = "1"
     meme = str(tmp_path / "o.meme")
-    r = subprocess.run([binary, os.path.join(DATA, fasta), *args, "--gpus", str(n), "-o", meme], capture_output=True, text=True, env=env)
+    r = subprocess.run([binary, os.path.join(DATA, fasta), *args, "--gpus", str(n), "-o", meme], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr
     assert r.stdout == open(os.path.join(GOLDEN, name + "_stdout.txt")).read()
     assert open(meme).read() == open(os.path.join(GOLDEN, name + ".meme")).read()
@@ -177,7 +177,7 @@ def test_gpu_multi_handle_small_w_host_sum(gpu_binary, tmp_path):
     outs = []
     for extra in ([], ["--gpus", "2"]):
         r = subprocess.run([gpu_binary, fasta, "-w", "6", *extra, "-o", str(tmp_path / "x.meme")], capture_output=True, text=True,
-                           env=dict(os.environ, PENG_GPUS_SAME_DEVICE="1"))
+                           env=dict(os.environ, PENG_GPUS_SAME_DEVICE="1"), timeout=600)
         assert r.returncode == 0, r.stderr
         outs.append((r.stdout, open(tmp_path / "x.meme").read()))
     assert outs[0] == outs[1]

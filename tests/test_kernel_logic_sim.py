@@ -488,6 +488,20 @@ def test_host_pack_implied_validity():
     assert 250 <= S.host_pack.last_exceptions <= 300 + phases * 34
 
 
+@pytest.mark.timeout(300, method="thread")
+def test_host_pack_pool_shared_by_several_callers():
+    """`peng_motif --gpus N` ingests its shards from one host thread per device, and all of them pack through the
+    process-wide pool: jobs of different callers must take turns (Pool::start .. finish), each caller with two phases in
+    flight as in ingest_host_hybrid.  Without that the workers' job state is torn and the callers hang."""
+    rng = np.random.RandomState(6)
+    lens = rng.randint(1, 400, 20000)
+    offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    codes = rng.randint(0, 5, int(offs[-1])).astype(np.uint8)
+    st = S.pack(codes, offs, False)
+    for n_callers, n_threads in ((4, 4), (3, 1), (2, 8)):
+        assert S.host_pack_concurrent(codes, offs, n_callers, n_threads, 10, 300, st.codes) == 0, (n_callers, n_threads)
+
+
 def test_host_pack_scalar_path_and_oversized_sequence():
     rng = np.random.RandomState(4)
     offs = np.array([0, 50, 5000, 5100], np.uint64)
