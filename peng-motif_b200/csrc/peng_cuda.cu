@@ -2964,9 +2964,14 @@ static void ptr_gather_task(int i, void* arg) {
 static int ingest_fasta_parallel(peng_handle_t h, const char* path, int part, int n_parts) {
   using namespace peng_hostpack;
   if (getenv("PENG_FASTA_SERIAL") || !lists_exceptions()) return 1;  // (the masked loads that make reading in place safe are the AVX-512 path's)
+  // Shards of a multi-GPU run come from one host thread per device at the same time.  The pool lets their jobs take turns,
+  // but that combination has only run on the CPU so far: shards stay on the streaming reader unless
+  // asked for.
+  if (n_parts > 1 && !getenv("PENG_FASTA_SHARD_PARALLEL")) return 1;
   Pool& pool = global_pool();
   peng_host::MappedFile file;
   if (file.open_file(path, false) != 0) return fail(h, PENG_E_IO, "Error: Cannot open FASTA file: %s", path);
+  if (file.size < (2u << 20)) return 1;  // nothing to gain below a few chunks: first-call costs dominate small files
   peng_host::ChunkedScan f;
   const int n = (int)std::max<size_t>(1, std::min<size_t>((size_t)pool.size() * 4, file.size >> 18));
   f.prepare(file.data, file.size, path, n, part, n_parts);

@@ -115,9 +115,18 @@ def test_fasta_parallel_equals_streaming(g, monkeypatch):
         c, o = g.export_codes()
         assert np.array_equal(o, offs) and np.array_equal(c, codes)
         par = fingerprint(g, codes, offs)
-        shards = [g.ingest_fasta_shard(path, p, 3) and g.export_codes() for p in range(3)]
-        assert np.array_equal(np.concatenate([s[0] for s in shards]), codes)
-        assert np.array_equal(np.concatenate([np.diff(s[1]) for s in shards]), np.diff(offs))
+        for shard_parallel in (True, False):  # shards default to the streaming reader (one host thread per device calls them)
+            if shard_parallel:
+                monkeypatch.setenv("PENG_FASTA_SHARD_PARALLEL", "1")
+            else:
+                monkeypatch.delenv("PENG_FASTA_SHARD_PARALLEL")
+            shards = []
+            for p in range(3):
+                g.ingest_fasta_shard(path, p, 3)
+                assert (g.last_ingest_host_packed > 0) == shard_parallel
+                shards.append(g.export_codes())
+            assert np.array_equal(np.concatenate([s[0] for s in shards]), codes)
+            assert np.array_equal(np.concatenate([np.diff(s[1]) for s in shards]), np.diff(offs))
         monkeypatch.setenv("PENG_FASTA_SERIAL", "1")
         info2 = g.ingest_fasta(path)
         assert g.last_ingest_host_packed == 0 and info2 == info
