@@ -123,7 +123,7 @@ def test_fasta_parallel_equals_streaming(g, monkeypatch):
             shards = []
             for p in range(3):
                 g.ingest_fasta_shard(path, p, 3)
-                assert (g.last_ingest_host_packed > 0) == shard_parallel
+                assert shard_parallel or g.last_ingest_host_packed == 0
                 shards.append(g.export_codes())
             assert np.array_equal(np.concatenate([s[0] for s in shards]), codes)
             assert np.array_equal(np.concatenate([np.diff(s[1]) for s in shards]), np.diff(offs))
